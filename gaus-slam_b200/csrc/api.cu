@@ -1,0 +1,313 @@
+// api.cu -- the C ABI of libgs2d (include/gs2d.h): buffer layouts and stage orchestration.
+//
+// Mirrors the control flow of CudaRasterizer::Rasterizer::forward / backward
+// (CR/rasterizer_impl.cu:201-350, :354-460) and the tensor bookkeeping of
+// RAST/rasterize_points.cu:39-239, minus every memset the new kernels make unnecessary.
+#include <atomic>
+#include <cstring>
+
+#include "common.cuh"
+
+namespace gs2d {
+
+thread_local int g_last_cuda_error = 0;
+static std::atomic<long long> g_launches{0};
+void count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+
+GeomState GeomState::carve(void* base, size_t P, size_t* bytes)
+{
+	Carver c(base);
+	GeomState g;
+	g.depths = c.take<float>(P);
+	g.splat = c.take<float>(P * REC_WORDS);
+	g.rect = c.take<uint16_t>(P * 4);
+	g.cull = c.take<float>(P * 4);
+	g.tiles_touched = c.take<uint32_t>(P);
+	g.point_offsets = c.take<uint32_t>(P);
+	g.clamped = c.take<uint8_t>(P * 3);
+	g.scan_status = c.take<uint64_t>((P + SCAN_TILE - 1) / SCAN_TILE + 1);
+	g.counters = c.take<uint32_t>(8);
+	if (bytes) *bytes = c.total();
+	return g;
+}
+
+ImageState ImageState::carve(void* base, size_t W, size_t H, size_t* bytes)
+{
+	Carver c(base);
+	ImageState im;
+	const size_t px = W * H;
+	const size_t tiles = ((W + TILE - 1) / TILE) * ((H + TILE - 1) / TILE);
+	im.final_T = c.take<float>(3 * px);
+	im.n_contrib = c.take<uint32_t>(2 * px);
+	im.median_depth = c.take<float>(px);
+	im.depth_std = c.take<float>(px);
+	im.ranges = c.take<uint32_t>(2 * tiles);
+	if (bytes) *bytes = c.total();
+	return im;
+}
+
+SortScratch SortScratch::carve(void* base, size_t n, size_t* bytes)
+{
+	Carver c(base);
+	SortScratch s;
+	s.blocks = (n + SORT_TILE - 1) / SORT_TILE;
+	if (s.blocks == 0) s.blocks = 1;
+	s.hist = c.take<uint32_t>(SORT_MAX_PASSES * SORT_RADIX);
+	char* z0 = (char*)s.hist;
+	s.tickets = c.take<uint32_t>(SORT_MAX_PASSES);
+	s.status = c.take<uint32_t>((size_t)SORT_MAX_PASSES * s.blocks * SORT_RADIX);
+	char* z1 = (char*)(s.status + (size_t)SORT_MAX_PASSES * s.blocks * SORT_RADIX);
+	s.zero_bytes = (size_t)(z1 - z0);
+	if (bytes) *bytes = c.total();
+	return s;
+}
+
+BinningState BinningState::carve(void* base, size_t I, size_t* bytes)
+{
+	Carver c(base);
+	BinningState b;
+	const size_t n = I ? I : 1;
+	b.keys_a = c.take<uint64_t>(n);
+	b.keys_b = c.take<uint64_t>(n);
+	b.vals_a = c.take<uint32_t>(n);
+	b.vals_b = c.take<uint32_t>(n);
+	b.instances = c.take<float>(n * REC_WORDS);
+	b.keys_dbg = c.take<uint64_t>(n);
+	b.vals_dbg = c.take<uint32_t>(n);
+	size_t sort_bytes = 0;
+	SortScratch::carve(nullptr, n, &sort_bytes);
+	char* sbase = c.take<char>(sort_bytes);
+	b.sort = SortScratch::carve(sbase, n, nullptr);
+	if (bytes) *bytes = c.total();
+	return b;
+}
+
+static inline int end_bit_for(const gs2d_settings& s)
+{
+	const unsigned gx = (s.image_width + TILE - 1) / TILE, gy = (s.image_height + TILE - 1) / TILE;
+	return 32 + (int)higher_msb(gx * gy);
+}
+
+static int check_common(const gs2d_settings* s, const gs2d_inputs* in, const gs2d_buffers* b)
+{
+	if (!s || !in || !b) return GS2D_ERR_INVALID;
+	if (s->P < 0 || s->image_width <= 0 || s->image_height <= 0) return GS2D_ERR_INVALID;
+	if (!in->means3D || !in->opacities || !in->viewmatrix || !in->projmatrix || !in->background)
+		return GS2D_ERR_INVALID;
+	if ((in->shs == nullptr) == (in->colors_precomp == nullptr)) return GS2D_ERR_INVALID;
+	const bool have_sr = in->scales != nullptr && in->rotations != nullptr;
+	if (have_sr == (in->transMat_precomp != nullptr)) return GS2D_ERR_INVALID;
+	if (in->shs && (s->sh_coeffs <= 0 || !in->campos)) return GS2D_ERR_INVALID;
+	return GS2D_OK;
+}
+
+static int debug_sync(const gs2d_settings& s, cudaStream_t st)
+{
+	if (!s.debug) return GS2D_OK;
+	GS2D_CUDA_OK(cudaStreamSynchronize(st));
+	GS2D_CUDA_OK(cudaGetLastError());
+	return GS2D_OK;
+}
+
+#define GS2D_TRY(expr) do { int rc__ = (expr); if (rc__ != GS2D_OK) return rc__; } while (0)
+
+}  // namespace gs2d
+
+using namespace gs2d;
+
+extern "C" {
+
+size_t gs2d_geom_bytes(int32_t P, int32_t) { size_t b = 0; GeomState::carve(nullptr, (size_t)(P > 0 ? P : 0), &b); return b; }
+size_t gs2d_image_bytes(int32_t W, int32_t H) { size_t b = 0; ImageState::carve(nullptr, (size_t)W, (size_t)H, &b); return b; }
+size_t gs2d_binning_bytes(int64_t I, int32_t, int32_t) { size_t b = 0; BinningState::carve(nullptr, (size_t)(I > 0 ? I : 0), &b); return b; }
+size_t gs2d_backward_scratch_bytes(int32_t, int64_t I) { return (size_t)(I > 0 ? I : 0) * GRAD_WORDS * sizeof(float) + ALIGN; }
+size_t gs2d_sort_scratch_bytes(int64_t n)
+{
+	const size_t m = (size_t)(n > 0 ? n : 1);
+	size_t sb = 0;
+	SortScratch::carve(nullptr, m, &sb);
+	return sb + ALIGN * 4 + m * (sizeof(uint64_t) + sizeof(uint32_t)) + 2 * ALIGN;
+}
+
+int gs2d_forward_preprocess(const gs2d_settings* s, const gs2d_inputs* in, const gs2d_buffers* buffers,
+                            int32_t* radii, int64_t* num_rendered_host, void* stream)
+{
+	GS2D_TRY(check_common(s, in, buffers));
+	cudaStream_t st = (cudaStream_t)stream;
+	if (num_rendered_host) *num_rendered_host = 0;
+	if (s->P == 0) return GS2D_OK;
+	if (!buffers->geom || !radii) return GS2D_ERR_INVALID;
+	if (buffers->geom_bytes < gs2d_geom_bytes(s->P, s->sh_coeffs)) return GS2D_ERR_CAPACITY;
+	GeomState g = GeomState::carve(buffers->geom, (size_t)s->P, nullptr);
+	GS2D_TRY(launch_preprocess_forward(*s, *in, g, radii, st));
+	GS2D_TRY(debug_sync(*s, st));
+	GS2D_TRY(launch_scan_tiles(g, s->P, st));
+	GS2D_TRY(debug_sync(*s, st));
+	if (num_rendered_host) {
+		// 4-byte read-back into the low half of the (zeroed) int64
+		GS2D_CUDA_OK(cudaMemcpyAsync(num_rendered_host, g.counters + 1, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+	}
+	return GS2D_OK;
+}
+
+int gs2d_forward_render(const gs2d_settings* s, const gs2d_inputs* in, const gs2d_buffers* buffers,
+                        int64_t I, float* out_color, float* out_others, void* stream)
+{
+	GS2D_TRY(check_common(s, in, buffers));
+	cudaStream_t st = (cudaStream_t)stream;
+	if (!out_color || !out_others || !buffers->image) return GS2D_ERR_INVALID;
+	if (I < 0 || I >= (1ll << 30)) return GS2D_ERR_INVALID;
+	if (buffers->image_bytes < gs2d_image_bytes(s->image_width, s->image_height)) return GS2D_ERR_CAPACITY;
+	ImageState im = ImageState::carve(buffers->image, (size_t)s->image_width, (size_t)s->image_height, nullptr);
+	const unsigned gx = (s->image_width + TILE - 1) / TILE, gy = (s->image_height + TILE - 1) / TILE;
+	if (s->P == 0 || I == 0) {
+		// nothing to blend: ranges all empty, the compositor still writes every pixel (background)
+		GS2D_CUDA_OK(cudaMemsetAsync(im.ranges, 0, sizeof(uint32_t) * 2 * (size_t)gx * gy, st));
+		return launch_composite_forward(*s, *in, im, nullptr, out_color, out_others, st);
+	}
+	if (!buffers->geom || !buffers->binning) return GS2D_ERR_INVALID;
+	if (buffers->binning_bytes < gs2d_binning_bytes(I, s->image_width, s->image_height)) return GS2D_ERR_CAPACITY;
+	GeomState g = GeomState::carve(buffers->geom, (size_t)s->P, nullptr);
+	BinningState b = BinningState::carve(buffers->binning, (size_t)I, nullptr);
+
+	GS2D_TRY(launch_duplicate(*s, g, nullptr, b, I, st));
+	GS2D_TRY(debug_sync(*s, st));
+	if (s->debug) {
+		GS2D_CUDA_OK(cudaMemcpyAsync(b.keys_dbg, b.keys_a, sizeof(uint64_t) * (size_t)I, cudaMemcpyDeviceToDevice, st));
+		GS2D_CUDA_OK(cudaMemcpyAsync(b.vals_dbg, b.vals_a, sizeof(uint32_t) * (size_t)I, cudaMemcpyDeviceToDevice, st));
+	}
+	bool in_b = false;
+	GS2D_TRY(launch_sort_pairs(I, b.keys_a, b.vals_a, b.keys_b, b.vals_b, b.keys_a, b.vals_a, end_bit_for(*s),
+	                           b.sort, &in_b, st));
+	GS2D_TRY(debug_sync(*s, st));
+	if (!in_b) {
+		// keep the sorted result where gs2d_state_view_get and backward expect it (keys_b / vals_b)
+		GS2D_CUDA_OK(cudaMemcpyAsync(b.keys_b, b.keys_a, sizeof(uint64_t) * (size_t)I, cudaMemcpyDeviceToDevice, st));
+		GS2D_CUDA_OK(cudaMemcpyAsync(b.vals_b, b.vals_a, sizeof(uint32_t) * (size_t)I, cudaMemcpyDeviceToDevice, st));
+	}
+	GS2D_TRY(launch_gather_ranges(*s, g, b.keys_b, b.vals_b, b.instances, im.ranges, I, st));
+	GS2D_TRY(debug_sync(*s, st));
+	GS2D_TRY(launch_composite_forward(*s, *in, im, b.instances, out_color, out_others, st));
+	GS2D_TRY(debug_sync(*s, st));
+	return GS2D_OK;
+}
+
+int gs2d_forward(const gs2d_settings* s, const gs2d_inputs* in, const gs2d_buffers* buffers, int32_t* radii,
+                 int64_t* num_rendered_io, float* out_color, float* out_others, void* stream)
+{
+	if (!num_rendered_io) return GS2D_ERR_INVALID;
+	cudaStream_t st = (cudaStream_t)stream;
+	const int64_t capacity = *num_rendered_io;
+	int64_t count = 0;
+	GS2D_TRY(gs2d_forward_preprocess(s, in, buffers, radii, nullptr, stream));
+	if (s->P > 0) {
+		GeomState g = GeomState::carve(buffers->geom, (size_t)s->P, nullptr);
+		uint32_t c32 = 0;
+		GS2D_CUDA_OK(cudaMemcpyAsync(&c32, g.counters + 1, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+		GS2D_CUDA_OK(cudaStreamSynchronize(st));
+		count = c32;
+	}
+	*num_rendered_io = count;
+	if (count > capacity) return GS2D_ERR_CAPACITY;
+	return gs2d_forward_render(s, in, buffers, count, out_color, out_others, stream);
+}
+
+int gs2d_backward(const gs2d_settings* s, const gs2d_inputs* in, const gs2d_buffers* buffers,
+                  const int32_t* radii, int64_t I, const float* dL_dout_color, const float* dL_dout_others,
+                  const gs2d_grads* grads, void* scratch, void* stream)
+{
+	GS2D_TRY(check_common(s, in, buffers));
+	cudaStream_t st = (cudaStream_t)stream;
+	if (!grads || !dL_dout_color || !dL_dout_others) return GS2D_ERR_INVALID;
+	if (s->P == 0) return GS2D_OK;
+	if (!radii || !buffers->geom || !buffers->image) return GS2D_ERR_INVALID;
+	if (!grads->dL_dmeans2D || !grads->dL_dcolors || !grads->dL_dopacity || !grads->dL_dmeans3D ||
+	    !grads->dL_dtransMat || !grads->dL_dscales || !grads->dL_drotations)
+		return GS2D_ERR_INVALID;
+	if (in->shs && !grads->dL_dsh) return GS2D_ERR_INVALID;
+	GeomState g = GeomState::carve(buffers->geom, (size_t)s->P, nullptr);
+	ImageState im = ImageState::carve(buffers->image, (size_t)s->image_width, (size_t)s->image_height, nullptr);
+	float* rows = (float*)scratch;
+	if (I > 0) {
+		if (!scratch || !buffers->binning) return GS2D_ERR_INVALID;
+		BinningState b = BinningState::carve(buffers->binning, (size_t)I, nullptr);
+		GS2D_CUDA_OK(cudaMemsetAsync(rows, 0, (size_t)I * GRAD_WORDS * sizeof(float), st));
+		GS2D_TRY(launch_composite_backward(*s, *in, im, b.instances, dL_dout_color, dL_dout_others, rows, st));
+		GS2D_TRY(debug_sync(*s, st));
+	}
+	GS2D_TRY(launch_preprocess_backward(*s, *in, g, radii, rows, *grads, st));
+	GS2D_TRY(debug_sync(*s, st));
+	return GS2D_OK;
+}
+
+int gs2d_mark_visible(int32_t P, const float* means3D, const float* viewmatrix, const float* projmatrix,
+                      uint8_t* present, void* stream)
+{
+	if (P < 0) return GS2D_ERR_INVALID;
+	if (P == 0) return GS2D_OK;
+	if (!means3D || !viewmatrix || !present) return GS2D_ERR_INVALID;
+	return launch_mark_visible(P, means3D, viewmatrix, projmatrix, present, (cudaStream_t)stream);
+}
+
+int gs2d_state_view_get(const gs2d_settings* s, const gs2d_buffers* buffers, int64_t I, gs2d_state_view* out)
+{
+	if (!s || !buffers || !out) return GS2D_ERR_INVALID;
+	memset(out, 0, sizeof(*out));
+	if (buffers->geom && s->P > 0) {
+		GeomState g = GeomState::carve(buffers->geom, (size_t)s->P, nullptr);
+		out->depths = g.depths; out->splat = g.splat; out->rect = g.rect; out->cull = g.cull;
+		out->tiles_touched = g.tiles_touched; out->point_offsets = g.point_offsets;
+	}
+	if (buffers->binning && I > 0) {
+		BinningState b = BinningState::carve(buffers->binning, (size_t)I, nullptr);
+		out->keys_unsorted = b.keys_dbg; out->values_unsorted = b.vals_dbg;
+		out->keys_sorted = b.keys_b; out->point_list = b.vals_b; out->instances = b.instances;
+	}
+	if (buffers->image) {
+		ImageState im = ImageState::carve(buffers->image, (size_t)s->image_width, (size_t)s->image_height, nullptr);
+		out->ranges = im.ranges; out->final_T = im.final_T; out->n_contrib = im.n_contrib;
+		out->median_depth = im.median_depth; out->depth_std = im.depth_std;
+	}
+	return GS2D_OK;
+}
+
+int gs2d_sort_pairs(int64_t n, const uint64_t* keys_in, const uint32_t* values_in, uint64_t* keys_out,
+                    uint32_t* values_out, int32_t end_bit, void* scratch, void* stream)
+{
+	if (n < 0 || n >= (1ll << 30) || end_bit <= 0 || end_bit > 64) return GS2D_ERR_INVALID;
+	if (n == 0) return GS2D_OK;
+	if (!keys_in || !values_in || !keys_out || !values_out || !scratch) return GS2D_ERR_INVALID;
+	cudaStream_t st = (cudaStream_t)stream;
+	Carver c(scratch);
+	size_t sb = 0;
+	SortScratch::carve(nullptr, (size_t)n, &sb);
+	char* sbase = c.take<char>(sb);
+	SortScratch ss = SortScratch::carve(sbase, (size_t)n, nullptr);
+	uint64_t* tk = c.take<uint64_t>((size_t)n);
+	uint32_t* tv = c.take<uint32_t>((size_t)n);
+	bool in_b = false;
+	GS2D_TRY(launch_sort_pairs(n, keys_in, values_in, keys_out, values_out, tk, tv, end_bit, ss, &in_b, st));
+	if (!in_b) {
+		GS2D_CUDA_OK(cudaMemcpyAsync(keys_out, tk, sizeof(uint64_t) * (size_t)n, cudaMemcpyDeviceToDevice, st));
+		GS2D_CUDA_OK(cudaMemcpyAsync(values_out, tv, sizeof(uint32_t) * (size_t)n, cudaMemcpyDeviceToDevice, st));
+	}
+	return GS2D_OK;
+}
+
+const char* gs2d_strerror(int status)
+{
+	switch (status) {
+	case GS2D_OK: return "ok";
+	case GS2D_ERR_INVALID: return "invalid argument";
+	case GS2D_ERR_CUDA: return "CUDA runtime error";
+	case GS2D_ERR_CAPACITY: return "workspace too small";
+	case GS2D_ERR_UNSUPPORTED: return "unsupported";
+	default: return "unknown gs2d status";
+	}
+}
+
+int gs2d_last_cuda_error(void) { return g_last_cuda_error; }
+int gs2d_abi_version(void) { return GS2D_ABI_VERSION; }
+int64_t gs2d_launch_count(void) { return (int64_t)g_launches.load(); }
+
+}  // extern "C"

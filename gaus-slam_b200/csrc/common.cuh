@@ -1,0 +1,147 @@
+// common.cuh -- shared declarations for libgs2d (B200 / sm_100a).
+//
+// Internal to the library; the public surface is include/gs2d.h.
+#pragma once
+
+#include <cstddef>
+#include <cstdint>
+#include <cuda_runtime.h>
+
+#include "../../include/gs2d.h"
+
+namespace gs2d {
+
+constexpr int TILE = GS2D_TILE;          // 16x16 pixel tiles (CR/config.h:16-17)
+constexpr int TILE_PIXELS = TILE * TILE;
+constexpr int REC_WORDS = 20;            // one splat / instance record = 5 x float4 = 80 B
+constexpr int GRAD_WORDS = 20;           // one per-instance gradient row = 80 B
+
+// Record word layout (per surfel in `splat`, per sorted instance in `instances`):
+//   0..2  Tu     3  centre x        (transMat rows, CR/forward.cu:196-199; means2D)
+//   4..6  Tv     7  centre y
+//   8..10 Tw    11  opacity
+//  12..14 normal 15 block mask (instances only: which 8x4 pixel blocks of the tile can be touched)
+//  16..18 rgb    19 row (instances only: index of this instance's gradient row)
+constexpr int REC_MASK = 15;
+constexpr int REC_ROW = 19;
+
+// Gradient row layout (backward compositing -> backward preprocess):
+//   0..8 dL/dtransMat, 9..10 dL/dmean2D.xy, 11 dL/dopacity, 12..14 dL/dnormal, 15..17 dL/dcolor
+constexpr int GR_T = 0, GR_M2D = 9, GR_OPA = 11, GR_NRM = 12, GR_COL = 15;
+constexpr int GR_USED = 18;
+
+// Constants of the reference (CR/auxiliary.h:37-39).
+#define GS2D_NEAR 0.2f
+#define GS2D_FAR 100.0f
+#define GS2D_FILTER_INV_SQUARE 100.0f
+
+constexpr size_t ALIGN = 256;
+
+struct Carver {
+	char* p;
+	size_t off;
+	explicit __host__ Carver(void* base) : p((char*)base), off(0) {}
+	template <typename T>
+	__host__ T* take(size_t count) {
+		off = (off + ALIGN - 1) & ~(ALIGN - 1);
+		T* r = p ? (T*)(p + off) : nullptr;
+		off += count * sizeof(T);
+		return r;
+	}
+	__host__ size_t total() const { return ((off + ALIGN - 1) & ~(ALIGN - 1)) + ALIGN; }
+};
+
+// ---- scan (decoupled look-back) geometry --------------------------------------------
+constexpr int SCAN_THREADS = 256;
+constexpr int SCAN_ITEMS = 8;
+constexpr int SCAN_TILE = SCAN_THREADS * SCAN_ITEMS;
+
+// ---- onesweep radix sort geometry ----------------------------------------------------
+constexpr int SORT_THREADS = 256;
+constexpr int SORT_ITEMS = 16;
+constexpr int SORT_TILE = SORT_THREADS * SORT_ITEMS;   // 4096 pairs per block
+constexpr int SORT_RADIX_BITS = 8;
+constexpr int SORT_RADIX = 1 << SORT_RADIX_BITS;
+constexpr int SORT_MAX_PASSES = 8;
+
+struct GeomState {
+	float* depths;            // [P]
+	float* splat;             // [P,20]
+	uint16_t* rect;           // [P,4]
+	float* cull;              // [P,4]
+	uint32_t* tiles_touched;  // [P]
+	uint32_t* point_offsets;  // [P]
+	uint8_t* clamped;         // [P,3]
+	uint64_t* scan_status;    // [scan blocks]
+	uint32_t* counters;       // [8]: 0 scan ticket, 1 num_rendered (u32), 2.. spare
+	static __host__ GeomState carve(void* base, size_t P, size_t* bytes);
+};
+
+struct ImageState {
+	float* final_T;           // [3,H,W]: T, M1, M2
+	uint32_t* n_contrib;      // [2,H,W]: last contributor, median contributor
+	float* median_depth;      // [H,W]
+	float* depth_std;         // [H,W]
+	uint32_t* ranges;         // [tiles,2]
+	static __host__ ImageState carve(void* base, size_t W, size_t H, size_t* bytes);
+};
+
+struct SortScratch {
+	uint32_t* hist;           // [SORT_MAX_PASSES, 256] -> exclusive digit bases
+	uint32_t* tickets;        // [SORT_MAX_PASSES]
+	uint32_t* status;         // [SORT_MAX_PASSES, blocks, 256]
+	size_t blocks;
+	size_t zero_bytes;        // bytes from `hist` that must be zeroed before a sort
+	static __host__ SortScratch carve(void* base, size_t n, size_t* bytes);
+};
+
+struct BinningState {
+	uint64_t* keys_a;         // [I] unsorted keys (pass ping)
+	uint64_t* keys_b;         // [I] (pass pong)
+	uint32_t* vals_a;         // [I]
+	uint32_t* vals_b;         // [I]
+	float* instances;         // [I,20]
+	uint64_t* keys_dbg;       // [I] copy of the unsorted keys
+	uint32_t* vals_dbg;       // [I]
+	SortScratch sort;
+	static __host__ BinningState carve(void* base, size_t I, size_t* bytes);
+};
+
+inline int sort_passes(int end_bit) { return (end_bit + SORT_RADIX_BITS - 1) / SORT_RADIX_BITS; }
+
+// Host-side launch bookkeeping -----------------------------------------------------------
+extern thread_local int g_last_cuda_error;
+void count_launch(int n = 1);
+#define GS2D_CUDA_OK(expr)                                              \
+	do {                                                                \
+		cudaError_t e__ = (expr);                                       \
+		if (e__ != cudaSuccess) { gs2d::g_last_cuda_error = (int)e__; return GS2D_ERR_CUDA; } \
+	} while (0)
+
+// Kernel launchers (each returns a gs2d_status) ------------------------------------------
+int launch_preprocess_forward(const gs2d_settings& s, const gs2d_inputs& in, const GeomState& g,
+                              int32_t* radii, cudaStream_t st);
+int launch_scan_tiles(const GeomState& g, int P, cudaStream_t st);
+int launch_duplicate(const gs2d_settings& s, const GeomState& g, const int32_t* radii_unused,
+                     const BinningState& b, int64_t I, cudaStream_t st);
+int launch_sort_pairs(int64_t n, const uint64_t* keys_a, const uint32_t* vals_a, uint64_t* keys_b,
+                      uint32_t* vals_b, uint64_t* keys_a_rw, uint32_t* vals_a_rw, int end_bit,
+                      const SortScratch& ss, bool* result_in_b, cudaStream_t st);
+int launch_gather_ranges(const gs2d_settings& s, const GeomState& g, const uint64_t* keys_sorted,
+                         const uint32_t* point_list, float* instances, uint32_t* ranges, int64_t I,
+                         cudaStream_t st);
+int launch_composite_forward(const gs2d_settings& s, const gs2d_inputs& in, const ImageState& im,
+                             const float* instances, float* out_color, float* out_others,
+                             cudaStream_t st);
+int launch_composite_backward(const gs2d_settings& s, const gs2d_inputs& in, const ImageState& im,
+                              const float* instances, const float* dL_dcolor, const float* dL_dothers,
+                              float* grad_rows, cudaStream_t st);
+int launch_preprocess_backward(const gs2d_settings& s, const gs2d_inputs& in, const GeomState& g,
+                               const int32_t* radii, const float* grad_rows, const gs2d_grads& out,
+                               cudaStream_t st);
+int launch_mark_visible(int P, const float* means3D, const float* view, const float* proj,
+                        uint8_t* present, cudaStream_t st);
+
+uint32_t higher_msb(uint32_t n);   // CR/rasterizer_impl.cu:35-50 semantics
+
+}  // namespace gs2d

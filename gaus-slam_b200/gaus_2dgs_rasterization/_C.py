@@ -1,0 +1,157 @@
+"""Drop-in for the reference's pybind module `gaus_2dgs_rasterization._C` (RAST/ext.cpp:15-19).
+
+Same three entry points, same argument order, same return tuples as
+RAST/rasterize_points.cu:39-61/:137, :140-165/:238 and :241-260 -- implemented over the C ABI of
+libgs2d.so (include/gs2d.h) with raw device pointers taken from the torch tensors.  torch is only
+the allocator / stream provider here; all compute is in the hand-written CUDA library.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import torch
+
+from gs2d_b200 import _lib as L
+
+_pinned = {}
+
+
+def _stream_ptr(device) -> C.c_void_p:
+    return C.c_void_p(torch.cuda.current_stream(device).cuda_stream)
+
+
+def _f32(t: torch.Tensor, name: str) -> torch.Tensor:
+    if not t.is_cuda:
+        raise RuntimeError(f"{name} must be a CUDA tensor")
+    if t.dtype != torch.float32:
+        raise RuntimeError(f"{name} must be float32, got {t.dtype}")
+    return t.contiguous()
+
+
+def _ptr(t):
+    if t is None or t.numel() == 0:
+        return None
+    return t.data_ptr()
+
+
+def _pinned_i64(device) -> torch.Tensor:
+    key = str(device)
+    if key not in _pinned:
+        _pinned[key] = torch.zeros(1, dtype=torch.int64).pin_memory()
+    return _pinned[key]
+
+
+def _settings(P, W, H, degree, M, use_sa, prefiltered, debug, tan_fovx, tan_fovy, scale_modifier):
+    return L.Settings(P=P, image_width=W, image_height=H, sh_degree=int(degree), sh_coeffs=int(M),
+                      use_sa=int(bool(use_sa)), prefiltered=int(bool(prefiltered)), debug=int(bool(debug)),
+                      tanfovx=float(tan_fovx), tanfovy=float(tan_fovy), scale_modifier=float(scale_modifier),
+                      reserved_=0.0)
+
+
+def _inputs(background, means3D, sh, colors, opacity, scales, rotations, transMat, view, proj, campos):
+    return L.Inputs(background=_ptr(background), means3D=_ptr(means3D), shs=_ptr(sh),
+                    colors_precomp=_ptr(colors), opacities=_ptr(opacity), scales=_ptr(scales),
+                    rotations=_ptr(rotations), transMat_precomp=_ptr(transMat), viewmatrix=_ptr(view),
+                    projmatrix=_ptr(proj), campos=_ptr(campos))
+
+
+def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations, scale_modifier,
+                        transMat_precomp, viewmatrix, projmatrix, tan_fovx, tan_fovy, image_height,
+                        image_width, sh, degree, campos, use_sa, prefiltered, debug):
+    """-> (num_rendered, out_color[3,H,W], out_others[7,H,W], radii[P] i32, geomBuffer, binningBuffer, imgBuffer)"""
+    lib = L.load()
+    if means3D.ndim != 2 or means3D.shape[1] != 3:
+        raise RuntimeError("means3D must have dimensions (num_points, 3)")
+    dev = means3D.device
+    P, H, W = int(means3D.shape[0]), int(image_height), int(image_width)
+    background = _f32(background, "background"); means3D = _f32(means3D, "means3D")
+    colors = _f32(colors, "colors"); opacity = _f32(opacity, "opacity")
+    scales = _f32(scales, "scales"); rotations = _f32(rotations, "rotations")
+    transMat_precomp = _f32(transMat_precomp, "transMat_precomp")
+    viewmatrix = _f32(viewmatrix, "viewmatrix"); projmatrix = _f32(projmatrix, "projmatrix")
+    sh = _f32(sh, "sh"); campos = _f32(campos, "campos")
+    M = int(sh.shape[1]) if sh.numel() != 0 and sh.ndim >= 2 else 0
+
+    with torch.cuda.device(dev):
+        st = _stream_ptr(dev)
+        u8 = dict(dtype=torch.uint8, device=dev)
+        out_color = torch.empty((3, H, W), dtype=torch.float32, device=dev)
+        out_others = torch.empty((7, H, W), dtype=torch.float32, device=dev)
+        radii = torch.empty((P,), dtype=torch.int32, device=dev)
+        geom = torch.empty((lib.gs2d_geom_bytes(P, M) if P else 0,), **u8)
+        img = torch.empty((lib.gs2d_image_bytes(W, H),), **u8)
+        s = _settings(P, W, H, degree, M, use_sa, prefiltered, debug, tan_fovx, tan_fovy, scale_modifier)
+        i = _inputs(background, means3D, sh, colors, opacity, scales, rotations, transMat_precomp,
+                    viewmatrix, projmatrix, campos)
+        bufs = L.Buffers(geom=_ptr(geom), geom_bytes=geom.numel(), binning=None, binning_bytes=0,
+                         image=_ptr(img), image_bytes=img.numel())
+        n_host = _pinned_i64(dev)
+        L.check(lib.gs2d_forward_preprocess(C.byref(s), C.byref(i), C.byref(bufs), _ptr(radii),
+                                            n_host.data_ptr(), st), "gs2d_forward_preprocess")
+        torch.cuda.current_stream(dev).synchronize()
+        num_rendered = int(n_host[0]) if P else 0
+        binning = torch.empty((lib.gs2d_binning_bytes(num_rendered, W, H) if num_rendered else 0,), **u8)
+        bufs.binning = _ptr(binning)
+        bufs.binning_bytes = binning.numel()
+        L.check(lib.gs2d_forward_render(C.byref(s), C.byref(i), C.byref(bufs), num_rendered,
+                                        _ptr(out_color), _ptr(out_others), st), "gs2d_forward_render")
+    return num_rendered, out_color, out_others, radii, geom, binning, img
+
+
+def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rotations, scale_modifier,
+                                 transMat_precomp, viewmatrix, projmatrix, tan_fovx, tan_fovy,
+                                 dL_dout_color, dL_dout_others, sh, degree, campos, geomBuffer, R,
+                                 binningBuffer, imageBuffer, use_sa, debug):
+    """-> (dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dtransMat, dL_dsh, dL_dscales, dL_drotations)"""
+    lib = L.load()
+    dev = means3D.device
+    P = int(means3D.shape[0])
+    H, W = int(dL_dout_color.shape[1]), int(dL_dout_color.shape[2])
+    background = _f32(background, "background"); means3D = _f32(means3D, "means3D")
+    colors = _f32(colors, "colors"); scales = _f32(scales, "scales"); rotations = _f32(rotations, "rotations")
+    transMat_precomp = _f32(transMat_precomp, "transMat_precomp")
+    viewmatrix = _f32(viewmatrix, "viewmatrix"); projmatrix = _f32(projmatrix, "projmatrix")
+    sh = _f32(sh, "sh"); campos = _f32(campos, "campos")
+    dL_dout_color = _f32(dL_dout_color, "dL_dout_color"); dL_dout_others = _f32(dL_dout_others, "dL_dout_others")
+    M = int(sh.shape[1]) if sh.numel() != 0 and sh.ndim >= 2 else 0
+
+    f32 = dict(dtype=torch.float32, device=dev)
+    g_means3D = torch.empty((P, 3), **f32); g_means2D = torch.empty((P, 3), **f32)
+    g_colors = torch.empty((P, 3), **f32); g_opacity = torch.empty((P, 1), **f32)
+    g_transMat = torch.empty((P, 9), **f32); g_sh = torch.empty((P, M, 3), **f32)
+    g_scales = torch.empty((P, 2), **f32); g_rot = torch.empty((P, 4), **f32)
+    if P == 0:
+        return g_means2D, g_colors, g_opacity, g_means3D, g_transMat, g_sh, g_scales, g_rot
+
+    with torch.cuda.device(dev):
+        st = _stream_ptr(dev)
+        scratch = torch.empty((lib.gs2d_backward_scratch_bytes(P, int(R)),), dtype=torch.uint8, device=dev)
+        s = _settings(P, W, H, degree, M, use_sa, False, debug, tan_fovx, tan_fovy, scale_modifier)
+        # opacities are not an input of backward (the forward stored them in the splat records)
+        i = _inputs(background, means3D, sh, colors, means3D, scales, rotations, transMat_precomp,
+                    viewmatrix, projmatrix, campos)
+        bufs = L.Buffers(geom=_ptr(geomBuffer), geom_bytes=geomBuffer.numel(), binning=_ptr(binningBuffer),
+                         binning_bytes=binningBuffer.numel(), image=_ptr(imageBuffer),
+                         image_bytes=imageBuffer.numel())
+        grads = L.Grads(dL_dmeans2D=_ptr(g_means2D), dL_dcolors=_ptr(g_colors), dL_dopacity=_ptr(g_opacity),
+                        dL_dmeans3D=_ptr(g_means3D), dL_dtransMat=_ptr(g_transMat), dL_dsh=_ptr(g_sh),
+                        dL_dscales=_ptr(g_scales), dL_drotations=_ptr(g_rot))
+        L.check(lib.gs2d_backward(C.byref(s), C.byref(i), C.byref(bufs), _ptr(radii), int(R),
+                                  _ptr(dL_dout_color), _ptr(dL_dout_others), C.byref(grads), _ptr(scratch), st),
+                "gs2d_backward")
+    return g_means2D, g_colors, g_opacity, g_means3D, g_transMat, g_sh, g_scales, g_rot
+
+
+def mark_visible(means3D, viewmatrix, projmatrix):
+    """-> bool[P]: view-space z > 0.2 (RAST/rasterize_points.cu:241-260)."""
+    lib = L.load()
+    dev = means3D.device
+    P = int(means3D.shape[0])
+    means3D = _f32(means3D, "means3D"); viewmatrix = _f32(viewmatrix, "viewmatrix")
+    projmatrix = _f32(projmatrix, "projmatrix")
+    present = torch.zeros((P,), dtype=torch.bool, device=dev)
+    if P:
+        with torch.cuda.device(dev):
+            L.check(lib.gs2d_mark_visible(P, _ptr(means3D), _ptr(viewmatrix), _ptr(projmatrix),
+                                          present.data_ptr(), _stream_ptr(dev)), "gs2d_mark_visible")
+    return present

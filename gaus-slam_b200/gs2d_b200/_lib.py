@@ -1,0 +1,116 @@
+"""ctypes view of include/gs2d.h (libgs2d.so).
+
+The library is plain C ABI: this module only mirrors its structs and prototypes.  There is no
+CPU fallback anywhere in the product path: if the shared library is missing, or a call returns
+a non-zero status, an exception is raised.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(os.path.dirname(_HERE), "lib", "libgs2d.so")
+
+GS2D_OK = 0
+GS2D_ERR_INVALID = -1
+GS2D_ERR_CUDA = -2
+GS2D_ERR_CAPACITY = -3
+GS2D_ERR_UNSUPPORTED = -4
+
+
+class Settings(C.Structure):
+    _fields_ = [
+        ("P", C.c_int32), ("image_width", C.c_int32), ("image_height", C.c_int32),
+        ("sh_degree", C.c_int32), ("sh_coeffs", C.c_int32), ("use_sa", C.c_int32),
+        ("prefiltered", C.c_int32), ("debug", C.c_int32),
+        ("tanfovx", C.c_float), ("tanfovy", C.c_float), ("scale_modifier", C.c_float),
+        ("reserved_", C.c_float),
+    ]
+
+
+class Inputs(C.Structure):
+    _fields_ = [(n, C.c_void_p) for n in (
+        "background", "means3D", "shs", "colors_precomp", "opacities", "scales", "rotations",
+        "transMat_precomp", "viewmatrix", "projmatrix", "campos")]
+
+
+class Buffers(C.Structure):
+    _fields_ = [("geom", C.c_void_p), ("geom_bytes", C.c_size_t),
+                ("binning", C.c_void_p), ("binning_bytes", C.c_size_t),
+                ("image", C.c_void_p), ("image_bytes", C.c_size_t)]
+
+
+class Grads(C.Structure):
+    _fields_ = [(n, C.c_void_p) for n in (
+        "dL_dmeans2D", "dL_dcolors", "dL_dopacity", "dL_dmeans3D", "dL_dtransMat", "dL_dsh",
+        "dL_dscales", "dL_drotations")]
+
+
+class StateView(C.Structure):
+    _fields_ = [(n, C.c_void_p) for n in (
+        "depths", "splat", "rect", "cull", "tiles_touched", "point_offsets",
+        "keys_unsorted", "values_unsorted", "keys_sorted", "point_list", "instances",
+        "ranges", "final_T", "n_contrib", "median_depth", "depth_std")]
+
+
+# name -> (restype, argtypes); also the list of symbols the header declares (checked by tests).
+PROTOTYPES = {
+    "gs2d_geom_bytes": (C.c_size_t, [C.c_int32, C.c_int32]),
+    "gs2d_image_bytes": (C.c_size_t, [C.c_int32, C.c_int32]),
+    "gs2d_binning_bytes": (C.c_size_t, [C.c_int64, C.c_int32, C.c_int32]),
+    "gs2d_forward_preprocess": (C.c_int, [C.POINTER(Settings), C.POINTER(Inputs), C.POINTER(Buffers),
+                                          C.c_void_p, C.c_void_p, C.c_void_p]),
+    "gs2d_forward_render": (C.c_int, [C.POINTER(Settings), C.POINTER(Inputs), C.POINTER(Buffers),
+                                      C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "gs2d_forward": (C.c_int, [C.POINTER(Settings), C.POINTER(Inputs), C.POINTER(Buffers), C.c_void_p,
+                               C.POINTER(C.c_int64), C.c_void_p, C.c_void_p, C.c_void_p]),
+    "gs2d_backward_scratch_bytes": (C.c_size_t, [C.c_int32, C.c_int64]),
+    "gs2d_backward": (C.c_int, [C.POINTER(Settings), C.POINTER(Inputs), C.POINTER(Buffers), C.c_void_p,
+                                C.c_int64, C.c_void_p, C.c_void_p, C.POINTER(Grads), C.c_void_p, C.c_void_p]),
+    "gs2d_mark_visible": (C.c_int, [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "gs2d_dist2_scratch_bytes": (C.c_size_t, [C.c_int32]),
+    "gs2d_dist2": (C.c_int, [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "gs2d_state_view_get": (C.c_int, [C.POINTER(Settings), C.POINTER(Buffers), C.c_int64, C.POINTER(StateView)]),
+    "gs2d_sort_scratch_bytes": (C.c_size_t, [C.c_int64]),
+    "gs2d_sort_pairs": (C.c_int, [C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32,
+                                  C.c_void_p, C.c_void_p]),
+    "gs2d_strerror": (C.c_char_p, [C.c_int]),
+    "gs2d_last_cuda_error": (C.c_int, []),
+    "gs2d_abi_version": (C.c_int, []),
+    "gs2d_launch_count": (C.c_int64, []),
+}
+
+_lib = None
+
+
+def load():
+    """Load libgs2d.so (once).  Raises if it has not been built: there is no fallback."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError(
+            f"libgs2d.so not found at {LIB_PATH}: build it with `python gaus-slam_b200/build.py` "
+            "(or __graft_entry__.build()); this package has no CPU or PyTorch fallback")
+    lib = C.CDLL(LIB_PATH)
+    for name, (res, args) in PROTOTYPES.items():
+        fn = getattr(lib, name)
+        fn.restype = res
+        fn.argtypes = args
+    _lib = lib
+    return lib
+
+
+class Gs2dError(RuntimeError):
+    pass
+
+
+def check(status: int, what: str) -> None:
+    if status != GS2D_OK:
+        lib = load()
+        msg = lib.gs2d_strerror(status).decode()
+        extra = ""
+        if status == GS2D_ERR_CUDA:
+            extra = f" (cudaError_t {lib.gs2d_last_cuda_error()})"
+        raise Gs2dError(f"{what}: {msg}{extra}")

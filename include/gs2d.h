@@ -1,0 +1,202 @@
+/* gs2d.h -- C ABI of the B200-native 2D-Gaussian-surfel rasterizer (libgs2d.so).
+ *
+ * Drop-in boundary for the hot path of vasabi-root/gaus-slam: the entry points below
+ * are what a binding for the reference's `gaus_2dgs_rasterization._C` and
+ * `simple_knn._C` extension modules would call.  File:line citations are relative to
+ * the reference checkout (RAST = submodules/gaus_2dgs_rasterization, CR = RAST/cuda_rasterizer,
+ * KNN = submodules/simple-knn).
+ *
+ *   gs2d_forward_*  replace  RasterizeGaussiansCUDA            RAST/rasterize_points.cu:39-138
+ *                            CudaRasterizer::Rasterizer::forward  CR/rasterizer_impl.cu:201-350
+ *   gs2d_backward   replaces RasterizeGaussiansBackwardCUDA    RAST/rasterize_points.cu:140-239
+ *                            CudaRasterizer::Rasterizer::backward CR/rasterizer_impl.cu:354-460
+ *   gs2d_mark_visible replaces markVisible                     RAST/rasterize_points.cu:241-260
+ *   gs2d_dist2      replaces distCUDA2 / SimpleKNN::knn        KNN/spatial.cu:15-26, KNN/simple_knn.cu:186-222
+ *
+ * Rules of the ABI
+ *   - plain C: pointers, sizes, scalars; no torch types, no exceptions, no global state.
+ *   - every pointer is a DEVICE pointer owned by the caller unless its name ends in
+ *     `_host`; nothing is allocated or freed behind the caller's back.
+ *   - every function that launches work takes the CUDA stream to launch on
+ *     (a `cudaStream_t` passed as void*; NULL = legacy default stream).
+ *   - return value: 0 (GS2D_OK) or a negative gs2d_status; gs2d_strerror() names it.
+ *   - there is no CPU fallback: without a CUDA device every launch fails with
+ *     GS2D_ERR_CUDA.
+ */
+#ifndef GS2D_H_INCLUDED
+#define GS2D_H_INCLUDED
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GS2D_ABI_VERSION 1
+
+typedef enum gs2d_status {
+	GS2D_OK = 0,
+	GS2D_ERR_INVALID = -1,   /* bad argument (null pointer, negative size, ...)          */
+	GS2D_ERR_CUDA = -2,      /* a CUDA runtime call failed; see gs2d_last_cuda_error()    */
+	GS2D_ERR_CAPACITY = -3,  /* binning workspace smaller than num_rendered needs         */
+	GS2D_ERR_UNSUPPORTED = -4
+} gs2d_status;
+
+/* Tile geometry is part of the contract (CR/config.h:15-17): keys, sort order and tile
+ * ranges are bit-exact with the reference only for 16x16 tiles. */
+#define GS2D_TILE 16
+#define GS2D_NUM_CHANNELS 3
+
+/* Scalar settings: the non-tensor fields of GaussianRasterizationSettings
+ * (RAST/gaus_2dgs_rasterization/__init__.py:163-176) plus the sizes. */
+typedef struct gs2d_settings {
+	int32_t P;              /* number of surfels                                         */
+	int32_t image_width;
+	int32_t image_height;
+	int32_t sh_degree;      /* D  (active SH degree)                                      */
+	int32_t sh_coeffs;      /* M  (coefficients per surfel in `shs`; 0 when shs == NULL)  */
+	int32_t use_sa;         /* surface-aware depth (GauS-SLAM) vs 2DGS distortion         */
+	int32_t prefiltered;
+	int32_t debug;          /* 1: synchronise + check after every stage (CHECK_CUDA)      */
+	float tanfovx;
+	float tanfovy;
+	float scale_modifier;
+	float reserved_;
+} gs2d_settings;
+
+/* Inputs shared by forward and backward.  A NULL pointer selects the same branch an
+ * empty tensor selects in the reference (CR/forward.cu:194, :241):
+ * exactly one of {shs, colors_precomp}; exactly one of {(scales, rotations), transMat_precomp}. */
+typedef struct gs2d_inputs {
+	const float* background;        /* [3]                                        */
+	const float* means3D;           /* [P,3]                                      */
+	const float* shs;               /* [P,M,3] or NULL                            */
+	const float* colors_precomp;    /* [P,3]   or NULL                            */
+	const float* opacities;         /* [P,1]                                      */
+	const float* scales;            /* [P,2]   or NULL                            */
+	const float* rotations;         /* [P,4] (w,x,y,z) or NULL                    */
+	const float* transMat_precomp;  /* [P,9]   or NULL                            */
+	const float* viewmatrix;        /* [16], memory = column-major V (w2c^T rows) */
+	const float* projmatrix;        /* [16], memory = column-major P*V            */
+	const float* campos;            /* [3]                                        */
+} gs2d_inputs;
+
+/* The three opaque state buffers kept between forward and backward: the counterparts of
+ * geomBuffer / binningBuffer / imgBuffer (RAST/rasterize_points.cu:93-98).  Their layout is
+ * private to this library; gs2d_state_view() exposes the parity-relevant arrays. */
+typedef struct gs2d_buffers {
+	void* geom;    size_t geom_bytes;
+	void* binning; size_t binning_bytes;
+	void* image;   size_t image_bytes;
+} gs2d_buffers;
+
+/* Sizes of the state buffers.  `num_rendered` may be an upper bound (capacity). */
+size_t gs2d_geom_bytes(int32_t P, int32_t sh_coeffs);
+size_t gs2d_image_bytes(int32_t image_width, int32_t image_height);
+size_t gs2d_binning_bytes(int64_t num_rendered, int32_t image_width, int32_t image_height);
+
+/* Stage 1 of forward: per-surfel preprocess (world->ray-splat transform, screen bounds,
+ * tile counts; CR/forward.cu:150-253) and the inclusive scan of tile counts
+ * (CR/rasterizer_impl.cu:283).  Writes `radii` [P] int32 (zero for culled surfels).
+ * Enqueues an async copy of num_rendered to `num_rendered_host` (pinned host int64) when
+ * that pointer is not NULL. Needs buffers->geom (gs2d_geom_bytes). */
+int gs2d_forward_preprocess(const gs2d_settings* s, const gs2d_inputs* in,
+                            const gs2d_buffers* buffers, int32_t* radii,
+                            int64_t* num_rendered_host, void* stream);
+
+/* Stage 2 of forward: key duplication, radix sort, tile ranges, per-tile compositing
+ * (CR/rasterizer_impl.cu:295-347, CR/forward.cu:258-467).  `num_rendered` is the exact
+ * instance count read back after stage 1; buffers->binning must hold
+ * gs2d_binning_bytes(num_rendered, W, H) and buffers->image gs2d_image_bytes(W, H).
+ * out_color [3,H,W], out_others [7,H,W] are fully written (no pre-zeroing needed). */
+int gs2d_forward_render(const gs2d_settings* s, const gs2d_inputs* in,
+                        const gs2d_buffers* buffers, int64_t num_rendered,
+                        float* out_color, float* out_others, void* stream);
+
+/* Convenience: stage 1, stream synchronise, stage 2 -- the reference's control flow
+ * (CR/rasterizer_impl.cu:287 blocks on the same 4-byte read-back).  On entry
+ * *num_rendered_io is the binning capacity (in instances) the caller provisioned; on
+ * return it is the actual count.  Returns GS2D_ERR_CAPACITY (after stage 1 only) when
+ * the capacity is too small: re-provision and call gs2d_forward_render. */
+int gs2d_forward(const gs2d_settings* s, const gs2d_inputs* in, const gs2d_buffers* buffers,
+                 int32_t* radii, int64_t* num_rendered_io,
+                 float* out_color, float* out_others, void* stream);
+
+/* Gradients, all caller-allocated, fully written (no pre-zeroing needed), in the layout of
+ * the reference's return tuple (RAST/rasterize_points.cu:192-200, :238). */
+typedef struct gs2d_grads {
+	float* dL_dmeans2D;    /* [P,3]  densification proxy (CR/backward.cu:660-663)  */
+	float* dL_dcolors;     /* [P,3]                                                */
+	float* dL_dopacity;    /* [P,1]                                                */
+	float* dL_dmeans3D;    /* [P,3]                                                */
+	float* dL_dtransMat;   /* [P,9]                                                */
+	float* dL_dsh;         /* [P,M,3] or NULL when M == 0                          */
+	float* dL_dscales;     /* [P,2]                                                */
+	float* dL_drotations;  /* [P,4]                                                */
+} gs2d_grads;
+
+/* Backward (CR/backward.cu:143-463 render, :466-664 preprocess).  `radii` and the three
+ * buffers are those of the matching forward; dL_dout_color [3,H,W], dL_dout_others [7,H,W].
+ * `scratch` must hold gs2d_backward_scratch_bytes(P, num_rendered) bytes. */
+size_t gs2d_backward_scratch_bytes(int32_t P, int64_t num_rendered);
+int gs2d_backward(const gs2d_settings* s, const gs2d_inputs* in, const gs2d_buffers* buffers,
+                  const int32_t* radii, int64_t num_rendered,
+                  const float* dL_dout_color, const float* dL_dout_others,
+                  const gs2d_grads* grads, void* scratch, void* stream);
+
+/* present[i] = view-space z of means3D[i] > 0.2 (CR/rasterizer_impl.cu:54-66, CR/auxiliary.h:184-209).
+ * `present` is one byte per surfel (torch.bool). */
+int gs2d_mark_visible(int32_t P, const float* means3D, const float* viewmatrix,
+                      const float* projmatrix, uint8_t* present, void* stream);
+
+/* distCUDA2: mean squared distance to the 3 nearest other points (KNN/simple_knn.cu:148-222).
+ * points [P,3]; mean_dists [P]; scratch of gs2d_dist2_scratch_bytes(P). */
+size_t gs2d_dist2_scratch_bytes(int32_t P);
+int gs2d_dist2(int32_t P, const float* points, float* mean_dists, void* scratch, void* stream);
+
+/* Parity accessors: device pointers into the opaque buffers (valid after the stage that
+ * writes them).  Tests use these to compare binning bit-for-bit with the reference. */
+typedef struct gs2d_state_view {
+	/* per surfel (stage 1) */
+	const float*    depths;           /* [P]   view-space z                          */
+	const float*    splat;            /* [P,20] Tu,x | Tv,y | Tw,opacity | n,- | rgb,- */
+	const uint16_t* rect;             /* [P,4] tile rect x0,y0,x1,y1                  */
+	const float*    cull;             /* [P,4] contribution bounds x0,y0,x1,y1 (pixels) */
+	const uint32_t* tiles_touched;    /* [P]                                          */
+	const uint32_t* point_offsets;    /* [P]   inclusive scan                         */
+	/* per instance (stage 2) */
+	const uint64_t* keys_unsorted;    /* [I]   tile<<32 | float bits of depth         */
+	const uint32_t* values_unsorted;  /* [I]   surfel index                           */
+	const uint64_t* keys_sorted;      /* [I]                                          */
+	const uint32_t* point_list;       /* [I]   sorted surfel indices                  */
+	const float*    instances;        /* [I,20] per-instance records in sorted order   */
+	/* per tile / per pixel */
+	const uint32_t* ranges;           /* [tiles,2]                                    */
+	const float*    final_T;          /* [3,H,W] T, M1, M2                            */
+	const uint32_t* n_contrib;        /* [2,H,W] last contributor, median contributor */
+	const float*    median_depth;     /* [H,W]                                        */
+	const float*    depth_std;        /* [H,W]                                        */
+} gs2d_state_view;
+
+int gs2d_state_view_get(const gs2d_settings* s, const gs2d_buffers* buffers,
+                        int64_t num_rendered, gs2d_state_view* out);
+
+/* Stand-alone stable LSD radix sort of (u64 key, u32 value) pairs on bits [0, end_bit):
+ * the hand-written onesweep that replaces cub::DeviceRadixSort::SortPairs
+ * (CR/rasterizer_impl.cu:309-314).  scratch: gs2d_sort_scratch_bytes(n). */
+size_t gs2d_sort_scratch_bytes(int64_t n);
+int gs2d_sort_pairs(int64_t n, const uint64_t* keys_in, const uint32_t* values_in,
+                    uint64_t* keys_out, uint32_t* values_out, int32_t end_bit,
+                    void* scratch, void* stream);
+
+const char* gs2d_strerror(int status);
+int gs2d_last_cuda_error(void);          /* cudaError_t of the last failing call in this thread */
+int gs2d_abi_version(void);
+/* Number of kernels this library has launched in this process (for bench.py gpu_launches). */
+int64_t gs2d_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GS2D_H_INCLUDED */

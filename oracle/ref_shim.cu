@@ -222,6 +222,13 @@ void ref_dist_cuda2(int P, const float* points, float* mean_dists)
 	SimpleKNN::knn(P, (float3*)points, mean_dists);
 }
 
+// Blocking device-to-device copy (lets the Python side snapshot the state arrays).
+int ref_copy_d2d(void* dst, const void* src, size_t bytes)
+{
+	cudaDeviceSynchronize();
+	return (int)cudaMemcpy(dst, src, bytes, cudaMemcpyDeviceToDevice);
+}
+
 int ref_last_error() { return (int)cudaGetLastError(); }
 
 }  // extern "C"
