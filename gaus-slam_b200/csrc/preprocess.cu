@@ -12,6 +12,7 @@
 // culling in the compositing kernels) is new.
 #include "common.cuh"
 #include "math.cuh"
+#include "exact.cuh"
 
 namespace gs2d {
 
@@ -116,7 +117,7 @@ preprocess_forward_kernel(int P, int D, int M,
 	tiles_touched[idx] = 0;
 
 	const float3 p_orig = make_float3(means3D[3 * idx], means3D[3 * idx + 1], means3D[3 * idx + 2]);
-	const float3 p_view = xform_point_4x3(p_orig, viewmatrix);
+	const float3 p_view = xform_point_exact(p_orig, viewmatrix);
 	if (p_view.z <= 0.2f) {
 		if (prefiltered) __trap();
 		return;
@@ -124,21 +125,9 @@ preprocess_forward_kernel(int P, int D, int M,
 
 	float3 Tu, Tv, Tw, normal;
 	if (transMat_precomp == nullptr) {
-		float4 q = rotations[idx];
-		float2 sc = scales[idx];
-		Mat<3, 3> R = quat_to_rot(q.x, q.y, q.z, q.w);
-		Mat<3, 3> S = scale_mat(sc.x, sc.y, scale_modifier);
-		Mat<3, 3> L = matmul<3, 3, 3>(R, S);
-		Mat<3, 4> s2w = splat2world_mat(L, p_orig);
-		Mat<4, 4> w2n = world2ndc_mat(projmatrix);
-		Mat<3, 4> n2p = ndc2pix_mat(W, H);
-		Mat<4, 3> s2wT = transpose(s2w);
-		Mat<4, 3> X = matmul<4, 3, 4>(s2wT, w2n);
-		Mat<3, 3> T = matmul<4, 3, 3>(X, n2p);
-		Tu = make_float3(T.c[0][0], T.c[0][1], T.c[0][2]);
-		Tv = make_float3(T.c[1][0], T.c[1][1], T.c[1][2]);
-		Tw = make_float3(T.c[2][0], T.c[2][1], T.c[2][2]);
-		normal = xform_vec_4x3(make_float3(L.c[2][0], L.c[2][1], L.c[2][2]), viewmatrix);
+		const SplatFrame fr = splat_frame_exact(p_orig, scales[idx], scale_modifier, rotations[idx], projmatrix, W, H);
+		Tu = fr.Tu; Tv = fr.Tv; Tw = fr.Tw;
+		normal = xform_vec_exact(fr.L2, viewmatrix);
 	} else {
 		const float* t = transMat_precomp + 9 * (size_t)idx;
 		Tu = make_float3(t[0], t[1], t[2]);
@@ -148,25 +137,18 @@ preprocess_forward_kernel(int P, int D, int M,
 	}
 
 	// two-sided surfels: make the normal face the camera (DUAL_VISIABLE, CR/forward.cu:211-216)
-	float cosv = -sum3(mul3(p_view, normal));
-	if (cosv == 0) return;
-	float multiplier = cosv > 0 ? 1 : -1;
-	normal = scale3(multiplier, normal);
+	const float pdotn = dot3_ref(p_view.x, normal.x, p_view.y, normal.y, p_view.z, normal.z);
+	if (pdotn == 0.0f) return;
+	const float multiplier = pdotn < 0.0f ? 1.0f : -1.0f;
+	normal = make_float3(__fmul_rn(normal.x, multiplier), __fmul_rn(normal.y, multiplier), __fmul_rn(normal.z, multiplier));
 
-	// centre + half extent of the 3-sigma bounding box (CR/forward.cu:119-147)
-	const float cutoff = 3.0f;
-	float3 tp = make_float3(cutoff * cutoff, cutoff * cutoff, -1.0f);
-	float distance = sum3(mul3(mul3(Tw, Tw), tp));
-	float3 f = scale3(1 / distance, tp);
-	if (distance == 0.0) return;
-	float2 centre = make_float2(sum3(mul3(mul3(f, Tu), Tw)), sum3(mul3(mul3(f, Tv), Tw)));
-	float2 tmp = make_float2(sum3(mul3(mul3(f, Tu), Tu)), sum3(mul3(mul3(f, Tv), Tv)));
-	float2 half_ext = make_float2(centre.x * centre.x - tmp.x, centre.y * centre.y - tmp.y);
-	float2 extent = make_float2(sqrtf(fmaxf(1e-4, half_ext.x)), sqrtf(fmaxf(1e-4, half_ext.y)));
-	float radius = ceilf(fmaxf(extent.x, extent.y));
+	// centre + half extent of the 3-sigma bounding box (CR/forward.cu:119-147, :221-232)
+	float2 centre, extent;
+	if (!aabb_exact(Tu, Tv, Tw, centre, extent)) return;
+	const float radius = ceilf(fmaxf(extent.x, extent.y));
 
 	uint2 rmin, rmax;
-	tile_rect(centre.x, centre.y, (int)radius, gx, gy, rmin, rmax);
+	tile_rect_exact(centre.x, centre.y, (int)radius, gx, gy, rmin, rmax);
 	if ((rmax.x - rmin.x) * (rmax.y - rmin.y) == 0) return;
 
 	float3 rgb;
@@ -265,7 +247,7 @@ __global__ void mark_visible_kernel(int P, const float* __restrict__ means3D,
 	int idx = blockIdx.x * blockDim.x + threadIdx.x;
 	if (idx >= P) return;
 	float3 p = make_float3(means3D[3 * idx], means3D[3 * idx + 1], means3D[3 * idx + 2]);
-	float3 pv = xform_point_4x3(p, viewmatrix);
+	float3 pv = xform_point_exact(p, viewmatrix);
 	present[idx] = pv.z <= 0.2f ? 0 : 1;
 }
 

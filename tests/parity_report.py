@@ -145,7 +145,12 @@ def main():
         names = ["depth", "alpha", "normal_x", "normal_y", "normal_z", "median_depth", "distortion"]
         for k, nm in enumerate(names):
             cmp_float("allmap." + nm, o[k], o_ref[k], rep)
-        cmp_exact("n_contrib", raw(sv.n_contrib, (2, H, W), torch.int32, dev), rs["n_contrib"], rep)
+        nc_m, nc_r = raw(sv.n_contrib, (2, H, W), torch.int32, dev), rs["n_contrib"]
+        if cmp_exact("n_contrib", nc_m, nc_r, rep):
+            for ch in range(2):
+                bad = (nc_m[ch] != nc_r[ch]).nonzero()
+                print(f"    channel {ch}: {bad.shape[0]} differ; samples (y,x,ours,ref):",
+                      [(int(y), int(x), int(nc_m[ch, y, x]), int(nc_r[ch, y, x])) for y, x in bad[:6].tolist()])
         cmp_float("final_T", raw(sv.final_T, (3, H, W), torch.float32, dev), rs["final_T"], rep)
         cmp_float("depth_std", raw(sv.depth_std, (H, W), torch.float32, dev), rs["depth_std"], rep)
         # ---- gradients
