@@ -5,6 +5,8 @@
 // RAST/rasterize_points.cu:39-239, minus every memset the new kernels make unnecessary.
 #include <atomic>
 #include <cstring>
+#include <mutex>
+#include <vector>
 
 #include "common.cuh"
 
@@ -13,6 +15,41 @@ namespace gs2d {
 thread_local int g_last_cuda_error = 0;
 static std::atomic<long long> g_launches{0};
 void count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+
+// ---- per-kernel event timing ---------------------------------------------------------------
+bool g_timing_on = false;
+namespace {
+struct ProfRec { int id; cudaEvent_t a, b; };
+std::mutex g_prof_mu;
+std::vector<ProfRec> g_prof_open;          // begun, not yet ended (LIFO)
+std::vector<ProfRec> g_prof_done;          // both events recorded
+std::vector<cudaEvent_t> g_prof_pool;
+cudaEvent_t prof_event()
+{
+	if (!g_prof_pool.empty()) { cudaEvent_t e = g_prof_pool.back(); g_prof_pool.pop_back(); return e; }
+	cudaEvent_t e = nullptr;
+	cudaEventCreate(&e);
+	return e;
+}
+const char* const kKernelNames[K_COUNT] = {
+	"preprocess_forward", "scan_tiles", "duplicate_keys", "histogram", "digit_base", "onesweep_pass",
+	"gather_ranges", "composite_forward", "composite_backward", "preprocess_backward", "mark_visible",
+	"memset", "memcpy", "knn"};
+}  // namespace
+void prof_mark(int id, cudaStream_t st, bool begin)
+{
+	std::lock_guard<std::mutex> lk(g_prof_mu);
+	if (begin) {
+		ProfRec r{id, prof_event(), prof_event()};
+		cudaEventRecord(r.a, st);
+		g_prof_open.push_back(r);
+	} else if (!g_prof_open.empty()) {
+		ProfRec r = g_prof_open.back();
+		g_prof_open.pop_back();
+		cudaEventRecord(r.b, st);
+		g_prof_done.push_back(r);
+	}
+}
 
 GeomState GeomState::carve(void* base, size_t P, size_t* bytes)
 {
@@ -231,7 +268,10 @@ int gs2d_backward(const gs2d_settings* s, const gs2d_inputs* in, const gs2d_buff
 	if (I > 0) {
 		if (!scratch || !buffers->binning) return GS2D_ERR_INVALID;
 		BinningState b = BinningState::carve(buffers->binning, (size_t)I, nullptr);
-		GS2D_CUDA_OK(cudaMemsetAsync(rows, 0, (size_t)I * GRAD_WORDS * sizeof(float), st));
+		{
+			ProfScope ps(K_MEMSET, st);
+			GS2D_CUDA_OK(cudaMemsetAsync(rows, 0, (size_t)I * GRAD_WORDS * sizeof(float), st));
+		}
 		GS2D_TRY(launch_composite_backward(*s, *in, im, b.instances, dL_dout_color, dL_dout_others, rows, st));
 		GS2D_TRY(debug_sync(*s, st));
 	}
@@ -291,6 +331,34 @@ int gs2d_sort_pairs(int64_t n, const uint64_t* keys_in, const uint32_t* values_i
 		GS2D_CUDA_OK(cudaMemcpyAsync(keys_out, tk, sizeof(uint64_t) * (size_t)n, cudaMemcpyDeviceToDevice, st));
 		GS2D_CUDA_OK(cudaMemcpyAsync(values_out, tv, sizeof(uint32_t) * (size_t)n, cudaMemcpyDeviceToDevice, st));
 	}
+	return GS2D_OK;
+}
+
+int gs2d_timing_enable(int on)
+{
+	std::lock_guard<std::mutex> lk(g_prof_mu);
+	g_timing_on = on != 0;
+	return GS2D_OK;
+}
+
+int gs2d_num_kernels(void) { return (int)K_COUNT; }
+const char* gs2d_kernel_name(int id) { return (id >= 0 && id < (int)K_COUNT) ? kKernelNames[id] : "?"; }
+
+int gs2d_timing_collect(double* total_ms, int64_t* launches)
+{
+	std::lock_guard<std::mutex> lk(g_prof_mu);
+	if (!total_ms || !launches) return GS2D_ERR_INVALID;
+	for (int i = 0; i < (int)K_COUNT; i++) { total_ms[i] = 0.0; launches[i] = 0; }
+	for (ProfRec& r : g_prof_done) {
+		GS2D_CUDA_OK(cudaEventSynchronize(r.b));
+		float ms = 0.f;
+		GS2D_CUDA_OK(cudaEventElapsedTime(&ms, r.a, r.b));
+		total_ms[r.id] += (double)ms;
+		launches[r.id] += 1;
+		g_prof_pool.push_back(r.a);
+		g_prof_pool.push_back(r.b);
+	}
+	g_prof_done.clear();
 	return GS2D_OK;
 }
 

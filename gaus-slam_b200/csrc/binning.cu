@@ -306,11 +306,14 @@ int launch_duplicate(const gs2d_settings& s, const GeomState& g, const int32_t*,
 	(void)I;
 	const unsigned gx = (s.image_width + TILE - 1) / TILE, gy = (s.image_height + TILE - 1) / TILE;
 	const int passes = sort_passes(32 + (int)higher_msb(gx * gy));
-	GS2D_CUDA_OK(cudaMemsetAsync(b.sort.hist, 0, b.sort.zero_bytes, st));
-	duplicate_kernel<<<(s.P + 255) / 256, 256, 0, st>>>(s.P, gx, g.depths, (const ushort4*)g.rect,
-	                                                    g.tiles_touched, g.point_offsets, b.keys_a, b.vals_a,
-	                                                    b.sort.hist, passes);
-	count_launch();
+	{ ProfScope ps(K_MEMSET, st); GS2D_CUDA_OK(cudaMemsetAsync(b.sort.hist, 0, b.sort.zero_bytes, st)); }
+	{
+		ProfScope ps(K_DUPLICATE, st);
+		duplicate_kernel<<<(s.P + 255) / 256, 256, 0, st>>>(s.P, gx, g.depths, (const ushort4*)g.rect,
+		                                                    g.tiles_touched, g.point_offsets, b.keys_a, b.vals_a,
+		                                                    b.sort.hist, passes);
+		count_launch();
+	}
 	GS2D_CUDA_OK(cudaGetLastError());
 	return GS2D_OK;
 }
@@ -329,8 +332,11 @@ static int sort_passes_run(int64_t n, uint64_t* keys_a, uint32_t* vals_a, uint64
 		                                  (int)sizeof(SortSmem)));
 		attr_set = true;
 	}
-	digit_base_kernel<<<passes, SORT_RADIX, 0, st>>>(ss.hist);
-	count_launch();
+	{
+		ProfScope ps(K_DIGIT_BASE, st);
+		digit_base_kernel<<<passes, SORT_RADIX, 0, st>>>(ss.hist);
+		count_launch();
+	}
 	const int blocks = (int)((n + SORT_TILE - 1) / SORT_TILE);
 	bool in_a = true;
 	for (int p = 0; p < passes; p++) {
@@ -338,10 +344,13 @@ static int sort_passes_run(int64_t n, uint64_t* keys_a, uint32_t* vals_a, uint64
 		const uint32_t* vi = in_a ? vals_a : vals_b;
 		uint64_t* ko = in_a ? keys_b : keys_a;
 		uint32_t* vo = in_a ? vals_b : vals_a;
-		onesweep_kernel<<<blocks, SORT_THREADS, sizeof(SortSmem), st>>>(
-			n, ki, vi, ko, vo, p * SORT_RADIX_BITS, ss.hist + p * SORT_RADIX,
-			ss.status + (size_t)p * ss.blocks * SORT_RADIX, ss.tickets + p);
-		count_launch();
+		{
+			ProfScope ps(K_ONESWEEP, st);
+			onesweep_kernel<<<blocks, SORT_THREADS, sizeof(SortSmem), st>>>(
+				n, ki, vi, ko, vo, p * SORT_RADIX_BITS, ss.hist + p * SORT_RADIX,
+				ss.status + (size_t)p * ss.blocks * SORT_RADIX, ss.tickets + p);
+			count_launch();
+		}
 		in_a = !in_a;
 	}
 	GS2D_CUDA_OK(cudaGetLastError());
@@ -358,13 +367,16 @@ int launch_sort_pairs(int64_t n, const uint64_t* keys_in, const uint32_t* vals_i
 	if (n <= 0) { *result_in_b = false; return GS2D_OK; }
 	if (keys_in != keys_a_rw) {
 		const int passes = sort_passes(end_bit);
-		GS2D_CUDA_OK(cudaMemsetAsync(ss.hist, 0, ss.zero_bytes, st));
+		{ ProfScope ps(K_MEMSET, st); GS2D_CUDA_OK(cudaMemsetAsync(ss.hist, 0, ss.zero_bytes, st)); }
 		GS2D_CUDA_OK(cudaMemcpyAsync(keys_a_rw, keys_in, sizeof(uint64_t) * (size_t)n, cudaMemcpyDeviceToDevice, st));
 		GS2D_CUDA_OK(cudaMemcpyAsync(vals_a_rw, vals_in, sizeof(uint32_t) * (size_t)n, cudaMemcpyDeviceToDevice, st));
 		int64_t want = (n + 256 * 16 - 1) / (256 * 16);
 		int blocks = (int)(want < 148 * 8 ? want : 148 * 8);
-		histogram_kernel<<<blocks, 256, 0, st>>>(n, keys_a_rw, ss.hist, passes);
-		count_launch();
+		{
+			ProfScope ps(K_HISTOGRAM, st);
+			histogram_kernel<<<blocks, 256, 0, st>>>(n, keys_a_rw, ss.hist, passes);
+			count_launch();
+		}
 	}
 	return sort_passes_run(n, keys_a_rw, vals_a_rw, keys_b, vals_b, end_bit, ss, result_in_b, st);
 }
@@ -374,12 +386,15 @@ int launch_gather_ranges(const gs2d_settings& s, const GeomState& g, const uint6
                          cudaStream_t st)
 {
 	const unsigned gx = (s.image_width + TILE - 1) / TILE, gy = (s.image_height + TILE - 1) / TILE;
-	GS2D_CUDA_OK(cudaMemsetAsync(ranges, 0, sizeof(uint32_t) * 2 * (size_t)gx * gy, st));
+	{ ProfScope ps(K_MEMSET, st); GS2D_CUDA_OK(cudaMemsetAsync(ranges, 0, sizeof(uint32_t) * 2 * (size_t)gx * gy, st)); }
 	if (I > 0) {
-		gather_ranges_kernel<<<(unsigned)((I + 255) / 256), 256, 0, st>>>(
-			I, gx, keys_sorted, point_list, (const float4*)g.splat, (const ushort4*)g.rect,
-			(const float4*)g.cull, g.point_offsets, (float4*)instances, ranges);
-		count_launch();
+		{
+			ProfScope ps(K_GATHER_RANGES, st);
+			gather_ranges_kernel<<<(unsigned)((I + 255) / 256), 256, 0, st>>>(
+				I, gx, keys_sorted, point_list, (const float4*)g.splat, (const ushort4*)g.rect,
+				(const float4*)g.cull, g.point_offsets, (float4*)instances, ranges);
+			count_launch();
+		}
 	}
 	GS2D_CUDA_OK(cudaGetLastError());
 	return GS2D_OK;

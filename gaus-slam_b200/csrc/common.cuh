@@ -118,6 +118,19 @@ void count_launch(int n = 1);
 		if (e__ != cudaSuccess) { gs2d::g_last_cuda_error = (int)e__; return GS2D_ERR_CUDA; } \
 	} while (0)
 
+// Optional per-kernel CUDA-event timing (gs2d_timing_* in include/gs2d.h) -------------------------
+enum KernelId {
+	K_PREPROCESS_FWD = 0, K_SCAN, K_DUPLICATE, K_HISTOGRAM, K_DIGIT_BASE, K_ONESWEEP, K_GATHER_RANGES,
+	K_COMPOSITE_FWD, K_COMPOSITE_BWD, K_PREPROCESS_BWD, K_MARK_VISIBLE, K_MEMSET, K_MEMCPY, K_KNN, K_COUNT
+};
+extern bool g_timing_on;
+void prof_mark(int id, cudaStream_t st, bool begin);
+struct ProfScope {
+	int id; cudaStream_t st;
+	ProfScope(int id_, cudaStream_t st_) : id(id_), st(st_) { if (g_timing_on) prof_mark(id, st, true); }
+	~ProfScope() { if (g_timing_on) prof_mark(id, st, false); }
+};
+
 // Kernel launchers (each returns a gs2d_status) ------------------------------------------
 int launch_preprocess_forward(const gs2d_settings& s, const gs2d_inputs& in, const GeomState& g,
                               int32_t* radii, cudaStream_t st);

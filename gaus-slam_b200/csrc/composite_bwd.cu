@@ -363,6 +363,7 @@ int launch_composite_backward(const gs2d_settings& s, const gs2d_inputs& in, con
 	const int W = s.image_width, H = s.image_height;
 	const unsigned gx = (W + TILE - 1) / TILE, gy = (H + TILE - 1) / TILE;
 	if (gx * gy == 0) return GS2D_OK;
+	ProfScope ps(K_COMPOSITE_BWD, st);
 	if (s.use_sa)
 		composite_backward_kernel<true><<<gx * gy, 256, 0, st>>>(
 			W, H, gx, (const uint2*)im.ranges, (const float4*)instances, in.background, im.final_T,

@@ -210,6 +210,7 @@ int launch_composite_forward(const gs2d_settings& s, const gs2d_inputs& in, cons
 	const int W = s.image_width, H = s.image_height;
 	const unsigned gx = (W + TILE - 1) / TILE, gy = (H + TILE - 1) / TILE;
 	if (gx * gy == 0) return GS2D_OK;
+	ProfScope ps(K_COMPOSITE_FWD, st);
 	if (s.use_sa)
 		composite_forward_kernel<true><<<gx * gy, 256, 0, st>>>(
 			W, H, gx, (const uint2*)im.ranges, (const float4*)instances, in.background, im.final_T,

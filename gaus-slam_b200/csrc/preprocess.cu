@@ -258,13 +258,16 @@ int launch_preprocess_forward(const gs2d_settings& s, const gs2d_inputs& in, con
 {
 	const int P = s.P;
 	const unsigned gx = (s.image_width + TILE - 1) / TILE, gy = (s.image_height + TILE - 1) / TILE;
-	preprocess_forward_kernel<<<(P + 255) / 256, 256, 0, st>>>(
-		P, s.sh_degree, s.sh_coeffs, in.means3D, (const float2*)in.scales, s.scale_modifier,
-		(const float4*)in.rotations, in.opacities, in.shs, g.clamped, in.transMat_precomp,
-		in.colors_precomp, in.viewmatrix, in.projmatrix, in.campos, s.image_width, s.image_height,
-		gx, gy, s.prefiltered, radii, g.depths, (float4*)g.splat, (ushort4*)g.rect, (float4*)g.cull,
-		g.tiles_touched);
-	count_launch();
+	{
+		ProfScope ps(K_PREPROCESS_FWD, st);
+		preprocess_forward_kernel<<<(P + 255) / 256, 256, 0, st>>>(
+			P, s.sh_degree, s.sh_coeffs, in.means3D, (const float2*)in.scales, s.scale_modifier,
+			(const float4*)in.rotations, in.opacities, in.shs, g.clamped, in.transMat_precomp,
+			in.colors_precomp, in.viewmatrix, in.projmatrix, in.campos, s.image_width, s.image_height,
+			gx, gy, s.prefiltered, radii, g.depths, (float4*)g.splat, (ushort4*)g.rect, (float4*)g.cull,
+			g.tiles_touched);
+		count_launch();
+	}
 	GS2D_CUDA_OK(cudaGetLastError());
 	return GS2D_OK;
 }
@@ -272,11 +275,14 @@ int launch_preprocess_forward(const gs2d_settings& s, const gs2d_inputs& in, con
 int launch_scan_tiles(const GeomState& g, int P, cudaStream_t st)
 {
 	const int blocks = (P + SCAN_TILE - 1) / SCAN_TILE;
-	GS2D_CUDA_OK(cudaMemsetAsync(g.scan_status, 0, sizeof(uint64_t) * (size_t)blocks, st));
-	GS2D_CUDA_OK(cudaMemsetAsync(g.counters, 0, sizeof(uint32_t) * 8, st));
-	scan_tiles_kernel<<<blocks, SCAN_THREADS, 0, st>>>(g.tiles_touched, g.point_offsets, P,
-	                                                   (unsigned long long*)g.scan_status, g.counters);
-	count_launch();
+	{ ProfScope ps(K_MEMSET, st); GS2D_CUDA_OK(cudaMemsetAsync(g.scan_status, 0, sizeof(uint64_t) * (size_t)blocks, st)); }
+	{ ProfScope ps(K_MEMSET, st); GS2D_CUDA_OK(cudaMemsetAsync(g.counters, 0, sizeof(uint32_t) * 8, st)); }
+	{
+		ProfScope ps(K_SCAN, st);
+		scan_tiles_kernel<<<blocks, SCAN_THREADS, 0, st>>>(g.tiles_touched, g.point_offsets, P,
+		                                                   (unsigned long long*)g.scan_status, g.counters);
+		count_launch();
+	}
 	GS2D_CUDA_OK(cudaGetLastError());
 	return GS2D_OK;
 }
@@ -285,8 +291,11 @@ int launch_mark_visible(int P, const float* means3D, const float* view, const fl
                         uint8_t* present, cudaStream_t st)
 {
 	(void)proj;
-	mark_visible_kernel<<<(P + 255) / 256, 256, 0, st>>>(P, means3D, view, present);
-	count_launch();
+	{
+		ProfScope ps(K_MARK_VISIBLE, st);
+		mark_visible_kernel<<<(P + 255) / 256, 256, 0, st>>>(P, means3D, view, present);
+		count_launch();
+	}
 	GS2D_CUDA_OK(cudaGetLastError());
 	return GS2D_OK;
 }

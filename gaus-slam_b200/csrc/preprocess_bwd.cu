@@ -267,13 +267,16 @@ int launch_preprocess_backward(const gs2d_settings& s, const gs2d_inputs& in, co
 	const int P = s.P;
 	const float focal_y = s.image_height / (2.0f * s.tanfovy);
 	const float focal_x = s.image_width / (2.0f * s.tanfovx);
-	preprocess_backward_kernel<<<(P + 255) / 256, 256, 0, st>>>(
-		P, s.sh_degree, s.sh_coeffs, (const float3*)in.means3D, radii, in.shs, g.clamped,
-		(const float2*)in.scales, (const float4*)in.rotations, in.transMat_precomp, g.splat,
-		in.viewmatrix, in.projmatrix, focal_x, focal_y, s.tanfovx, s.tanfovy, in.campos,
-		g.tiles_touched, g.point_offsets, grad_rows, out.dL_dtransMat, out.dL_dcolors, out.dL_dopacity,
-		out.dL_dsh, out.dL_dmeans2D, out.dL_dmeans3D, out.dL_dscales, out.dL_drotations);
-	count_launch();
+	{
+		ProfScope ps(K_PREPROCESS_BWD, st);
+		preprocess_backward_kernel<<<(P + 255) / 256, 256, 0, st>>>(
+			P, s.sh_degree, s.sh_coeffs, (const float3*)in.means3D, radii, in.shs, g.clamped,
+			(const float2*)in.scales, (const float4*)in.rotations, in.transMat_precomp, g.splat,
+			in.viewmatrix, in.projmatrix, focal_x, focal_y, s.tanfovx, s.tanfovy, in.campos,
+			g.tiles_touched, g.point_offsets, grad_rows, out.dL_dtransMat, out.dL_dcolors, out.dL_dopacity,
+			out.dL_dsh, out.dL_dmeans2D, out.dL_dmeans3D, out.dL_dscales, out.dL_drotations);
+		count_launch();
+	}
 	GS2D_CUDA_OK(cudaGetLastError());
 	return GS2D_OK;
 }

@@ -75,6 +75,10 @@ PROTOTYPES = {
     "gs2d_sort_scratch_bytes": (C.c_size_t, [C.c_int64]),
     "gs2d_sort_pairs": (C.c_int, [C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32,
                                   C.c_void_p, C.c_void_p]),
+    "gs2d_timing_enable": (C.c_int, [C.c_int]),
+    "gs2d_num_kernels": (C.c_int, []),
+    "gs2d_kernel_name": (C.c_char_p, [C.c_int]),
+    "gs2d_timing_collect": (C.c_int, [C.POINTER(C.c_double), C.POINTER(C.c_int64)]),
     "gs2d_strerror": (C.c_char_p, [C.c_int]),
     "gs2d_last_cuda_error": (C.c_int, []),
     "gs2d_abi_version": (C.c_int, []),

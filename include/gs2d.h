@@ -190,6 +190,15 @@ int gs2d_sort_pairs(int64_t n, const uint64_t* keys_in, const uint32_t* values_i
                     uint64_t* keys_out, uint32_t* values_out, int32_t end_bit,
                     void* scratch, void* stream);
 
+/* Optional per-kernel timing for bench.py's roofline line: while enabled, every kernel launch
+ * (and memset) of this library is bracketed by CUDA events on the launching stream.
+ * gs2d_timing_collect() waits for the recorded events, writes the summed device time (ms) and
+ * the launch count per kernel id [0, gs2d_num_kernels()) and clears the record. */
+int gs2d_timing_enable(int on);
+int gs2d_num_kernels(void);
+const char* gs2d_kernel_name(int id);
+int gs2d_timing_collect(double* total_ms, int64_t* launches);
+
 const char* gs2d_strerror(int status);
 int gs2d_last_cuda_error(void);          /* cudaError_t of the last failing call in this thread */
 int gs2d_abi_version(void);
