@@ -1,0 +1,488 @@
+#!/usr/bin/env python
+"""bench.py -- rasterized fwd+bwd frames/sec @1200x680, 500k surfels (BASELINE.json `metric`).
+
+A "step" is one mapping-shaped iteration of the hot path on ONE keyframe view per GPU: forward
+(preprocess -> binning -> compositing) and backward (compositing -> preprocess) of the surfel
+rasterizer over the 500k-surfel submap (BASELINE.json configs[2]: "Frontend submap mapping ... 8-keyframe
+window, 500k surfels, view-sharded at 1/2/4/8 GPUs").  With N GPUs every rank renders its own keyframe of
+the window each step (weak scaling: work per GPU is fixed) and the map gradients [P,13] go through one
+NCCL all-reduce; `value` = N views / max-over-ranks step time.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W]          # product (libgs2d.so through the drop-in API)
+    python bench.py --impl reference ...                        # the unmodified reference CUDA rasterizer
+
+The JSON line carries `roofline` (dominant kernel, CUDA events around every launch), `cpu_baseline`
+(the C restatement oracle/gs2d_oracle.c on the host cores), `e2e` (public API, per-step inputs from pinned
+host memory, loss read back) and `clocks` (nvidia-smi sampled during the timed region).
+See DESIGN.md "Measurement" for the definitions.
+"""
+from __future__ import annotations
+
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+METRIC = "rasterized fwd+bwd frames/sec @1200x680, 500k surfels"
+UNIT = "frames/s"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=64)
+    ap.add_argument("--warmup", type=int, default=8)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--surfels", type=int, default=500_000)
+    ap.add_argument("--views", type=int, default=8, help="keyframes in the window")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-kernel-timing", action="store_true")
+    ap.add_argument("--cpu-frames", type=int, default=2)
+    return ap.parse_args()
+
+
+# ----------------------------------------------------------------------------------------------------
+# clocks: nvidia-smi sampled DURING the timed region (B200_PROFILING.md recipe)
+# ----------------------------------------------------------------------------------------------------
+class ClockSampler:
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+    NAMES = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+
+    def __init__(self, index: int):
+        self.index = index
+        self.rows = []
+        self.proc = None
+        self.thread = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                 "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except OSError:
+            self.proc = None
+            return
+        self.thread = threading.Thread(target=self._read, daemon=True)
+        self.thread.start()
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"], "samples": 0}
+        time.sleep(0.12)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=3)
+        except Exception:
+            self.proc.kill()
+        sm, mx, pw, reasons = [], [], [], set()
+        for r in self.rows:
+            f = [x.strip() for x in r.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0])); mx.append(float(f[1])); pw.append(float(f[2]))
+            except ValueError:
+                continue
+            for name, v in zip(self.NAMES, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"], "samples": 0}
+        return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(mx)), "power_w_max": float(max(pw)),
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ----------------------------------------------------------------------------------------------------
+# workload
+# ----------------------------------------------------------------------------------------------------
+def build_workload(a, dev):
+    """The 500k-surfel room submap + an 8-keyframe window.  One full input set PER VIEW (own parameter copy,
+    own upstream image gradients): 8 x 58.6 MB > the 126 MB L2, so no step finds its inputs in L2."""
+    import torch
+    sys.path.insert(0, os.path.join(ROOT, "gaus-slam_b200"))
+    from gs2d_b200 import scene
+    intr = scene.REPLICA
+    W, H = intr["W"], intr["H"]
+    sc = scene.room_scene(a.surfels, intr, seed=0)
+    cams = scene.view_sweep(a.views, intr, seed=0)
+    sets = []
+    for v, cam in enumerate(cams):
+        gc, go = scene.image_grads(W, H, seed=v)
+        host = dict(viewmatrix=cam.viewmatrix.reshape(16), projmatrix=cam.projmatrix.reshape(16), campos=cam.campos,
+                    dL_dcolor=gc, dL_dothers=go)
+        host = {k: torch.from_numpy(np.ascontiguousarray(x, dtype=np.float32)).pin_memory() for k, x in host.items()}
+        d = {k: x.to(dev) for k, x in host.items()}
+        for k in ("means3D", "scales", "rotations", "opacities", "colors"):
+            d[k] = torch.from_numpy(sc[k]).to(dev)
+        d["tanfovx"], d["tanfovy"] = float(cam.tanfovx), float(cam.tanfovy)
+        d["host"] = host
+        sets.append(d)
+    return dict(W=W, H=H, P=a.surfels, sets=sets, scene=sc, cams=cams, bg=torch.zeros(3, device=dev),
+                empty=torch.empty(0, device=dev))
+
+
+def algorithmic_bytes(P, Pv, I, W, H):
+    """Compulsory HBM bytes per launch, SURVEY.md §8(d) (each stage reads its inputs once, writes its outputs
+    once).  Keys are gs2d kernel names."""
+    Px, Tl = W * H, ((W + 15) // 16) * ((H + 15) // 16)
+    return {
+        "preprocess_forward": 40 * P + 8 * P + 64 * Pv,
+        "scan_tiles": 8 * P,
+        "duplicate_keys": 20 * P + 12 * I,
+        "onesweep_pass": 24 * I,                       # per pass: read + write (u64 key, u32 value)
+        "histogram": 8 * I,
+        "gather_ranges": 8 * I + 8 * Tl + 12 * I + 76 * I,   # sorted pairs in, per-instance records out
+        "composite_forward": 76 * I + 8 * Tl + 68 * Px,
+        "composite_backward": 76 * I + 8 * Tl + 68 * Px + 64 * Pv,
+        "preprocess_backward": 4 * P + 136 * Pv + 48 * Pv,
+    }
+
+
+# ----------------------------------------------------------------------------------------------------
+# the two arms: each exposes forward_backward(set) -> (color, others, grads dict) on device tensors
+# ----------------------------------------------------------------------------------------------------
+class B200Arm:
+    name = "b200"
+
+    def __init__(self, wl, dev):
+        sys.path.insert(0, os.path.join(ROOT, "gaus-slam_b200"))
+        import gaus_2dgs_rasterization as G
+        from gs2d_b200 import _lib
+        self.G, self.GC, self.L = G, G._C, _lib
+        self.lib = _lib.load()          # raises if libgs2d.so is missing: no fallback
+        self.wl, self.dev = wl, dev
+
+    def launches(self):
+        return int(self.lib.gs2d_launch_count())
+
+    def forward_backward(self, s):
+        wl, GC = self.wl, self.GC
+        e = wl["empty"]
+        n, color, others, radii, geom, binning, img = GC.rasterize_gaussians(
+            wl["bg"], s["means3D"], s["colors"], s["opacities"], s["scales"], s["rotations"], 1.0, e,
+            s["viewmatrix"], s["projmatrix"], s["tanfovx"], s["tanfovy"], wl["H"], wl["W"], e, 0, s["campos"],
+            True, False, False)
+        g = GC.rasterize_gaussians_backward(
+            wl["bg"], s["means3D"], radii, s["colors"], s["scales"], s["rotations"], 1.0, e, s["viewmatrix"],
+            s["projmatrix"], s["tanfovx"], s["tanfovy"], s["dL_dcolor"], s["dL_dothers"], e, 0, s["campos"],
+            geom, n, binning, img, True, False)
+        self.last_n, self.last_radii = n, radii
+        # reference order: (means2D, colors, opacity, means3D, transMat, sh, scales, rotations)
+        return color, others, dict(means3D=g[3], opacities=g[2], scales=g[6], rotations=g[7], colors=g[1])
+
+    def rasterizer(self, s):
+        G, wl = self.G, self.wl
+        st = G.GaussianRasterizationSettings(
+            image_height=wl["H"], image_width=wl["W"], tanfovx=s["tanfovx"], tanfovy=s["tanfovy"], bg=wl["bg"],
+            scale_modifier=1.0, viewmatrix=s["viewmatrix"], projmatrix=s["projmatrix"], sh_degree=0,
+            campos=s["campos"], use_sa=True, prefiltered=False, debug=False)
+        return G.GaussianRasterizer(st)
+
+
+class ReferenceArm:
+    """The UNMODIFIED reference CUDA rasterizer (forward.cu / backward.cu / rasterizer_impl.cu compiled for
+    sm_100a into oracle/_ref/libgs2d_ref.so), driven the way RAST/rasterize_points.cu drives it."""
+    name = "reference"
+
+    def __init__(self, wl, dev):
+        import torch
+        sys.path.insert(0, os.path.join(ROOT, "oracle"))
+        import refgpu
+        if not refgpu.available():
+            raise FileNotFoundError("oracle/_ref/libgs2d_ref.so missing (built by oracle/build.py where /root/reference exists)")
+        self.ref = refgpu.RefRasterizer()
+        self.wl, self.dev, self.torch = wl, dev, torch
+
+    def launches(self):
+        return 0
+
+    def forward_backward(self, s):
+        wl = self.wl
+        kw = dict(bg=wl["bg"], means3D=s["means3D"], viewmatrix=s["viewmatrix"], projmatrix=s["projmatrix"],
+                  campos=s["campos"], W=wl["W"], H=wl["H"], tanfovx=s["tanfovx"], tanfovy=s["tanfovy"],
+                  colors=s["colors"], scales=s["scales"], rotations=s["rotations"], use_sa=True)
+        n, color, others, radii = self.ref.forward(opacities=s["opacities"], **kw)
+        g = self.ref.backward(radii=radii, dL_dcolor=s["dL_dcolor"], dL_dothers=s["dL_dothers"], **kw)
+        self.last_n, self.last_radii = n, radii
+        return color, others, dict(means3D=g["means3D"], opacities=g["opacity"], scales=g["scales"],
+                                   rotations=g["rotations"], colors=g["colors"])
+
+    def rasterizer(self, s):
+        torch, arm = self.torch, self
+
+        class _Fn(torch.autograd.Function):
+            @staticmethod
+            def forward(ctx, means3D, opacities, colors, scales, rotations):
+                wl = arm.wl
+                kw = dict(bg=wl["bg"], means3D=means3D, viewmatrix=s["viewmatrix"], projmatrix=s["projmatrix"],
+                          campos=s["campos"], W=wl["W"], H=wl["H"], tanfovx=s["tanfovx"], tanfovy=s["tanfovy"],
+                          colors=colors, scales=scales, rotations=rotations, use_sa=True)
+                n, color, others, radii = arm.ref.forward(opacities=opacities, **kw)
+                ctx.kw, ctx.radii = kw, radii
+                ctx.mark_non_differentiable(radii)
+                return color, radii, others
+
+            @staticmethod
+            def backward(ctx, gc, gr, go):
+                g = arm.ref.backward(radii=ctx.radii, dL_dcolor=gc.contiguous(), dL_dothers=go.contiguous(), **ctx.kw)
+                return g["means3D"], g["opacity"], g["colors"], g["scales"], g["rotations"]
+
+        def call(means3D, means2D, opacities, colors_precomp, scales, rotations):
+            return _Fn.apply(means3D, opacities, colors_precomp, scales, rotations)
+        return call
+
+
+# ----------------------------------------------------------------------------------------------------
+# CPU baseline: the C restatement (oracle/gs2d_oracle.c, OpenMP over tiles/surfels) on the host cores
+# ----------------------------------------------------------------------------------------------------
+def cpu_baseline(wl, frames):
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import cpu as O
+    sc, cam = wl["scene"], wl["cams"][0]
+    W, H = wl["W"], wl["H"]
+    from gs2d_b200 import scene
+    gc, go = scene.image_grads(W, H, seed=0)
+    bg = np.zeros(3, np.float32)
+    t0 = time.perf_counter()
+    for _ in range(frames):
+        st = O.forward(sc["means3D"], sc["opacities"], cam.viewmatrix, cam.projmatrix, W, H, bg, scales=sc["scales"],
+                       rotations=sc["rotations"], colors=sc["colors"], campos=cam.campos)
+        O.backward(st, sc["means3D"], cam.viewmatrix, cam.projmatrix, W, H, cam.tanfovx, cam.tanfovy, bg, gc, go,
+                   scales=sc["scales"], rotations=sc["rotations"], campos=cam.campos)
+    dt = time.perf_counter() - t0
+    return {"value": frames / dt, "unit": UNIT, "cores": O.num_threads(), "kind": "port",
+            "sample": f"{frames} whole fwd+bwd frame(s) of view 0 of the same workload (P={wl['P']}, {W}x{H}, "
+                      f"I={int(st['num_rendered'])}), C restatement oracle/gs2d_oracle.c, OpenMP",
+            "seconds": dt}
+
+
+# ----------------------------------------------------------------------------------------------------
+def main():
+    a = parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if a.impl == "reference" and rank != 0:
+        return 0          # the reference is single-GPU: rank 0 alone runs and prints it
+    import torch
+    import torch.distributed as dist
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the product has no CPU path")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    multi = world > 1 and a.impl == "b200"
+    if multi:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+
+    wl = build_workload(a, dev)
+    try:
+        arm = B200Arm(wl, dev) if a.impl == "b200" else ReferenceArm(wl, dev)
+    except FileNotFoundError as e:
+        print(json.dumps({"impl": "reference", "unavailable": str(e)}))
+        return 0
+    P, W, H, V = wl["P"], wl["W"], wl["H"], a.views
+    flat = torch.zeros(P * 13, dtype=torch.float32, device=dev)      # map gradient [P,13], all-reduced when N > 1
+    order = ["means3D", "opacities", "scales", "rotations", "colors"]
+
+    def view_of(step):
+        return wl["sets"][(step * world + rank) % V]
+
+    def step_resident(step):
+        color, others, g = arm.forward_backward(view_of(step))
+        if multi:
+            torch.cat([g[k].reshape(-1) for k in order], out=flat)
+            dist.all_reduce(flat)
+        return color
+
+    def barrier():
+        if multi:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps, first_step):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for i in range(steps):
+            fn(first_step + i)
+        e1.record()
+        barrier()
+        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        if multi:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms.item())
+
+    # ---- device-resident `value`
+    for i in range(a.warmup):
+        step_resident(i)
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    l0 = arm.launches()
+    ms_total = timed(step_resident, a.steps, a.warmup)
+    launches = arm.launches() - l0
+    clocks = sampler.stop() if rank == 0 else None
+    ms_per_step = ms_total / a.steps
+    value = world * 1000.0 / ms_per_step if multi else 1000.0 / ms_per_step
+
+    # scene statistics of the views timed (rank 0's share)
+    stats = []
+    for v in range(min(V, 8)):
+        arm.forward_backward(wl["sets"][v])
+        stats.append((int(arm.last_n), int((arm.last_radii > 0).sum())))
+    I_mean = float(np.mean([s[0] for s in stats])); Pv_mean = float(np.mean([s[1] for s in stats]))
+
+    # ---- per-kernel CUDA-event timing over a second pass of the same K steps -> roofline of the dominant kernel
+    roofline, kernels = None, None
+    if a.impl == "b200" and not a.no_kernel_timing:
+        lib = arm.lib
+        nk = lib.gs2d_num_kernels()
+        lib.gs2d_timing_enable(1)
+        ms_timed_pass = timed(step_resident, a.steps, a.warmup)
+        lib.gs2d_timing_enable(0)
+        tot = (C.c_double * nk)(); cnt = (C.c_int64 * nk)()
+        lib.gs2d_timing_collect(tot, cnt)
+        alg = algorithmic_bytes(P, Pv_mean, I_mean, W, H)
+        peaks = {}
+        try:
+            with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+                peaks = json.load(f)
+        except OSError:
+            pass
+        peak, peak_src = (float(peaks["hbm_gbs"]), "measured") if "hbm_gbs" in peaks else (6650.0, "fallback")
+        kernels = {}
+        for i in range(nk):
+            if cnt[i] == 0:
+                continue
+            name = lib.gs2d_kernel_name(i).decode()
+            avg_ms = tot[i] / cnt[i]
+            k = {"launches_per_step": cnt[i] / a.steps, "avg_us": 1e3 * avg_ms, "ms_per_step": tot[i] / a.steps}
+            if name in alg:
+                k["alg_bytes"] = alg[name]
+                k["gbs"] = alg[name] / (avg_ms * 1e-3) / 1e9
+                k["frac_hbm"] = k["gbs"] / peak
+            kernels[name] = k
+        dom = max((n for n in kernels if n in alg), key=lambda n: kernels[n]["ms_per_step"])
+        roofline = {"kernel": dom, "bound": "hbm", "achieved": kernels[dom]["gbs"], "peak": peak, "unit": "GB/s",
+                    "frac": kernels[dom]["frac_hbm"], "traffic": None, "peak_source": peak_src,
+                    "avg_launch_us": kernels[dom]["avg_us"], "alg_bytes_per_launch": kernels[dom]["alg_bytes"],
+                    "share_of_step": kernels[dom]["ms_per_step"] / (ms_timed_pass / a.steps),
+                    "note": "compositing is FP32-issue/MUFU-bound, not HBM-bound (DESIGN.md): the HBM fraction of this "
+                            "kernel is small by construction; see `kernels` for the HBM-bound stages",
+                    "timed_over": f"second pass of {a.steps} steps with CUDA events around every launch "
+                                  f"({ms_timed_pass / a.steps:.3f} ms/step vs {ms_per_step:.3f} untimed)"}
+        traffic_file = os.path.join(ROOT, "profiles", "traffic.json")
+        if os.path.exists(traffic_file):
+            try:
+                roofline["traffic"] = json.load(open(traffic_file)).get(dom)
+            except Exception:
+                pass
+
+    # ---- e2e: public API, per-step inputs from pinned host memory, loss read back to the host
+    e2e = None
+    if not a.no_e2e:
+        params = {k: wl["sets"][0][k].clone().requires_grad_(True) for k in order}
+        means2D = torch.zeros((P, 3), device=dev, requires_grad=True)
+        copy_stream = torch.cuda.Stream(device=dev)
+        slots = [{k: torch.empty_like(v, device=dev) for k, v in wl["sets"][0]["host"].items()} for _ in range(2)]
+        ready = [torch.cuda.Event(), torch.cuda.Event()]
+        freed = [torch.cuda.Event(), torch.cuda.Event()]
+        loss_host = torch.zeros(1).pin_memory()
+        h2d = sum(v.numel() * 4 for v in wl["sets"][0]["host"].values())
+
+        def prefetch(step):
+            sl = step & 1
+            host = view_of(step)["host"]
+            with torch.cuda.stream(copy_stream):
+                copy_stream.wait_event(freed[sl])
+                for k, v in host.items():
+                    slots[sl][k].copy_(v, non_blocking=True)
+                ready[sl].record(copy_stream)
+
+        def step_e2e(step):
+            sl = step & 1
+            cur = torch.cuda.current_stream(dev)
+            cur.wait_event(ready[sl])
+            s = dict(view_of(step)); s.update(slots[sl])
+            prefetch(step + 1)            # next step's inputs travel while this step computes
+            for p in params.values():
+                p.grad = None
+            means2D.grad = None
+            rast = arm.rasterizer(s)
+            color, radii, allmap = rast(means3D=params["means3D"], means2D=means2D, opacities=params["opacities"],
+                                        colors_precomp=params["colors"], scales=params["scales"],
+                                        rotations=params["rotations"])
+            loss = (color * s["dL_dcolor"]).sum() + (allmap * s["dL_dothers"]).sum()
+            loss.backward()
+            if multi:
+                torch.cat([params[k].grad.reshape(-1) for k in order], out=flat)
+                dist.all_reduce(flat)
+            freed[sl].record(cur)
+            loss_host.copy_(loss.detach().reshape(1), non_blocking=True)
+            cur.synchronize()             # the loop reads the loss on the host every step
+            return loss_host
+
+        for ev in freed:
+            ev.record(torch.cuda.current_stream(dev))
+        prefetch(0)
+        for i in range(a.warmup):
+            step_e2e(i)
+        ms_e2e = timed(step_e2e, a.steps, a.warmup) / a.steps
+        e2e = {"value": (world if multi else 1) * 1000.0 / ms_e2e, "unit": UNIT, "h2d_bytes_per_step": h2d,
+               "d2h_bytes_per_step": 4 + 4, "ms_per_step": ms_e2e,
+               "what": "GaussianRasterizer(...)(...) + loss.backward() through the drop-in python API; camera + "
+                       "upstream image gradients copied from pinned host memory every step (double-buffered on a "
+                       "copy stream), num_rendered and the loss read back every step; surfel parameters are "
+                       "optimiser state and stay in HBM"}
+
+    if rank != 0:
+        if multi:
+            dist.destroy_process_group()
+        return 0
+
+    out = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world if multi else 1, "steps": a.steps,
+           "warmup": a.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
+           "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+           "config": {"workload": f"mapping-shaped fwd+bwd of one keyframe view per GPU per step, {W}x{H}, "
+                                  f"{P} surfels, {V}-keyframe window (BASELINE.json configs[2]), use_sa=True",
+                      "surfels": P, "visible_mean": Pv_mean, "instances_mean": I_mean, "views": V,
+                      "parallelism": f"view-sharded x{world if multi else 1}" + (", NCCL all-reduce of [P,13] map gradients" if multi else ""),
+                      "l2": f"inputs rotate over {V} per-view sets ({V} x 58.6 MB > 126 MB L2); no explicit flush"},
+           "gpu_launches": launches, "clocks": clocks}
+    if a.impl == "reference":
+        out["impl"] = "reference"
+        out["cpu_baseline"] = {"value": value, "unit": UNIT, "cores": 0, "kind": "reference",
+                               "sample": "the reference has no CPU implementation of this path (SURVEY.md §8c): this arm "
+                                         "is the UNMODIFIED reference CUDA rasterizer compiled for sm_100a "
+                                         "(oracle/_ref/libgs2d_ref.so) on the same B200, same workload"}
+        out["gpu_launches"] = None
+    else:
+        out["roofline"] = roofline
+        out["kernels"] = kernels
+        if not a.no_cpu_baseline and not multi:
+            out["cpu_baseline"] = cpu_baseline(wl, a.cpu_frames)
+    if e2e is not None:
+        out["e2e"] = e2e
+    print(json.dumps(out))
+    if multi:
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

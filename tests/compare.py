@@ -1,0 +1,98 @@
+"""Field-by-field comparison of two stage dicts (see tests/gpu_run.py for the key names).
+
+Acceptance thresholds are BASELINE.json's: tile keys / sort order / tile ranges bit-exact, images within
+1e-4 absolute, gradients within 1e-3 relative.
+"""
+from __future__ import annotations
+
+import numpy as np
+
+IMG_ATOL = 1e-4        # BASELINE.json north_star: "rendered images within 1e-4 absolute"
+GRAD_RTOL = 1e-3       # "gradients within 1e-3 relative"
+
+INT_SURFEL = ["radii", "tiles_touched", "point_offsets"]
+INT_BINNING = ["keys_unsorted", "values_unsorted", "keys_sorted", "point_list", "ranges"]
+F32_SURFEL = ["depths", "means2D", "transMat", "normal_opacity"]
+IMAGES = ["color", "others", "final_T", "median_depth", "depth_std"]
+GRADS = ["means2D", "colors", "opacity", "means3D", "transMat", "sh", "scales", "rotations"]
+
+
+def grad_rel(a, b):
+    """Relative L2 error of a against b (whole tensor), the metric of the gradient threshold."""
+    a = np.asarray(a, np.float64); b = np.asarray(b, np.float64)
+    return float(np.linalg.norm(a - b) / (np.linalg.norm(b) + 1e-30))
+
+
+def grad_elem_rel(a, b):
+    """Worst element error relative to the tensor's largest magnitude (catches single wrong rows)."""
+    a = np.asarray(a, np.float64); b = np.asarray(b, np.float64)
+    if b.size == 0:
+        return 0.0
+    return float(np.abs(a - b).max() / (np.abs(b).max() + 1e-30))
+
+
+def bits_differ(a, b):
+    a = np.ascontiguousarray(a, np.float32).view(np.uint32)
+    b = np.ascontiguousarray(b, np.float32).view(np.uint32)
+    return int((a != b).sum())
+
+
+def check_binning(got, want, exact_float_state=False):
+    """Integer stages: must be bit-exact.  Returns a list of failure strings."""
+    fails = []
+    if int(got["num_rendered"]) != int(want["num_rendered"]):
+        fails.append(f"num_rendered {int(got['num_rendered'])} != {int(want['num_rendered'])}")
+        return fails
+    for k in INT_SURFEL + INT_BINNING:
+        if k not in got or k not in want:
+            continue
+        nd = int((np.asarray(got[k]) != np.asarray(want[k])).sum())
+        if nd:
+            fails.append(f"{k}: {nd} of {np.asarray(want[k]).size} differ")
+    vis = np.asarray(want["radii"]) > 0
+    for k in F32_SURFEL:
+        if k not in got or k not in want:
+            continue
+        a, b = np.asarray(got[k])[vis], np.asarray(want[k])[vis]
+        if exact_float_state:
+            nd = bits_differ(a, b)
+            if nd:
+                fails.append(f"{k}: {nd} of {b.size} floats differ bitwise (max abs {np.abs(a - b).max():.3e})")
+        else:
+            scale = np.abs(b).max() + 1e-30 if b.size else 1.0
+            err = np.abs(a - b).max() / scale if b.size else 0.0
+            if not err < 1e-5:
+                fails.append(f"{k}: max rel-to-absmax {err:.3e}")
+    return fails
+
+
+def check_images(got, want, atol=IMG_ATOL, exact=False):
+    fails = []
+    for k in IMAGES:
+        if k not in got or k not in want:
+            continue
+        a, b = np.asarray(got[k]), np.asarray(want[k])
+        if exact:
+            nd = bits_differ(a, b)
+            if nd:
+                fails.append(f"{k}: {nd} floats differ bitwise (max abs {np.abs(a - b).max():.3e})")
+        else:
+            err = float(np.abs(a - b).max()) if b.size else 0.0
+            if not err <= atol:
+                fails.append(f"{k}: max abs {err:.3e} > {atol}")
+    return fails
+
+
+def check_grads(got, want, rtol=GRAD_RTOL):
+    fails = []
+    for k in GRADS:
+        a, b = got.get("grad_" + k), want.get("grad_" + k)
+        if a is None or b is None or np.asarray(b).size == 0:
+            continue
+        if not np.isfinite(a).all():
+            fails.append(f"grad_{k}: non-finite values")
+            continue
+        r, e = grad_rel(a, b), grad_elem_rel(a, b)
+        if not (r <= rtol and e <= rtol):
+            fails.append(f"grad_{k}: rel_l2 {r:.3e}, worst element/absmax {e:.3e} > {rtol}")
+    return fails

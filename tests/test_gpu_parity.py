@@ -1,0 +1,162 @@
+"""GPU parity tests proper: the product (libgs2d.so, called through the drop-in `_C` module = the C ABI of
+include/gs2d.h) against (1) the golden fixtures written by the unmodified reference CUDA rasterizer on a B200
+(tests/golden/*.npz), (2) the CPU oracle on the same seeded inputs, (3) the compiled reference itself when
+oracle/_ref/libgs2d_ref.so travelled to the box.
+
+Bars (BASELINE.json): tile keys, sort order, tile ranges bit-exact; images <= 1e-4 abs; gradients <= 1e-3 rel.
+"""
+import numpy as np
+import pytest
+
+import cases
+import compare
+
+pytestmark = pytest.mark.gpu
+
+
+def _oracle_full(case):
+    import cpu as O
+    st = O.forward(case["means3D"], case["opacities"], case["viewmatrix"], case["projmatrix"], case["W"], case["H"],
+                   case["bg"], scales=case["scales"], rotations=case["rotations"], transMat=case["transMat"],
+                   colors=case["colors"], shs=case["shs"], sh_degree=case["sh_degree"], campos=case["campos"],
+                   scale_modifier=float(case["scale_modifier"]), use_sa=case["use_sa"])
+    g = O.backward(st, case["means3D"], case["viewmatrix"], case["projmatrix"], case["W"], case["H"],
+                   float(case["tanfovx"]), float(case["tanfovy"]), case["bg"], case["dL_dcolor"], case["dL_dothers"],
+                   scales=case["scales"], rotations=case["rotations"], transMat=case["transMat"], shs=case["shs"],
+                   sh_degree=case["sh_degree"], campos=case["campos"], use_sa=case["use_sa"])
+    out = dict(st)
+    for k, v in g.items():
+        out["grad_" + k] = v
+    return out
+
+
+def _ref_from_golden(g):
+    return {k[4:]: v for k, v in g.items() if k.startswith("ref_")}
+
+
+@pytest.mark.parametrize("name", cases.GOLDEN_CASES)
+def test_against_golden(name):
+    """Product vs what the unmodified reference wrote for the same inputs (committed fixture)."""
+    import gpu_run
+    g = cases.load_golden(name)
+    assert g is not None, f"tests/golden/{name}.npz missing (tests/golden/make_golden.py writes it on a GPU box)"
+    case = cases.case_from_golden(g)
+    ref = _ref_from_golden(g)
+    ours = gpu_run.run_ours(case, debug=True)
+    fails = compare.check_binning(ours, ref, exact_float_state=True)   # keys, values, sort order, ranges: bit-exact
+    fails += compare.check_images(ours, ref, atol=compare.IMG_ATOL)
+    fails += compare.check_grads(ours, ref, rtol=compare.GRAD_RTOL)
+    assert not fails, "\n".join(fails)
+    # the production path (debug=False: no per-stage synchronisation, no key snapshot) gives the same bits
+    fast = gpu_run.run_ours(case, debug=False)
+    assert not compare.check_images(fast, ours, exact=True)
+    assert not compare.check_binning(fast, ours, exact_float_state=True)
+
+
+@pytest.mark.parametrize("name", list(cases.CASES))
+def test_against_oracle(name):
+    """Product vs the CPU restatement on the same seeded inputs.  The oracle cannot reproduce the GPU's
+    approximate rsqrt (oracle/gs2d_oracle.c header), so per-surfel floats are compared to 1e-5 and a radius may
+    sit across an integer boundary for a handful of surfels: binning is compared through the images then."""
+    import gpu_run
+    case = cases.CASES[name]()
+    want = _oracle_full(case)
+    ours = gpu_run.run_ours(case, debug=True)
+    bin_fails = compare.check_binning(ours, want)
+    if bin_fails:
+        # tolerate only ulp-boundary radii: at most 0.1 % of the surfels may differ
+        nd = int((ours["radii"] != want["radii"]).sum())
+        assert nd <= max(1, case["means3D"].shape[0] // 1000), "\n".join(bin_fails)
+    fails = compare.check_images(ours, want, atol=compare.IMG_ATOL) + compare.check_grads(ours, want)
+    assert not fails, "\n".join(fails)
+
+
+def test_against_compiled_reference_500k():
+    """BASELINE.json's full size (1200x680, 500k surfels): product vs the compiled reference, every stage."""
+    import refgpu
+    if not refgpu.available():
+        pytest.skip("oracle/_ref/libgs2d_ref.so not on this box")
+    import gpu_run
+    from gs2d_b200 import scene
+    intr = scene.REPLICA
+    sc = scene.room_scene(500_000, intr, seed=0)
+    cam = scene.view_sweep(8, intr, seed=0)[3]
+    gc, go = scene.image_grads(intr["W"], intr["H"], seed=3)
+    case = dict(W=intr["W"], H=intr["H"], tanfovx=np.float32(cam.tanfovx), tanfovy=np.float32(cam.tanfovy),
+                viewmatrix=cam.viewmatrix.reshape(16), projmatrix=cam.projmatrix.reshape(16), campos=cam.campos,
+                bg=np.zeros(3, np.float32), use_sa=True, scale_modifier=np.float32(1.0), sh_degree=0, shs=None,
+                transMat=None, dL_dcolor=gc, dL_dothers=go, **sc)
+    ref = gpu_run.run_ref(case)
+    ours = gpu_run.run_ours(case, debug=True)
+    fails = compare.check_binning(ours, ref, exact_float_state=True)
+    fails += compare.check_images(ours, ref) + compare.check_grads(ours, ref)
+    assert not fails, "\n".join(fails)
+
+
+def test_full_size_properties():
+    """Size-independent properties at full size without any oracle: sortedness of the keys, ranges partition
+    the instance list by tile, offsets are the inclusive scan of tiles_touched, determinism of the images."""
+    import gpu_run
+    from gs2d_b200 import scene
+    intr = scene.REPLICA
+    sc = scene.room_scene(500_000, intr, seed=5)
+    cam = scene.view_sweep(4, intr, seed=5)[2]
+    gc, go = scene.image_grads(intr["W"], intr["H"], seed=5)
+    case = dict(W=intr["W"], H=intr["H"], tanfovx=np.float32(cam.tanfovx), tanfovy=np.float32(cam.tanfovy),
+                viewmatrix=cam.viewmatrix.reshape(16), projmatrix=cam.projmatrix.reshape(16), campos=cam.campos,
+                bg=np.zeros(3, np.float32), use_sa=True, scale_modifier=np.float32(1.0), sh_degree=0, shs=None,
+                transMat=None, dL_dcolor=gc, dL_dothers=go, **sc)
+    a = gpu_run.run_ours(case, debug=True)
+    n = int(a["num_rendered"])
+    assert n == int(a["tiles_touched"].astype(np.int64).sum())
+    assert np.array_equal(np.cumsum(a["tiles_touched"].astype(np.int64)), a["point_offsets"].astype(np.int64))
+    ks = a["keys_sorted"]
+    assert np.all(ks[1:] >= ks[:-1]), "keys not sorted"
+    # stable: equal keys keep the order of the unsorted list == a stable argsort of the unsorted keys
+    order = np.argsort(a["keys_unsorted"], kind="stable")
+    assert np.array_equal(a["keys_unsorted"][order], ks)
+    assert np.array_equal(a["values_unsorted"][order], a["point_list"])
+    tiles = (ks >> np.uint64(32)).astype(np.int64)
+    r = a["ranges"].astype(np.int64)
+    cnt = np.bincount(tiles, minlength=r.shape[0])
+    assert np.array_equal(r[:, 1] - r[:, 0], cnt)
+    nz = cnt > 0
+    assert np.array_equal(r[nz, 0], (np.cumsum(cnt) - cnt)[nz])
+    b = gpu_run.run_ours(case, debug=False)
+    assert not compare.check_images(a, b, exact=True), "forward is not deterministic"
+    for k in compare.GRADS:
+        if a["grad_" + k].size:
+            assert compare.grad_rel(b["grad_" + k], a["grad_" + k]) < 1e-5
+
+
+def test_mark_visible_golden():
+    import torch
+    import gaus_2dgs_rasterization._C as GC
+    g = cases.load_golden("mark_visible")
+    assert g is not None
+    t = lambda a: torch.from_numpy(a).cuda()
+    got = GC.mark_visible(t(g["in_means3D"]), t(g["in_viewmatrix"]), t(g["in_projmatrix"])).cpu().numpy()
+    assert np.array_equal(got, g["ref_present"])
+
+
+@pytest.mark.parametrize("name", cases.KNN_CASES)
+def test_dist2_golden(name):
+    """distCUDA2: bit-exact against the reference simple-knn output."""
+    import torch
+    from simple_knn._C import distCUDA2
+    g = cases.load_golden(name)
+    assert g is not None
+    got = distCUDA2(torch.from_numpy(g["in_points"]).cuda()).cpu().numpy()
+    assert compare.bits_differ(got, g["ref_dist2"]) == 0, f"max abs {np.abs(got - g['ref_dist2']).max():.3e}"
+
+
+def test_dist2_large_vs_bruteforce():
+    import torch
+    from simple_knn._C import distCUDA2
+    rng = np.random.default_rng(3)
+    pts = torch.from_numpy(rng.normal(size=(20000, 3)).astype(np.float32)).cuda()
+    got = distCUDA2(pts)
+    d = torch.cdist(pts.double(), pts.double()) ** 2
+    d.fill_diagonal_(float("inf"))
+    want = d.topk(3, dim=1, largest=False).values.mean(dim=1).float()
+    assert torch.allclose(got, want, rtol=1e-4, atol=1e-9)
