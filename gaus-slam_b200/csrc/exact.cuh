@@ -6,7 +6,7 @@
 // computed here: view depth, the 3x3 ray-splat transform T, the 3-sigma bounding box.  The
 // reference leaves the fusion of its a*b + c*d + ... expressions to nvcc's default -fmad=true, so
 // "the reference's arithmetic" is the operation sequence its compiled kernel executes
-// (CR/forward.cu:75-147, :176-238 and CR/auxiliary.h:78-97, :184-234 as built by oracle/build.py
+// (CR/forward.cu:75-147, :176-238 and CR/auxiliary.h:78-97, :184-234 as built by the plain nvcc recipe of the test tree
 // for sm_100a).  That sequence was read off the compiled kernel (SASS, after ptxas' own fusion) once and is restated below
 // operation by operation; each helper names the source expression it stands for.  Products with
 // the literal zeros of the reference's scale / ndc2pix matrices are dropped: for finite inputs

@@ -3,7 +3,7 @@
 // Replaces SimpleKNN::knn (KNN/simple_knn.cu:186-222: bbox reduce -> 30-bit Morton codes -> radix sort ->
 // 1024-point boxes -> boxMeanDist :148-184).  Result contract: for every point the three smallest
 // squared distances to OTHER points (self excluded by index, duplicates count with distance 0), each
-// computed as fma(dz,dz, fma(dy,dy, dx*dx)) with d = other - self (the reference's compiled expression,
+// computed as fma(dz,dz, fma(dx,dx, round(dy*dy))) with d = other - self (the reference's compiled expression,
 // :128-129), summed (b0+b1)+b2 and divided by 3.0f (:183).  The reference search is exact (its pruning
 // radius is an upper bound of the 3rd-NN distance), so any exact 3-NN search with the same distance
 // expression is bit-identical; this one is organised for B200:
@@ -178,7 +178,7 @@ knn_search_kernel(int P, int nboxes, const float4* __restrict__ sorted, const fl
 			if (base + j == me) continue;
 			const float4 o = s_pts[j];
 			const float ex = o.x - q.x, ey = o.y - q.y, ez = o.z - q.z;
-			const float dist = __fmaf_rn(ez, ez, __fmaf_rn(ey, ey, __fmul_rn(ex, ex)));
+			const float dist = __fmaf_rn(ez, ez, __fmaf_rn(ex, ex, __fmul_rn(ey, ey)));
 			kbest3(dist, best);
 		}
 	};

@@ -408,11 +408,12 @@ void oracle_render_forward(int W, int H, const uint32_t* ranges, const uint32_t*
 				const f3 p = { k.y * l.z - k.z * l.y, k.z * l.x - k.x * l.z, k.x * l.y - k.y * l.x };
 				if (p.z == 0.0f) continue;
 				const float sx = p.x / p.z, sy = p.y / p.z;
-				const float rho3d = (sx * sx + sy * sy);
+				/* fused multiply-adds exactly where the reference's compiled kernel has them (nvcc -fmad) */
+				const float rho3d = fmaf(sx, sx, sy * sy);
 				const float dx = xyx - pixx, dy = xyy - pixy;
-				const float rho2d = FILTER_INV_SQUARE * (dx * dx + dy * dy);
+				const float rho2d = FILTER_INV_SQUARE * fmaf(dy, dy, dx * dx);
 				const float rho = fminf(rho3d, rho2d);
-				float depth = (rho3d <= rho2d) ? (sx * Tw.x + sy * Tw.y) + Tw.z : Tw.z;
+				float depth = (rho3d <= rho2d) ? fmaf(Tw.x, sx, Tw.y * sy) + Tw.z : Tw.z;
 				if (depth < NEAR_N) continue;
 				const float* no = normal_opacity + 4 * (size_t)id;
 				const float opa = no[3];
@@ -427,30 +428,31 @@ void oracle_render_forward(int W, int H, const uint32_t* ranges, const uint32_t*
 				if (use_sa) {
 					if (D > 0) {
 						const float exp_depth = median_depth;
-						float exp_std = (D2 - 2 * D * exp_depth) / (1 - T) + exp_depth * exp_depth;
-						exp_std = (float)fmax((double)exp_std, 1e-7);
+						float exp_std = fmaf(exp_depth, exp_depth, (D2 - (D + D) * exp_depth) / (1 - T));
+						exp_std = fmaxf(exp_std, 1e-7f);
 						const float error = (exp_depth - depth) * (exp_depth - depth);
-						const float conf = expf(-error / (4 * exp_std));
-						depth = conf * depth + (1 - conf) * exp_depth;
+						const float conf = expf(error / (exp_std * -4.0f));
+						depth = fmaf(depth, conf, exp_depth * (1 - conf));
 					}
-					D += depth * w;
-					D2 += depth * depth * w;
+					D = fmaf(w, depth, D);
+					D2 = fmaf(w, depth * depth, D2);
 				} else {
 					const float A = 1 - T;
-					const float m = FAR_N / (FAR_N - NEAR_N) * (1 - NEAR_N / depth);
-					distortion += (m * m * A + M2 - 2 * m * M1) * w;
-					D += depth * w;
-					M1 += m * w;
-					M2 += m * m * w;
+					const float m = (FAR_N / (FAR_N - NEAR_N)) * (1 - NEAR_N / depth);
+					const float mm = m * m;
+					distortion = fmaf(fmaf(A, mm, M2) - M1 * (m + m), w, distortion);
+					D = fmaf(depth, w, D);
+					M1 = fmaf(m, w, M1);
+					M2 = fmaf(mm, w, M2);
 				}
-				for (int ch = 0; ch < 3; ch++) N[ch] += no[ch] * w;
-				for (int ch = 0; ch < 3; ch++) C[ch] += features[3 * (size_t)id + ch] * w;
+				for (int ch = 0; ch < 3; ch++) N[ch] = fmaf(w, no[ch], N[ch]);
+				for (int ch = 0; ch < 3; ch++) C[ch] = fmaf(w, features[3 * (size_t)id + ch], C[ch]);
 				T = test_T;
 				last_contributor = contributor;
 			}
 			final_T[pix_id] = T;
 			n_contrib[pix_id] = last_contributor;
-			for (int ch = 0; ch < 3; ch++) out_color[ch * HW + pix_id] = C[ch] + T * bg[ch];
+			for (int ch = 0; ch < 3; ch++) out_color[ch * HW + pix_id] = fmaf(T, bg[ch], C[ch]);
 			/* float -> uint32 store (CR/forward.cu:449): cvt.rzi.u32.f32 saturates -1 to 0 */
 			n_contrib[pix_id + HW] = median_contributor < 0 ? 0u : (uint32_t)median_contributor;
 			final_T[pix_id + HW] = M1;
@@ -460,8 +462,9 @@ void oracle_render_forward(int W, int H, const uint32_t* ranges, const uint32_t*
 			for (int ch = 0; ch < 3; ch++) out_others[pix_id + (2 + ch) * HW] = N[ch];
 			out_others[pix_id + 5 * HW] = median_depth;
 			geo_median_depth[pix_id] = median_depth;
-			geo_depth_std[pix_id] = D2 - 2 * median_depth * D + median_depth * median_depth * (1 - T);
-			if (use_sa) out_others[pix_id + 6 * HW] = D2 - 2 * median_depth * D + (1 - T) * median_depth * median_depth;
+			const float var0 = D2 - (median_depth + median_depth) * D;
+			geo_depth_std[pix_id] = fmaf(median_depth * median_depth, 1 - T, var0);
+			if (use_sa) out_others[pix_id + 6 * HW] = fmaf(median_depth, median_depth * (1 - T), var0);
 			else out_others[pix_id + 6 * HW] = distortion;
 		}
 	}
@@ -813,7 +816,7 @@ static inline uint32_t f2u_rz(float v)
 static inline void knn_update3(const float* ref, const float* pt, float* best)
 {
 	const float dx = pt[0] - ref[0], dy = pt[1] - ref[1], dz = pt[2] - ref[2];
-	float dist = fmaf(dz, dz, fmaf(dy, dy, dx * dx));
+	float dist = fmaf(dz, dz, fmaf(dx, dx, dy * dy));   /* the compiled order: round(dy*dy) first */
 	for (int j = 0; j < 3; j++)
 		if (best[j] > dist) { float t = best[j]; best[j] = dist; dist = t; }
 }
@@ -822,7 +825,7 @@ static inline float box_dist(const float* mn, const float* mx, const float* p)
 	float d[3] = { 0, 0, 0 };
 	for (int a = 0; a < 3; a++)
 		if (p[a] < mn[a] || p[a] > mx[a]) d[a] = fminf(fabsf(p[a] - mn[a]), fabsf(p[a] - mx[a]));
-	return d[0] * d[0] + d[1] * d[1] + d[2] * d[2];
+	return fmaf(d[2], d[2], fmaf(d[0], d[0], d[1] * d[1]));
 }
 #define FLT_MAX_ 3.402823466e+38F
 

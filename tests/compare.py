@@ -66,6 +66,37 @@ def check_binning(got, want, exact_float_state=False):
     return fails
 
 
+# Tolerances for comparisons against the CPU ORACLE only (never for product-vs-reference, which uses the
+# BASELINE bars above).  With use_sa the per-pixel depth confidence is exp(-(d - md)^2 / (4 var)) where
+# var = D2 - 2 D md + md^2 (1 - T) is a catastrophic cancellation of O(10) terms down to ~1e-6, i.e. fp32
+# rounding noise: its value depends on the last bit of every alpha, and alpha goes through the GPU's
+# ex2.approx, which a CPU cannot reproduce.  The surface-aware depth channel, the variance channel and the
+# gradients that flow through `conf` are therefore compared more loosely against the oracle; a handful of
+# pixels may also take a different discrete branch (T > 0.5, alpha < 1/255) and are allowed as outliers.
+ORACLE_SA_DEPTH_ATOL = 1e-3
+ORACLE_SA_GRAD_RTOL = 1e-2
+ORACLE_OUTLIER_FRAC = 2e-4
+
+
+def check_images_oracle(got, want, use_sa):
+    """Oracle-vs-GPU image comparison (see the note above): per channel tolerances + outlier budget."""
+    fails = []
+    for k in IMAGES:
+        if k not in got or k not in want:
+            continue
+        a, b = np.asarray(got[k], np.float32), np.asarray(want[k], np.float32)
+        if a.ndim == 2:
+            a, b = a[None], b[None]
+        for ch in range(a.shape[0]):
+            loose = use_sa and ((k == "others" and ch in (0, 6)) or k == "depth_std")
+            atol = ORACLE_SA_DEPTH_ATOL if loose else IMG_ATOL
+            d = np.abs(a[ch] - b[ch])
+            nbad = int((d > atol).sum())
+            if nbad > max(1, int(ORACLE_OUTLIER_FRAC * d.size)):
+                fails.append(f"{k}[{ch}]: {nbad} of {d.size} pixels off by more than {atol} (max {d.max():.3e})")
+    return fails
+
+
 def check_images(got, want, atol=IMG_ATOL, exact=False):
     fails = []
     for k in IMAGES:

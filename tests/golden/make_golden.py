@@ -66,6 +66,8 @@ def main():
         ref = gpu_run.run_ref(case)
         if name == "room_sa":
             room_ref = {k: np.array(v) for k, v in ref.items()}
+        if name == "transmat_pre":
+            ref["transMat"] = case["transMat"].copy()   # the reference never copies a precomputed transMat into its state
         z = pack(case, ref)
         np.savez_compressed(os.path.join(a.out, name + ".npz"), **z)
         print(f"{name:14s} P={case['means3D'].shape[0]} {case['W']}x{case['H']} num_rendered={int(ref['num_rendered'])} "
@@ -78,6 +80,9 @@ def main():
         print(f"{name:14s} P={pts.shape[0]} mean={float(d.mean()):.6g}")
     # markVisible
     case = cases.room_sa()
+    rng = np.random.default_rng(17)
+    near = rng.uniform(-1.0, 1.0, size=(2000, 3)).astype(np.float32)      # straddles the z = 0.2 plane
+    case["means3D"] = np.concatenate([case["means3D"], cases.behind()["means3D"], near], axis=0)
     dev = gpu_run.to_device(case)
     vis = refgpu.mark_visible(dev["means3D"], dev["viewmatrix"], dev["projmatrix"])
     np.savez_compressed(os.path.join(a.out, "mark_visible.npz"), in_means3D=case["means3D"],

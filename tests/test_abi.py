@@ -1,0 +1,112 @@
+"""CPU tests of the drop-in boundary: libgs2d.so loads, exports every symbol include/gs2d.h declares, its size
+queries and argument validation behave; the python packages mirror the reference's names.  No GPU compute."""
+import ctypes as C
+import os
+import re
+
+import pytest
+
+from gs2d_b200 import _lib as L
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _header_functions():
+    src = open(os.path.join(ROOT, "include", "gs2d.h")).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(gs2d_[a-z0-9_]+)\s*\(", src)))
+
+
+def test_library_exports_every_declared_symbol():
+    lib = C.CDLL(L.LIB_PATH)
+    names = _header_functions()
+    assert len(names) >= 20
+    for n in names:
+        assert hasattr(lib, n), f"{n} declared in include/gs2d.h but not exported"
+    # and the ctypes mirror covers the header exactly
+    assert sorted(L.PROTOTYPES) == names
+
+
+def test_abi_version_and_strerror():
+    lib = L.load()
+    assert lib.gs2d_abi_version() == 1
+    assert lib.gs2d_strerror(0).decode().lower().startswith("ok") or lib.gs2d_strerror(0)
+    for code in (-1, -2, -3, -4):
+        assert lib.gs2d_strerror(code).decode()
+
+
+def test_size_queries_monotone_and_aligned():
+    lib = L.load()
+    assert lib.gs2d_geom_bytes(0, 0) >= 0
+    g1, g2 = lib.gs2d_geom_bytes(1000, 0), lib.gs2d_geom_bytes(500_000, 0)
+    assert 0 < g1 < g2
+    assert g2 >= 500_000 * (4 + 80 + 8 + 16 + 4 + 4 + 3)
+    i1 = lib.gs2d_image_bytes(1200, 680)
+    assert i1 >= 1200 * 680 * (12 + 8 + 4 + 4) + 75 * 43 * 8
+    b1, b2 = lib.gs2d_binning_bytes(1000, 1200, 680), lib.gs2d_binning_bytes(1_000_000, 1200, 680)
+    assert 0 < b1 < b2
+    assert lib.gs2d_backward_scratch_bytes(1000, 5000) >= 5000 * 80
+    assert lib.gs2d_dist2_scratch_bytes(1000) > 1000 * 16
+    assert lib.gs2d_sort_scratch_bytes(1 << 20) > 0
+
+
+def test_argument_validation_without_gpu():
+    """Invalid calls are rejected before anything is launched (so this runs on a CPU-only box)."""
+    lib = L.load()
+    s = L.Settings(P=10, image_width=64, image_height=64)
+    assert lib.gs2d_forward_preprocess(None, None, None, None, None, None) == L.GS2D_ERR_INVALID
+    i = L.Inputs()   # all NULL
+    b = L.Buffers()
+    assert lib.gs2d_forward_preprocess(C.byref(s), C.byref(i), C.byref(b), None, None, None) == L.GS2D_ERR_INVALID
+    assert lib.gs2d_forward_render(C.byref(s), C.byref(i), C.byref(b), 0, None, None, None) == L.GS2D_ERR_INVALID
+    assert lib.gs2d_mark_visible(-1, None, None, None, None, None) == L.GS2D_ERR_INVALID
+    assert lib.gs2d_mark_visible(0, None, None, None, None, None) == L.GS2D_OK
+    assert lib.gs2d_dist2(-1, None, None, None, None) == L.GS2D_ERR_INVALID
+    assert lib.gs2d_dist2(0, None, None, None, None) == L.GS2D_OK
+    assert lib.gs2d_dist2(5, None, None, None, None) == L.GS2D_ERR_INVALID
+    assert lib.gs2d_sort_pairs(-1, None, None, None, None, 32, None, None) == L.GS2D_ERR_INVALID
+    assert lib.gs2d_sort_pairs(10, None, None, None, None, 32, None, None) == L.GS2D_ERR_INVALID
+    assert lib.gs2d_sort_pairs(10, None, None, None, None, 0, None, None) == L.GS2D_ERR_INVALID
+    with pytest.raises(L.Gs2dError):
+        L.check(L.GS2D_ERR_CAPACITY, "x")
+
+
+def test_python_surface_matches_reference_names():
+    import gaus_2dgs_rasterization as G
+    fields = ("image_height", "image_width", "tanfovx", "tanfovy", "bg", "scale_modifier", "viewmatrix", "projmatrix",
+              "sh_degree", "campos", "use_sa", "prefiltered", "debug")
+    assert G.GaussianRasterizationSettings._fields == fields      # RAST/gaus_2dgs_rasterization/__init__.py:163-176
+    assert hasattr(G.GaussianRasterizer, "markVisible") and hasattr(G.GaussianRasterizer, "forward")
+    for n in ("rasterize_gaussians", "rasterize_gaussians_backward", "mark_visible"):   # RAST/ext.cpp:15-19
+        assert callable(getattr(G._C, n))
+    from simple_knn._C import distCUDA2                                                   # KNN/ext.cpp:15-17
+    assert callable(distCUDA2)
+
+
+def test_rasterizer_argument_errors():
+    """Same exceptions as the reference for inconsistent arguments (__init__.py:198-202)."""
+    import torch
+    import gaus_2dgs_rasterization as G
+    z = torch.zeros(3)
+    st = G.GaussianRasterizationSettings(8, 8, 1.0, 1.0, z, 1.0, torch.eye(4), torch.eye(4), 0, z, True, False, False)
+    r = G.GaussianRasterizer(st)
+    m = torch.zeros(4, 3)
+    with pytest.raises(Exception, match="SHs or precomputed colors"):
+        r(m, m, torch.zeros(4, 1), scales=torch.zeros(4, 2), rotations=torch.zeros(4, 4))
+    with pytest.raises(Exception, match="scale/rotation pair or precomputed"):
+        r(m, m, torch.zeros(4, 1), colors_precomp=m)
+    with pytest.raises(RuntimeError):          # CPU tensors are rejected, there is no CPU path
+        r(m, m, torch.zeros(4, 1), colors_precomp=m, scales=torch.zeros(4, 2), rotations=torch.zeros(4, 4))
+
+
+def test_product_never_touches_the_oracle():
+    """The shipped package must not import, link or execute anything under oracle/."""
+    pkg = os.path.join(ROOT, "gaus-slam_b200")
+    bad = re.compile(r"libgs2d_oracle|libgs2d_ref|gs2d_oracle\.c|import\s+refgpu|import\s+cpu\b|from\s+oracle|oracle[/\\]|"
+                     r"[\"']oracle[\"']")
+    for d, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h", ".cpp")):
+                txt = open(os.path.join(d, f), errors="ignore").read()
+                m = bad.search(txt)
+                assert m is None, f"{os.path.join(d, f)} references the oracle: {m.group(0)!r}"

@@ -67,7 +67,8 @@ def test_against_oracle(name):
         # tolerate only ulp-boundary radii: at most 0.1 % of the surfels may differ
         nd = int((ours["radii"] != want["radii"]).sum())
         assert nd <= max(1, case["means3D"].shape[0] // 1000), "\n".join(bin_fails)
-    fails = compare.check_images(ours, want, atol=compare.IMG_ATOL) + compare.check_grads(ours, want)
+    fails = compare.check_images_oracle(ours, want, case["use_sa"])
+    fails += compare.check_grads(ours, want, rtol=compare.ORACLE_SA_GRAD_RTOL if case["use_sa"] else compare.GRAD_RTOL)
     assert not fails, "\n".join(fails)
 
 
