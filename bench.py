@@ -30,6 +30,7 @@ import time
 import numpy as np
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
+PARAMS = ["means3D", "opacities", "scales", "rotations", "colors"]
 METRIC = "rasterized fwd+bwd frames/sec @1200x680, 500k surfels"
 UNIT = "frames/s"
 
@@ -146,6 +147,7 @@ def algorithmic_bytes(P, Pv, I, W, H):
         "onesweep_pass": 24 * I,                       # per pass: read + write (u64 key, u32 value)
         "histogram": 8 * I,
         "gather_ranges": 8 * I + 8 * Tl + 12 * I + 76 * I,   # sorted pairs in, per-instance records out
+        "footprint": 88 * I + 32 * I,                     # record + key in, 256-bit mask out (new stage)
         "composite_forward": 76 * I + 8 * Tl + 68 * Px,
         "composite_backward": 76 * I + 8 * Tl + 68 * Px + 64 * Pv,
         "preprocess_backward": 4 * P + 136 * Pv + 48 * Pv,
@@ -155,34 +157,22 @@ def algorithmic_bytes(P, Pv, I, W, H):
 # ----------------------------------------------------------------------------------------------------
 # the two arms: each exposes forward_backward(set) -> (color, others, grads dict) on device tensors
 # ----------------------------------------------------------------------------------------------------
-class B200Arm:
-    name = "b200"
+class ApiArm:
+    """Drives a module with the reference's public API (`GaussianRasterizationSettings` / `GaussianRasterizer`,
+    RAST/gaus_2dgs_rasterization/__init__.py:163-227): ours (gaus-slam_b200/gaus_2dgs_rasterization over
+    libgs2d.so) or the UNMODIFIED reference package pip-installed into baseline/_ref."""
 
-    def __init__(self, wl, dev):
-        sys.path.insert(0, os.path.join(ROOT, "gaus-slam_b200"))
-        import gaus_2dgs_rasterization as G
-        from gs2d_b200 import _lib
-        self.G, self.GC, self.L = G, G._C, _lib
-        self.lib = _lib.load()          # raises if libgs2d.so is missing: no fallback
-        self.wl, self.dev = wl, dev
+    def __init__(self, G, wl, dev, name, lib=None):
+        import torch
+        self.G, self.wl, self.dev, self.name, self.lib, self.torch = G, wl, dev, name, lib, torch
+        self.last_n, self.last_radii = None, None
+        for s in wl["sets"]:
+            for k in PARAMS:
+                s[k].requires_grad_(True)
+            s["means2D"] = torch.zeros((wl["P"], 3), device=dev, requires_grad=True)
 
     def launches(self):
-        return int(self.lib.gs2d_launch_count())
-
-    def forward_backward(self, s):
-        wl, GC = self.wl, self.GC
-        e = wl["empty"]
-        n, color, others, radii, geom, binning, img = GC.rasterize_gaussians(
-            wl["bg"], s["means3D"], s["colors"], s["opacities"], s["scales"], s["rotations"], 1.0, e,
-            s["viewmatrix"], s["projmatrix"], s["tanfovx"], s["tanfovy"], wl["H"], wl["W"], e, 0, s["campos"],
-            True, False, False)
-        g = GC.rasterize_gaussians_backward(
-            wl["bg"], s["means3D"], radii, s["colors"], s["scales"], s["rotations"], 1.0, e, s["viewmatrix"],
-            s["projmatrix"], s["tanfovx"], s["tanfovy"], s["dL_dcolor"], s["dL_dothers"], e, 0, s["campos"],
-            geom, n, binning, img, True, False)
-        self.last_n, self.last_radii = n, radii
-        # reference order: (means2D, colors, opacity, means3D, transMat, sh, scales, rotations)
-        return color, others, dict(means3D=g[3], opacities=g[2], scales=g[6], rotations=g[7], colors=g[1])
+        return int(self.lib.gs2d_launch_count()) if self.lib is not None else 0
 
     def rasterizer(self, s):
         G, wl = self.G, self.wl
@@ -191,6 +181,47 @@ class B200Arm:
             scale_modifier=1.0, viewmatrix=s["viewmatrix"], projmatrix=s["projmatrix"], sh_degree=0,
             campos=s["campos"], use_sa=True, prefiltered=False, debug=False)
         return G.GaussianRasterizer(st)
+
+    def forward_backward(self, s):
+        """One fwd+bwd of one view through the public API; returns (color, allmap, {param: grad})."""
+        torch = self.torch
+        for k in PARAMS:
+            s[k].grad = None
+        s["means2D"].grad = None
+        color, radii, allmap = self.rasterizer(s)(
+            means3D=s["means3D"], means2D=s["means2D"], opacities=s["opacities"], colors_precomp=s["colors"],
+            scales=s["scales"], rotations=s["rotations"])
+        torch.autograd.backward([color, allmap], [s["dL_dcolor"], s["dL_dothers"]])
+        self.last_radii = radii
+        return color, allmap, {k: s[k].grad for k in PARAMS}
+
+
+def make_b200_arm(wl, dev):
+    sys.path.insert(0, os.path.join(ROOT, "gaus-slam_b200"))
+    import gaus_2dgs_rasterization as G
+    from gs2d_b200 import _lib
+    lib = _lib.load()          # raises if libgs2d.so is missing: there is no fallback
+    return ApiArm(G, wl, dev, "b200", lib)
+
+
+def make_reference_arm(wl, dev):
+    """The reference arm.  Preferred: the UNMODIFIED reference package built by
+    `pip install --no-index --no-build-isolation --no-deps --target baseline/_ref <copy of RAST>`,
+    imported from baseline/_ref and driven through its own GaussianRasterizer.  Fallback: the same reference
+    CUDA sources behind the C shim (oracle/_ref/libgs2d_ref.so)."""
+    pkg = os.path.join(ROOT, "baseline", "_ref")
+    if os.path.isdir(os.path.join(pkg, "gaus_2dgs_rasterization")):
+        sys.path[:] = [p for p in sys.path if os.path.basename(p.rstrip("/")) != "gaus-slam_b200"]
+        sys.modules.pop("gaus_2dgs_rasterization", None)
+        sys.path.insert(0, pkg)
+        import gaus_2dgs_rasterization as G
+        assert os.path.realpath(G.__file__).startswith(os.path.realpath(pkg)), G.__file__
+        arm = ApiArm(G, wl, dev, "reference")
+        arm.how = "unmodified reference package (baseline/_ref), its own GaussianRasterizer + autograd"
+        return arm
+    arm = ReferenceArm(wl, dev)
+    arm.how = "reference CUDA sources behind the C shim oracle/_ref/libgs2d_ref.so"
+    return arm
 
 
 class ReferenceArm:
@@ -291,7 +322,7 @@ def main():
 
     wl = build_workload(a, dev)
     try:
-        arm = B200Arm(wl, dev) if a.impl == "b200" else ReferenceArm(wl, dev)
+        arm = make_b200_arm(wl, dev) if a.impl == "b200" else make_reference_arm(wl, dev)
     except FileNotFoundError as e:
         print(json.dumps({"impl": "reference", "unavailable": str(e)}))
         return 0
@@ -340,11 +371,21 @@ def main():
     ms_per_step = ms_total / a.steps
     value = world * 1000.0 / ms_per_step if multi else 1000.0 / ms_per_step
 
-    # scene statistics of the views timed (rank 0's share)
+    # scene statistics of the window (instances I = num_rendered, visible surfels Pv), outside the timed region
     stats = []
-    for v in range(min(V, 8)):
-        arm.forward_backward(wl["sets"][v])
-        stats.append((int(arm.last_n), int((arm.last_radii > 0).sum())))
+    with torch.no_grad():
+        for v in range(V):
+            s_ = wl["sets"][v]
+            if isinstance(arm, ApiArm):
+                e_ = wl["empty"]
+                r_ = arm.G._C.rasterize_gaussians(
+                    wl["bg"], s_["means3D"].detach(), s_["colors"].detach(), s_["opacities"].detach(),
+                    s_["scales"].detach(), s_["rotations"].detach(), 1.0, e_, s_["viewmatrix"], s_["projmatrix"],
+                    s_["tanfovx"], s_["tanfovy"], wl["H"], wl["W"], e_, 0, s_["campos"], True, False, False)
+                stats.append((int(r_[0]), int((r_[3] > 0).sum())))
+            else:
+                arm.forward_backward(s_)
+                stats.append((int(arm.last_n), int((arm.last_radii > 0).sum())))
     I_mean = float(np.mean([s[0] for s in stats])); Pv_mean = float(np.mean([s[1] for s in stats]))
 
     # ---- per-kernel CUDA-event timing over a second pass of the same K steps -> roofline of the dominant kernel
@@ -396,7 +437,7 @@ def main():
     # ---- e2e: public API, per-step inputs from pinned host memory, loss read back to the host
     e2e = None
     if not a.no_e2e:
-        params = {k: wl["sets"][0][k].clone().requires_grad_(True) for k in order}
+        params = {k: wl["sets"][0][k].detach().clone().requires_grad_(True) for k in order}
         means2D = torch.zeros((P, 3), device=dev, requires_grad=True)
         copy_stream = torch.cuda.Stream(device=dev)
         slots = [{k: torch.empty_like(v, device=dev) for k, v in wl["sets"][0]["host"].items()} for _ in range(2)]
@@ -468,8 +509,8 @@ def main():
         out["impl"] = "reference"
         out["cpu_baseline"] = {"value": value, "unit": UNIT, "cores": 0, "kind": "reference",
                                "sample": "the reference has no CPU implementation of this path (SURVEY.md §8c): this arm "
-                                         "is the UNMODIFIED reference CUDA rasterizer compiled for sm_100a "
-                                         "(oracle/_ref/libgs2d_ref.so) on the same B200, same workload"}
+                                         "is the UNMODIFIED reference CUDA rasterizer compiled for sm_100a on the same "
+                                         "B200, same workload, every step; " + getattr(arm, "how", "")}
         out["gpu_launches"] = None
     else:
         out["roofline"] = roofline

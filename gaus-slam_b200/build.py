@@ -13,9 +13,9 @@ from concurrent.futures import ThreadPoolExecutor
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "lib", "libgs2d.so")
-SOURCES = ["api.cu", "preprocess.cu", "binning.cu", "composite_fwd.cu", "composite_bwd.cu",
+SOURCES = ["api.cu", "preprocess.cu", "binning.cu", "footprint.cu", "composite_fwd.cu", "composite_bwd.cu",
            "preprocess_bwd.cu", "knn.cu"]
-HEADERS = ["common.cuh", "math.cuh", "exact.cuh", "tma.cuh", os.path.join("..", "..", "include", "gs2d.h")]
+HEADERS = ["common.cuh", "math.cuh", "exact.cuh", "tma.cuh", "pair.cuh", os.path.join("..", "..", "include", "gs2d.h")]
 NVCC_FLAGS = ["-std=c++17", "-O3", "-lineinfo", "-Xcompiler", "-fPIC",
               "-gencode", "arch=compute_100a,code=sm_100a"]
 

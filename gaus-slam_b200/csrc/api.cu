@@ -34,7 +34,7 @@ cudaEvent_t prof_event()
 const char* const kKernelNames[K_COUNT] = {
 	"preprocess_forward", "scan_tiles", "duplicate_keys", "histogram", "digit_base", "onesweep_pass",
 	"gather_ranges", "composite_forward", "composite_backward", "preprocess_backward", "mark_visible",
-	"memset", "memcpy", "knn"};
+	"memset", "memcpy", "knn", "footprint"};
 }  // namespace
 void prof_mark(int id, cudaStream_t st, bool begin)
 {
@@ -109,6 +109,7 @@ BinningState BinningState::carve(void* base, size_t I, size_t* bytes)
 	b.vals_a = c.take<uint32_t>(n);
 	b.vals_b = c.take<uint32_t>(n);
 	b.instances = c.take<float>(n * REC_WORDS);
+	b.hit_inst = c.take<uint32_t>(n * 8 + 64);
 	b.keys_dbg = c.take<uint64_t>(n);
 	b.vals_dbg = c.take<uint32_t>(n);
 	size_t sort_bytes = 0;
@@ -200,7 +201,7 @@ int gs2d_forward_render(const gs2d_settings* s, const gs2d_inputs* in, const gs2
 	if (s->P == 0 || I == 0) {
 		// nothing to blend: ranges all empty, the compositor still writes every pixel (background)
 		GS2D_CUDA_OK(cudaMemsetAsync(im.ranges, 0, sizeof(uint32_t) * 2 * (size_t)gx * gy, st));
-		return launch_composite_forward(*s, *in, im, nullptr, out_color, out_others, st);
+		return launch_composite_forward(*s, *in, im, nullptr, nullptr, out_color, out_others, st);
 	}
 	if (!buffers->geom || !buffers->binning) return GS2D_ERR_INVALID;
 	if (buffers->binning_bytes < gs2d_binning_bytes(I, s->image_width, s->image_height)) return GS2D_ERR_CAPACITY;
@@ -224,7 +225,9 @@ int gs2d_forward_render(const gs2d_settings* s, const gs2d_inputs* in, const gs2
 	}
 	GS2D_TRY(launch_gather_ranges(*s, g, b.keys_b, b.vals_b, b.instances, im.ranges, I, st));
 	GS2D_TRY(debug_sync(*s, st));
-	GS2D_TRY(launch_composite_forward(*s, *in, im, b.instances, out_color, out_others, st));
+	GS2D_TRY(launch_footprint(*s, b.instances, b.keys_b, b.hit_inst, I, st));
+	GS2D_TRY(debug_sync(*s, st));
+	GS2D_TRY(launch_composite_forward(*s, *in, im, b.instances, b.hit_inst, out_color, out_others, st));
 	GS2D_TRY(debug_sync(*s, st));
 	return GS2D_OK;
 }
@@ -272,7 +275,7 @@ int gs2d_backward(const gs2d_settings* s, const gs2d_inputs* in, const gs2d_buff
 			ProfScope ps(K_MEMSET, st);
 			GS2D_CUDA_OK(cudaMemsetAsync(rows, 0, (size_t)I * GRAD_WORDS * sizeof(float), st));
 		}
-		GS2D_TRY(launch_composite_backward(*s, *in, im, b.instances, dL_dout_color, dL_dout_others, rows, st));
+		GS2D_TRY(launch_composite_backward(*s, *in, im, b.instances, b.hit_inst, dL_dout_color, dL_dout_others, rows, st));
 		GS2D_TRY(debug_sync(*s, st));
 	}
 	GS2D_TRY(launch_preprocess_backward(*s, *in, g, radii, rows, *grads, st));
@@ -308,6 +311,23 @@ int gs2d_state_view_get(const gs2d_settings* s, const gs2d_buffers* buffers, int
 		out->ranges = im.ranges; out->final_T = im.final_T; out->n_contrib = im.n_contrib;
 		out->median_depth = im.median_depth; out->depth_std = im.depth_std;
 	}
+	return GS2D_OK;
+}
+
+int gs2d_footprint_audit(const gs2d_settings* s, const gs2d_buffers* buffers, int64_t I, uint64_t* counts_host,
+                         void* stream)
+{
+	if (!s || !buffers || !counts_host) return GS2D_ERR_INVALID;
+	counts_host[0] = counts_host[1] = counts_host[2] = 0;
+	if (I <= 0) return GS2D_OK;
+	if (!buffers->binning) return GS2D_ERR_INVALID;
+	cudaStream_t st = (cudaStream_t)stream;
+	BinningState b = BinningState::carve(buffers->binning, (size_t)I, nullptr);
+	unsigned long long* counts = (unsigned long long*)(b.hit_inst + 8 * (size_t)I + 8);   // padding of hit_inst
+	GS2D_CUDA_OK(cudaMemsetAsync(counts, 0, 3 * sizeof(unsigned long long), st));
+	GS2D_TRY(launch_footprint_audit(*s, b.instances, b.keys_b, b.hit_inst, I, counts, st));
+	GS2D_CUDA_OK(cudaMemcpyAsync(counts_host, counts, 3 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
+	GS2D_CUDA_OK(cudaStreamSynchronize(st));
 	return GS2D_OK;
 }
 

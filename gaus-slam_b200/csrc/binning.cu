@@ -237,25 +237,24 @@ onesweep_kernel(long long n, const uint64_t* __restrict__ keys_in, const uint32_
 // One warp-quarter... one thread group of 5 lanes would complicate things: keep one thread per
 // sorted instance for the bookkeeping and let 5 consecutive float4 stores per thread carry the
 // record (80 B, contiguous in the output).
-__device__ __forceinline__ uint32_t block_mask_for_tile(float4 cb, int tx, int ty)
+// In-tile footprint box of an instance: the surfel's contribution bounds (preprocess.cu) clipped to the
+// tile and to the image, packed as described in pair.cuh (x0 | y0<<4 | x1<<8 | y1<<12 | valid<<16).
+__device__ __forceinline__ uint32_t tile_box_word(float4 cb, int tx, int ty, int W, int H)
 {
-	// pixel blocks: 2 columns x 4 rows of 8x4 pixels; bit = by*2 + bx
-	const float ox = (float)(tx * TILE), oy = (float)(ty * TILE);
-	uint32_t m = 0;
-#pragma unroll
-	for (int by = 0; by < 4; by++) {
-#pragma unroll
-		for (int bx = 0; bx < 2; bx++) {
-			float x0 = ox + bx * 8, x1 = x0 + 7.0f, y0 = oy + by * 4, y1 = y0 + 3.0f;
-			bool hit = (cb.x <= x1) && (cb.z >= x0) && (cb.y <= y1) && (cb.w >= y0);
-			m |= (hit ? 1u : 0u) << (by * 2 + bx);
-		}
-	}
-	return m;
+	const int tx0 = tx * TILE, ty0 = ty * TILE;
+	const int tx1 = min(tx0 + TILE - 1, W - 1), ty1 = min(ty0 + TILE - 1, H - 1);
+	// clamp in float first: the bounds may be +-inf ("no culling")
+	const int x0 = (int)ceilf(fminf(fmaxf(cb.x, (float)tx0), (float)(tx1 + 1)));
+	const int y0 = (int)ceilf(fminf(fmaxf(cb.y, (float)ty0), (float)(ty1 + 1)));
+	const int x1 = (int)floorf(fmaxf(fminf(cb.z, (float)tx1), (float)(tx0 - 1)));
+	const int y1 = (int)floorf(fmaxf(fminf(cb.w, (float)ty1), (float)(ty0 - 1)));
+	if (x0 > x1 || y0 > y1) return 0u;
+	return (uint32_t)(x0 - tx0) | ((uint32_t)(y0 - ty0) << 4) | ((uint32_t)(x1 - tx0) << 8) |
+	       ((uint32_t)(y1 - ty0) << 12) | (1u << 16);
 }
 
 __global__ void __launch_bounds__(256)
-gather_ranges_kernel(long long I, unsigned gx, const uint64_t* __restrict__ keys,
+gather_ranges_kernel(long long I, unsigned gx, int W, int H, const uint64_t* __restrict__ keys,
                      const uint32_t* __restrict__ point_list, const float4* __restrict__ splat,
                      const ushort4* __restrict__ rect, const float4* __restrict__ cull,
                      const uint32_t* __restrict__ offsets, float4* __restrict__ instances,
@@ -281,7 +280,7 @@ gather_ranges_kernel(long long I, unsigned gx, const uint64_t* __restrict__ keys
 	const ushort4 r = rect[idx];
 	const uint32_t start = idx == 0 ? 0u : offsets[idx - 1];
 	const uint32_t row = start + (uint32_t)(ty - r.y) * (uint32_t)(r.z - r.x) + (uint32_t)(tx - r.x);
-	const uint32_t mask = block_mask_for_tile(cull[idx], tx, ty);
+	const uint32_t mask = tile_box_word(cull[idx], tx, ty, W, H);
 	const float4* src = splat + 5 * (size_t)idx;
 	float4 a = src[0], b = src[1], c = src[2], d = src[3], e = src[4];
 	d.w = __uint_as_float(mask);
@@ -391,7 +390,7 @@ int launch_gather_ranges(const gs2d_settings& s, const GeomState& g, const uint6
 		{
 			ProfScope ps(K_GATHER_RANGES, st);
 			gather_ranges_kernel<<<(unsigned)((I + 255) / 256), 256, 0, st>>>(
-				I, gx, keys_sorted, point_list, (const float4*)g.splat, (const ushort4*)g.rect,
+				I, gx, s.image_width, s.image_height, keys_sorted, point_list, (const float4*)g.splat, (const ushort4*)g.rect,
 				(const float4*)g.cull, g.point_offsets, (float4*)instances, ranges);
 			count_launch();
 		}

@@ -20,7 +20,7 @@ constexpr int GRAD_WORDS = 20;           // one per-instance gradient row = 80 B
 //   0..2  Tu     3  centre x        (transMat rows, CR/forward.cu:196-199; means2D)
 //   4..6  Tv     7  centre y
 //   8..10 Tw    11  opacity
-//  12..14 normal 15 block mask (instances only: which 8x4 pixel blocks of the tile can be touched)
+//  12..14 normal 15 footprint box (instances only: in-tile pixel box, packed as in pair.cuh)
 //  16..18 rgb    19 row (instances only: index of this instance's gradient row)
 constexpr int REC_MASK = 15;
 constexpr int REC_ROW = 19;
@@ -101,6 +101,7 @@ struct BinningState {
 	uint32_t* vals_a;         // [I]
 	uint32_t* vals_b;         // [I]
 	float* instances;         // [I,20]
+	uint32_t* hit_inst;       // [I,8] per-instance footprint mask, box-local pixel order (footprint.cu)
 	uint64_t* keys_dbg;       // [I] copy of the unsorted keys
 	uint32_t* vals_dbg;       // [I]
 	SortScratch sort;
@@ -121,7 +122,7 @@ void count_launch(int n = 1);
 // Optional per-kernel CUDA-event timing (gs2d_timing_* in include/gs2d.h) -------------------------
 enum KernelId {
 	K_PREPROCESS_FWD = 0, K_SCAN, K_DUPLICATE, K_HISTOGRAM, K_DIGIT_BASE, K_ONESWEEP, K_GATHER_RANGES,
-	K_COMPOSITE_FWD, K_COMPOSITE_BWD, K_PREPROCESS_BWD, K_MARK_VISIBLE, K_MEMSET, K_MEMCPY, K_KNN, K_COUNT
+	K_COMPOSITE_FWD, K_COMPOSITE_BWD, K_PREPROCESS_BWD, K_MARK_VISIBLE, K_MEMSET, K_MEMCPY, K_KNN, K_FOOTPRINT, K_COUNT
 };
 extern bool g_timing_on;
 void prof_mark(int id, cudaStream_t st, bool begin);
@@ -143,12 +144,16 @@ int launch_sort_pairs(int64_t n, const uint64_t* keys_a, const uint32_t* vals_a,
 int launch_gather_ranges(const gs2d_settings& s, const GeomState& g, const uint64_t* keys_sorted,
                          const uint32_t* point_list, float* instances, uint32_t* ranges, int64_t I,
                          cudaStream_t st);
+int launch_footprint(const gs2d_settings& s, const float* instances, const uint64_t* keys_sorted,
+                     uint32_t* hit_inst, int64_t I, cudaStream_t st);
+int launch_footprint_audit(const gs2d_settings& s, const float* instances, const uint64_t* keys_sorted,
+                           const uint32_t* hit_inst, int64_t I, unsigned long long* counts, cudaStream_t st);
 int launch_composite_forward(const gs2d_settings& s, const gs2d_inputs& in, const ImageState& im,
-                             const float* instances, float* out_color, float* out_others,
-                             cudaStream_t st);
+                             const float* instances, const uint32_t* hit_inst, float* out_color,
+                             float* out_others, cudaStream_t st);
 int launch_composite_backward(const gs2d_settings& s, const gs2d_inputs& in, const ImageState& im,
-                              const float* instances, const float* dL_dcolor, const float* dL_dothers,
-                              float* grad_rows, cudaStream_t st);
+                              const float* instances, const uint32_t* hit_inst, const float* dL_dcolor,
+                              const float* dL_dothers, float* grad_rows, cudaStream_t st);
 int launch_preprocess_backward(const gs2d_settings& s, const gs2d_inputs& in, const GeomState& g,
                                const int32_t* radii, const float* grad_rows, const gs2d_grads& out,
                                cudaStream_t st);

@@ -328,7 +328,12 @@ composite_backward_kernel(int W, int H, unsigned gx, const uint2* __restrict__ r
 			const int mine = g0 + lane;
 			bool want = false;
 			if (mine < cnt && (uint32_t)(q0 + mine) < wmax)
-				want = (__float_as_uint(recs[mine * 5 + 3].w) >> warp) & 1u;
+			{
+				const uint32_t bw = __float_as_uint(recs[mine * 5 + 3].w);
+				const int bx0 = (warp & 1) * 8, by0 = (warp >> 1) * 4;
+				want = ((bw >> 16) & 1u) && (int)(bw & 15) <= bx0 + 7 && (int)((bw >> 8) & 15) >= bx0 &&
+				       (int)((bw >> 4) & 15) <= by0 + 3 && (int)((bw >> 12) & 15) >= by0;
+			}
 			uint32_t bal = __ballot_sync(0xffffffffu, want);
 			while (bal) {
 				const int jl = 31 - __clz(bal);
@@ -357,8 +362,8 @@ composite_backward_kernel(int W, int H, unsigned gx, const uint2* __restrict__ r
 }  // namespace
 
 int launch_composite_backward(const gs2d_settings& s, const gs2d_inputs& in, const ImageState& im,
-                              const float* instances, const float* dL_dcolor, const float* dL_dothers,
-                              float* grad_rows, cudaStream_t st)
+                              const float* instances, const uint32_t* hit_inst, const float* dL_dcolor,
+                              const float* dL_dothers, float* grad_rows, cudaStream_t st)
 {
 	const int W = s.image_width, H = s.image_height;
 	const unsigned gx = (W + TILE - 1) / TILE, gy = (H + TILE - 1) / TILE;

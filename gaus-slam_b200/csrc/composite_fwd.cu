@@ -3,21 +3,21 @@
 // Replaces FORWARD::render / renderCUDA<3> (CR/forward.cu:258-467): ray-splat intersection,
 // low-pass filter, alpha, early ray termination, surface-aware (SA) depth or 2DGS distortion,
 // normals, median depth.  The per-(pixel, instance) arithmetic keeps the reference's operation
-// order, so a pixel's result is the same sequence of fp32 operations; what changes is how the
-// work is fed:
-//   * one CTA per 16x16 tile, each warp owns an 8x4 pixel block;
-//   * the tile's instance records (80 B each, already in sorted order and contiguous in HBM)
-//     are staged with one TMA bulk copy per 128-instance batch into a two-stage shared-memory
-//     ring guarded by mbarriers, so the copy of batch b+1 overlaps the math of batch b;
-//   * every record carries an 8-bit block mask (which 8x4 blocks its >= 1/255-alpha footprint can
-//     touch); each warp ballots 32 masks at a time and only visits the instances whose bit is
-//     set -- a skipped instance provably changes no pixel state, so results are unchanged;
-//   * a warp whose 32 pixels have all terminated stops evaluating; the CTA stops staging when
-//     all 256 have.
-// Bound by FP32 issue + MUFU (exp, reciprocal) on the surviving pairs; HBM traffic is
-// 80 B per instance + 68 B per pixel.
+// order, so a pixel's result is the same sequence of fp32 operations (images are bit-identical to
+// the reference build).  What changes is which pairs are visited and how the data is fed:
+//   * one CTA per 16x16 tile, one thread per pixel, warp k owns tile rows 2k and 2k+1;
+//   * the tile's instance records (80 B each, sorted, contiguous in HBM) and their footprint masks
+//     (32 B each, footprint.cu) are staged by TMA bulk copies, 128 instances per batch, into a
+//     two-stage shared-memory ring guarded by mbarriers: batch b+1 lands while batch b is blended;
+//   * per batch the instance-major footprint masks are transposed into per-PIXEL hit words with warp
+//     ballots (registers only: word k of a mask is exactly warp k's 32 pixels), and every pixel thread
+//     then walks only ITS OWN set bits in depth order.  A pixel visits ~17 instances per tile instead of ~250; lanes of a
+//     warp run independent lists (the trip count of a warp is the longest list among its 32 pixels);
+//   * a pixel stops at T < 1e-4 like the reference; the CTA stops staging when all 256 have.
+// Bound by FP32 issue + MUFU on the visited pairs; HBM traffic is 112 B per instance + 68 B per pixel.
 #include "common.cuh"
 #include "tma.cuh"
+#include "pair.cuh"
 
 namespace gs2d {
 
@@ -40,31 +40,10 @@ template <bool USE_SA>
 __device__ __forceinline__ void eval_pair(const float4* __restrict__ rec, float pxf, float pyf,
                                           uint32_t contributor, PixelFwd& px, bool& done)
 {
-	const float4 r0 = rec[0], r1 = rec[1], r2 = rec[2];
-	const float3 Tu = make_float3(r0.x, r0.y, r0.z);
-	const float3 Tv = make_float3(r1.x, r1.y, r1.z);
-	const float3 Tw = make_float3(r2.x, r2.y, r2.z);
-	const float2 xy = make_float2(r0.w, r1.w);
-	const float opa = r2.w;
-
-	// two homogeneous planes through the pixel, intersected with the splat plane
-	const float3 k = make_float3(pxf * Tw.x - Tu.x, pxf * Tw.y - Tu.y, pxf * Tw.z - Tu.z);
-	const float3 l = make_float3(pyf * Tw.x - Tv.x, pyf * Tw.y - Tv.y, pyf * Tw.z - Tv.z);
-	const float3 p = make_float3(k.y * l.z - k.z * l.y, k.z * l.x - k.x * l.z, k.x * l.y - k.y * l.x);
-	if (p.z == 0.0) return;
-	const float2 s = make_float2(p.x / p.z, p.y / p.z);
-	const float rho3d = (s.x * s.x + s.y * s.y);
-	const float2 d = make_float2(xy.x - pxf, xy.y - pyf);
-	const float rho2d = GS2D_FILTER_INV_SQUARE * (d.x * d.x + d.y * d.y);
-
-	const float rho = fminf(rho3d, rho2d);
-	float depth = (rho3d <= rho2d) ? (s.x * Tw.x + s.y * Tw.y) + Tw.z : Tw.z;
-	if (depth < GS2D_NEAR) return;
-
-	const float power = -0.5f * rho;
-	if (power > 0.0f) return;
-	const float alpha = fminf(0.99f, opa * expf(power));
-	if (alpha < 1.0f / 255.0f) return;
+	PairFront f;
+	if (!pair_front(rec[0], rec[1], rec[2], pxf, pyf, f)) return;
+	const float alpha = f.alpha;
+	float depth = f.depth;
 	const float test_T = px.T * (1 - alpha);
 	if (test_T < 0.0001f) {
 		done = true;
@@ -105,19 +84,21 @@ __device__ __forceinline__ void eval_pair(const float4* __restrict__ rec, float 
 template <bool USE_SA>
 __global__ void __launch_bounds__(256)
 composite_forward_kernel(int W, int H, unsigned gx, const uint2* __restrict__ ranges,
-                         const float4* __restrict__ instances, const float* __restrict__ bg,
-                         float* __restrict__ final_T, uint32_t* __restrict__ n_contrib,
-                         float* __restrict__ median_depth_out, float* __restrict__ depth_std_out,
-                         float* __restrict__ out_color, float* __restrict__ out_others)
+                         const float4* __restrict__ instances, const uint32_t* __restrict__ hit_inst,
+                         const float* __restrict__ bg, float* __restrict__ final_T,
+                         uint32_t* __restrict__ n_contrib, float* __restrict__ median_depth_out,
+                         float* __restrict__ depth_std_out, float* __restrict__ out_color,
+                         float* __restrict__ out_others)
 {
 	__shared__ __align__(128) float4 s_rec[FWD_STAGES][FWD_BATCH * 5];
+	__shared__ __align__(128) uint32_t s_mask[FWD_STAGES][FWD_BATCH * 8];
 	__shared__ __align__(8) uint64_t s_bar[FWD_STAGES];
 
 	const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 	const unsigned tile = blockIdx.x;
 	const unsigned tx = tile % gx, ty = tile / gx;
-	const unsigned pix_x = tx * TILE + (warp & 1) * 8 + (lane & 7);
-	const unsigned pix_y = ty * TILE + (warp >> 1) * 4 + (lane >> 3);
+	const unsigned pix_x = tx * TILE + (tid & 15);       // thread t <-> tile pixel (t & 15, t >> 4), pair.cuh
+	const unsigned pix_y = ty * TILE + (tid >> 4);
 	const bool inside = pix_x < (unsigned)W && pix_y < (unsigned)H;
 	const float pxf = (float)pix_x, pyf = (float)pix_y;
 
@@ -130,12 +111,15 @@ composite_forward_kernel(int W, int H, unsigned gx, const uint2* __restrict__ ra
 		mbar_fence_init();
 	}
 	__syncthreads();
-	const float4* tile_src = instances + 5 * (size_t)range.x;
-	if (tid == 0 && nb > 0) {
-		const uint32_t bytes = (uint32_t)min(n, FWD_BATCH) * 80u;
-		mbar_arrive_expect_tx(&s_bar[0], bytes);
-		tma_load_1d(&s_rec[0][0], tile_src, bytes, &s_bar[0]);
-	}
+	const float4* tile_rec = instances + 5 * (size_t)range.x;
+	const uint32_t* tile_mask = hit_inst + 8 * (size_t)range.x;
+	auto issue = [&](int b, int stage) {
+		const uint32_t cnt = (uint32_t)min(n - b * FWD_BATCH, FWD_BATCH);
+		mbar_arrive_expect_tx(&s_bar[stage], cnt * (80u + 32u));
+		tma_load_1d(&s_rec[stage][0], tile_rec + 5 * (size_t)b * FWD_BATCH, cnt * 80u, &s_bar[stage]);
+		tma_load_1d(&s_mask[stage][0], tile_mask + 8 * (size_t)b * FWD_BATCH, cnt * 32u, &s_bar[stage]);
+	};
+	if (tid == 0 && nb > 0) issue(0, 0);
 
 	PixelFwd px;
 	bool done = !inside;
@@ -143,34 +127,46 @@ composite_forward_kernel(int W, int H, unsigned gx, const uint2* __restrict__ ra
 	for (int b = 0; b < nb; b++) {
 		const int stage = b & 1;
 		const uint32_t parity = (uint32_t)(b >> 1) & 1u;
-		// everyone is finished with the other stage (batch b-1); also the CTA-wide exit vote
+		// everyone is finished with batch b-1 (its stage and s_hit may be reused); CTA-wide exit vote
 		const int num_done = __syncthreads_count(done);
 		if (num_done == TILE_PIXELS) {
 			mbar_wait(&s_bar[stage], parity);   // do not exit with a bulk copy in flight
 			break;
 		}
-		if (tid == 0 && b + 1 < nb) {
-			const int cnt = min(n - (b + 1) * FWD_BATCH, FWD_BATCH);
-			const uint32_t bytes = (uint32_t)cnt * 80u;
-			mbar_arrive_expect_tx(&s_bar[stage ^ 1], bytes);
-			tma_load_1d(&s_rec[stage ^ 1][0], tile_src + 5 * (size_t)(b + 1) * FWD_BATCH, bytes, &s_bar[stage ^ 1]);
-		}
-		mbar_wait(&s_bar[stage], parity);
+		if (tid == 0 && b + 1 < nb) issue(b + 1, stage ^ 1);
+		if (warp == 0) mbar_wait(&s_bar[stage], parity);
+		__syncthreads();   // warp 0 observed the copy; the barrier publishes it to the other warps
 
-		if (__all_sync(0xffffffffu, done)) continue;
 		const int cnt = min(n - b * FWD_BATCH, FWD_BATCH);
 		const float4* recs = &s_rec[stage][0];
-		for (int g = 0; g < cnt; g += 32) {
-			const int mine = g + lane;
-			bool want = false;
-			if (mine < cnt) want = (__float_as_uint(recs[mine * 5 + 3].w) >> warp) & 1u;
-			uint32_t bal = __ballot_sync(0xffffffffu, want);
-			while (bal) {
-				const int j = g + (__ffs(bal) - 1);
-				bal &= bal - 1;
-				if (!done) eval_pair<USE_SA>(recs + j * 5, pxf, pyf, (uint32_t)(b * FWD_BATCH + j + 1), px, done);
+		const uint32_t* masks = &s_mask[stage][0];
+		// Transpose in registers: word `warp` of instance j holds this warp's 32 pixels; 32 ballots turn the
+		// words of 32 instances into one hit word per pixel (bit j <-> instance g*32 + j).
+		uint32_t hits[FWD_BATCH / 32];
+#pragma unroll
+		for (int g = 0; g < FWD_BATCH / 32; g++) {
+			const int j = g * 32 + lane;
+			const uint32_t mine = j < cnt ? masks[j * 8 + warp] : 0u;
+			uint32_t h = 0;
+			if (__any_sync(0xffffffffu, mine != 0u)) {
+#pragma unroll
+				for (int bit = 0; bit < 32; bit++) {
+					const uint32_t v = __ballot_sync(0xffffffffu, (mine >> bit) & 1u);
+					if (lane == bit) h = v;
+				}
 			}
-			if (__all_sync(0xffffffffu, done)) break;
+			hits[g] = h;
+		}
+
+		// every pixel walks its own hits, front to back
+#pragma unroll
+		for (int g = 0; g < FWD_BATCH / 32; g++) {
+			uint32_t m = hits[g];
+			while (m && !done) {
+				const int j = g * 32 + (__ffs(m) - 1);
+				m &= m - 1;
+				eval_pair<USE_SA>(recs + j * 5, pxf, pyf, (uint32_t)(b * FWD_BATCH + j + 1), px, done);
+			}
 		}
 	}
 
@@ -205,7 +201,8 @@ composite_forward_kernel(int W, int H, unsigned gx, const uint2* __restrict__ ra
 }  // namespace
 
 int launch_composite_forward(const gs2d_settings& s, const gs2d_inputs& in, const ImageState& im,
-                             const float* instances, float* out_color, float* out_others, cudaStream_t st)
+                             const float* instances, const uint32_t* hit_inst, float* out_color,
+                             float* out_others, cudaStream_t st)
 {
 	const int W = s.image_width, H = s.image_height;
 	const unsigned gx = (W + TILE - 1) / TILE, gy = (H + TILE - 1) / TILE;
@@ -213,11 +210,11 @@ int launch_composite_forward(const gs2d_settings& s, const gs2d_inputs& in, cons
 	ProfScope ps(K_COMPOSITE_FWD, st);
 	if (s.use_sa)
 		composite_forward_kernel<true><<<gx * gy, 256, 0, st>>>(
-			W, H, gx, (const uint2*)im.ranges, (const float4*)instances, in.background, im.final_T,
+			W, H, gx, (const uint2*)im.ranges, (const float4*)instances, hit_inst, in.background, im.final_T,
 			im.n_contrib, im.median_depth, im.depth_std, out_color, out_others);
 	else
 		composite_forward_kernel<false><<<gx * gy, 256, 0, st>>>(
-			W, H, gx, (const uint2*)im.ranges, (const float4*)instances, in.background, im.final_T,
+			W, H, gx, (const uint2*)im.ranges, (const float4*)instances, hit_inst, in.background, im.final_T,
 			im.n_contrib, im.median_depth, im.depth_std, out_color, out_others);
 	count_launch();
 	GS2D_CUDA_OK(cudaGetLastError());

@@ -1,0 +1,107 @@
+// pair.cuh -- the per-(pixel, instance) ray-splat evaluation shared by the footprint, forward and
+// backward compositing kernels.
+//
+// pair_front() is the first half of the reference's inner loop body (CR/forward.cu:355-386,
+// CR/backward.cu:283-316): intersect the two pixel planes with the splat plane, low-pass filter,
+// depth, Gaussian weight, alpha, and the four "skip this instance" tests.  The expressions are kept
+// in the reference's form so that nvcc fuses them the same way (the forward images are bit-identical
+// to the reference build; tests/test_gpu_parity.py).
+#pragma once
+#include "common.cuh"
+
+namespace gs2d {
+
+// In-tile footprint box of an instance, packed in record word REC_MASK:
+//   bits 0..3 x0, 4..7 y0, 8..11 x1, 12..15 y1 (tile-local pixel coordinates, inclusive), bit 16 valid.
+struct TileBox {
+	int x0, y0, w, h, area;
+};
+__device__ __forceinline__ TileBox unpack_box(uint32_t word)
+{
+	TileBox b;
+	b.x0 = word & 15; b.y0 = (word >> 4) & 15;
+	b.w = (int)((word >> 8) & 15) - b.x0 + 1;
+	b.h = (int)((word >> 12) & 15) - b.y0 + 1;
+	b.area = (word >> 16) & 1 ? b.w * b.h : 0;
+	return b;
+}
+// ceil(65536 / w) for w = 1..16: floor(idx / w) == (idx * kInvW[w]) >> 16 for idx < 256.
+__device__ __constant__ const uint32_t kInvW[17] = {0,     65536, 32768, 21846, 16384, 13108, 10923, 9363, 8192,
+                                                    7282,  6554,  5958,  5462,  5042,  4682,  4370, 4096};
+// idx -> tile-local pixel inside a box (row-major inside the box)
+__device__ __forceinline__ void box_xy(const TileBox& b, int idx, int& lx, int& ly)
+{
+	const uint32_t q = ((uint32_t)idx * kInvW[b.w]) >> 16;
+	lx = b.x0 + idx - (int)q * b.w;
+	ly = b.y0 + (int)q;
+}
+// Compositing CTAs own one pixel per thread in tile row-major order: thread t <-> pixel (t & 15, t >> 4), so
+// warp k owns rows 2k and 2k+1.  Footprint masks use the same order: word k, bit (ly & 1) * 16 + lx.
+__device__ __forceinline__ int pixel_thread(int lx, int ly) { return (ly << 4) | lx; }
+
+struct PairFront {
+	float3 k, l;      // pixel planes in splat space
+	float pz;         // p.z of k x l
+	float2 s;         // intersection in splat coordinates
+	float2 d;         // centre - pixel
+	float rho3d, rho2d;
+	float depth;      // ray depth of the intersection (or of the centre for the 2D filter branch)
+	float G;          // exp(-rho/2)
+	float alpha;
+};
+
+// Returns false when the reference `continue`s (no contribution possible); fills f otherwise.
+// ALPHA_MIN / DEPTH_MIN let the footprint kernel use slightly relaxed thresholds (superset).
+__device__ __forceinline__ bool pair_front(const float4 r0, const float4 r1, const float4 r2, const float pxf,
+                                           const float pyf, PairFront& f, const float alpha_min = 1.0f / 255.0f,
+                                           const float depth_min = GS2D_NEAR)
+{
+	const float3 Tu = make_float3(r0.x, r0.y, r0.z);
+	const float3 Tv = make_float3(r1.x, r1.y, r1.z);
+	const float3 Tw = make_float3(r2.x, r2.y, r2.z);
+	const float2 xy = make_float2(r0.w, r1.w);
+	const float opa = r2.w;
+	f.k = make_float3(pxf * Tw.x - Tu.x, pxf * Tw.y - Tu.y, pxf * Tw.z - Tu.z);
+	f.l = make_float3(pyf * Tw.x - Tv.x, pyf * Tw.y - Tv.y, pyf * Tw.z - Tv.z);
+	const float3 p = make_float3(f.k.y * f.l.z - f.k.z * f.l.y, f.k.z * f.l.x - f.k.x * f.l.z,
+	                             f.k.x * f.l.y - f.k.y * f.l.x);
+	f.pz = p.z;
+	if (p.z == 0.0) return false;
+	f.s = make_float2(p.x / p.z, p.y / p.z);
+	f.rho3d = (f.s.x * f.s.x + f.s.y * f.s.y);
+	f.d = make_float2(xy.x - pxf, xy.y - pyf);
+	f.rho2d = GS2D_FILTER_INV_SQUARE * (f.d.x * f.d.x + f.d.y * f.d.y);
+	const float rho = fminf(f.rho3d, f.rho2d);
+	f.depth = (f.rho3d <= f.rho2d) ? (f.s.x * Tw.x + f.s.y * Tw.y) + Tw.z : Tw.z;
+	if (f.depth < depth_min) return false;
+	const float power = -0.5f * rho;
+	if (power > 0.0f) return false;
+	f.G = expf(power);
+	f.alpha = fminf(0.99f, opa * f.G);
+	if (f.alpha < alpha_min) return false;
+	return true;
+}
+
+// Same tests with approximate reciprocal / exp2 (for the footprint kernel only, which compensates with
+// relaxed thresholds): true when the pair may contribute.
+__device__ __forceinline__ bool pair_may_contribute(const float4 r0, const float4 r1, const float4 r2, const float pxf,
+                                                    const float pyf, const float alpha_min, const float depth_min)
+{
+	const float3 k = make_float3(pxf * r2.x - r0.x, pxf * r2.y - r0.y, pxf * r2.z - r0.z);
+	const float3 l = make_float3(pyf * r2.x - r1.x, pyf * r2.y - r1.y, pyf * r2.z - r1.z);
+	const float3 p = make_float3(k.y * l.z - k.z * l.y, k.z * l.x - k.x * l.z, k.x * l.y - k.y * l.x);
+	// p.z == 0 is not an early-out here: inf / NaN fall through fminf to the 2D-filter branch (superset)
+	const float inv = __frcp_rn(p.z);
+	const float sx = p.x * inv, sy = p.y * inv;
+	const float rho3d = sx * sx + sy * sy;
+	const float dx = r0.w - pxf, dy = r1.w - pyf;
+	const float rho2d = GS2D_FILTER_INV_SQUARE * (dx * dx + dy * dy);
+	const float depth = (rho3d <= rho2d) ? (sx * r2.x + sy * r2.y) + r2.z : r2.z;
+	if (depth < depth_min) return false;
+	const float rho = fminf(rho3d, rho2d);
+	if (rho < 0.0f) return false;
+	const float alpha = fminf(0.99f, r2.w * exp2f(-0.72134752f * rho));
+	return !(alpha < alpha_min);
+}
+
+}  // namespace gs2d

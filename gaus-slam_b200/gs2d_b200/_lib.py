@@ -72,6 +72,8 @@ PROTOTYPES = {
     "gs2d_dist2_scratch_bytes": (C.c_size_t, [C.c_int32]),
     "gs2d_dist2": (C.c_int, [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "gs2d_state_view_get": (C.c_int, [C.POINTER(Settings), C.POINTER(Buffers), C.c_int64, C.POINTER(StateView)]),
+    "gs2d_footprint_audit": (C.c_int, [C.POINTER(Settings), C.POINTER(Buffers), C.c_int64, C.POINTER(C.c_uint64),
+                                       C.c_void_p]),
     "gs2d_sort_scratch_bytes": (C.c_size_t, [C.c_int64]),
     "gs2d_sort_pairs": (C.c_int, [C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32,
                                   C.c_void_p, C.c_void_p]),

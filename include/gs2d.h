@@ -182,6 +182,13 @@ typedef struct gs2d_state_view {
 int gs2d_state_view_get(const gs2d_settings* s, const gs2d_buffers* buffers,
                         int64_t num_rendered, gs2d_state_view* out);
 
+/* Parity accessor for the footprint stage (csrc/footprint.cu): re-evaluates the reference's per-pixel
+ * contribution tests for every (instance, tile pixel) pair of the last forward and compares them with the
+ * footprint masks.  counts_host[0] = pairs that pass the tests, [1] = mask bits set, [2] = passing pairs
+ * whose bit is NOT set (must be 0: the masks are a superset).  Synchronises the stream. */
+int gs2d_footprint_audit(const gs2d_settings* s, const gs2d_buffers* buffers, int64_t num_rendered,
+                         uint64_t* counts_host, void* stream);
+
 /* Stand-alone stable LSD radix sort of (u64 key, u32 value) pairs on bits [0, end_bit):
  * the hand-written onesweep that replaces cub::DeviceRadixSort::SortPairs
  * (CR/rasterizer_impl.cu:309-314).  scratch: gs2d_sort_scratch_bytes(n). */

@@ -67,6 +67,9 @@ def run_ours(case, dev="cuda:0", debug=True, backward=True):
     L.check(lib.gs2d_state_view_get(C.byref(s), C.byref(bufs), n, C.byref(sv)), "state_view")
     tiles = ((W + 15) // 16) * ((H + 15) // 16)
     i32, f32 = torch.int32, torch.float32
+    counts = (C.c_uint64 * 3)()
+    L.check(lib.gs2d_footprint_audit(C.byref(s), C.byref(bufs), n, counts, None), "footprint_audit")
+    out["footprint_audit"] = np.array(list(counts), dtype=np.int64)   # [exact hits, mask bits, missed hits]
     if P:
         splat = _raw(sv.splat, (P, 20), f32, dev).cpu().numpy()
         out.update(

@@ -31,6 +31,8 @@ def main():
                      str([(tuple(i), int(ours['n_contrib'][tuple(i)]), int(ref['n_contrib'][tuple(i)])) for i in idx]))
         gr = {k: compare.grad_rel(ours["grad_" + k], ref["grad_" + k]) for k in compare.GRADS
               if ref["grad_" + k].size}
+        f += [] if int(ours["footprint_audit"][2]) == 0 else [f"footprint audit: {ours['footprint_audit']}"]
+        print(f"  footprint audit (exact hits, mask bits, missed): {ours['footprint_audit']}")
         print(f"[{name}] I={int(ref['num_rendered'])} visible={int((ref['radii'] > 0).sum())} "
               f"{'OK' if not f else 'FAIL'}  grad rel: " + " ".join(f"{k}={v:.1e}" for k, v in gr.items()))
         for x in f:

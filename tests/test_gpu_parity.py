@@ -47,6 +47,7 @@ def test_against_golden(name):
     fails += compare.check_images(ours, ref, atol=compare.IMG_ATOL)
     fails += compare.check_grads(ours, ref, rtol=compare.GRAD_RTOL)
     assert not fails, "\n".join(fails)
+    assert int(ours["footprint_audit"][2]) == 0, f"footprint masks miss contributing pairs: {ours['footprint_audit']}"
     # the production path (debug=False: no per-stage synchronisation, no key snapshot) gives the same bits
     fast = gpu_run.run_ours(case, debug=False)
     assert not compare.check_images(fast, ours, exact=True)
@@ -92,6 +93,9 @@ def test_against_compiled_reference_500k():
     fails = compare.check_binning(ours, ref, exact_float_state=True)
     fails += compare.check_images(ours, ref) + compare.check_grads(ours, ref)
     assert not fails, "\n".join(fails)
+    hits, bits, missed = (int(x) for x in ours["footprint_audit"])
+    assert missed == 0 and bits >= hits
+    assert bits <= 1.25 * hits, f"footprint masks too loose: {bits} bits for {hits} contributing pairs"
 
 
 def test_full_size_properties():
@@ -161,3 +165,27 @@ def test_dist2_large_vs_bruteforce():
     d.fill_diagonal_(float("inf"))
     want = d.topk(3, dim=1, largest=False).values.mean(dim=1).float()
     assert torch.allclose(got, want, rtol=1e-4, atol=1e-9)
+
+
+@pytest.mark.parametrize("P,size,scale_mult,view,seed", [
+    (200_000, (1200, 680), 1.0, 7, 11),     # oblique view of the room: grazing walls
+    (60_000, (640, 360), 4.0, 2, 12),       # big splats, many per tile
+    (50_000, (1752, 1168), 0.5, 5, 13),     # ScanNet++-shaped, small splats (low-pass filter dominated)
+    (20_000, (333, 211), 12.0, 1, 14),      # huge splats covering many tiles, ragged image
+])
+def test_footprint_masks_are_a_superset(P, size, scale_mult, view, seed):
+    """The closed-form footprint rows must contain every pair that passes the reference's per-pixel tests."""
+    import gpu_run
+    from gs2d_b200 import scene
+    W, H = size
+    intr = dict(W=W, H=H, fx=0.5 * W, fy=0.5 * W, cx=(W - 1) / 2, cy=(H - 1) / 2)
+    sc = scene.room_scene(P, intr, seed=seed, scale_mult=scale_mult)
+    cam = scene.view_sweep(8, intr, seed=seed)[view]
+    gc, go = scene.image_grads(W, H, seed=seed)
+    case = dict(W=W, H=H, tanfovx=np.float32(cam.tanfovx), tanfovy=np.float32(cam.tanfovy),
+                viewmatrix=cam.viewmatrix.reshape(16), projmatrix=cam.projmatrix.reshape(16), campos=cam.campos,
+                bg=np.zeros(3, np.float32), use_sa=True, scale_modifier=np.float32(1.0), sh_degree=0, shs=None,
+                transMat=None, dL_dcolor=gc, dL_dothers=go, **sc)
+    out = gpu_run.run_ours(case, debug=False, backward=False)
+    hits, bits, missed = (int(x) for x in out["footprint_audit"])
+    assert hits > 0 and missed == 0, (hits, bits, missed)
