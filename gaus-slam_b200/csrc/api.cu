@@ -271,10 +271,7 @@ int gs2d_backward(const gs2d_settings* s, const gs2d_inputs* in, const gs2d_buff
 	if (I > 0) {
 		if (!scratch || !buffers->binning) return GS2D_ERR_INVALID;
 		BinningState b = BinningState::carve(buffers->binning, (size_t)I, nullptr);
-		{
-			ProfScope ps(K_MEMSET, st);
-			GS2D_CUDA_OK(cudaMemsetAsync(rows, 0, (size_t)I * GRAD_WORDS * sizeof(float), st));
-		}
+		// no zero-fill: composite_backward writes every instance row exactly once
 		GS2D_TRY(launch_composite_backward(*s, *in, im, b.instances, b.hit_inst, dL_dout_color, dL_dout_others, rows, st));
 		GS2D_TRY(debug_sync(*s, st));
 	}

@@ -1,21 +1,30 @@
 // composite_bwd.cu -- per-tile back-to-front re-traversal (backward of the compositing).
 //
 // Replaces BACKWARD::render / renderCUDA<3> (CR/backward.cu:143-463).  Same per-(pixel, instance)
-// gradient algebra (including the reference's deliberate non-analytic parts: SA confidence from
-// the *final* per-pixel statistics, opacity gradient through the clamped alpha), different
-// data flow:
-//   * instance records staged by TMA bulk copies, newest-first, two-stage mbarrier ring;
-//   * per-warp ballot over the records' 8-bit block masks, so a warp only re-evaluates
-//     instances that can touch its 8x4 pixels, and only those not behind the warp's deepest
-//     last contributor;
-//   * the 18 per-pair gradient terms are summed across the warp with a shuffle reduce-scatter
-//     (21 SHFL) and leave the SM as ONE 18-lane RED per (warp, instance) into the instance's own
-//     80-byte gradient row -- the reference issues 16 scattered atomicAdd per contributing
-//     *pixel* (CR/backward.cu:343, :396, :441-449, :454-456, :460).  Rows are indexed by the
-//     instance's position in surfel-major (unsorted) order, so the per-surfel reduction in
-//     preprocess_bwd.cu reads contiguous rows and needs no atomics at all.
+// gradient algebra (including the reference's deliberate non-analytic parts: SA confidence from the
+// *final* per-pixel statistics, opacity gradient through the clamped alpha), but the work is split by
+// what it depends on, so that every lane does useful work and nothing is reduced with atomics:
+//
+//   phase A (per PIXEL, sequential back to front, lanes = 32 pixels of a warp):
+//       the order-dependent part only -- transmittance T = T / (1 - alpha), the suffix recurrences for
+//       colour / depth / alpha / normal / dL_dT (CR/backward.cu:323-410).  Every pixel walks ITS OWN hit
+//       list (footprint masks transposed with ballots, as in the forward), i.e. ~17 instances per tile
+//       instead of ~250, and leaves three scalars per pair -- dL/dalpha, dL/dz, w = alpha * T -- plus its
+//       pixel id in the pair's 16-byte slot in shared memory.  Slots are laid out per instance
+//       (slot = instance base + rank of the pixel inside the instance's mask).
+//   phase B (per INSTANCE, lanes = that instance's contributing pixels, half a warp per instance):
+//       the geometric chain rule dL/d{Tu,Tv,Tw}, dL/dmean2D, dL/dopacity, dL/dnormal, dL/dcolour
+//       (CR/backward.cu:343, :396, :412-460) from the slot + the instance record, summed over the
+//       instance's pixels with 19 shuffles, and written as ONE plain 72-byte store into the instance's own
+//       gradient row: the reference issues 16 global atomicAdd per contributing (pixel, instance) pair;
+//       here a row is written exactly once, so no atomics and no zero-fill of the rows are needed.
+//
+// Instances come in batches of 128 (records + masks staged by TMA, two-stage mbarrier ring); a batch is
+// cut into sub-ranges whose pair count fits the slot buffer.  Rows are indexed by the instance's position
+// in surfel-major (unsorted) order, so preprocess_bwd.cu reads each surfel's rows contiguously.
 #include "common.cuh"
 #include "tma.cuh"
+#include "pair.cuh"
 
 namespace gs2d {
 
@@ -23,6 +32,7 @@ namespace {
 
 constexpr int BWD_BATCH = 128;
 constexpr int BWD_STAGES = 2;
+constexpr int BWD_CAP = 2304;     // pair slots (16 B each) per sub-range; >= 256 = one full-tile instance
 
 struct PixelConst {
 	float T_final, final_A, final_D, final_D2;
@@ -44,35 +54,29 @@ struct PixelBwd {
 	float last_dL_dT = 0.f;
 };
 
-// Evaluates one (pixel, instance) pair; on contribution fills g[0..17] and returns true.
+struct BwdSmem {
+	float4 rec[BWD_STAGES][BWD_BATCH * 5];
+	uint32_t mask[BWD_STAGES][BWD_BATCH * 8];
+	float4 slot[BWD_CAP];
+	float pix[6][TILE_PIXELS];          // dL_dpix (3), dL_dnormal (3) per pixel, for phase B
+	uint2 pref[BWD_BATCH];              // 8 packed bytes: hits of the instance in mask words 0..k-1
+	uint32_t base[BWD_BATCH + 1];       // exclusive prefix of the instances' hit counts within the batch
+	uint32_t wsum[8];
+	uint32_t max_last[8];
+	uint64_t bar[BWD_STAGES];
+};
+
+// Phase A for one (pixel, instance) pair: CR/backward.cu:283-410 minus the geometric chain.
+// Returns false when the pair does not contribute (the reference's `continue`s).
 template <bool USE_SA>
-__device__ __forceinline__ bool grad_pair(const float4* __restrict__ rec, float pxf, float pyf, uint32_t q,
-                                          const PixelConst& pc, PixelBwd& st, float (&g)[GR_USED])
+__device__ __forceinline__ bool pixel_step(const float4* __restrict__ rec, float pxf, float pyf, uint32_t q,
+                                           const PixelConst& pc, PixelBwd& st, float& dL_dalpha_out,
+                                           float& dL_dz_out, float& w_out)
 {
-	const float4 r0 = rec[0], r1 = rec[1], r2 = rec[2];
-	const float3 Tu = make_float3(r0.x, r0.y, r0.z);
-	const float3 Tv = make_float3(r1.x, r1.y, r1.z);
-	const float3 Tw = make_float3(r2.x, r2.y, r2.z);
-	const float2 xy = make_float2(r0.w, r1.w);
-	const float opa = r2.w;
-
-	const float3 k = make_float3(pxf * Tw.x - Tu.x, pxf * Tw.y - Tu.y, pxf * Tw.z - Tu.z);
-	const float3 l = make_float3(pyf * Tw.x - Tv.x, pyf * Tw.y - Tv.y, pyf * Tw.z - Tv.z);
-	const float3 p = make_float3(k.y * l.z - k.z * l.y, k.z * l.x - k.x * l.z, k.x * l.y - k.y * l.x);
-	if (p.z == 0.0) return false;
-	const float2 s = make_float2(p.x / p.z, p.y / p.z);
-	const float rho3d = (s.x * s.x + s.y * s.y);
-	const float2 d = make_float2(xy.x - pxf, xy.y - pyf);
-	const float rho2d = GS2D_FILTER_INV_SQUARE * (d.x * d.x + d.y * d.y);
-	const float rho = fminf(rho3d, rho2d);
-	float c_d = (rho3d <= rho2d) ? (s.x * Tw.x + s.y * Tw.y) + Tw.z : Tw.z;
-	if (c_d < GS2D_NEAR) return false;
-	const float power = -0.5f * rho;
-	if (power > 0.0f) return false;
-	const float G = expf(power);
-	const float alpha = fminf(0.99f, opa * G);
-	if (alpha < 1.0f / 255.0f) return false;
-
+	PairFront f;
+	if (!pair_front(rec[0], rec[1], rec[2], pxf, pyf, f)) return false;
+	const float alpha = f.alpha;
+	float c_d = f.depth;
 	const float4 r3 = rec[3], r4 = rec[4];
 	st.T = st.T / (1.f - alpha);
 	const float T = st.T;
@@ -88,9 +92,6 @@ __device__ __forceinline__ bool grad_pair(const float4* __restrict__ rec, float 
 	st.acc_c2 = st.last_alpha * st.last_c2 + (1.f - st.last_alpha) * st.acc_c2;
 	st.last_c2 = r4.z;
 	dL_dalpha += (r4.z - st.acc_c2) * pc.dpix2;
-	g[GR_COL + 0] = w * pc.dpix0;
-	g[GR_COL + 1] = w * pc.dpix1;
-	g[GR_COL + 2] = w * pc.dpix2;
 
 	float conf = 1;
 	if (USE_SA) {
@@ -133,116 +134,123 @@ __device__ __forceinline__ bool grad_pair(const float4* __restrict__ rec, float 
 	st.acc_n2 = st.last_alpha * st.last_n2 + (1.f - st.last_alpha) * st.acc_n2;
 	st.last_n2 = r3.z;
 	dL_dalpha += (r3.z - st.acc_n2) * pc.dn2;
-	g[GR_NRM + 0] = alpha * T * pc.dn0;
-	g[GR_NRM + 1] = alpha * T * pc.dn1;
-	g[GR_NRM + 2] = alpha * T * pc.dn2;
 
 	dL_dalpha *= T;
 	st.last_alpha = alpha;
 	dL_dalpha += (-pc.T_final / (1.f - alpha)) * pc.bg_dot;
-
-	const float dL_dG = opa * dL_dalpha;
 	dL_dz += conf * alpha * T * pc.dL_ddepth;
 
-	if (rho3d <= rho2d) {
-		const float dL_dsx = dL_dG * -G * s.x + dL_dz * Tw.x;
-		const float dL_dsy = dL_dG * -G * s.y + dL_dz * Tw.y;
-		const float dsx_pz = dL_dsx / p.z;
-		const float dsy_pz = dL_dsy / p.z;
-		const float3 dL_dp = make_float3(dsx_pz, dsy_pz, -(dsx_pz * s.x + dsy_pz * s.y));
+	dL_dalpha_out = dL_dalpha;
+	dL_dz_out = dL_dz;
+	w_out = w;
+	return true;
+}
+
+// Phase B for one (instance, pixel) pair: the geometric chain (CR/backward.cu:343, :396, :412-460).
+// A = dL/dalpha, dz = dL/dz, w = alpha * T from phase A; adds the 18 per-instance terms into g.
+__device__ __forceinline__ void instance_step(const float4 r0, const float4 r1, const float4 r2, float pxf, float pyf,
+                                              float A, float dz, float w, const float* __restrict__ pixc, int pid,
+                                              float (&g)[GR_USED])
+{
+	PairFront f;
+	pair_geom(r0, r1, r2, pxf, pyf, f);
+	const float3 Tw = make_float3(r2.x, r2.y, r2.z);
+	const float opa = r2.w, G = f.G;
+	g[GR_COL + 0] += w * pixc[0 * TILE_PIXELS + pid];
+	g[GR_COL + 1] += w * pixc[1 * TILE_PIXELS + pid];
+	g[GR_COL + 2] += w * pixc[2 * TILE_PIXELS + pid];
+	g[GR_NRM + 0] += w * pixc[3 * TILE_PIXELS + pid];
+	g[GR_NRM + 1] += w * pixc[4 * TILE_PIXELS + pid];
+	g[GR_NRM + 2] += w * pixc[5 * TILE_PIXELS + pid];
+	const float dL_dG = opa * A;
+	if (f.rho3d <= f.rho2d) {
+		const float dL_dsx = dL_dG * -G * f.s.x + dz * Tw.x;
+		const float dL_dsy = dL_dG * -G * f.s.y + dz * Tw.y;
+		const float dsx_pz = dL_dsx / f.pz;
+		const float dsy_pz = dL_dsy / f.pz;
+		const float3 dL_dp = make_float3(dsx_pz, dsy_pz, -(dsx_pz * f.s.x + dsy_pz * f.s.y));
+		const float3 k = f.k, l = f.l;
 		const float3 dL_dk = make_float3(l.y * dL_dp.z - l.z * dL_dp.y, l.z * dL_dp.x - l.x * dL_dp.z,
 		                                 l.x * dL_dp.y - l.y * dL_dp.x);
 		const float3 dL_dl = make_float3(dL_dp.y * k.z - dL_dp.z * k.y, dL_dp.z * k.x - dL_dp.x * k.z,
 		                                 dL_dp.x * k.y - dL_dp.y * k.x);
-		g[0] = -dL_dk.x; g[1] = -dL_dk.y; g[2] = -dL_dk.z;
-		g[3] = -dL_dl.x; g[4] = -dL_dl.y; g[5] = -dL_dl.z;
-		g[6] = pxf * dL_dk.x + pyf * dL_dl.x + dL_dz * s.x;
-		g[7] = pxf * dL_dk.y + pyf * dL_dl.y + dL_dz * s.y;
-		g[8] = pxf * dL_dk.z + pyf * dL_dl.z + dL_dz * 1.0f;
-		g[GR_M2D + 0] = 0.f;
-		g[GR_M2D + 1] = 0.f;
+		g[0] += -dL_dk.x; g[1] += -dL_dk.y; g[2] += -dL_dk.z;
+		g[3] += -dL_dl.x; g[4] += -dL_dl.y; g[5] += -dL_dl.z;
+		g[6] += pxf * dL_dk.x + pyf * dL_dl.x + dz * f.s.x;
+		g[7] += pxf * dL_dk.y + pyf * dL_dl.y + dz * f.s.y;
+		g[8] += pxf * dL_dk.z + pyf * dL_dl.z + dz * 1.0f;
 	} else {
-		const float dG_ddelx = -G * GS2D_FILTER_INV_SQUARE * d.x;
-		const float dG_ddely = -G * GS2D_FILTER_INV_SQUARE * d.y;
-#pragma unroll
-		for (int i = 0; i < 8; i++) g[i] = 0.f;
-		g[8] = dL_dz;
-		g[GR_M2D + 0] = dL_dG * dG_ddelx;
-		g[GR_M2D + 1] = dL_dG * dG_ddely;
+		g[8] += dz;
+		g[GR_M2D + 0] += dL_dG * (-G * GS2D_FILTER_INV_SQUARE * f.d.x);
+		g[GR_M2D + 1] += dL_dG * (-G * GS2D_FILTER_INV_SQUARE * f.d.y);
 	}
-	g[GR_OPA] = G * dL_dalpha;
-	return true;
+	g[GR_OPA] += G * A;
 }
 
-// Sum g[0..17] over the 32 lanes.  On return lane L (L < 16) holds the total of g[L] in `a`,
-// and lanes with bit 4 clear / set hold the totals of g[16] / g[17] in `b`.
-__device__ __forceinline__ void warp_reduce18(float (&g)[GR_USED], int lane, float& a, float& b)
+// Sum g[0..17] over the 16 lanes of each half-warp.  On return lane L of a half holds the total of
+// g[L] in `a`; lanes with bit 3 clear / set hold the totals of g[16] / g[17] in `b`.
+__device__ __forceinline__ void half_reduce18(float (&g)[GR_USED], int lane, float& a, float& b)
 {
-	// values 0..15: recursive halving over lane bits 3..0, then fold the two half-warps
 	{
 		const bool up = lane & 8;
 #pragma unroll
 		for (int i = 0; i < 8; i++) {
-			float send = up ? g[i] : g[i + 8];
-			float keep = up ? g[i + 8] : g[i];
+			const float send = up ? g[i] : g[i + 8];
+			const float keep = up ? g[i + 8] : g[i];
 			g[i] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
 		}
+		const float send = up ? g[16] : g[17];
+		const float keep = up ? g[17] : g[16];
+		g[16] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
 	}
 	{
 		const bool up = lane & 4;
 #pragma unroll
 		for (int i = 0; i < 4; i++) {
-			float send = up ? g[i] : g[i + 4];
-			float keep = up ? g[i + 4] : g[i];
+			const float send = up ? g[i] : g[i + 4];
+			const float keep = up ? g[i + 4] : g[i];
 			g[i] = keep + __shfl_xor_sync(0xffffffffu, send, 4);
 		}
+		g[16] += __shfl_xor_sync(0xffffffffu, g[16], 4);
 	}
 	{
 		const bool up = lane & 2;
 #pragma unroll
 		for (int i = 0; i < 2; i++) {
-			float send = up ? g[i] : g[i + 2];
-			float keep = up ? g[i + 2] : g[i];
+			const float send = up ? g[i] : g[i + 2];
+			const float keep = up ? g[i + 2] : g[i];
 			g[i] = keep + __shfl_xor_sync(0xffffffffu, send, 2);
 		}
+		g[16] += __shfl_xor_sync(0xffffffffu, g[16], 2);
 	}
 	{
 		const bool up = lane & 1;
-		float send = up ? g[0] : g[1];
-		float keep = up ? g[1] : g[0];
+		const float send = up ? g[0] : g[1];
+		const float keep = up ? g[1] : g[0];
 		g[0] = keep + __shfl_xor_sync(0xffffffffu, send, 1);
+		g[16] += __shfl_xor_sync(0xffffffffu, g[16], 1);
 	}
-	a = g[0] + __shfl_xor_sync(0xffffffffu, g[0], 16);
-	// values 16, 17
-	{
-		const bool up = lane & 16;
-		float send = up ? g[16] : g[17];
-		float keep = up ? g[17] : g[16];
-		float v = keep + __shfl_xor_sync(0xffffffffu, send, 16);
-#pragma unroll
-		for (int o = 8; o >= 1; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-		b = v;
-	}
+	a = g[0];
+	b = g[16];
 }
 
 template <bool USE_SA>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, 3)
 composite_backward_kernel(int W, int H, unsigned gx, const uint2* __restrict__ ranges,
-                          const float4* __restrict__ instances, const float* __restrict__ bg,
-                          const float* __restrict__ final_T, const uint32_t* __restrict__ n_contrib,
-                          const float* __restrict__ median_depth, const float* __restrict__ depth_std,
-                          const float* __restrict__ dL_dpix, const float* __restrict__ dL_dothers,
-                          float* __restrict__ grad_rows)
+                          const float4* __restrict__ instances, const uint32_t* __restrict__ hit_inst,
+                          const float* __restrict__ bg, const float* __restrict__ final_T,
+                          const uint32_t* __restrict__ n_contrib, const float* __restrict__ median_depth,
+                          const float* __restrict__ depth_std, const float* __restrict__ dL_dpix,
+                          const float* __restrict__ dL_dothers, float* __restrict__ grad_rows)
 {
-	__shared__ __align__(128) float4 s_rec[BWD_STAGES][BWD_BATCH * 5];
-	__shared__ __align__(8) uint64_t s_bar[BWD_STAGES];
-	__shared__ uint32_t s_max_last[8];
+	extern __shared__ __align__(128) unsigned char smem_raw[];
+	BwdSmem& sm = *reinterpret_cast<BwdSmem*>(smem_raw);
 
 	const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 	const unsigned tile = blockIdx.x;
 	const unsigned tx = tile % gx, ty = tile / gx;
-	const unsigned pix_x = tx * TILE + (warp & 1) * 8 + (lane & 7);
-	const unsigned pix_y = ty * TILE + (warp >> 1) * 4 + (lane >> 3);
+	const unsigned pix_x = tx * TILE + (tid & 15);       // thread t <-> tile pixel (t & 15, t >> 4), pair.cuh
+	const unsigned pix_y = ty * TILE + (tid >> 4);
 	const bool inside = pix_x < (unsigned)W && pix_y < (unsigned)H;
 	const float pxf = (float)pix_x, pyf = (float)pix_y;
 	const size_t HW = (size_t)H * W;
@@ -283,34 +291,47 @@ composite_backward_kernel(int W, int H, unsigned gx, const uint2* __restrict__ r
 		acc += bg[2] * pc.dpix2;
 		pc.bg_dot = acc;
 	}
+	sm.pix[0][tid] = pc.dpix0; sm.pix[1][tid] = pc.dpix1; sm.pix[2][tid] = pc.dpix2;
+	sm.pix[3][tid] = pc.dn0;   sm.pix[4][tid] = pc.dn1;   sm.pix[5][tid] = pc.dn2;
 	PixelBwd st;
 	st.T = pc.T_final;
 
-	// deepest last contributor of the warp / of the tile: nothing behind it is ever visited
+	// deepest last contributor of the tile: nothing behind it is ever visited
 	uint32_t wmax = pc.last_contributor;
 #pragma unroll
 	for (int o = 16; o >= 1; o >>= 1) wmax = max(wmax, __shfl_xor_sync(0xffffffffu, wmax, o));
-	if (lane == 0) s_max_last[warp] = wmax;
+	if (lane == 0) sm.max_last[warp] = wmax;
 	if (tid == 0) {
-		for (int s = 0; s < BWD_STAGES; s++) mbar_init(&s_bar[s], 1);
+		for (int s = 0; s < BWD_STAGES; s++) mbar_init(&sm.bar[s], 1);
 		mbar_fence_init();
 	}
 	__syncthreads();
 	uint32_t bmax = 0;
 #pragma unroll
-	for (int i = 0; i < 8; i++) bmax = max(bmax, s_max_last[i]);
+	for (int i = 0; i < 8; i++) bmax = max(bmax, sm.max_last[i]);
 	const int n_used = min((int)bmax, n);            // instances [0, n_used) can matter
 	const int nb = (n_used + BWD_BATCH - 1) / BWD_BATCH;
-	if (nb == 0) return;
 
-	const float4* tile_src = instances + 5 * (size_t)range.x;
+	const float4* tile_rec = instances + 5 * (size_t)range.x;
+	const uint32_t* tile_mask = hit_inst + 8 * (size_t)range.x;
 	auto issue = [&](int b, int stage) {
-		const int cnt = min(n_used - b * BWD_BATCH, BWD_BATCH);
-		const uint32_t bytes = (uint32_t)cnt * 80u;
-		mbar_arrive_expect_tx(&s_bar[stage], bytes);
-		tma_load_1d(&s_rec[stage][0], tile_src + 5 * (size_t)b * BWD_BATCH, bytes, &s_bar[stage]);
+		const uint32_t cnt = (uint32_t)min(n_used - b * BWD_BATCH, BWD_BATCH);
+		mbar_arrive_expect_tx(&sm.bar[stage], cnt * (80u + 32u));
+		tma_load_1d(&sm.rec[stage][0], tile_rec + 5 * (size_t)b * BWD_BATCH, cnt * 80u, &sm.bar[stage]);
+		tma_load_1d(&sm.mask[stage][0], tile_mask + 8 * (size_t)b * BWD_BATCH, cnt * 32u, &sm.bar[stage]);
 	};
-	if (tid == 0) issue(nb - 1, 0);
+	if (tid == 0 && nb > 0) issue(nb - 1, 0);
+
+	// rows of the instances nobody reaches (behind every pixel's last contributor): zeros
+	for (int q = n_used + (tid >> 2); q < n; q += 64) {
+		const uint32_t row = __float_as_uint(tile_rec[5 * (size_t)q + 4].w);
+		float4* dst = reinterpret_cast<float4*>(grad_rows + (size_t)row * GRAD_WORDS);
+		dst[tid & 3] = make_float4(0.f, 0.f, 0.f, 0.f);
+		if ((tid & 3) == 0) dst[4] = make_float4(0.f, 0.f, 0.f, 0.f);
+	}
+
+	const uint32_t lane_lt = (1u << lane) - 1u;
+	const int hw = tid >> 4, hl = tid & 15;          // half-warp id / lane inside it (phase B)
 
 	for (int it = 0; it < nb; it++) {
 		const int b = nb - 1 - it;
@@ -318,43 +339,120 @@ composite_backward_kernel(int W, int H, unsigned gx, const uint2* __restrict__ r
 		const uint32_t parity = (uint32_t)(it >> 1) & 1u;
 		__syncthreads();   // batch it-1 fully consumed -> its stage may be overwritten
 		if (tid == 0 && it + 1 < nb) issue(b - 1, stage ^ 1);
-		mbar_wait(&s_bar[stage], parity);
+		if (warp == 0) mbar_wait(&sm.bar[stage], parity);
+		__syncthreads();
 
 		const int cnt = min(n_used - b * BWD_BATCH, BWD_BATCH);
-		const float4* recs = &s_rec[stage][0];
-		const int q0 = b * BWD_BATCH;
-		if ((uint32_t)q0 >= wmax) continue;
-		for (int g0 = ((cnt - 1) / 32) * 32; g0 >= 0; g0 -= 32) {
-			const int mine = g0 + lane;
-			bool want = false;
-			if (mine < cnt && (uint32_t)(q0 + mine) < wmax)
-			{
-				const uint32_t bw = __float_as_uint(recs[mine * 5 + 3].w);
-				const int bx0 = (warp & 1) * 8, by0 = (warp >> 1) * 4;
-				want = ((bw >> 16) & 1u) && (int)(bw & 15) <= bx0 + 7 && (int)((bw >> 8) & 15) >= bx0 &&
-				       (int)((bw >> 4) & 15) <= by0 + 3 && (int)((bw >> 12) & 15) >= by0;
-			}
-			uint32_t bal = __ballot_sync(0xffffffffu, want);
-			while (bal) {
-				const int jl = 31 - __clz(bal);
-				bal &= ~(1u << jl);
-				const int j = g0 + jl;
-				const uint32_t q = (uint32_t)(q0 + j);
-				float g[GR_USED];
-				bool hit = false;
-				if (q < pc.last_contributor) hit = grad_pair<USE_SA>(recs + j * 5, pxf, pyf, q, pc, st, g);
-				if (!__any_sync(0xffffffffu, hit)) continue;
-				if (!hit) {
+		const float4* recs = &sm.rec[stage][0];
+		const uint32_t* masks = &sm.mask[stage][0];
+
+		// per-instance hit counts: packed prefix over the 8 mask words, block-wide exclusive scan
+		if (tid < BWD_BATCH) {
+			uint32_t run = 0, lo = 0, hi = 0;
+			if (tid < cnt) {
 #pragma unroll
-					for (int i = 0; i < GR_USED; i++) g[i] = 0.f;
+				for (int k = 0; k < 8; k++) {
+					if (k < 4) lo |= run << (8 * k); else hi |= run << (8 * (k - 4));
+					run += __popc(masks[tid * 8 + k]);
 				}
-				float a, bsum;
-				warp_reduce18(g, lane, a, bsum);
-				const uint32_t row = __float_as_uint(recs[j * 5 + 4].w);
-				float* dst = grad_rows + (size_t)row * GRAD_WORDS;
-				if (lane < 16) atomicAdd(dst + lane, a);
-				if ((lane & 15) == 0) atomicAdd(dst + 16 + (lane >> 4), bsum);
 			}
+			sm.pref[tid] = make_uint2(lo, hi);
+			uint32_t incl = run;
+#pragma unroll
+			for (int o = 1; o < 32; o <<= 1) {
+				const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+				if (lane >= o) incl += t;
+			}
+			if (lane == 31) sm.wsum[warp] = incl;
+			sm.base[tid + 1] = incl;   // warp-local inclusive value; the other warps' totals are added below
+		}
+		__syncthreads();
+		if (tid < BWD_BATCH) {
+			uint32_t off = 0;
+			for (int w = 0; w < warp; w++) off += sm.wsum[w];
+			if (off) sm.base[tid + 1] += off;
+		}
+		if (tid == 0) sm.base[0] = 0;
+
+		// transpose the masks into one hit word per pixel and 32 instances (registers only)
+		uint32_t hits[BWD_BATCH / 32];
+#pragma unroll
+		for (int g = 0; g < BWD_BATCH / 32; g++) {
+			const int j = g * 32 + lane;
+			const uint32_t mine = j < cnt ? masks[j * 8 + warp] : 0u;
+			uint32_t h = 0;
+			if (__any_sync(0xffffffffu, mine != 0u)) {
+#pragma unroll
+				for (int bit = 0; bit < 32; bit++) {
+					const uint32_t v = __ballot_sync(0xffffffffu, (mine >> bit) & 1u);
+					if (lane == bit) h = v;
+				}
+			}
+			hits[g] = h;
+		}
+		__syncthreads();
+
+		int hi = cnt;
+		while (hi > 0) {
+			// largest sub-range [lo, hi) whose pairs fit the slot buffer
+			const uint32_t total_hi = sm.base[hi];
+			const bool fits = tid < hi && (total_hi - sm.base[tid] <= (uint32_t)BWD_CAP);
+			const int lo = hi - __syncthreads_count(fits);   // also: phase B of the previous sub-range is done
+			const uint32_t base_lo = sm.base[lo];
+
+			// ---- phase A: every pixel walks its hits in [lo, hi), back to front
+#pragma unroll
+			for (int g = BWD_BATCH / 32 - 1; g >= 0; g--) {
+				const int a = max(lo - 32 * g, 0), e = min(hi - 32 * g, 32);
+				if (e <= a) continue;
+				uint32_t m = hits[g] & (e == 32 ? 0xffffffffu : ((1u << e) - 1u)) & ~((1u << a) - 1u);
+				while (m) {
+					const int jl = 31 - __clz(m);
+					m &= ~(1u << jl);
+					const int j = g * 32 + jl;
+					const uint32_t q = (uint32_t)(b * BWD_BATCH + j);
+					const uint2 pf = sm.pref[j];
+					const uint32_t before = ((warp < 4 ? pf.x >> (8 * warp) : pf.y >> (8 * (warp - 4))) & 0xffu);
+					const uint32_t si = sm.base[j] - base_lo + before + __popc(masks[j * 8 + warp] & lane_lt);
+					float A, dz, w;
+					if (q < pc.last_contributor && pixel_step<USE_SA>(recs + j * 5, pxf, pyf, q, pc, st, A, dz, w))
+						sm.slot[si] = make_float4(A, dz, w, __int_as_float(tid));
+					else
+						sm.slot[si] = make_float4(0.f, 0.f, 0.f, __int_as_float(-1));
+				}
+			}
+			__syncthreads();
+
+			// ---- phase B: half a warp per instance, lanes over the instance's pairs
+			const int rounds = (hi - lo + 15) >> 4;
+			for (int r = 0; r < rounds; r++) {
+				const int j = hi - 1 - (r * 16 + hw);
+				float g[GR_USED];
+#pragma unroll
+				for (int i = 0; i < GR_USED; i++) g[i] = 0.f;
+				uint32_t row = 0;
+				if (j >= lo) {
+					const float4 r0 = recs[j * 5], r1 = recs[j * 5 + 1], r2 = recs[j * 5 + 2];
+					row = __float_as_uint(recs[j * 5 + 4].w);
+					const uint32_t s0 = sm.base[j] - base_lo, c = sm.base[j + 1] - sm.base[j];
+					for (uint32_t k = hl; k < c; k += 16) {
+						const float4 sl = sm.slot[s0 + k];
+						const int p = __float_as_int(sl.w);
+						if (p >= 0)
+							instance_step(r0, r1, r2, (float)(tx * TILE + (p & 15)), (float)(ty * TILE + (p >> 4)),
+							              sl.x, sl.y, sl.z, &sm.pix[0][0], p, g);
+					}
+				}
+				__syncwarp();
+				float a, bsum;
+				half_reduce18(g, lane, a, bsum);
+				if (j >= lo) {
+					float* dst = grad_rows + (size_t)row * GRAD_WORDS;
+					dst[hl] = a;
+					if ((hl & 7) == 0) dst[16 + (hl >> 3)] = bsum;
+				}
+			}
+			hi = lo;
 		}
 	}
 }
@@ -368,14 +466,22 @@ int launch_composite_backward(const gs2d_settings& s, const gs2d_inputs& in, con
 	const int W = s.image_width, H = s.image_height;
 	const unsigned gx = (W + TILE - 1) / TILE, gy = (H + TILE - 1) / TILE;
 	if (gx * gy == 0) return GS2D_OK;
+	static bool attr_set = false;
+	if (!attr_set) {
+		GS2D_CUDA_OK(cudaFuncSetAttribute(composite_backward_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+		                                  (int)sizeof(BwdSmem)));
+		GS2D_CUDA_OK(cudaFuncSetAttribute(composite_backward_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+		                                  (int)sizeof(BwdSmem)));
+		attr_set = true;
+	}
 	ProfScope ps(K_COMPOSITE_BWD, st);
 	if (s.use_sa)
-		composite_backward_kernel<true><<<gx * gy, 256, 0, st>>>(
-			W, H, gx, (const uint2*)im.ranges, (const float4*)instances, in.background, im.final_T,
+		composite_backward_kernel<true><<<gx * gy, 256, sizeof(BwdSmem), st>>>(
+			W, H, gx, (const uint2*)im.ranges, (const float4*)instances, hit_inst, in.background, im.final_T,
 			im.n_contrib, im.median_depth, im.depth_std, dL_dcolor, dL_dothers, grad_rows);
 	else
-		composite_backward_kernel<false><<<gx * gy, 256, 0, st>>>(
-			W, H, gx, (const uint2*)im.ranges, (const float4*)instances, in.background, im.final_T,
+		composite_backward_kernel<false><<<gx * gy, 256, sizeof(BwdSmem), st>>>(
+			W, H, gx, (const uint2*)im.ranges, (const float4*)instances, hit_inst, in.background, im.final_T,
 			im.n_contrib, im.median_depth, im.depth_std, dL_dcolor, dL_dothers, grad_rows);
 	count_launch();
 	GS2D_CUDA_OK(cudaGetLastError());

@@ -82,6 +82,25 @@ __device__ __forceinline__ bool pair_front(const float4 r0, const float4 r1, con
 	return true;
 }
 
+// The same quantities without the tests (phase B of the backward: the pair was accepted by pair_front already).
+__device__ __forceinline__ void pair_geom(const float4 r0, const float4 r1, const float4 r2, const float pxf,
+                                          const float pyf, PairFront& f)
+{
+	const float3 Tu = make_float3(r0.x, r0.y, r0.z);
+	const float3 Tv = make_float3(r1.x, r1.y, r1.z);
+	const float3 Tw = make_float3(r2.x, r2.y, r2.z);
+	f.k = make_float3(pxf * Tw.x - Tu.x, pxf * Tw.y - Tu.y, pxf * Tw.z - Tu.z);
+	f.l = make_float3(pyf * Tw.x - Tv.x, pyf * Tw.y - Tv.y, pyf * Tw.z - Tv.z);
+	const float3 p = make_float3(f.k.y * f.l.z - f.k.z * f.l.y, f.k.z * f.l.x - f.k.x * f.l.z,
+	                             f.k.x * f.l.y - f.k.y * f.l.x);
+	f.pz = p.z;
+	f.s = make_float2(p.x / p.z, p.y / p.z);
+	f.rho3d = (f.s.x * f.s.x + f.s.y * f.s.y);
+	f.d = make_float2(r0.w - pxf, r1.w - pyf);
+	f.rho2d = GS2D_FILTER_INV_SQUARE * (f.d.x * f.d.x + f.d.y * f.d.y);
+	f.G = expf(-0.5f * fminf(f.rho3d, f.rho2d));
+}
+
 // Same tests with approximate reciprocal / exp2 (for the footprint kernel only, which compensates with
 // relaxed thresholds): true when the pair may contribute.
 __device__ __forceinline__ bool pair_may_contribute(const float4 r0, const float4 r1, const float4 r2, const float pxf,
