@@ -99,7 +99,7 @@ SortScratch SortScratch::carve(void* base, size_t n, size_t* bytes)
 	return s;
 }
 
-BinningState BinningState::carve(void* base, size_t I, size_t* bytes)
+BinningState BinningState::carve(void* base, size_t I, size_t tiles, size_t* bytes)
 {
 	Carver c(base);
 	BinningState b;
@@ -110,6 +110,7 @@ BinningState BinningState::carve(void* base, size_t I, size_t* bytes)
 	b.vals_b = c.take<uint32_t>(n);
 	b.instances = c.take<float>(n * REC_WORDS);
 	b.hit_inst = c.take<uint32_t>(n * 8 + 64);
+	b.hit_pix = c.take<uint32_t>((n / 32 + 4 * tiles + 8) * TILE_PIXELS);
 	b.keys_dbg = c.take<uint64_t>(n);
 	b.vals_dbg = c.take<uint32_t>(n);
 	size_t sort_bytes = 0;
@@ -118,6 +119,11 @@ BinningState BinningState::carve(void* base, size_t I, size_t* bytes)
 	b.sort = SortScratch::carve(sbase, n, nullptr);
 	if (bytes) *bytes = c.total();
 	return b;
+}
+
+static inline size_t tiles_of(int W, int H)
+{
+	return (size_t)((W + TILE - 1) / TILE) * (size_t)((H + TILE - 1) / TILE);
 }
 
 static inline int end_bit_for(const gs2d_settings& s)
@@ -157,7 +163,7 @@ extern "C" {
 
 size_t gs2d_geom_bytes(int32_t P, int32_t) { size_t b = 0; GeomState::carve(nullptr, (size_t)(P > 0 ? P : 0), &b); return b; }
 size_t gs2d_image_bytes(int32_t W, int32_t H) { size_t b = 0; ImageState::carve(nullptr, (size_t)W, (size_t)H, &b); return b; }
-size_t gs2d_binning_bytes(int64_t I, int32_t, int32_t) { size_t b = 0; BinningState::carve(nullptr, (size_t)(I > 0 ? I : 0), &b); return b; }
+size_t gs2d_binning_bytes(int64_t I, int32_t W, int32_t H) { size_t b = 0; BinningState::carve(nullptr, (size_t)(I > 0 ? I : 0), tiles_of(W, H), &b); return b; }
 size_t gs2d_backward_scratch_bytes(int32_t, int64_t I) { return (size_t)(I > 0 ? I : 0) * GRAD_WORDS * sizeof(float) + ALIGN; }
 size_t gs2d_sort_scratch_bytes(int64_t n)
 {
@@ -201,12 +207,12 @@ int gs2d_forward_render(const gs2d_settings* s, const gs2d_inputs* in, const gs2
 	if (s->P == 0 || I == 0) {
 		// nothing to blend: ranges all empty, the compositor still writes every pixel (background)
 		GS2D_CUDA_OK(cudaMemsetAsync(im.ranges, 0, sizeof(uint32_t) * 2 * (size_t)gx * gy, st));
-		return launch_composite_forward(*s, *in, im, nullptr, nullptr, out_color, out_others, st);
+		return launch_composite_forward(*s, *in, im, nullptr, nullptr, nullptr, out_color, out_others, st);
 	}
 	if (!buffers->geom || !buffers->binning) return GS2D_ERR_INVALID;
 	if (buffers->binning_bytes < gs2d_binning_bytes(I, s->image_width, s->image_height)) return GS2D_ERR_CAPACITY;
 	GeomState g = GeomState::carve(buffers->geom, (size_t)s->P, nullptr);
-	BinningState b = BinningState::carve(buffers->binning, (size_t)I, nullptr);
+	BinningState b = BinningState::carve(buffers->binning, (size_t)I, tiles_of(s->image_width, s->image_height), nullptr);
 
 	GS2D_TRY(launch_duplicate(*s, g, nullptr, b, I, st));
 	GS2D_TRY(debug_sync(*s, st));
@@ -227,7 +233,7 @@ int gs2d_forward_render(const gs2d_settings* s, const gs2d_inputs* in, const gs2
 	GS2D_TRY(debug_sync(*s, st));
 	GS2D_TRY(launch_footprint(*s, b.instances, b.keys_b, b.hit_inst, I, st));
 	GS2D_TRY(debug_sync(*s, st));
-	GS2D_TRY(launch_composite_forward(*s, *in, im, b.instances, b.hit_inst, out_color, out_others, st));
+	GS2D_TRY(launch_composite_forward(*s, *in, im, b.instances, b.hit_inst, b.hit_pix, out_color, out_others, st));
 	GS2D_TRY(debug_sync(*s, st));
 	return GS2D_OK;
 }
@@ -270,9 +276,9 @@ int gs2d_backward(const gs2d_settings* s, const gs2d_inputs* in, const gs2d_buff
 	float* rows = (float*)scratch;
 	if (I > 0) {
 		if (!scratch || !buffers->binning) return GS2D_ERR_INVALID;
-		BinningState b = BinningState::carve(buffers->binning, (size_t)I, nullptr);
+		BinningState b = BinningState::carve(buffers->binning, (size_t)I, tiles_of(s->image_width, s->image_height), nullptr);
 		// no zero-fill: composite_backward writes every instance row exactly once
-		GS2D_TRY(launch_composite_backward(*s, *in, im, b.instances, b.hit_inst, dL_dout_color, dL_dout_others, rows, st));
+		GS2D_TRY(launch_composite_backward(*s, *in, im, b.instances, b.hit_inst, b.hit_pix, dL_dout_color, dL_dout_others, rows, st));
 		GS2D_TRY(debug_sync(*s, st));
 	}
 	GS2D_TRY(launch_preprocess_backward(*s, *in, g, radii, rows, *grads, st));
@@ -299,7 +305,7 @@ int gs2d_state_view_get(const gs2d_settings* s, const gs2d_buffers* buffers, int
 		out->tiles_touched = g.tiles_touched; out->point_offsets = g.point_offsets;
 	}
 	if (buffers->binning && I > 0) {
-		BinningState b = BinningState::carve(buffers->binning, (size_t)I, nullptr);
+		BinningState b = BinningState::carve(buffers->binning, (size_t)I, tiles_of(s->image_width, s->image_height), nullptr);
 		out->keys_unsorted = b.keys_dbg; out->values_unsorted = b.vals_dbg;
 		out->keys_sorted = b.keys_b; out->point_list = b.vals_b; out->instances = b.instances;
 	}
@@ -319,7 +325,7 @@ int gs2d_footprint_audit(const gs2d_settings* s, const gs2d_buffers* buffers, in
 	if (I <= 0) return GS2D_OK;
 	if (!buffers->binning) return GS2D_ERR_INVALID;
 	cudaStream_t st = (cudaStream_t)stream;
-	BinningState b = BinningState::carve(buffers->binning, (size_t)I, nullptr);
+	BinningState b = BinningState::carve(buffers->binning, (size_t)I, tiles_of(s->image_width, s->image_height), nullptr);
 	unsigned long long* counts = (unsigned long long*)(b.hit_inst + 8 * (size_t)I + 8);   // padding of hit_inst
 	GS2D_CUDA_OK(cudaMemsetAsync(counts, 0, 3 * sizeof(unsigned long long), st));
 	GS2D_TRY(launch_footprint_audit(*s, b.instances, b.keys_b, b.hit_inst, I, counts, st));

@@ -101,11 +101,13 @@ struct BinningState {
 	uint32_t* vals_a;         // [I]
 	uint32_t* vals_b;         // [I]
 	float* instances;         // [I,20]
-	uint32_t* hit_inst;       // [I,8] per-instance footprint mask, box-local pixel order (footprint.cu)
+	uint32_t* hit_inst;       // [I,8] per-instance footprint mask in tile pixel order (footprint.cu)
+	uint32_t* hit_pix;        // [I/32 + 4*tiles, 256] per-pixel contribution words written by the forward pass:
+	                          // tile t, batch b, word g at ((range.x >> 5) + 4*t + 4*b + g) * 256 + pixel thread
 	uint64_t* keys_dbg;       // [I] copy of the unsorted keys
 	uint32_t* vals_dbg;       // [I]
 	SortScratch sort;
-	static __host__ BinningState carve(void* base, size_t I, size_t* bytes);
+	static __host__ BinningState carve(void* base, size_t I, size_t tiles, size_t* bytes);
 };
 
 inline int sort_passes(int end_bit) { return (end_bit + SORT_RADIX_BITS - 1) / SORT_RADIX_BITS; }
@@ -149,10 +151,11 @@ int launch_footprint(const gs2d_settings& s, const float* instances, const uint6
 int launch_footprint_audit(const gs2d_settings& s, const float* instances, const uint64_t* keys_sorted,
                            const uint32_t* hit_inst, int64_t I, unsigned long long* counts, cudaStream_t st);
 int launch_composite_forward(const gs2d_settings& s, const gs2d_inputs& in, const ImageState& im,
-                             const float* instances, const uint32_t* hit_inst, float* out_color,
+                             const float* instances, const uint32_t* hit_inst, uint32_t* hit_pix, float* out_color,
                              float* out_others, cudaStream_t st);
 int launch_composite_backward(const gs2d_settings& s, const gs2d_inputs& in, const ImageState& im,
-                              const float* instances, const uint32_t* hit_inst, const float* dL_dcolor,
+                              const float* instances, const uint32_t* hit_inst, const uint32_t* hit_pix,
+                              const float* dL_dcolor,
                               const float* dL_dothers, float* grad_rows, cudaStream_t st);
 int launch_preprocess_backward(const gs2d_settings& s, const gs2d_inputs& in, const GeomState& g,
                                const int32_t* radii, const float* grad_rows, const gs2d_grads& out,

@@ -7,9 +7,9 @@
 //
 //   phase A (per PIXEL, sequential back to front, lanes = 32 pixels of a warp):
 //       the order-dependent part only -- transmittance T = T / (1 - alpha), the suffix recurrences for
-//       colour / depth / alpha / normal / dL_dT (CR/backward.cu:323-410).  Every pixel walks ITS OWN hit
-//       list (footprint masks transposed with ballots, as in the forward), i.e. ~17 instances per tile
-//       instead of ~250, and leaves three scalars per pair -- dL/dalpha, dL/dz, w = alpha * T -- plus its
+//       colour / depth / alpha / normal / dL_dT (CR/backward.cu:323-410).  Every pixel walks ITS OWN list of
+//       the pairs that contributed in the forward pass (recorded there, one word per pixel and 32
+//       instances), i.e. ~17 instances per tile instead of ~250 and no skip tests, and leaves three scalars per pair -- dL/dalpha, dL/dz, w = alpha * T -- plus its
 //       pixel id in the pair's 16-byte slot in shared memory.  Slots are laid out per instance
 //       (slot = instance base + rank of the pixel inside the instance's mask).
 //   phase B (per INSTANCE, lanes = that instance's contributing pixels, half a warp per instance):
@@ -39,8 +39,8 @@ struct PixelConst {
 	float dpix0, dpix1, dpix2;
 	float dL_ddepth, dL_daccum, dL_dreg, dL_dmedian;
 	float dn0, dn1, dn2;
-	float mm, mstd, bg_dot;
-	uint32_t last_contributor, median_contributor;
+	float mm, inv_4std, bg_dot;      // inv_4std = 1 / (4 max(mstd / (1 - T_final), 1e-7)), CR/backward.cu:349
+	uint32_t median_contributor;
 };
 
 struct PixelBwd {
@@ -67,18 +67,20 @@ struct BwdSmem {
 };
 
 // Phase A for one (pixel, instance) pair: CR/backward.cu:283-410 minus the geometric chain.
-// Returns false when the pair does not contribute (the reference's `continue`s).
+// The forward pass recorded which pairs contributed (hit_pix), so there are no tests here.
 template <bool USE_SA>
-__device__ __forceinline__ bool pixel_step(const float4* __restrict__ rec, float pxf, float pyf, uint32_t q,
+__device__ __forceinline__ void pixel_step(const float4* __restrict__ rec, float pxf, float pyf, uint32_t q,
                                            const PixelConst& pc, PixelBwd& st, float& dL_dalpha_out,
                                            float& dL_dz_out, float& w_out)
 {
 	PairFront f;
-	if (!pair_front(rec[0], rec[1], rec[2], pxf, pyf, f)) return false;
+	float inv_pz;
+	pair_geom_fast(rec[0], rec[1], rec[2], pxf, pyf, f, inv_pz);
 	const float alpha = f.alpha;
 	float c_d = f.depth;
 	const float4 r3 = rec[3], r4 = rec[4];
-	st.T = st.T / (1.f - alpha);
+	const float inv_1ma = __fdividef(1.0f, 1.f - alpha);
+	st.T = st.T * inv_1ma;
 	const float T = st.T;
 	const float w = alpha * T;
 
@@ -96,7 +98,7 @@ __device__ __forceinline__ bool pixel_step(const float4* __restrict__ rec, float
 	float conf = 1;
 	if (USE_SA) {
 		// confidence from the FINAL per-pixel statistics, treated as a constant (CR/backward.cu:349)
-		conf = T < 0.5f ? expf(-(c_d - pc.mm) * (c_d - pc.mm) / (4 * fmaxf(pc.mstd / (1 - pc.T_final), 1e-7f))) : 1.f;
+		conf = T < 0.5f ? __expf(-(c_d - pc.mm) * (c_d - pc.mm) * pc.inv_4std) : 1.f;
 		c_d = c_d * conf + pc.mm * (1 - conf);
 	}
 
@@ -137,13 +139,12 @@ __device__ __forceinline__ bool pixel_step(const float4* __restrict__ rec, float
 
 	dL_dalpha *= T;
 	st.last_alpha = alpha;
-	dL_dalpha += (-pc.T_final / (1.f - alpha)) * pc.bg_dot;
+	dL_dalpha += (-pc.T_final * inv_1ma) * pc.bg_dot;
 	dL_dz += conf * alpha * T * pc.dL_ddepth;
 
 	dL_dalpha_out = dL_dalpha;
 	dL_dz_out = dL_dz;
 	w_out = w;
-	return true;
 }
 
 // Phase B for one (instance, pixel) pair: the geometric chain (CR/backward.cu:343, :396, :412-460).
@@ -153,7 +154,8 @@ __device__ __forceinline__ void instance_step(const float4 r0, const float4 r1, 
                                               float (&g)[GR_USED])
 {
 	PairFront f;
-	pair_geom(r0, r1, r2, pxf, pyf, f);
+	float inv_pz;
+	pair_geom_fast(r0, r1, r2, pxf, pyf, f, inv_pz);
 	const float3 Tw = make_float3(r2.x, r2.y, r2.z);
 	const float opa = r2.w, G = f.G;
 	g[GR_COL + 0] += w * pixc[0 * TILE_PIXELS + pid];
@@ -166,8 +168,8 @@ __device__ __forceinline__ void instance_step(const float4 r0, const float4 r1, 
 	if (f.rho3d <= f.rho2d) {
 		const float dL_dsx = dL_dG * -G * f.s.x + dz * Tw.x;
 		const float dL_dsy = dL_dG * -G * f.s.y + dz * Tw.y;
-		const float dsx_pz = dL_dsx / f.pz;
-		const float dsy_pz = dL_dsy / f.pz;
+		const float dsx_pz = dL_dsx * inv_pz;
+		const float dsy_pz = dL_dsy * inv_pz;
 		const float3 dL_dp = make_float3(dsx_pz, dsy_pz, -(dsx_pz * f.s.x + dsy_pz * f.s.y));
 		const float3 k = f.k, l = f.l;
 		const float3 dL_dk = make_float3(l.y * dL_dp.z - l.z * dL_dp.y, l.z * dL_dp.x - l.x * dL_dp.z,
@@ -238,7 +240,8 @@ template <bool USE_SA>
 __global__ void __launch_bounds__(256, 3)
 composite_backward_kernel(int W, int H, unsigned gx, const uint2* __restrict__ ranges,
                           const float4* __restrict__ instances, const uint32_t* __restrict__ hit_inst,
-                          const float* __restrict__ bg, const float* __restrict__ final_T,
+                          const uint32_t* __restrict__ hit_pix, const float* __restrict__ bg,
+                          const float* __restrict__ final_T,
                           const uint32_t* __restrict__ n_contrib, const float* __restrict__ median_depth,
                           const float* __restrict__ depth_std, const float* __restrict__ dL_dpix,
                           const float* __restrict__ dL_dothers, float* __restrict__ grad_rows)
@@ -261,7 +264,7 @@ composite_backward_kernel(int W, int H, unsigned gx, const uint2* __restrict__ r
 
 	PixelConst pc;
 	pc.T_final = inside ? final_T[pid] : 0.f;
-	pc.last_contributor = inside ? n_contrib[pid] : 0u;
+	const uint32_t last_contributor = inside ? n_contrib[pid] : 0u;
 	pc.median_contributor = inside ? n_contrib[pid + HW] : 0u;
 	pc.final_A = 1 - pc.T_final;
 	pc.final_D = inside ? final_T[pid + HW] : 0.f;
@@ -269,7 +272,8 @@ composite_backward_kernel(int W, int H, unsigned gx, const uint2* __restrict__ r
 	pc.dpix0 = pc.dpix1 = pc.dpix2 = 0.f;
 	pc.dL_ddepth = pc.dL_daccum = pc.dL_dreg = pc.dL_dmedian = 0.f;
 	pc.dn0 = pc.dn1 = pc.dn2 = 0.f;
-	pc.mm = pc.mstd = 0.f;
+	pc.mm = 0.f;
+	pc.inv_4std = 0.f;
 	if (inside) {
 		pc.dpix0 = dL_dpix[pid];
 		pc.dpix1 = dL_dpix[pid + HW];
@@ -282,7 +286,7 @@ composite_backward_kernel(int W, int H, unsigned gx, const uint2* __restrict__ r
 		pc.dL_dmedian = dL_dothers[pid + 5 * HW];
 		pc.dL_dreg = dL_dothers[pid + 6 * HW];
 		pc.mm = median_depth[pid];
-		pc.mstd = depth_std[pid];
+		pc.inv_4std = 1.0f / (4 * fmaxf(depth_std[pid] / (1 - pc.T_final), 1e-7f));
 	}
 	{
 		float acc = 0;
@@ -297,7 +301,7 @@ composite_backward_kernel(int W, int H, unsigned gx, const uint2* __restrict__ r
 	st.T = pc.T_final;
 
 	// deepest last contributor of the tile: nothing behind it is ever visited
-	uint32_t wmax = pc.last_contributor;
+	uint32_t wmax = last_contributor;
 #pragma unroll
 	for (int o = 16; o >= 1; o >>= 1) wmax = max(wmax, __shfl_xor_sync(0xffffffffu, wmax, o));
 	if (lane == 0) sm.max_last[warp] = wmax;
@@ -331,6 +335,7 @@ composite_backward_kernel(int W, int H, unsigned gx, const uint2* __restrict__ r
 	}
 
 	const uint32_t lane_lt = (1u << lane) - 1u;
+	const uint32_t* pix_words = hit_pix + ((size_t)(range.x >> 5) + 4 * (size_t)tile) * TILE_PIXELS;
 	const int hw = tid >> 4, hl = tid & 15;          // half-warp id / lane inside it (phase B)
 
 	for (int it = 0; it < nb; it++) {
@@ -374,31 +379,28 @@ composite_backward_kernel(int W, int H, unsigned gx, const uint2* __restrict__ r
 		}
 		if (tid == 0) sm.base[0] = 0;
 
-		// transpose the masks into one hit word per pixel and 32 instances (registers only)
+		// the pairs of this batch that contributed in the forward pass, one word per pixel and 32 instances
 		uint32_t hits[BWD_BATCH / 32];
 #pragma unroll
-		for (int g = 0; g < BWD_BATCH / 32; g++) {
-			const int j = g * 32 + lane;
-			const uint32_t mine = j < cnt ? masks[j * 8 + warp] : 0u;
-			uint32_t h = 0;
-			if (__any_sync(0xffffffffu, mine != 0u)) {
-#pragma unroll
-				for (int bit = 0; bit < 32; bit++) {
-					const uint32_t v = __ballot_sync(0xffffffffu, (mine >> bit) & 1u);
-					if (lane == bit) h = v;
-				}
-			}
-			hits[g] = h;
-		}
+		for (int g = 0; g < BWD_BATCH / 32; g++)
+			hits[g] = pix_words[(size_t)(b * (BWD_BATCH / 32) + g) * TILE_PIXELS + tid];
 		__syncthreads();
 
+		// sub-ranges of roughly equal pair counts, each fitting the slot buffer
+		const uint32_t total = sm.base[cnt];
+		const uint32_t parts = (total + BWD_CAP - 1) / BWD_CAP;
+		const uint32_t target = parts ? (total + parts - 1) / parts + 128 : 0;
+		const uint32_t cap = min((uint32_t)BWD_CAP, max(target, 256u));
 		int hi = cnt;
 		while (hi > 0) {
 			// largest sub-range [lo, hi) whose pairs fit the slot buffer
 			const uint32_t total_hi = sm.base[hi];
-			const bool fits = tid < hi && (total_hi - sm.base[tid] <= (uint32_t)BWD_CAP);
+			const bool fits = tid < hi && (total_hi - sm.base[tid] <= cap);
 			const int lo = hi - __syncthreads_count(fits);   // also: phase B of the previous sub-range is done
 			const uint32_t base_lo = sm.base[lo];
+			// slots of pairs that did not contribute (mask superset, terminated pixels) stay marked empty
+			for (uint32_t k = tid; k < total_hi - base_lo; k += 256) sm.slot[k].w = __int_as_float(-1);
+			__syncthreads();
 
 			// ---- phase A: every pixel walks its hits in [lo, hi), back to front
 #pragma unroll
@@ -415,10 +417,8 @@ composite_backward_kernel(int W, int H, unsigned gx, const uint2* __restrict__ r
 					const uint32_t before = ((warp < 4 ? pf.x >> (8 * warp) : pf.y >> (8 * (warp - 4))) & 0xffu);
 					const uint32_t si = sm.base[j] - base_lo + before + __popc(masks[j * 8 + warp] & lane_lt);
 					float A, dz, w;
-					if (q < pc.last_contributor && pixel_step<USE_SA>(recs + j * 5, pxf, pyf, q, pc, st, A, dz, w))
-						sm.slot[si] = make_float4(A, dz, w, __int_as_float(tid));
-					else
-						sm.slot[si] = make_float4(0.f, 0.f, 0.f, __int_as_float(-1));
+					pixel_step<USE_SA>(recs + j * 5, pxf, pyf, q, pc, st, A, dz, w);
+					sm.slot[si] = make_float4(A, dz, w, __int_as_float(tid));
 				}
 			}
 			__syncthreads();
@@ -460,8 +460,8 @@ composite_backward_kernel(int W, int H, unsigned gx, const uint2* __restrict__ r
 }  // namespace
 
 int launch_composite_backward(const gs2d_settings& s, const gs2d_inputs& in, const ImageState& im,
-                              const float* instances, const uint32_t* hit_inst, const float* dL_dcolor,
-                              const float* dL_dothers, float* grad_rows, cudaStream_t st)
+                              const float* instances, const uint32_t* hit_inst, const uint32_t* hit_pix,
+                              const float* dL_dcolor, const float* dL_dothers, float* grad_rows, cudaStream_t st)
 {
 	const int W = s.image_width, H = s.image_height;
 	const unsigned gx = (W + TILE - 1) / TILE, gy = (H + TILE - 1) / TILE;
@@ -477,11 +477,11 @@ int launch_composite_backward(const gs2d_settings& s, const gs2d_inputs& in, con
 	ProfScope ps(K_COMPOSITE_BWD, st);
 	if (s.use_sa)
 		composite_backward_kernel<true><<<gx * gy, 256, sizeof(BwdSmem), st>>>(
-			W, H, gx, (const uint2*)im.ranges, (const float4*)instances, hit_inst, in.background, im.final_T,
+			W, H, gx, (const uint2*)im.ranges, (const float4*)instances, hit_inst, hit_pix, in.background, im.final_T,
 			im.n_contrib, im.median_depth, im.depth_std, dL_dcolor, dL_dothers, grad_rows);
 	else
 		composite_backward_kernel<false><<<gx * gy, 256, sizeof(BwdSmem), st>>>(
-			W, H, gx, (const uint2*)im.ranges, (const float4*)instances, hit_inst, in.background, im.final_T,
+			W, H, gx, (const uint2*)im.ranges, (const float4*)instances, hit_inst, hit_pix, in.background, im.final_T,
 			im.n_contrib, im.median_depth, im.depth_std, dL_dcolor, dL_dothers, grad_rows);
 	count_launch();
 	GS2D_CUDA_OK(cudaGetLastError());

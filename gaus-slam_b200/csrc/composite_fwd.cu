@@ -37,17 +37,17 @@ struct PixelFwd {
 };
 
 template <bool USE_SA>
-__device__ __forceinline__ void eval_pair(const float4* __restrict__ rec, float pxf, float pyf,
+__device__ __forceinline__ bool eval_pair(const float4* __restrict__ rec, float pxf, float pyf,
                                           uint32_t contributor, PixelFwd& px, bool& done)
 {
 	PairFront f;
-	if (!pair_front(rec[0], rec[1], rec[2], pxf, pyf, f)) return;
+	if (!pair_front(rec[0], rec[1], rec[2], pxf, pyf, f)) return false;
 	const float alpha = f.alpha;
 	float depth = f.depth;
 	const float test_T = px.T * (1 - alpha);
 	if (test_T < 0.0001f) {
 		done = true;
-		return;
+		return false;
 	}
 	const float w = alpha * px.T;
 	if (px.T > 0.5) {
@@ -79,13 +79,14 @@ __device__ __forceinline__ void eval_pair(const float4* __restrict__ rec, float 
 	px.C0 += r4.x * w; px.C1 += r4.y * w; px.C2 += r4.z * w;
 	px.T = test_T;
 	px.last_contributor = contributor;
+	return true;
 }
 
 template <bool USE_SA>
 __global__ void __launch_bounds__(256)
 composite_forward_kernel(int W, int H, unsigned gx, const uint2* __restrict__ ranges,
                          const float4* __restrict__ instances, const uint32_t* __restrict__ hit_inst,
-                         const float* __restrict__ bg, float* __restrict__ final_T,
+                         uint32_t* __restrict__ hit_pix, const float* __restrict__ bg, float* __restrict__ final_T,
                          uint32_t* __restrict__ n_contrib, float* __restrict__ median_depth_out,
                          float* __restrict__ depth_std_out, float* __restrict__ out_color,
                          float* __restrict__ out_others)
@@ -120,6 +121,8 @@ composite_forward_kernel(int W, int H, unsigned gx, const uint2* __restrict__ ra
 		tma_load_1d(&s_mask[stage][0], tile_mask + 8 * (size_t)b * FWD_BATCH, cnt * 32u, &s_bar[stage]);
 	};
 	if (tid == 0 && nb > 0) issue(0, 0);
+
+	uint32_t* pix_words = hit_pix + ((size_t)(range.x >> 5) + 4 * (size_t)tile) * TILE_PIXELS;
 
 	PixelFwd px;
 	bool done = !inside;
@@ -161,12 +164,15 @@ composite_forward_kernel(int W, int H, unsigned gx, const uint2* __restrict__ ra
 		// every pixel walks its own hits, front to back
 #pragma unroll
 		for (int g = 0; g < FWD_BATCH / 32; g++) {
-			uint32_t m = hits[g];
+			uint32_t m = hits[g], used = 0u;
 			while (m && !done) {
-				const int j = g * 32 + (__ffs(m) - 1);
+				const int jl = __ffs(m) - 1;
 				m &= m - 1;
-				eval_pair<USE_SA>(recs + j * 5, pxf, pyf, (uint32_t)(b * FWD_BATCH + j + 1), px, done);
+				if (eval_pair<USE_SA>(recs + (g * 32 + jl) * 5, pxf, pyf, (uint32_t)(b * FWD_BATCH + g * 32 + jl + 1), px, done))
+					used |= 1u << jl;
 			}
+			// the pairs that really contributed, for the backward pass (coalesced: one word per pixel thread)
+			pix_words[(size_t)(b * (FWD_BATCH / 32) + g) * TILE_PIXELS + tid] = used;
 		}
 	}
 
@@ -201,7 +207,7 @@ composite_forward_kernel(int W, int H, unsigned gx, const uint2* __restrict__ ra
 }  // namespace
 
 int launch_composite_forward(const gs2d_settings& s, const gs2d_inputs& in, const ImageState& im,
-                             const float* instances, const uint32_t* hit_inst, float* out_color,
+                             const float* instances, const uint32_t* hit_inst, uint32_t* hit_pix, float* out_color,
                              float* out_others, cudaStream_t st)
 {
 	const int W = s.image_width, H = s.image_height;
@@ -210,11 +216,11 @@ int launch_composite_forward(const gs2d_settings& s, const gs2d_inputs& in, cons
 	ProfScope ps(K_COMPOSITE_FWD, st);
 	if (s.use_sa)
 		composite_forward_kernel<true><<<gx * gy, 256, 0, st>>>(
-			W, H, gx, (const uint2*)im.ranges, (const float4*)instances, hit_inst, in.background, im.final_T,
+			W, H, gx, (const uint2*)im.ranges, (const float4*)instances, hit_inst, hit_pix, in.background, im.final_T,
 			im.n_contrib, im.median_depth, im.depth_std, out_color, out_others);
 	else
 		composite_forward_kernel<false><<<gx * gy, 256, 0, st>>>(
-			W, H, gx, (const uint2*)im.ranges, (const float4*)instances, hit_inst, in.background, im.final_T,
+			W, H, gx, (const uint2*)im.ranges, (const float4*)instances, hit_inst, hit_pix, in.background, im.final_T,
 			im.n_contrib, im.median_depth, im.depth_std, out_color, out_others);
 	count_launch();
 	GS2D_CUDA_OK(cudaGetLastError());

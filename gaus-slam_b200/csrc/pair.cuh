@@ -101,6 +101,26 @@ __device__ __forceinline__ void pair_geom(const float4 r0, const float4 r1, cons
 	f.G = expf(-0.5f * fminf(f.rho3d, f.rho2d));
 }
 
+// Backward-pass variant: MUFU reciprocal / exp2 instead of IEEE division / expf (the gradient tolerance is
+// 1e-3 relative; these are ~1e-6), no tests: the forward pass recorded which pairs contributed.
+__device__ __forceinline__ void pair_geom_fast(const float4 r0, const float4 r1, const float4 r2, const float pxf,
+                                               const float pyf, PairFront& f, float& inv_pz)
+{
+	f.k = make_float3(pxf * r2.x - r0.x, pxf * r2.y - r0.y, pxf * r2.z - r0.z);
+	f.l = make_float3(pyf * r2.x - r1.x, pyf * r2.y - r1.y, pyf * r2.z - r1.z);
+	const float3 p = make_float3(f.k.y * f.l.z - f.k.z * f.l.y, f.k.z * f.l.x - f.k.x * f.l.z,
+	                             f.k.x * f.l.y - f.k.y * f.l.x);
+	f.pz = p.z;
+	inv_pz = __fdividef(1.0f, p.z);
+	f.s = make_float2(p.x * inv_pz, p.y * inv_pz);
+	f.rho3d = (f.s.x * f.s.x + f.s.y * f.s.y);
+	f.d = make_float2(r0.w - pxf, r1.w - pyf);
+	f.rho2d = GS2D_FILTER_INV_SQUARE * (f.d.x * f.d.x + f.d.y * f.d.y);
+	f.depth = (f.rho3d <= f.rho2d) ? (f.s.x * r2.x + f.s.y * r2.y) + r2.z : r2.z;
+	f.G = __expf(-0.5f * fminf(f.rho3d, f.rho2d));
+	f.alpha = fminf(0.99f, r2.w * f.G);
+}
+
 // Same tests with approximate reciprocal / exp2 (for the footprint kernel only, which compensates with
 // relaxed thresholds): true when the pair may contribute.
 __device__ __forceinline__ bool pair_may_contribute(const float4 r0, const float4 r1, const float4 r2, const float pxf,
