@@ -112,7 +112,7 @@ class ClockSampler:
 # ----------------------------------------------------------------------------------------------------
 def build_workload(a, dev):
     """The 500k-surfel room submap + an 8-keyframe window.  One full input set PER VIEW (own parameter copy,
-    own upstream image gradients): 8 x 58.6 MB > the 126 MB L2, so no step finds its inputs in L2."""
+    own image gradients / RGB-D frame): 8 x 71.7 MB > the 126 MB L2, so no step finds its inputs in L2."""
     import torch
     sys.path.insert(0, os.path.join(ROOT, "gaus-slam_b200"))
     from gs2d_b200 import scene
@@ -123,10 +123,14 @@ def build_workload(a, dev):
     sets = []
     for v, cam in enumerate(cams):
         gc, go = scene.image_grads(W, H, seed=v)
+        rng = np.random.default_rng(500 + v)
+        # what a SLAM step gets from the host: the keyframe's camera and its RGB-D image (e2e path)
         host = dict(viewmatrix=cam.viewmatrix.reshape(16), projmatrix=cam.projmatrix.reshape(16), campos=cam.campos,
-                    dL_dcolor=gc, dL_dothers=go)
+                    gt_color=rng.uniform(0.0, 1.0, size=(3, H, W)), gt_depth=rng.uniform(1.0, 4.0, size=(1, H, W)))
         host = {k: torch.from_numpy(np.ascontiguousarray(x, dtype=np.float32)).pin_memory() for k, x in host.items()}
         d = {k: x.to(dev) for k, x in host.items()}
+        d["dL_dcolor"] = torch.from_numpy(gc).to(dev)      # upstream image gradients of the device-resident path
+        d["dL_dothers"] = torch.from_numpy(go).to(dev)
         for k in ("means3D", "scales", "rotations", "opacities", "colors"):
             d[k] = torch.from_numpy(sc[k]).to(dev)
         d["tanfovx"], d["tanfovy"] = float(cam.tanfovx), float(cam.tanfovy)
@@ -134,6 +138,21 @@ def build_workload(a, dev):
         sets.append(d)
     return dict(W=W, H=H, P=a.surfels, sets=sets, scene=sc, cams=cams, bg=torch.zeros(3, device=dev),
                 empty=torch.empty(0, device=dev))
+
+
+def mapping_loss(color, allmap, gt_color, gt_depth):
+    """Mapping loss of slam/Loss.py:51-58 on one view (masked means of L1 colour, L1 depth, + 0.1 * distortion /
+    depth-variance channel), with the weight-normalised depth of render/__init__.py:46-49.  Mask multiplications
+    instead of boolean indexing so the step has no extra host synchronisation."""
+    import torch
+    alpha = torch.nan_to_num(allmap[1:2])
+    depth = torch.nan_to_num(allmap[0:1]) / (alpha + 1e-6)
+    mask = ((gt_depth > 1e-5) & (depth > 1e-5)).to(color.dtype)
+    cnt = mask.sum().clamp(min=1.0)
+    l_color = ((torch.nan_to_num(color) - gt_color).abs() * mask).sum() / (3.0 * cnt)
+    l_depth = ((depth - gt_depth).abs() * mask).sum() / cnt
+    l_dist = (torch.nan_to_num(allmap[6:7]) * mask).sum() / cnt
+    return l_color + l_depth + 0.1 * l_dist
 
 
 def algorithmic_bytes(P, Pv, I, W, H):
@@ -468,7 +487,7 @@ def main():
             color, radii, allmap = rast(means3D=params["means3D"], means2D=means2D, opacities=params["opacities"],
                                         colors_precomp=params["colors"], scales=params["scales"],
                                         rotations=params["rotations"])
-            loss = (color * s["dL_dcolor"]).sum() + (allmap * s["dL_dothers"]).sum()
+            loss = mapping_loss(color, allmap, s["gt_color"], s["gt_depth"])
             loss.backward()
             if multi:
                 torch.cat([params[k].grad.reshape(-1) for k in order], out=flat)
@@ -486,10 +505,11 @@ def main():
         ms_e2e = timed(step_e2e, a.steps, a.warmup) / a.steps
         e2e = {"value": (world if multi else 1) * 1000.0 / ms_e2e, "unit": UNIT, "h2d_bytes_per_step": h2d,
                "d2h_bytes_per_step": 4 + 4, "ms_per_step": ms_e2e,
-               "what": "GaussianRasterizer(...)(...) + loss.backward() through the drop-in python API; camera + "
-                       "upstream image gradients copied from pinned host memory every step (double-buffered on a "
-                       "copy stream), num_rendered and the loss read back every step; surfel parameters are "
-                       "optimiser state and stay in HBM"}
+               "what": "one mapping iteration through the public python API: GaussianRasterizer(...)(...) -> mapping "
+                       "loss (slam/Loss.py:51-58, torch) -> loss.backward(); the keyframe's camera and RGB-D image "
+                       "(3+1 channels fp32) are copied from pinned host memory every step (double-buffered on a copy "
+                       "stream), num_rendered and the loss are read back every step; surfel parameters are optimiser "
+                       "state and stay in HBM"}
 
     if rank != 0:
         if multi:
@@ -503,7 +523,7 @@ def main():
                                   f"{P} surfels, {V}-keyframe window (BASELINE.json configs[2]), use_sa=True",
                       "surfels": P, "visible_mean": Pv_mean, "instances_mean": I_mean, "views": V,
                       "parallelism": f"view-sharded x{world if multi else 1}" + (", NCCL all-reduce of [P,13] map gradients" if multi else ""),
-                      "l2": f"inputs rotate over {V} per-view sets ({V} x 58.6 MB > 126 MB L2); no explicit flush"},
+                      "l2": f"inputs rotate over {V} per-view sets ({V} x {(P * 52 + W * H * 56) / 1e6:.1f} MB > 126 MB L2); no explicit flush"},
            "gpu_launches": launches, "clocks": clocks}
     if a.impl == "reference":
         out["impl"] = "reference"

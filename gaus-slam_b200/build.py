@@ -16,6 +16,10 @@ LIB = os.path.join(HERE, "lib", "libgs2d.so")
 SOURCES = ["api.cu", "preprocess.cu", "binning.cu", "footprint.cu", "composite_fwd.cu", "composite_bwd.cu",
            "preprocess_bwd.cu", "knn.cu"]
 HEADERS = ["common.cuh", "math.cuh", "exact.cuh", "tma.cuh", "pair.cuh", os.path.join("..", "..", "include", "gs2d.h")]
+# Kernels whose results only have to meet a tolerance (backward gradients: 1e-3 relative; footprint masks: a
+# superset) may use MUFU division / flush-to-zero; everything that decides bit-exact outputs keeps IEEE math.
+FAST_MATH = {"composite_bwd.cu": ["-ftz=true", "-prec-div=false", "-prec-sqrt=false"],
+             "footprint.cu": ["-ftz=true", "-prec-div=false", "-prec-sqrt=false"]}
 NVCC_FLAGS = ["-std=c++17", "-O3", "-lineinfo", "-Xcompiler", "-fPIC",
               "-gencode", "arch=compute_100a,code=sm_100a"]
 
@@ -37,7 +41,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
 
     def one(src: str) -> str:
         obj = os.path.join(objdir, src + ".o")
-        cmd = ["nvcc"] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-c", os.path.join(CSRC, src), "-o", obj]
+        cmd = ["nvcc"] + NVCC_FLAGS + FAST_MATH.get(src, []) + (["-Xptxas", "-v"] if verbose else []) + ["-c", os.path.join(CSRC, src), "-o", obj]
         r = subprocess.run(cmd, capture_output=True, text=True)
         if r.returncode != 0:
             sys.stderr.write(" ".join(cmd) + "\n" + r.stdout + r.stderr)
