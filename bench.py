@@ -349,14 +349,15 @@ def main():
     flat = torch.zeros(P * 13, dtype=torch.float32, device=dev)      # map gradient [P,13], all-reduced when N > 1
     order = ["means3D", "opacities", "scales", "rotations", "colors"]
 
+    from gs2d_b200 import mapping
+
     def view_of(step):
-        return wl["sets"][(step * world + rank) % V]
+        return wl["sets"][mapping.view_of(step, rank, world if multi else 1, V)]
 
     def step_resident(step):
         color, others, g = arm.forward_backward(view_of(step))
         if multi:
-            torch.cat([g[k].reshape(-1) for k in order], out=flat)
-            dist.all_reduce(flat)
+            mapping.allreduce_map_gradient(mapping.pack_grads(g, flat))
         return color
 
     def barrier():
@@ -490,8 +491,7 @@ def main():
             loss = mapping_loss(color, allmap, s["gt_color"], s["gt_depth"])
             loss.backward()
             if multi:
-                torch.cat([params[k].grad.reshape(-1) for k in order], out=flat)
-                dist.all_reduce(flat)
+                mapping.allreduce_map_gradient(mapping.pack_grads({k: params[k].grad for k in order}, flat))
             freed[sl].record(cur)
             loss_host.copy_(loss.detach().reshape(1), non_blocking=True)
             cur.synchronize()             # the loop reads the loss on the host every step
