@@ -34,7 +34,7 @@ cudaEvent_t prof_event()
 const char* const kKernelNames[K_COUNT] = {
 	"preprocess_forward", "scan_tiles", "duplicate_keys", "histogram", "digit_base", "onesweep_pass",
 	"gather_ranges", "composite_forward", "composite_backward", "preprocess_backward", "mark_visible",
-	"memset", "memcpy", "knn", "footprint"};
+	"memset", "memcpy", "knn", "footprint", "composite_backward_instances"};
 }  // namespace
 void prof_mark(int id, cudaStream_t st, bool begin)
 {
@@ -110,7 +110,11 @@ BinningState BinningState::carve(void* base, size_t I, size_t tiles, size_t* byt
 	b.vals_b = c.take<uint32_t>(n);
 	b.instances = c.take<float>(n * REC_WORDS);
 	b.hit_inst = c.take<uint32_t>(n * 8 + 64);
-	b.hit_pix = c.take<uint32_t>((n / 32 + 4 * tiles + 8) * TILE_PIXELS);
+	b.hit_pix = c.take<uint32_t>((n / 32 + 4 * tiles + 8) * 2 * TILE_PIXELS);
+	b.hit_count = c.take<uint32_t>(n);
+	b.pair_incl = c.take<uint32_t>(n);
+	b.pair_status = c.take<uint64_t>(n / SCAN_TILE + 2);
+	b.pair_counters = c.take<uint32_t>(8);
 	b.keys_dbg = c.take<uint64_t>(n);
 	b.vals_dbg = c.take<uint32_t>(n);
 	size_t sort_bytes = 0;
@@ -164,7 +168,10 @@ extern "C" {
 size_t gs2d_geom_bytes(int32_t P, int32_t) { size_t b = 0; GeomState::carve(nullptr, (size_t)(P > 0 ? P : 0), &b); return b; }
 size_t gs2d_image_bytes(int32_t W, int32_t H) { size_t b = 0; ImageState::carve(nullptr, (size_t)W, (size_t)H, &b); return b; }
 size_t gs2d_binning_bytes(int64_t I, int32_t W, int32_t H) { size_t b = 0; BinningState::carve(nullptr, (size_t)(I > 0 ? I : 0), tiles_of(W, H), &b); return b; }
-size_t gs2d_backward_scratch_bytes(int32_t, int64_t I) { return (size_t)(I > 0 ? I : 0) * GRAD_WORDS * sizeof(float) + ALIGN; }
+size_t gs2d_backward_scratch_bytes(int32_t, int64_t I, int64_t pairs, int32_t W, int32_t H)
+{
+	return composite_backward_scratch_bytes(I, pairs, (int64_t)tiles_of(W, H));
+}
 size_t gs2d_sort_scratch_bytes(int64_t n)
 {
 	const size_t m = (size_t)(n > 0 ? n : 1);
@@ -195,7 +202,7 @@ int gs2d_forward_preprocess(const gs2d_settings* s, const gs2d_inputs* in, const
 }
 
 int gs2d_forward_render(const gs2d_settings* s, const gs2d_inputs* in, const gs2d_buffers* buffers,
-                        int64_t I, float* out_color, float* out_others, void* stream)
+                        int64_t I, float* out_color, float* out_others, int64_t* num_pairs_host, void* stream)
 {
 	GS2D_TRY(check_common(s, in, buffers));
 	cudaStream_t st = (cudaStream_t)stream;
@@ -231,7 +238,10 @@ int gs2d_forward_render(const gs2d_settings* s, const gs2d_inputs* in, const gs2
 	}
 	GS2D_TRY(launch_gather_ranges(*s, g, b.keys_b, b.vals_b, b.instances, im.ranges, I, st));
 	GS2D_TRY(debug_sync(*s, st));
-	GS2D_TRY(launch_footprint(*s, b.instances, b.keys_b, b.hit_inst, I, st));
+	GS2D_TRY(launch_footprint(*s, b.instances, b.keys_b, b.hit_inst, b.hit_count, I, st));
+	GS2D_TRY(launch_scan_u32(b.hit_count, b.pair_incl, I, b.pair_status, b.pair_counters, st));
+	if (num_pairs_host)   // 8 bytes: counters[1] = total, counters[2] = 0 -> a whole int64, before the compositing kernel
+		GS2D_CUDA_OK(cudaMemcpyAsync(num_pairs_host, b.pair_counters + 1, 2 * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
 	GS2D_TRY(debug_sync(*s, st));
 	GS2D_TRY(launch_composite_forward(*s, *in, im, b.instances, b.hit_inst, b.hit_pix, out_color, out_others, st));
 	GS2D_TRY(debug_sync(*s, st));
@@ -255,12 +265,24 @@ int gs2d_forward(const gs2d_settings* s, const gs2d_inputs* in, const gs2d_buffe
 	}
 	*num_rendered_io = count;
 	if (count > capacity) return GS2D_ERR_CAPACITY;
-	return gs2d_forward_render(s, in, buffers, count, out_color, out_others, stream);
+	return gs2d_forward_render(s, in, buffers, count, out_color, out_others, nullptr, stream);
+}
+
+int gs2d_forward_pair_count(const gs2d_settings* s, const gs2d_buffers* buffers, int64_t I, int64_t* num_pairs_host,
+                            void* stream)
+{
+	if (!s || !buffers || !num_pairs_host) return GS2D_ERR_INVALID;
+	if (I <= 0) { *num_pairs_host = 0; return GS2D_OK; }
+	if (!buffers->binning) return GS2D_ERR_INVALID;
+	BinningState b = BinningState::carve(buffers->binning, (size_t)I, tiles_of(s->image_width, s->image_height), nullptr);
+	GS2D_CUDA_OK(cudaMemcpyAsync(num_pairs_host, b.pair_counters + 1, 2 * sizeof(uint32_t), cudaMemcpyDeviceToHost,
+	                             (cudaStream_t)stream));
+	return GS2D_OK;
 }
 
 int gs2d_backward(const gs2d_settings* s, const gs2d_inputs* in, const gs2d_buffers* buffers,
-                  const int32_t* radii, int64_t I, const float* dL_dout_color, const float* dL_dout_others,
-                  const gs2d_grads* grads, void* scratch, void* stream)
+                  const int32_t* radii, int64_t I, int64_t num_pairs, const float* dL_dout_color,
+                  const float* dL_dout_others, const gs2d_grads* grads, void* scratch, void* stream)
 {
 	GS2D_TRY(check_common(s, in, buffers));
 	cudaStream_t st = (cudaStream_t)stream;
@@ -271,14 +293,15 @@ int gs2d_backward(const gs2d_settings* s, const gs2d_inputs* in, const gs2d_buff
 	    !grads->dL_dtransMat || !grads->dL_dscales || !grads->dL_drotations)
 		return GS2D_ERR_INVALID;
 	if (in->shs && !grads->dL_dsh) return GS2D_ERR_INVALID;
+	if (num_pairs < 0) return GS2D_ERR_INVALID;
 	GeomState g = GeomState::carve(buffers->geom, (size_t)s->P, nullptr);
 	ImageState im = ImageState::carve(buffers->image, (size_t)s->image_width, (size_t)s->image_height, nullptr);
-	float* rows = (float*)scratch;
+	float* rows = nullptr;
 	if (I > 0) {
 		if (!scratch || !buffers->binning) return GS2D_ERR_INVALID;
 		BinningState b = BinningState::carve(buffers->binning, (size_t)I, tiles_of(s->image_width, s->image_height), nullptr);
-		// no zero-fill: composite_backward writes every instance row exactly once
-		GS2D_TRY(launch_composite_backward(*s, *in, im, b.instances, b.hit_inst, b.hit_pix, dL_dout_color, dL_dout_others, rows, st));
+		// no zero-fill: every instance row is written exactly once
+		GS2D_TRY(launch_composite_backward(*s, *in, im, b, I, num_pairs, dL_dout_color, dL_dout_others, scratch, &rows, st));
 		GS2D_TRY(debug_sync(*s, st));
 	}
 	GS2D_TRY(launch_preprocess_backward(*s, *in, g, radii, rows, *grads, st));

@@ -102,8 +102,13 @@ struct BinningState {
 	uint32_t* vals_b;         // [I]
 	float* instances;         // [I,20]
 	uint32_t* hit_inst;       // [I,8] per-instance footprint mask in tile pixel order (footprint.cu)
-	uint32_t* hit_pix;        // [I/32 + 4*tiles, 256] per-pixel contribution words written by the forward pass:
-	                          // tile t, batch b, word g at ((range.x >> 5) + 4*t + 4*b + g) * 256 + pixel thread
+	uint32_t* hit_pix;        // [I/32 + 4*tiles, 2, 256] per-pixel words written by the forward pass: tile t, batch b,
+	                          // word g at ((((range.x >> 5) + 4*t + 4*b + g) * 2 + k) * 256 + pixel thread;
+	                          // k = 0: pairs that contributed, k = 1: pairs of the footprint masks
+	uint32_t* hit_count;      // [I] footprint-mask bits per instance
+	uint32_t* pair_incl;      // [I] inclusive scan of hit_count = end of the instance's pair-slot range
+	uint64_t* pair_status;    // scan look-back status
+	uint32_t* pair_counters;  // [8]: [1] = total number of pair slots
 	uint64_t* keys_dbg;       // [I] copy of the unsorted keys
 	uint32_t* vals_dbg;       // [I]
 	SortScratch sort;
@@ -124,7 +129,7 @@ void count_launch(int n = 1);
 // Optional per-kernel CUDA-event timing (gs2d_timing_* in include/gs2d.h) -------------------------
 enum KernelId {
 	K_PREPROCESS_FWD = 0, K_SCAN, K_DUPLICATE, K_HISTOGRAM, K_DIGIT_BASE, K_ONESWEEP, K_GATHER_RANGES,
-	K_COMPOSITE_FWD, K_COMPOSITE_BWD, K_PREPROCESS_BWD, K_MARK_VISIBLE, K_MEMSET, K_MEMCPY, K_KNN, K_FOOTPRINT, K_COUNT
+	K_COMPOSITE_FWD, K_COMPOSITE_BWD, K_PREPROCESS_BWD, K_MARK_VISIBLE, K_MEMSET, K_MEMCPY, K_KNN, K_FOOTPRINT, K_COMPOSITE_BWD_INST, K_COUNT
 };
 extern bool g_timing_on;
 void prof_mark(int id, cudaStream_t st, bool begin);
@@ -138,6 +143,7 @@ struct ProfScope {
 int launch_preprocess_forward(const gs2d_settings& s, const gs2d_inputs& in, const GeomState& g,
                               int32_t* radii, cudaStream_t st);
 int launch_scan_tiles(const GeomState& g, int P, cudaStream_t st);
+int launch_scan_u32(const uint32_t* in, uint32_t* out, long long n, uint64_t* status, uint32_t* counters, cudaStream_t st);
 int launch_duplicate(const gs2d_settings& s, const GeomState& g, const int32_t* radii_unused,
                      const BinningState& b, int64_t I, cudaStream_t st);
 int launch_sort_pairs(int64_t n, const uint64_t* keys_a, const uint32_t* vals_a, uint64_t* keys_b,
@@ -147,16 +153,16 @@ int launch_gather_ranges(const gs2d_settings& s, const GeomState& g, const uint6
                          const uint32_t* point_list, float* instances, uint32_t* ranges, int64_t I,
                          cudaStream_t st);
 int launch_footprint(const gs2d_settings& s, const float* instances, const uint64_t* keys_sorted,
-                     uint32_t* hit_inst, int64_t I, cudaStream_t st);
+                     uint32_t* hit_inst, uint32_t* hit_count, int64_t I, cudaStream_t st);
 int launch_footprint_audit(const gs2d_settings& s, const float* instances, const uint64_t* keys_sorted,
                            const uint32_t* hit_inst, int64_t I, unsigned long long* counts, cudaStream_t st);
 int launch_composite_forward(const gs2d_settings& s, const gs2d_inputs& in, const ImageState& im,
                              const float* instances, const uint32_t* hit_inst, uint32_t* hit_pix, float* out_color,
                              float* out_others, cudaStream_t st);
+size_t composite_backward_scratch_bytes(int64_t I, int64_t pairs, int64_t tiles);
 int launch_composite_backward(const gs2d_settings& s, const gs2d_inputs& in, const ImageState& im,
-                              const float* instances, const uint32_t* hit_inst, const uint32_t* hit_pix,
-                              const float* dL_dcolor,
-                              const float* dL_dothers, float* grad_rows, cudaStream_t st);
+                              const BinningState& b, int64_t I, int64_t pairs, const float* dL_dcolor,
+                              const float* dL_dothers, void* scratch, float** grad_rows_out, cudaStream_t st);
 int launch_preprocess_backward(const gs2d_settings& s, const gs2d_inputs& in, const GeomState& g,
                                const int32_t* radii, const float* grad_rows, const gs2d_grads& out,
                                cudaStream_t st);

@@ -5,23 +5,25 @@
 // *final* per-pixel statistics, opacity gradient through the clamped alpha), but the work is split by
 // what it depends on, so that every lane does useful work and nothing is reduced with atomics:
 //
-//   phase A (per PIXEL, sequential back to front, lanes = 32 pixels of a warp):
+//   kernel A (per PIXEL, sequential back to front; one CTA per tile, lanes = 32 pixels of a warp):
 //       the order-dependent part only -- transmittance T = T / (1 - alpha), the suffix recurrences for
 //       colour / depth / alpha / normal / dL_dT (CR/backward.cu:323-410).  Every pixel walks ITS OWN list of
 //       the pairs that contributed in the forward pass (recorded there, one word per pixel and 32
-//       instances), i.e. ~17 instances per tile instead of ~250 and no skip tests, and leaves three scalars per pair -- dL/dalpha, dL/dz, w = alpha * T -- plus its
-//       pixel id in the pair's 16-byte slot in shared memory.  Slots are laid out per instance
-//       (slot = instance base + rank of the pixel inside the instance's mask).
-//   phase B (per INSTANCE, lanes = that instance's contributing pixels, half a warp per instance):
+//       instances), i.e. ~17 instances per tile instead of ~250 and no skip tests, and leaves three scalars
+//       per pair -- dL/dalpha, dL/dz, w = alpha * T -- plus its pixel id in the pair's 16-byte slot.  Slots
+//       live in global memory (L2), laid out per instance: slot = first slot of the instance (exclusive
+//       scan of the footprint-mask popcounts, computed in the forward pass) + rank of the pixel inside the
+//       instance's mask.  Pairs of the mask that did not contribute get an "empty" marker.
+//   kernel B (per INSTANCE, fully parallel over all instances of the frame, half a warp per instance):
 //       the geometric chain rule dL/d{Tu,Tv,Tw}, dL/dmean2D, dL/dopacity, dL/dnormal, dL/dcolour
-//       (CR/backward.cu:343, :396, :412-460) from the slot + the instance record, summed over the
-//       instance's pixels with 19 shuffles, and written as ONE plain 72-byte store into the instance's own
-//       gradient row: the reference issues 16 global atomicAdd per contributing (pixel, instance) pair;
-//       here a row is written exactly once, so no atomics and no zero-fill of the rows are needed.
+//       (CR/backward.cu:343, :396, :412-460) from the instance's slots (one coalesced read) + its record,
+//       summed over the instance's pixels with 19 shuffles, and written as ONE plain 72-byte store into the
+//       instance's own gradient row: the reference issues 16 global atomicAdd per contributing
+//       (pixel, instance) pair; here a row is written exactly once, so no atomics and no zero-fill.
 //
-// Instances come in batches of 128 (records + masks staged by TMA, two-stage mbarrier ring); a batch is
-// cut into sub-ranges whose pair count fits the slot buffer.  Rows are indexed by the instance's position
-// in surfel-major (unsorted) order, so preprocess_bwd.cu reads each surfel's rows contiguously.
+// Records + masks of a tile arrive in batches of 128 by TMA (two-stage mbarrier ring).  Rows are indexed by
+// the instance's position in surfel-major (unsorted) order, so preprocess_bwd.cu reads each surfel's rows
+// contiguously.
 #include "common.cuh"
 #include "tma.cuh"
 #include "pair.cuh"
@@ -32,7 +34,6 @@ namespace {
 
 constexpr int BWD_BATCH = 128;
 constexpr int BWD_STAGES = 2;
-constexpr int BWD_CAP = 2304;     // pair slots (16 B each) per sub-range; >= 256 = one full-tile instance
 
 struct PixelConst {
 	float T_final, final_A, final_D, final_D2;
@@ -57,11 +58,9 @@ struct PixelBwd {
 struct BwdSmem {
 	float4 rec[BWD_STAGES][BWD_BATCH * 5];
 	uint32_t mask[BWD_STAGES][BWD_BATCH * 8];
-	float4 slot[BWD_CAP];
-	float pix[6][TILE_PIXELS];          // dL_dpix (3), dL_dnormal (3) per pixel, for phase B
 	uint2 pref[BWD_BATCH];              // 8 packed bytes: hits of the instance in mask words 0..k-1
-	uint32_t base[BWD_BATCH + 1];       // exclusive prefix of the instances' hit counts within the batch
-	uint32_t wsum[8];
+	uint32_t base[BWD_BATCH];           // first pair slot of every instance of the batch (global index)
+	float pix[6][TILE_PIXELS];          // dL_dpix (3), dL_dnormal (3) per pixel, for phase B
 	uint32_t max_last[8];
 	uint64_t bar[BWD_STAGES];
 };
@@ -237,17 +236,17 @@ __device__ __forceinline__ void half_reduce18(float (&g)[GR_USED], int lane, flo
 }
 
 template <bool USE_SA>
-__global__ void __launch_bounds__(256, 3)
-composite_backward_kernel(int W, int H, unsigned gx, const uint2* __restrict__ ranges,
-                          const float4* __restrict__ instances, const uint32_t* __restrict__ hit_inst,
-                          const uint32_t* __restrict__ hit_pix, const float* __restrict__ bg,
-                          const float* __restrict__ final_T,
-                          const uint32_t* __restrict__ n_contrib, const float* __restrict__ median_depth,
-                          const float* __restrict__ depth_std, const float* __restrict__ dL_dpix,
-                          const float* __restrict__ dL_dothers, float* __restrict__ grad_rows)
+__global__ void __launch_bounds__(256)
+composite_backward_pixels_kernel(int W, int H, unsigned gx, const uint2* __restrict__ ranges,
+                                 const float4* __restrict__ instances, const uint32_t* __restrict__ hit_inst,
+                                 const uint32_t* __restrict__ hit_pix, const uint32_t* __restrict__ pair_incl,
+                                 const float* __restrict__ bg, const float* __restrict__ final_T,
+                                 const uint32_t* __restrict__ n_contrib, const float* __restrict__ median_depth,
+                                 const float* __restrict__ depth_std, const float* __restrict__ dL_dpix,
+                                 const float* __restrict__ dL_dothers, float4* __restrict__ slots,
+                                 float* __restrict__ grad_rows)
 {
-	extern __shared__ __align__(128) unsigned char smem_raw[];
-	BwdSmem& sm = *reinterpret_cast<BwdSmem*>(smem_raw);
+	__shared__ BwdSmem sm;
 
 	const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 	const unsigned tile = blockIdx.x;
@@ -315,175 +314,158 @@ composite_backward_kernel(int W, int H, unsigned gx, const uint2* __restrict__ r
 	for (int i = 0; i < 8; i++) bmax = max(bmax, sm.max_last[i]);
 	const int n_used = min((int)bmax, n);            // instances [0, n_used) can matter
 	const int nb = (n_used + BWD_BATCH - 1) / BWD_BATCH;
-
+	const int n_done = min(nb * BWD_BATCH, n);       // instances of whole batches: all their slots get written
 	const float4* tile_rec = instances + 5 * (size_t)range.x;
-	const uint32_t* tile_mask = hit_inst + 8 * (size_t)range.x;
-	auto issue = [&](int b, int stage) {
-		const uint32_t cnt = (uint32_t)min(n_used - b * BWD_BATCH, BWD_BATCH);
-		mbar_arrive_expect_tx(&sm.bar[stage], cnt * (80u + 32u));
-		tma_load_1d(&sm.rec[stage][0], tile_rec + 5 * (size_t)b * BWD_BATCH, cnt * 80u, &sm.bar[stage]);
-		tma_load_1d(&sm.mask[stage][0], tile_mask + 8 * (size_t)b * BWD_BATCH, cnt * 32u, &sm.bar[stage]);
-	};
-	if (tid == 0 && nb > 0) issue(nb - 1, 0);
-
 	// rows of the instances nobody reaches (behind every pixel's last contributor): zeros
-	for (int q = n_used + (tid >> 2); q < n; q += 64) {
+	for (int q = n_done + (tid >> 2); q < n; q += 64) {
 		const uint32_t row = __float_as_uint(tile_rec[5 * (size_t)q + 4].w);
 		float4* dst = reinterpret_cast<float4*>(grad_rows + (size_t)row * GRAD_WORDS);
 		dst[tid & 3] = make_float4(0.f, 0.f, 0.f, 0.f);
 		if ((tid & 3) == 0) dst[4] = make_float4(0.f, 0.f, 0.f, 0.f);
 	}
+	if (nb == 0) return;
+
+	const uint32_t* tile_mask = hit_inst + 8 * (size_t)range.x;
+	auto issue = [&](int b, int stage) {
+		const uint32_t cnt = (uint32_t)min(n - b * BWD_BATCH, BWD_BATCH);
+		mbar_arrive_expect_tx(&sm.bar[stage], cnt * (80u + 32u));
+		tma_load_1d(&sm.rec[stage][0], tile_rec + 5 * (size_t)b * BWD_BATCH, cnt * 80u, &sm.bar[stage]);
+		tma_load_1d(&sm.mask[stage][0], tile_mask + 8 * (size_t)b * BWD_BATCH, cnt * 32u, &sm.bar[stage]);
+	};
+	if (tid == 0) issue(nb - 1, 0);
 
 	const uint32_t lane_lt = (1u << lane) - 1u;
-	const uint32_t* pix_words = hit_pix + ((size_t)(range.x >> 5) + 4 * (size_t)tile) * TILE_PIXELS;
-	const int hw = tid >> 4, hl = tid & 15;          // half-warp id / lane inside it (phase B)
+	const uint32_t* pix_words = hit_pix + ((size_t)(range.x >> 5) + 4 * (size_t)tile) * 2 * TILE_PIXELS;
+	const float4 empty = make_float4(0.f, 0.f, 0.f, __int_as_float(-1));
 
 	for (int it = 0; it < nb; it++) {
 		const int b = nb - 1 - it;
 		const int stage = it & 1;
 		const uint32_t parity = (uint32_t)(it >> 1) & 1u;
-		__syncthreads();   // batch it-1 fully consumed -> its stage may be overwritten
+		__syncthreads();   // batch it-1 fully consumed -> its stage and pref/base may be overwritten
 		if (tid == 0 && it + 1 < nb) issue(b - 1, stage ^ 1);
+		const int cnt = min(n - b * BWD_BATCH, BWD_BATCH);
+		// words of this pixel: pairs that contributed / pairs that own a slot
+		uint32_t used[BWD_BATCH / 32], foot[BWD_BATCH / 32];
+#pragma unroll
+		for (int g = 0; g < BWD_BATCH / 32; g++) {
+			used[g] = pix_words[(size_t)((b * (BWD_BATCH / 32) + g) * 2 + 0) * TILE_PIXELS + tid];
+			foot[g] = pix_words[(size_t)((b * (BWD_BATCH / 32) + g) * 2 + 1) * TILE_PIXELS + tid];
+		}
+		if (tid < cnt) {
+			const size_t gi = (size_t)range.x + (size_t)b * BWD_BATCH + tid;
+			sm.base[tid] = gi ? pair_incl[gi - 1] : 0u;
+		}
 		if (warp == 0) mbar_wait(&sm.bar[stage], parity);
 		__syncthreads();
 
-		const int cnt = min(n_used - b * BWD_BATCH, BWD_BATCH);
 		const float4* recs = &sm.rec[stage][0];
 		const uint32_t* masks = &sm.mask[stage][0];
-
-		// per-instance hit counts: packed prefix over the 8 mask words, block-wide exclusive scan
-		if (tid < BWD_BATCH) {
+		if (tid < cnt) {
 			uint32_t run = 0, lo = 0, hi = 0;
-			if (tid < cnt) {
 #pragma unroll
-				for (int k = 0; k < 8; k++) {
-					if (k < 4) lo |= run << (8 * k); else hi |= run << (8 * (k - 4));
-					run += __popc(masks[tid * 8 + k]);
-				}
+			for (int k = 0; k < 8; k++) {
+				if (k < 4) lo |= run << (8 * k); else hi |= run << (8 * (k - 4));
+				run += __popc(masks[tid * 8 + k]);
 			}
 			sm.pref[tid] = make_uint2(lo, hi);
-			uint32_t incl = run;
-#pragma unroll
-			for (int o = 1; o < 32; o <<= 1) {
-				const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
-				if (lane >= o) incl += t;
-			}
-			if (lane == 31) sm.wsum[warp] = incl;
-			sm.base[tid + 1] = incl;   // warp-local inclusive value; the other warps' totals are added below
 		}
 		__syncthreads();
-		if (tid < BWD_BATCH) {
-			uint32_t off = 0;
-			for (int w = 0; w < warp; w++) off += sm.wsum[w];
-			if (off) sm.base[tid + 1] += off;
-		}
-		if (tid == 0) sm.base[0] = 0;
 
-		// the pairs of this batch that contributed in the forward pass, one word per pixel and 32 instances
-		uint32_t hits[BWD_BATCH / 32];
+		// every pixel walks the pairs of its footprint words, back to front
 #pragma unroll
-		for (int g = 0; g < BWD_BATCH / 32; g++)
-			hits[g] = pix_words[(size_t)(b * (BWD_BATCH / 32) + g) * TILE_PIXELS + tid];
-		__syncthreads();
-
-		// sub-ranges of roughly equal pair counts, each fitting the slot buffer
-		const uint32_t total = sm.base[cnt];
-		const uint32_t parts = (total + BWD_CAP - 1) / BWD_CAP;
-		const uint32_t target = parts ? (total + parts - 1) / parts + 128 : 0;
-		const uint32_t cap = min((uint32_t)BWD_CAP, max(target, 256u));
-		int hi = cnt;
-		while (hi > 0) {
-			// largest sub-range [lo, hi) whose pairs fit the slot buffer
-			const uint32_t total_hi = sm.base[hi];
-			const bool fits = tid < hi && (total_hi - sm.base[tid] <= cap);
-			const int lo = hi - __syncthreads_count(fits);   // also: phase B of the previous sub-range is done
-			const uint32_t base_lo = sm.base[lo];
-			// slots of pairs that did not contribute (mask superset, terminated pixels) stay marked empty
-			for (uint32_t k = tid; k < total_hi - base_lo; k += 256) sm.slot[k].w = __int_as_float(-1);
-			__syncthreads();
-
-			// ---- phase A: every pixel walks its hits in [lo, hi), back to front
-#pragma unroll
-			for (int g = BWD_BATCH / 32 - 1; g >= 0; g--) {
-				const int a = max(lo - 32 * g, 0), e = min(hi - 32 * g, 32);
-				if (e <= a) continue;
-				uint32_t m = hits[g] & (e == 32 ? 0xffffffffu : ((1u << e) - 1u)) & ~((1u << a) - 1u);
-				while (m) {
-					const int jl = 31 - __clz(m);
-					m &= ~(1u << jl);
-					const int j = g * 32 + jl;
-					const uint32_t q = (uint32_t)(b * BWD_BATCH + j);
-					const uint2 pf = sm.pref[j];
-					const uint32_t before = ((warp < 4 ? pf.x >> (8 * warp) : pf.y >> (8 * (warp - 4))) & 0xffu);
-					const uint32_t si = sm.base[j] - base_lo + before + __popc(masks[j * 8 + warp] & lane_lt);
+		for (int g = BWD_BATCH / 32 - 1; g >= 0; g--) {
+			uint32_t m = foot[g];
+			while (m) {
+				const int jl = 31 - __clz(m);
+				m &= ~(1u << jl);
+				const int j = g * 32 + jl;
+				const uint2 pf = sm.pref[j];
+				const uint32_t before = ((warp < 4 ? pf.x >> (8 * warp) : pf.y >> (8 * (warp - 4))) & 0xffu);
+				float4* dst = slots + (sm.base[j] + before + __popc(masks[j * 8 + warp] & lane_lt));
+				if ((used[g] >> jl) & 1u) {
 					float A, dz, w;
-					pixel_step<USE_SA>(recs + j * 5, pxf, pyf, q, pc, st, A, dz, w);
-					sm.slot[si] = make_float4(A, dz, w, __int_as_float(tid));
+					pixel_step<USE_SA>(recs + j * 5, pxf, pyf, (uint32_t)(b * BWD_BATCH + j), pc, st, A, dz, w);
+					*dst = make_float4(A, dz, w, __int_as_float(tid));
+				} else {
+					*dst = empty;
 				}
 			}
-			__syncthreads();
+		}
+	}
 
-			// ---- phase B: half a warp per instance, lanes over the instance's pairs
-			const int rounds = (hi - lo + 15) >> 4;
-			for (int r = 0; r < rounds; r++) {
-				const int j = hi - 1 - (r * 16 + hw);
-				float g[GR_USED];
+	// ---- phase B: half a warp per instance of the tile, lanes over the instance's pair slots (just written by
+	// this CTA: L2-hot); pixel constants from shared memory, the record straight from global memory.
+	__syncthreads();
+	const int hw = tid >> 4, hl = tid & 15;
+	for (int q0 = 0; q0 < n_done; q0 += 16) {
+		const int q = q0 + hw;
+		float g[GR_USED];
 #pragma unroll
-				for (int i = 0; i < GR_USED; i++) g[i] = 0.f;
-				uint32_t row = 0;
-				if (j >= lo) {
-					const float4 r0 = recs[j * 5], r1 = recs[j * 5 + 1], r2 = recs[j * 5 + 2];
-					row = __float_as_uint(recs[j * 5 + 4].w);
-					const uint32_t s0 = sm.base[j] - base_lo, c = sm.base[j + 1] - sm.base[j];
-					for (uint32_t k = hl; k < c; k += 16) {
-						const float4 sl = sm.slot[s0 + k];
-						const int p = __float_as_int(sl.w);
-						if (p >= 0)
-							instance_step(r0, r1, r2, (float)(tx * TILE + (p & 15)), (float)(ty * TILE + (p >> 4)),
-							              sl.x, sl.y, sl.z, &sm.pix[0][0], p, g);
-					}
-				}
-				__syncwarp();
-				float a, bsum;
-				half_reduce18(g, lane, a, bsum);
-				if (j >= lo) {
-					float* dst = grad_rows + (size_t)row * GRAD_WORDS;
-					dst[hl] = a;
-					if ((hl & 7) == 0) dst[16 + (hl >> 3)] = bsum;
-				}
+		for (int k = 0; k < GR_USED; k++) g[k] = 0.f;
+		uint32_t row = 0;
+		if (q < n_done) {
+			const float4* rec = tile_rec + 5 * (size_t)q;
+			const float4 r0 = rec[0], r1 = rec[1], r2 = rec[2];
+			row = __float_as_uint(rec[4].w);
+			const size_t gi = (size_t)range.x + q;
+			const uint32_t s0 = gi ? pair_incl[gi - 1] : 0u, s1 = pair_incl[gi];
+			for (uint32_t k = s0 + hl; k < s1; k += 16) {
+				const float4 sl = slots[k];
+				const int p = __float_as_int(sl.w);
+				if (p >= 0)
+					instance_step(r0, r1, r2, (float)(tx * TILE + (p & 15)), (float)(ty * TILE + (p >> 4)), sl.x, sl.y,
+					              sl.z, &sm.pix[0][0], p, g);
 			}
-			hi = lo;
+		}
+		__syncwarp();
+		float a, bsum;
+		half_reduce18(g, lane, a, bsum);
+		if (q < n_done) {
+			float* dst = grad_rows + (size_t)row * GRAD_WORDS;
+			dst[hl] = a;
+			if ((hl & 7) == 0) dst[16 + (hl >> 3)] = bsum;
 		}
 	}
 }
 
 }  // namespace
 
+size_t composite_backward_scratch_bytes(int64_t I, int64_t pairs, int64_t tiles)
+{
+	Carver c(nullptr);
+	c.take<float>((size_t)(I > 0 ? I : 0) * GRAD_WORDS);
+	c.take<float4>((size_t)(pairs > 0 ? pairs : 0) + 16);
+	(void)tiles;
+	return c.total();
+}
+
 int launch_composite_backward(const gs2d_settings& s, const gs2d_inputs& in, const ImageState& im,
-                              const float* instances, const uint32_t* hit_inst, const uint32_t* hit_pix,
-                              const float* dL_dcolor, const float* dL_dothers, float* grad_rows, cudaStream_t st)
+                              const BinningState& b, int64_t I, int64_t pairs, const float* dL_dcolor,
+                              const float* dL_dothers, void* scratch, float** grad_rows_out, cudaStream_t st)
 {
 	const int W = s.image_width, H = s.image_height;
 	const unsigned gx = (W + TILE - 1) / TILE, gy = (H + TILE - 1) / TILE;
-	if (gx * gy == 0) return GS2D_OK;
-	static bool attr_set = false;
-	if (!attr_set) {
-		GS2D_CUDA_OK(cudaFuncSetAttribute(composite_backward_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-		                                  (int)sizeof(BwdSmem)));
-		GS2D_CUDA_OK(cudaFuncSetAttribute(composite_backward_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-		                                  (int)sizeof(BwdSmem)));
-		attr_set = true;
+	Carver c(scratch);
+	float* rows = c.take<float>((size_t)I * GRAD_WORDS);
+	float4* slots = c.take<float4>((size_t)(pairs > 0 ? pairs : 0) + 16);
+	*grad_rows_out = rows;
+	if (gx * gy == 0 || I <= 0) return GS2D_OK;
+	{
+		ProfScope ps(K_COMPOSITE_BWD, st);
+		if (s.use_sa)
+			composite_backward_pixels_kernel<true><<<gx * gy, 256, 0, st>>>(
+				W, H, gx, (const uint2*)im.ranges, (const float4*)b.instances, b.hit_inst, b.hit_pix, b.pair_incl,
+				in.background, im.final_T, im.n_contrib, im.median_depth, im.depth_std, dL_dcolor, dL_dothers, slots,
+				rows);
+		else
+			composite_backward_pixels_kernel<false><<<gx * gy, 256, 0, st>>>(
+				W, H, gx, (const uint2*)im.ranges, (const float4*)b.instances, b.hit_inst, b.hit_pix, b.pair_incl,
+				in.background, im.final_T, im.n_contrib, im.median_depth, im.depth_std, dL_dcolor, dL_dothers, slots,
+				rows);
+		count_launch();
 	}
-	ProfScope ps(K_COMPOSITE_BWD, st);
-	if (s.use_sa)
-		composite_backward_kernel<true><<<gx * gy, 256, sizeof(BwdSmem), st>>>(
-			W, H, gx, (const uint2*)im.ranges, (const float4*)instances, hit_inst, hit_pix, in.background, im.final_T,
-			im.n_contrib, im.median_depth, im.depth_std, dL_dcolor, dL_dothers, grad_rows);
-	else
-		composite_backward_kernel<false><<<gx * gy, 256, sizeof(BwdSmem), st>>>(
-			W, H, gx, (const uint2*)im.ranges, (const float4*)instances, hit_inst, hit_pix, in.background, im.final_T,
-			im.n_contrib, im.median_depth, im.depth_std, dL_dcolor, dL_dothers, grad_rows);
-	count_launch();
+	GS2D_CUDA_OK(cudaGetLastError());
 	GS2D_CUDA_OK(cudaGetLastError());
 	return GS2D_OK;
 }

@@ -122,7 +122,7 @@ composite_forward_kernel(int W, int H, unsigned gx, const uint2* __restrict__ ra
 	};
 	if (tid == 0 && nb > 0) issue(0, 0);
 
-	uint32_t* pix_words = hit_pix + ((size_t)(range.x >> 5) + 4 * (size_t)tile) * TILE_PIXELS;
+	uint32_t* pix_words = hit_pix + ((size_t)(range.x >> 5) + 4 * (size_t)tile) * 2 * TILE_PIXELS;
 
 	PixelFwd px;
 	bool done = !inside;
@@ -171,8 +171,10 @@ composite_forward_kernel(int W, int H, unsigned gx, const uint2* __restrict__ ra
 				if (eval_pair<USE_SA>(recs + (g * 32 + jl) * 5, pxf, pyf, (uint32_t)(b * FWD_BATCH + g * 32 + jl + 1), px, done))
 					used |= 1u << jl;
 			}
-			// the pairs that really contributed, for the backward pass (coalesced: one word per pixel thread)
-			pix_words[(size_t)(b * (FWD_BATCH / 32) + g) * TILE_PIXELS + tid] = used;
+			// for the backward pass (coalesced, one word per pixel thread): the pairs that really contributed,
+			// and the pairs of the footprint masks (they own a gradient-pair slot each)
+			pix_words[(size_t)((b * (FWD_BATCH / 32) + g) * 2 + 0) * TILE_PIXELS + tid] = used;
+			pix_words[(size_t)((b * (FWD_BATCH / 32) + g) * 2 + 1) * TILE_PIXELS + tid] = hits[g];
 		}
 	}
 

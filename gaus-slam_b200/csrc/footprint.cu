@@ -42,11 +42,12 @@ __device__ __forceinline__ uint32_t span_bits(int xa, int xb, int lo, int hi)
 
 __global__ void __launch_bounds__(256)
 footprint_kernel(long long I, unsigned gx, float inv_gx, const float4* __restrict__ instances,
-                 const uint64_t* __restrict__ keys_sorted, uint16_t* __restrict__ hit_rows)
+                 const uint64_t* __restrict__ keys_sorted, uint16_t* __restrict__ hit_rows,
+                 uint32_t* __restrict__ hit_count)
 {
 	const int row = threadIdx.x & 15;                                              // tile row of this lane
 	const long long i = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 4;   // instance of this half-warp
-	if (i >= I) return;
+	if (i >= I) return;      // whole half-warps leave together (I * 16 threads are live)
 	const float4* rec = instances + 5 * (size_t)i;
 	const float4 r0 = rec[0], r1 = rec[1], r2 = rec[2];
 	const uint32_t bw = __float_as_uint(rec[3].w);
@@ -59,7 +60,7 @@ footprint_kernel(long long I, unsigned gx, float inv_gx, const float4* __restric
 		const float ox = (float)((tile - ty * gx) * TILE), oy = (float)(ty * TILE);
 		const uint32_t full = span_bits(bx0, bx1, 0, 15);
 		bits = full;                                                       // fallback: the whole box row
-		if (!(a255 == a255)) { hit_rows[16 * (size_t)i + row] = (uint16_t)bits; return; }   // NaN opacity: no culling
+		const bool nan_opacity = !(a255 == a255);   // NaN opacity: no culling
 		const float c = 2.0f * __logf(fmaxf(a255, 1.0f)) * FOOT_C_SCALE + FOOT_C_BIAS;
 		const float3 Tu = make_float3(r0.x, r0.y, r0.z), Tv = make_float3(r1.x, r1.y, r1.z),
 		             Tw = make_float3(r2.x, r2.y, r2.z);
@@ -76,7 +77,7 @@ footprint_kernel(long long I, unsigned gx, float inv_gx, const float4* __restric
 		const float qc = q.x * q.x + q.y * q.y - c * q.z * q.z;
 		// scale-free conditioning test: qa must be clearly positive (an ellipse section along the row)
 		const float a2 = A.x * A.x + A.y * A.y;
-		if (qa > 1e-3f * a2 && qa == qa && qb == qb && qc == qc) {
+		if (!nan_opacity && qa > 1e-3f * a2 && qa == qa && qb == qb && qc == qc) {
 			const float disc = qb * qb - qa * qc;
 			const float off = xc - ox;   // u -> tile-local x
 			uint32_t m = 0;
@@ -103,6 +104,12 @@ footprint_kernel(long long I, unsigned gx, float inv_gx, const float4* __restric
 		}
 	}
 	hit_rows[16 * (size_t)i + row] = (uint16_t)bits;
+	// number of pairs of this instance (sum over the 16 rows of this half-warp)
+	const uint32_t hmask = (threadIdx.x & 16) ? 0xffff0000u : 0x0000ffffu;
+	uint32_t cnt = __popc(bits);
+#pragma unroll
+	for (int o = 8; o; o >>= 1) cnt += __shfl_xor_sync(hmask, cnt, o);
+	if (row == 0) hit_count[i] = cnt;
 }
 
 // Audit (tests only): one thread per instance evaluates the exact tests (pair_front) at all 256 tile pixels
@@ -158,14 +165,14 @@ int launch_footprint_audit(const gs2d_settings& s, const float* instances, const
 }
 
 int launch_footprint(const gs2d_settings& s, const float* instances, const uint64_t* keys_sorted,
-                     uint32_t* hit_inst, int64_t I, cudaStream_t st)
+                     uint32_t* hit_inst, uint32_t* hit_count, int64_t I, cudaStream_t st)
 {
 	if (I <= 0) return GS2D_OK;
 	const unsigned gx = (s.image_width + TILE - 1) / TILE;
 	const long long threads = I * 16;
 	ProfScope ps(K_FOOTPRINT, st);
 	footprint_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, st>>>(I, gx, 1.0f / (float)gx, (const float4*)instances,
-	                                                                    keys_sorted, (uint16_t*)hit_inst);
+	                                                                    keys_sorted, (uint16_t*)hit_inst, hit_count);
 	count_launch();
 	GS2D_CUDA_OK(cudaGetLastError());
 	return GS2D_OK;

@@ -272,19 +272,25 @@ int launch_preprocess_forward(const gs2d_settings& s, const gs2d_inputs& in, con
 	return GS2D_OK;
 }
 
-int launch_scan_tiles(const GeomState& g, int P, cudaStream_t st)
+// Inclusive scan of n u32 values (single pass, decoupled look-back).  status: n / SCAN_TILE + 1 u64 words,
+// counters: 8 u32 words (both zeroed here); counters[1] receives the total.
+int launch_scan_u32(const uint32_t* in, uint32_t* out, long long n, uint64_t* status, uint32_t* counters, cudaStream_t st)
 {
-	const int blocks = (P + SCAN_TILE - 1) / SCAN_TILE;
-	{ ProfScope ps(K_MEMSET, st); GS2D_CUDA_OK(cudaMemsetAsync(g.scan_status, 0, sizeof(uint64_t) * (size_t)blocks, st)); }
-	{ ProfScope ps(K_MEMSET, st); GS2D_CUDA_OK(cudaMemsetAsync(g.counters, 0, sizeof(uint32_t) * 8, st)); }
-	{
+	const int blocks = (int)((n + SCAN_TILE - 1) / SCAN_TILE);
+	{ ProfScope ps(K_MEMSET, st); GS2D_CUDA_OK(cudaMemsetAsync(status, 0, sizeof(uint64_t) * (size_t)(blocks + 1), st)); }
+	{ ProfScope ps(K_MEMSET, st); GS2D_CUDA_OK(cudaMemsetAsync(counters, 0, sizeof(uint32_t) * 8, st)); }
+	if (blocks > 0) {
 		ProfScope ps(K_SCAN, st);
-		scan_tiles_kernel<<<blocks, SCAN_THREADS, 0, st>>>(g.tiles_touched, g.point_offsets, P,
-		                                                   (unsigned long long*)g.scan_status, g.counters);
+		scan_tiles_kernel<<<blocks, SCAN_THREADS, 0, st>>>(in, out, (int)n, (unsigned long long*)status, counters);
 		count_launch();
 	}
 	GS2D_CUDA_OK(cudaGetLastError());
 	return GS2D_OK;
+}
+
+int launch_scan_tiles(const GeomState& g, int P, cudaStream_t st)
+{
+	return launch_scan_u32(g.tiles_touched, g.point_offsets, P, g.scan_status, g.counters, st);
 }
 
 int launch_mark_visible(int P, const float* means3D, const float* view, const float* proj,

@@ -14,6 +14,11 @@ import torch
 from gs2d_b200 import _lib as L
 
 _pinned = {}
+# Pair-slot counts of recent forward passes (a by-product like num_rendered, needed to size the backward
+# scratch): ring of pinned int64 slots per device, looked up by the binning buffer's address.
+_PAIR_RING = 64
+_pair_slots = {}
+_pair_of_binning = {}
 
 
 def _stream_ptr(device) -> C.c_void_p:
@@ -39,6 +44,23 @@ def _pinned_i64(device) -> torch.Tensor:
     if key not in _pinned:
         _pinned[key] = torch.zeros(1, dtype=torch.int64).pin_memory()
     return _pinned[key]
+
+
+def _bucket(nbytes: int) -> int:
+    """Round a big scratch size up to a 32 MiB bucket: consecutive views differ a little in num_rendered, and
+    identical sizes let torch's caching allocator reuse the block instead of calling cudaMalloc."""
+    g = 1 << 25
+    return nbytes if nbytes < g else (nbytes + g - 1) // g * g
+
+
+def _pair_slot(device):
+    key = str(device)
+    if key not in _pair_slots:
+        _pair_slots[key] = [torch.zeros(_PAIR_RING, dtype=torch.int64).pin_memory(), 0]
+    ring = _pair_slots[key]
+    i = ring[1]
+    ring[1] = (i + 1) % _PAIR_RING
+    return ring[0], i
 
 
 def _settings(P, W, H, degree, M, use_sa, prefiltered, debug, tan_fovx, tan_fovy, scale_modifier):
@@ -90,11 +112,19 @@ def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations,
                                             n_host.data_ptr(), st), "gs2d_forward_preprocess")
         torch.cuda.current_stream(dev).synchronize()
         num_rendered = int(n_host[0]) if P else 0
-        binning = torch.empty((lib.gs2d_binning_bytes(num_rendered, W, H) if num_rendered else 0,), **u8)
+        binning = torch.empty((_bucket(lib.gs2d_binning_bytes(num_rendered, W, H)) if num_rendered else 0,), **u8)
         bufs.binning = _ptr(binning)
         bufs.binning_bytes = binning.numel()
+        pairs_ptr = None
+        if num_rendered:
+            ring, slot = _pair_slot(dev)
+            pairs_ptr = ring.data_ptr() + 8 * slot
+            C.c_int64.from_address(pairs_ptr).value = -1      # "not there yet"
+            if len(_pair_of_binning) > 4 * _PAIR_RING:
+                _pair_of_binning.clear()
+            _pair_of_binning[binning.data_ptr()] = pairs_ptr
         L.check(lib.gs2d_forward_render(C.byref(s), C.byref(i), C.byref(bufs), num_rendered,
-                                        _ptr(out_color), _ptr(out_others), st), "gs2d_forward_render")
+                                        _ptr(out_color), _ptr(out_others), pairs_ptr, st), "gs2d_forward_render")
     return num_rendered, out_color, out_others, radii, geom, binning, img
 
 
@@ -123,9 +153,20 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
     if P == 0:
         return g_means2D, g_colors, g_opacity, g_means3D, g_transMat, g_sh, g_scales, g_rot
 
+    num_pairs = 0
+    if int(R) > 0:
+        entry = _pair_of_binning.get(binningBuffer.data_ptr())
+        if entry is None:
+            raise RuntimeError("rasterize_gaussians_backward: binningBuffer does not come from a forward pass of this "
+                               "process (pair-slot count unknown)")
+        cell = C.c_int64.from_address(entry)
+        while cell.value < 0:       # copied right after the footprint scan, long before the forward pass ended
+            pass
+        num_pairs = int(cell.value)
     with torch.cuda.device(dev):
         st = _stream_ptr(dev)
-        scratch = torch.empty((lib.gs2d_backward_scratch_bytes(P, int(R)),), dtype=torch.uint8, device=dev)
+        scratch = torch.empty((_bucket(lib.gs2d_backward_scratch_bytes(P, int(R), num_pairs, W, H)),),
+                              dtype=torch.uint8, device=dev)
         s = _settings(P, W, H, degree, M, use_sa, False, debug, tan_fovx, tan_fovy, scale_modifier)
         # opacities are not an input of backward (the forward stored them in the splat records)
         i = _inputs(background, means3D, sh, colors, means3D, scales, rotations, transMat_precomp,
@@ -136,7 +177,7 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
         grads = L.Grads(dL_dmeans2D=_ptr(g_means2D), dL_dcolors=_ptr(g_colors), dL_dopacity=_ptr(g_opacity),
                         dL_dmeans3D=_ptr(g_means3D), dL_dtransMat=_ptr(g_transMat), dL_dsh=_ptr(g_sh),
                         dL_dscales=_ptr(g_scales), dL_drotations=_ptr(g_rot))
-        L.check(lib.gs2d_backward(C.byref(s), C.byref(i), C.byref(bufs), _ptr(radii), int(R),
+        L.check(lib.gs2d_backward(C.byref(s), C.byref(i), C.byref(bufs), _ptr(radii), int(R), num_pairs,
                                   _ptr(dL_dout_color), _ptr(dL_dout_others), C.byref(grads), _ptr(scratch), st),
                 "gs2d_backward")
     return g_means2D, g_colors, g_opacity, g_means3D, g_transMat, g_sh, g_scales, g_rot

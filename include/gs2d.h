@@ -33,7 +33,7 @@
 extern "C" {
 #endif
 
-#define GS2D_ABI_VERSION 1
+#define GS2D_ABI_VERSION 2
 
 typedef enum gs2d_status {
 	GS2D_OK = 0,
@@ -109,10 +109,12 @@ int gs2d_forward_preprocess(const gs2d_settings* s, const gs2d_inputs* in,
  * (CR/rasterizer_impl.cu:295-347, CR/forward.cu:258-467).  `num_rendered` is the exact
  * instance count read back after stage 1; buffers->binning must hold
  * gs2d_binning_bytes(num_rendered, W, H) and buffers->image gs2d_image_bytes(W, H).
- * out_color [3,H,W], out_others [7,H,W] are fully written (no pre-zeroing needed). */
+ * out_color [3,H,W], out_others [7,H,W] are fully written (no pre-zeroing needed).
+ * When `num_pairs_host` (pinned host int64) is not NULL the pair-slot count (see gs2d_forward_pair_count) is
+ * copied into it asynchronously as soon as it is known, i.e. before the compositing kernel runs. */
 int gs2d_forward_render(const gs2d_settings* s, const gs2d_inputs* in,
                         const gs2d_buffers* buffers, int64_t num_rendered,
-                        float* out_color, float* out_others, void* stream);
+                        float* out_color, float* out_others, int64_t* num_pairs_host, void* stream);
 
 /* Convenience: stage 1, stream synchronise, stage 2 -- the reference's control flow
  * (CR/rasterizer_impl.cu:287 blocks on the same 4-byte read-back).  On entry
@@ -136,12 +138,19 @@ typedef struct gs2d_grads {
 	float* dL_drotations;  /* [P,4]                                                */
 } gs2d_grads;
 
+/* Number of (pixel, instance) pair slots of the last forward pass (sum of the footprint-mask popcounts): the
+ * backward pass keeps 16 bytes per pair in its scratch.  Enqueues an async 4-byte copy into `num_pairs_host`
+ * (pinned host int64; all 8 bytes are written); valid once the stream has passed gs2d_forward_render. */
+int gs2d_forward_pair_count(const gs2d_settings* s, const gs2d_buffers* buffers, int64_t num_rendered,
+                            int64_t* num_pairs_host, void* stream);
+
 /* Backward (CR/backward.cu:143-463 render, :466-664 preprocess).  `radii` and the three
  * buffers are those of the matching forward; dL_dout_color [3,H,W], dL_dout_others [7,H,W].
- * `scratch` must hold gs2d_backward_scratch_bytes(P, num_rendered) bytes. */
-size_t gs2d_backward_scratch_bytes(int32_t P, int64_t num_rendered);
+ * `scratch` must hold gs2d_backward_scratch_bytes(P, num_rendered, num_pairs, W, H) bytes. */
+size_t gs2d_backward_scratch_bytes(int32_t P, int64_t num_rendered, int64_t num_pairs, int32_t image_width,
+                                   int32_t image_height);
 int gs2d_backward(const gs2d_settings* s, const gs2d_inputs* in, const gs2d_buffers* buffers,
-                  const int32_t* radii, int64_t num_rendered,
+                  const int32_t* radii, int64_t num_rendered, int64_t num_pairs,
                   const float* dL_dout_color, const float* dL_dout_others,
                   const gs2d_grads* grads, void* scratch, void* stream);
 

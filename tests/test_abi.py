@@ -29,7 +29,7 @@ def test_library_exports_every_declared_symbol():
 
 def test_abi_version_and_strerror():
     lib = L.load()
-    assert lib.gs2d_abi_version() == 1
+    assert lib.gs2d_abi_version() == 2
     assert lib.gs2d_strerror(0).decode().lower().startswith("ok") or lib.gs2d_strerror(0)
     for code in (-1, -2, -3, -4):
         assert lib.gs2d_strerror(code).decode()
@@ -45,7 +45,7 @@ def test_size_queries_monotone_and_aligned():
     assert i1 >= 1200 * 680 * (12 + 8 + 4 + 4) + 75 * 43 * 8
     b1, b2 = lib.gs2d_binning_bytes(1000, 1200, 680), lib.gs2d_binning_bytes(1_000_000, 1200, 680)
     assert 0 < b1 < b2
-    assert lib.gs2d_backward_scratch_bytes(1000, 5000) >= 5000 * 80
+    assert lib.gs2d_backward_scratch_bytes(1000, 5000, 90000, 1200, 680) >= 5000 * 80 + 90000 * 16
     assert lib.gs2d_dist2_scratch_bytes(1000) > 1000 * 16
     assert lib.gs2d_sort_scratch_bytes(1 << 20) > 0
 
@@ -58,7 +58,7 @@ def test_argument_validation_without_gpu():
     i = L.Inputs()   # all NULL
     b = L.Buffers()
     assert lib.gs2d_forward_preprocess(C.byref(s), C.byref(i), C.byref(b), None, None, None) == L.GS2D_ERR_INVALID
-    assert lib.gs2d_forward_render(C.byref(s), C.byref(i), C.byref(b), 0, None, None, None) == L.GS2D_ERR_INVALID
+    assert lib.gs2d_forward_render(C.byref(s), C.byref(i), C.byref(b), 0, None, None, None, None) == L.GS2D_ERR_INVALID
     assert lib.gs2d_mark_visible(-1, None, None, None, None, None) == L.GS2D_ERR_INVALID
     assert lib.gs2d_mark_visible(0, None, None, None, None, None) == L.GS2D_OK
     assert lib.gs2d_dist2(-1, None, None, None, None) == L.GS2D_ERR_INVALID
