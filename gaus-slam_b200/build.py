@@ -32,16 +32,18 @@ def _stale() -> bool:
     return any(os.path.getmtime(d) > t for d in deps)
 
 
-def build(force: bool = False, verbose: bool = False) -> str:
-    if not force and not _stale():
+def build(force: bool = False, verbose: bool = False, variant: str = "", defines: tuple = ()) -> str:
+    """variant/defines build a tuning variant (lib/libgs2d_<variant>.so with extra -D flags) next to the default."""
+    lib = LIB if not variant else os.path.join(HERE, "lib", f"libgs2d_{variant}.so")
+    if not variant and not force and not _stale():
         return LIB
     os.makedirs(os.path.dirname(LIB), exist_ok=True)
-    objdir = os.path.join(HERE, "lib", "obj")
+    objdir = os.path.join(HERE, "lib", "obj" + ("_" + variant if variant else ""))
     os.makedirs(objdir, exist_ok=True)
 
     def one(src: str) -> str:
         obj = os.path.join(objdir, src + ".o")
-        cmd = ["nvcc"] + NVCC_FLAGS + FAST_MATH.get(src, []) + (["-Xptxas", "-v"] if verbose else []) + ["-c", os.path.join(CSRC, src), "-o", obj]
+        cmd = ["nvcc"] + NVCC_FLAGS + ["-D" + d for d in defines] + FAST_MATH.get(src, []) + (["-Xptxas", "-v"] if verbose else []) + ["-c", os.path.join(CSRC, src), "-o", obj]
         r = subprocess.run(cmd, capture_output=True, text=True)
         if r.returncode != 0:
             sys.stderr.write(" ".join(cmd) + "\n" + r.stdout + r.stderr)
@@ -52,13 +54,15 @@ def build(force: bool = False, verbose: bool = False) -> str:
 
     with ThreadPoolExecutor(max_workers=8) as ex:
         objs = list(ex.map(one, SOURCES))
-    r = subprocess.run(["nvcc", "-shared", "-o", LIB] + objs + ["-gencode", "arch=compute_100a,code=sm_100a"],
+    r = subprocess.run(["nvcc", "-shared", "-o", lib] + objs + ["-gencode", "arch=compute_100a,code=sm_100a"],
                        capture_output=True, text=True)
     if r.returncode != 0:
         sys.stderr.write(r.stdout + r.stderr)
         raise RuntimeError("link failed")
-    return LIB
+    return lib
 
 
 if __name__ == "__main__":
-    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))
+    _variant = next((a.split("=", 1)[1] for a in sys.argv if a.startswith("--variant=")), "")
+    _defs = tuple(a[2:] for a in sys.argv if a.startswith("-D"))
+    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv, variant=_variant, defines=_defs))

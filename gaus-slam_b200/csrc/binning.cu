@@ -172,13 +172,27 @@ onesweep_kernel(long long n, const uint64_t* __restrict__ keys_in, const uint32_
 		atomicExch(my_status, LB_PREFIX | total);
 	} else {
 		atomicExch(my_status, LB_AGG | total);
+		// look back eight predecessors at a time: the loads are independent, so their L2 latencies overlap
 		int pb = (int)bid - 1;
-		while (true) {
-			uint32_t s = *((volatile uint32_t*)(status + (size_t)pb * SORT_RADIX + tid));
-			if ((s >> 30) == 0) continue;
-			excl += s & LB_MASK;
-			if ((s >> 30) == 2) break;
-			pb--;
+		bool done = false;
+		while (!done) {
+			uint32_t sv[8];
+#pragma unroll
+			for (int k = 0; k < 8; k++)
+			{
+				sv[k] = 2u << 30;  // before block 0: an inclusive prefix of 0
+				if (pb - k >= 0) sv[k] = *((volatile uint32_t*)(status + (size_t)(pb - k) * SORT_RADIX + tid));
+			}
+			int used = 0;
+#pragma unroll
+			for (int k = 0; k < 8; k++) {
+				if (!done && used == k && (sv[k] >> 30) != 0) {
+					excl += sv[k] & LB_MASK;
+					used = k + 1;
+					done = (sv[k] >> 30) == 2;
+				}
+			}
+			pb -= used;
 		}
 		atomicExch(my_status, LB_PREFIX | (excl + total));
 	}

@@ -53,12 +53,18 @@ struct Carver {
 
 // ---- scan (decoupled look-back) geometry --------------------------------------------
 constexpr int SCAN_THREADS = 256;
-constexpr int SCAN_ITEMS = 8;
+#ifndef GS2D_SCAN_ITEMS
+#define GS2D_SCAN_ITEMS 8
+#endif
+constexpr int SCAN_ITEMS = GS2D_SCAN_ITEMS;
 constexpr int SCAN_TILE = SCAN_THREADS * SCAN_ITEMS;
 
 // ---- onesweep radix sort geometry ----------------------------------------------------
 constexpr int SORT_THREADS = 256;
-constexpr int SORT_ITEMS = 16;
+#ifndef GS2D_SORT_ITEMS
+#define GS2D_SORT_ITEMS 16
+#endif
+constexpr int SORT_ITEMS = GS2D_SORT_ITEMS;
 constexpr int SORT_TILE = SORT_THREADS * SORT_ITEMS;   // 4096 pairs per block
 constexpr int SORT_RADIX_BITS = 8;
 constexpr int SORT_RADIX = 1 << SORT_RADIX_BITS;

@@ -150,7 +150,7 @@ __device__ __forceinline__ void pixel_step(const float4* __restrict__ rec, float
 // A = dL/dalpha, dz = dL/dz, w = alpha * T from phase A; adds the 18 per-instance terms into g.
 __device__ __forceinline__ void instance_step(const float4 r0, const float4 r1, const float4 r2, float pxf, float pyf,
                                               float A, float dz, float w, const float* __restrict__ pixc, int pid,
-                                              float (&g)[GR_USED])
+                                              float (&g)[24])
 {
 	PairFront f;
 	float inv_pz;
@@ -188,51 +188,38 @@ __device__ __forceinline__ void instance_step(const float4 r0, const float4 r1, 
 	g[GR_OPA] += G * A;
 }
 
-// Sum g[0..17] over the 16 lanes of each half-warp.  On return lane L of a half holds the total of
-// g[L] in `a`; lanes with bit 3 clear / set hold the totals of g[16] / g[17] in `b`.
-__device__ __forceinline__ void half_reduce18(float (&g)[GR_USED], int lane, float& a, float& b)
+// Sum g[0..17] over the 8 lanes of each quarter-warp (reduce-scatter: 12 + 6 + 3 shuffles for four instances
+// at once).  g is padded to 24 values; on return lane L of a group (L = lane & 7) holds the totals of
+// g[3L], g[3L+1], g[3L+2] in g[0..2] (lanes 6, 7 hold padding).
+__device__ __forceinline__ void oct_reduce24(float (&g)[24], int lane)
 {
-	{
-		const bool up = lane & 8;
-#pragma unroll
-		for (int i = 0; i < 8; i++) {
-			const float send = up ? g[i] : g[i + 8];
-			const float keep = up ? g[i + 8] : g[i];
-			g[i] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
-		}
-		const float send = up ? g[16] : g[17];
-		const float keep = up ? g[17] : g[16];
-		g[16] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
-	}
 	{
 		const bool up = lane & 4;
 #pragma unroll
-		for (int i = 0; i < 4; i++) {
-			const float send = up ? g[i] : g[i + 4];
-			const float keep = up ? g[i + 4] : g[i];
+		for (int i = 0; i < 12; i++) {
+			const float send = up ? g[i] : g[i + 12];
+			const float keep = up ? g[i + 12] : g[i];
 			g[i] = keep + __shfl_xor_sync(0xffffffffu, send, 4);
 		}
-		g[16] += __shfl_xor_sync(0xffffffffu, g[16], 4);
 	}
 	{
 		const bool up = lane & 2;
 #pragma unroll
-		for (int i = 0; i < 2; i++) {
-			const float send = up ? g[i] : g[i + 2];
-			const float keep = up ? g[i + 2] : g[i];
+		for (int i = 0; i < 6; i++) {
+			const float send = up ? g[i] : g[i + 6];
+			const float keep = up ? g[i + 6] : g[i];
 			g[i] = keep + __shfl_xor_sync(0xffffffffu, send, 2);
 		}
-		g[16] += __shfl_xor_sync(0xffffffffu, g[16], 2);
 	}
 	{
 		const bool up = lane & 1;
-		const float send = up ? g[0] : g[1];
-		const float keep = up ? g[1] : g[0];
-		g[0] = keep + __shfl_xor_sync(0xffffffffu, send, 1);
-		g[16] += __shfl_xor_sync(0xffffffffu, g[16], 1);
+#pragma unroll
+		for (int i = 0; i < 3; i++) {
+			const float send = up ? g[i] : g[i + 3];
+			const float keep = up ? g[i + 3] : g[i];
+			g[i] = keep + __shfl_xor_sync(0xffffffffu, send, 1);
+		}
 	}
-	a = g[0];
-	b = g[16];
 }
 
 template <bool USE_SA>
@@ -394,15 +381,15 @@ composite_backward_pixels_kernel(int W, int H, unsigned gx, const uint2* __restr
 		}
 	}
 
-	// ---- phase B: half a warp per instance of the tile, lanes over the instance's pair slots (just written by
+	// ---- phase B: a quarter-warp per instance of the tile, lanes over the instance's pair slots (just written by
 	// this CTA: L2-hot); pixel constants from shared memory, the record straight from global memory.
 	__syncthreads();
-	const int hw = tid >> 4, hl = tid & 15;
-	for (int q0 = 0; q0 < n_done; q0 += 16) {
-		const int q = q0 + hw;
-		float g[GR_USED];
+	const int grp = tid >> 3, gl = tid & 7;
+	for (int q0 = 0; q0 < n_done; q0 += 32) {
+		const int q = q0 + grp;
+		float g[24];
 #pragma unroll
-		for (int k = 0; k < GR_USED; k++) g[k] = 0.f;
+		for (int k = 0; k < 24; k++) g[k] = 0.f;
 		uint32_t row = 0;
 		if (q < n_done) {
 			const float4* rec = tile_rec + 5 * (size_t)q;
@@ -410,7 +397,7 @@ composite_backward_pixels_kernel(int W, int H, unsigned gx, const uint2* __restr
 			row = __float_as_uint(rec[4].w);
 			const size_t gi = (size_t)range.x + q;
 			const uint32_t s0 = gi ? pair_incl[gi - 1] : 0u, s1 = pair_incl[gi];
-			for (uint32_t k = s0 + hl; k < s1; k += 16) {
+			for (uint32_t k = s0 + gl; k < s1; k += 8) {
 				const float4 sl = slots[k];
 				const int p = __float_as_int(sl.w);
 				if (p >= 0)
@@ -419,12 +406,10 @@ composite_backward_pixels_kernel(int W, int H, unsigned gx, const uint2* __restr
 			}
 		}
 		__syncwarp();
-		float a, bsum;
-		half_reduce18(g, lane, a, bsum);
-		if (q < n_done) {
-			float* dst = grad_rows + (size_t)row * GRAD_WORDS;
-			dst[hl] = a;
-			if ((hl & 7) == 0) dst[16 + (hl >> 3)] = bsum;
+		oct_reduce24(g, lane);
+		if (q < n_done && gl < 6) {
+			float* dst = grad_rows + (size_t)row * GRAD_WORDS + 3 * gl;
+			dst[0] = g[0]; dst[1] = g[1]; dst[2] = g[2];
 		}
 	}
 }

@@ -193,10 +193,9 @@ scan_tiles_kernel(const uint32_t* __restrict__ in, uint32_t* __restrict__ out, i
 	uint32_t v[SCAN_ITEMS];
 	uint32_t tsum = 0;
 #pragma unroll
-	for (int i = 0; i < SCAN_ITEMS; i++) {
-		v[i] = (base + i < n) ? in[base + i] : 0u;
-		tsum += v[i];
-	}
+	for (int i = 0; i < SCAN_ITEMS; i++) v[i] = (base + i < n) ? in[base + i] : 0u;
+#pragma unroll
+	for (int i = 0; i < SCAN_ITEMS; i++) tsum += v[i];
 	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 	uint32_t incl = tsum;
 #pragma unroll
@@ -213,24 +212,37 @@ scan_tiles_kernel(const uint32_t* __restrict__ in, uint32_t* __restrict__ out, i
 		if (w < warp) warp_off += t;
 		block_total += t;
 	}
-	if (threadIdx.x == 0) {
+	if (warp == 0) {
+		// warp-wide look-back: lane l inspects predecessor pb - l; a window is consumed up to its first inclusive prefix
 		unsigned long long excl = 0;
 		if (bid == 0) {
-			atomicExch(&status[0], ST_PREFIX | (unsigned long long)block_total);
+			if (lane == 0) atomicExch(&status[0], ST_PREFIX | (unsigned long long)block_total);
 		} else {
-			atomicExch(&status[bid], ST_AGG | (unsigned long long)block_total);
+			if (lane == 0) atomicExch(&status[bid], ST_AGG | (unsigned long long)block_total);
 			int pb = (int)bid - 1;
 			while (true) {
-				unsigned long long s = *((volatile unsigned long long*)&status[pb]);
-				if ((s >> 62) == 0) continue;
-				excl += s & ST_MASK;
-				if ((s >> 62) == 2) break;
-				pb--;
+				const int idx = pb - lane;
+				unsigned long long sv = 2ull << 62;  // before block 0: an inclusive prefix of 0
+				if (idx >= 0) sv = *((volatile unsigned long long*)&status[idx]);
+				const uint32_t flag = (uint32_t)(sv >> 62);
+				const uint32_t ready = __ballot_sync(0xffffffffu, flag != 0);
+				const uint32_t pref = __ballot_sync(0xffffffffu, flag == 2);
+				const int last = pref ? __ffs(pref) - 1 : 31;
+				const uint32_t need = last == 31 ? 0xffffffffu : ((2u << last) - 1u);
+				if ((ready & need) != need) continue;
+				unsigned long long part = lane <= last ? (sv & ST_MASK) : 0ull;
+#pragma unroll
+				for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
+				excl += part;
+				if (pref) break;
+				pb -= 32;
 			}
-			atomicExch(&status[bid], ST_PREFIX | (excl + block_total));
+			if (lane == 0) atomicExch(&status[bid], ST_PREFIX | (excl + block_total));
 		}
-		s_prefix = excl;
-		if ((long long)(bid + 1) * SCAN_TILE >= n) counters[1] = (uint32_t)(excl + block_total);
+		if (lane == 0) {
+			s_prefix = excl;
+			if ((long long)(bid + 1) * SCAN_TILE >= n) counters[1] = (uint32_t)(excl + block_total);
+		}
 	}
 	__syncthreads();
 	uint32_t run = (uint32_t)s_prefix + warp_off + (incl - tsum);

@@ -10,7 +10,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(os.path.dirname(_HERE), "lib", "libgs2d.so")
+# GS2D_LIBRARY points at another build of the same ABI (tuning variants); it is still the CUDA library, never a fallback.
+LIB_PATH = os.environ.get("GS2D_LIBRARY") or os.path.join(os.path.dirname(_HERE), "lib", "libgs2d.so")
 
 GS2D_OK = 0
 GS2D_ERR_INVALID = -1

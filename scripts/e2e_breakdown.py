@@ -11,6 +11,10 @@ arm = bench.make_b200_arm(wl, dev) if len(sys.argv) < 2 else bench.make_referenc
 s = wl["sets"][0]
 params = {k: s[k].detach().clone().requires_grad_(True) for k in bench.PARAMS}
 means2D = torch.zeros((wl["P"], 3), device=dev, requires_grad=True)
+H, W = wl["H"], wl["W"]
+loss_fn = torch.cuda.make_graphed_callables(bench.mapping_loss, (
+    torch.rand((3, H, W), device=dev, requires_grad=True), torch.rand((7, H, W), device=dev, requires_grad=True),
+    s["gt_color"].clone(), s["gt_depth"].clone()))
 seg = {k: 0.0 for k in ("raster_ctor", "forward", "loss", "backward", "sync")}
 gpu = {k: 0.0 for k in ("forward", "loss", "backward")}
 N = 40
@@ -26,7 +30,7 @@ for it in range(N + 10):
     color, radii, allmap = rast(means3D=params["means3D"], means2D=means2D, opacities=params["opacities"],
                                 colors_precomp=params["colors"], scales=params["scales"], rotations=params["rotations"])
     t2 = time.perf_counter(); ev[1].record()
-    loss = bench.mapping_loss(color, allmap, s["gt_color"], s["gt_depth"])
+    loss = loss_fn(color, allmap, s["gt_color"], s["gt_depth"])
     t3 = time.perf_counter(); ev[2].record()
     loss.backward()
     t4 = time.perf_counter(); ev[3].record()
