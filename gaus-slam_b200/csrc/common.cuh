@@ -62,10 +62,10 @@ constexpr int SCAN_TILE = SCAN_THREADS * SCAN_ITEMS;
 // ---- onesweep radix sort geometry ----------------------------------------------------
 constexpr int SORT_THREADS = 256;
 #ifndef GS2D_SORT_ITEMS
-#define GS2D_SORT_ITEMS 16
+#define GS2D_SORT_ITEMS 8
 #endif
 constexpr int SORT_ITEMS = GS2D_SORT_ITEMS;
-constexpr int SORT_TILE = SORT_THREADS * SORT_ITEMS;   // 4096 pairs per block
+constexpr int SORT_TILE = SORT_THREADS * SORT_ITEMS;   // pairs per block
 constexpr int SORT_RADIX_BITS = 8;
 constexpr int SORT_RADIX = 1 << SORT_RADIX_BITS;
 constexpr int SORT_MAX_PASSES = 8;

