@@ -110,7 +110,7 @@ BinningState BinningState::carve(void* base, size_t I, size_t tiles, size_t* byt
 	b.vals_b = c.take<uint32_t>(n);
 	b.instances = c.take<float>(n * REC_WORDS);
 	b.hit_inst = c.take<uint32_t>(n * 8 + 64);
-	b.hit_pix = c.take<uint32_t>((n / 32 + 4 * tiles + 8) * 2 * TILE_PIXELS);
+	b.hit_pix = c.take<uint32_t>((n / 32 + HIT_PIX_PAD * tiles + 8) * 2 * TILE_PIXELS);
 	b.hit_count = c.take<uint32_t>(n);
 	b.pair_incl = c.take<uint32_t>(n);
 	b.pair_status = c.take<uint64_t>(n / SCAN_TILE + 2);

@@ -52,6 +52,9 @@ struct Carver {
 };
 
 // ---- scan (decoupled look-back) geometry --------------------------------------------
+// hit_pix holds, per tile, one word pair per 32 instances rounded up to whole compositing batches: HIT_PIX_PAD
+// spare words per tile cover the rounding for batches of up to 32 * HIT_PIX_PAD instances.
+constexpr int HIT_PIX_PAD = 8;
 constexpr int SCAN_THREADS = 256;
 #ifndef GS2D_SCAN_ITEMS
 #define GS2D_SCAN_ITEMS 8
@@ -108,7 +111,7 @@ struct BinningState {
 	uint32_t* vals_b;         // [I]
 	float* instances;         // [I,20]
 	uint32_t* hit_inst;       // [I,8] per-instance footprint mask in tile pixel order (footprint.cu)
-	uint32_t* hit_pix;        // [I/32 + 4*tiles, 2, 256] per-pixel words written by the forward pass: tile t, batch b,
+	uint32_t* hit_pix;        // [I/32 + HIT_PIX_PAD*tiles, 2, 256] per-pixel words written by the forward pass: tile t, batch b,
 	                          // word g at ((((range.x >> 5) + 4*t + 4*b + g) * 2 + k) * 256 + pixel thread;
 	                          // k = 0: pairs that contributed, k = 1: pairs of the footprint masks
 	uint32_t* hit_count;      // [I] footprint-mask bits per instance

@@ -322,7 +322,7 @@ composite_backward_pixels_kernel(int W, int H, unsigned gx, const uint2* __restr
 	if (tid == 0) issue(nb - 1, 0);
 
 	const uint32_t lane_lt = (1u << lane) - 1u;
-	const uint32_t* pix_words = hit_pix + ((size_t)(range.x >> 5) + 4 * (size_t)tile) * 2 * TILE_PIXELS;
+	const uint32_t* pix_words = hit_pix + ((size_t)(range.x >> 5) + HIT_PIX_PAD * (size_t)tile) * 2 * TILE_PIXELS;
 	const float4 empty = make_float4(0.f, 0.f, 0.f, __int_as_float(-1));
 
 	for (int it = 0; it < nb; it++) {
@@ -359,23 +359,38 @@ composite_backward_pixels_kernel(int W, int H, unsigned gx, const uint2* __restr
 		}
 		__syncthreads();
 
-		// every pixel walks the pairs of its footprint words, back to front
+		// every pixel walks the pairs of its footprint words of the WHOLE batch, back to front, in one loop (a warp
+		// iterates as often as its longest pixel list; lists of 128 instances balance better than lists of 32)
+		{
+			constexpr int NG = BWD_BATCH / 32;
+			int g = NG - 1;
+			uint32_t m = foot[NG - 1], u = used[NG - 1];
+			auto next_word = [&]() {
+				while (m == 0u && g > 0) {
+					g--;
 #pragma unroll
-		for (int g = BWD_BATCH / 32 - 1; g >= 0; g--) {
-			uint32_t m = foot[g];
-			while (m) {
-				const int jl = 31 - __clz(m);
-				m &= ~(1u << jl);
-				const int j = g * 32 + jl;
-				const uint2 pf = sm.pref[j];
-				const uint32_t before = ((warp < 4 ? pf.x >> (8 * warp) : pf.y >> (8 * (warp - 4))) & 0xffu);
-				float4* dst = slots + (sm.base[j] + before + __popc(masks[j * 8 + warp] & lane_lt));
-				if ((used[g] >> jl) & 1u) {
-					float A, dz, w;
-					pixel_step<USE_SA>(recs + j * 5, pxf, pyf, (uint32_t)(b * BWD_BATCH + j), pc, st, A, dz, w);
-					*dst = make_float4(A, dz, w, __int_as_float(tid));
-				} else {
-					*dst = empty;
+					for (int k = 0; k < NG - 1; k++)
+						if (g == k) { m = foot[k]; u = used[k]; }
+				}
+				return m != 0u;
+			};
+			bool has = next_word();
+			while (__any_sync(0xffffffffu, has)) {
+				if (has) {
+					const int jl = 31 - __clz(m);
+					m &= ~(1u << jl);
+					const int j = g * 32 + jl;
+					const uint2 pf = sm.pref[j];
+					const uint32_t before = ((warp < 4 ? pf.x >> (8 * warp) : pf.y >> (8 * (warp - 4))) & 0xffu);
+					float4* dst = slots + (sm.base[j] + before + __popc(masks[j * 8 + warp] & lane_lt));
+					if ((u >> jl) & 1u) {
+						float A, dz, w;
+						pixel_step<USE_SA>(recs + j * 5, pxf, pyf, (uint32_t)(b * BWD_BATCH + j), pc, st, A, dz, w);
+						*dst = make_float4(A, dz, w, __int_as_float(tid));
+					} else {
+						*dst = empty;
+					}
+					has = next_word();
 				}
 			}
 		}

@@ -23,8 +23,21 @@ namespace gs2d {
 
 namespace {
 
-constexpr int FWD_BATCH = 128;
+#ifndef GS2D_FWD_BATCH
+#define GS2D_FWD_BATCH 128
+#endif
+constexpr int FWD_BATCH = GS2D_FWD_BATCH;   // instances per staged batch (a multiple of 32)
+constexpr int FWD_GROUPS = FWD_BATCH / 32;  // hit words per pixel per batch
 constexpr int FWD_STAGES = 2;
+static_assert(FWD_BATCH % 32 == 0 && FWD_BATCH / 32 <= HIT_PIX_PAD, "hit_pix padding");
+
+struct FwdSmem {
+	float4 rec[FWD_STAGES][FWD_BATCH * 5];
+	uint32_t mask[FWD_STAGES][FWD_BATCH * 8];
+	uint32_t hits[FWD_GROUPS][TILE_PIXELS];   // per-pixel hit words of the current batch
+	uint32_t used[FWD_GROUPS][TILE_PIXELS];   // the pairs that really contributed
+	uint64_t bar[FWD_STAGES];
+};
 
 struct PixelFwd {
 	float T = 1.0f;
@@ -111,9 +124,11 @@ composite_forward_kernel(int W, int H, unsigned gx, const uint2* __restrict__ ra
                          float* __restrict__ depth_std_out, float* __restrict__ out_color,
                          float* __restrict__ out_others)
 {
-	__shared__ __align__(128) float4 s_rec[FWD_STAGES][FWD_BATCH * 5];
-	__shared__ __align__(128) uint32_t s_mask[FWD_STAGES][FWD_BATCH * 8];
-	__shared__ __align__(8) uint64_t s_bar[FWD_STAGES];
+	extern __shared__ __align__(128) unsigned char fwd_smem_raw[];
+	FwdSmem& sm = *reinterpret_cast<FwdSmem*>(fwd_smem_raw);
+	float4 (*s_rec)[FWD_BATCH * 5] = sm.rec;
+	uint32_t (*s_mask)[FWD_BATCH * 8] = sm.mask;
+	uint64_t* s_bar = sm.bar;
 
 	const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 	const unsigned tile = blockIdx.x;
@@ -142,7 +157,7 @@ composite_forward_kernel(int W, int H, unsigned gx, const uint2* __restrict__ ra
 	};
 	if (tid == 0 && nb > 0) issue(0, 0);
 
-	uint32_t* pix_words = hit_pix + ((size_t)(range.x >> 5) + 4 * (size_t)tile) * 2 * TILE_PIXELS;
+	uint32_t* pix_words = hit_pix + ((size_t)(range.x >> 5) + HIT_PIX_PAD * (size_t)tile) * 2 * TILE_PIXELS;
 
 	PixelFwd px;
 	bool done = !inside;
@@ -165,28 +180,48 @@ composite_forward_kernel(int W, int H, unsigned gx, const uint2* __restrict__ ra
 		const uint32_t* masks = &s_mask[stage][0];
 		// Transpose in registers: word `warp` of instance j holds this warp's 32 pixels; a 32x32 bit transpose turns
 		// the words of 32 instances into one hit word per pixel (bit j <-> instance g*32 + j).
-		uint32_t hits[FWD_BATCH / 32];
 #pragma unroll
-		for (int g = 0; g < FWD_BATCH / 32; g++) {
+		for (int g = 0; g < FWD_GROUPS; g++) {
 			const int j = g * 32 + lane;
 			const uint32_t mine = j < cnt ? masks[j * 8 + warp] : 0u;
-			hits[g] = __any_sync(0xffffffffu, mine != 0u) ? transpose32(mine, lane) : 0u;
+			sm.hits[g][tid] = __any_sync(0xffffffffu, mine != 0u) ? transpose32(mine, lane) : 0u;
+			sm.used[g][tid] = 0u;
 		}
 
-		// every pixel walks its own hits, front to back
-#pragma unroll
-		for (int g = 0; g < FWD_BATCH / 32; g++) {
-			uint32_t m = hits[g], used = 0u;
-			while (m && !done) {
-				const int jl = __ffs(m) - 1;
-				m &= m - 1;
-				if (eval_pair<USE_SA>(recs + (g * 32 + jl) * 5, pxf, pyf, (uint32_t)(b * FWD_BATCH + g * 32 + jl + 1), px, done))
-					used |= 1u << jl;
+		// Every pixel walks its own hits of the WHOLE batch front to back, in one loop: a warp iterates as often as
+		// its longest pixel list (lists of 128 instances balance better between the lanes than lists of 32).
+		{
+			int g = 0;
+			uint32_t m = done ? 0u : sm.hits[0][tid], used = 0u;
+			// advance to the next non-empty word; false when the pixel has no hit left in this batch
+			auto next_word = [&]() {
+				while (m == 0u && g + 1 < FWD_GROUPS) {
+					sm.used[g][tid] = used;
+					used = 0u;
+					g++;
+					m = sm.hits[g][tid];
+				}
+				return m != 0u;
+			};
+			bool has = !done && next_word();
+			while (__any_sync(0xffffffffu, has)) {
+				if (has) {
+					const int jl = __ffs(m) - 1;
+					m &= m - 1;
+					const int j = g * 32 + jl;
+					if (eval_pair<USE_SA>(recs + j * 5, pxf, pyf, (uint32_t)(b * FWD_BATCH + j + 1), px, done))
+						used |= 1u << jl;
+					has = !done && next_word();
+				}
 			}
-			// for the backward pass (coalesced, one word per pixel thread): the pairs that really contributed,
-			// and the pairs of the footprint masks (they own a gradient-pair slot each)
-			pix_words[(size_t)((b * (FWD_BATCH / 32) + g) * 2 + 0) * TILE_PIXELS + tid] = used;
-			pix_words[(size_t)((b * (FWD_BATCH / 32) + g) * 2 + 1) * TILE_PIXELS + tid] = hits[g];
+			sm.used[g][tid] = used;
+		}
+		// for the backward pass (coalesced, one word per pixel thread): the pairs that really contributed,
+		// and the pairs of the footprint masks (they own a gradient-pair slot each)
+#pragma unroll
+		for (int g = 0; g < FWD_GROUPS; g++) {
+			pix_words[(size_t)((b * FWD_GROUPS + g) * 2 + 0) * TILE_PIXELS + tid] = sm.used[g][tid];
+			pix_words[(size_t)((b * FWD_GROUPS + g) * 2 + 1) * TILE_PIXELS + tid] = sm.hits[g][tid];
 		}
 	}
 
@@ -227,13 +262,19 @@ int launch_composite_forward(const gs2d_settings& s, const gs2d_inputs& in, cons
 	const int W = s.image_width, H = s.image_height;
 	const unsigned gx = (W + TILE - 1) / TILE, gy = (H + TILE - 1) / TILE;
 	if (gx * gy == 0) return GS2D_OK;
+	static bool attr_set = false;
+	if (!attr_set) {
+		GS2D_CUDA_OK(cudaFuncSetAttribute(composite_forward_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(FwdSmem)));
+		GS2D_CUDA_OK(cudaFuncSetAttribute(composite_forward_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(FwdSmem)));
+		attr_set = true;
+	}
 	ProfScope ps(K_COMPOSITE_FWD, st);
 	if (s.use_sa)
-		composite_forward_kernel<true><<<gx * gy, 256, 0, st>>>(
+		composite_forward_kernel<true><<<gx * gy, 256, sizeof(FwdSmem), st>>>(
 			W, H, gx, (const uint2*)im.ranges, (const float4*)instances, hit_inst, hit_pix, in.background, im.final_T,
 			im.n_contrib, im.median_depth, im.depth_std, out_color, out_others);
 	else
-		composite_forward_kernel<false><<<gx * gy, 256, 0, st>>>(
+		composite_forward_kernel<false><<<gx * gy, 256, sizeof(FwdSmem), st>>>(
 			W, H, gx, (const uint2*)im.ranges, (const float4*)instances, hit_inst, hit_pix, in.background, im.final_T,
 			im.n_contrib, im.median_depth, im.depth_std, out_color, out_others);
 	count_launch();
