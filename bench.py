@@ -66,19 +66,32 @@ class ClockSampler:
         self.thread = None
 
     def start(self):
+        """Started BEFORE the warm-up: nvidia-smi's start-up (NVML initialisation) perturbs the GPU for a moment
+        and must not fall into the timed region.  Samples are time-stamped as they arrive; stop() keeps those
+        taken between mark_begin() and mark_end()."""
+        self.t0 = self.t1 = None
         try:
             self.proc = subprocess.Popen(
                 ["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                 "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+                 "-lms", "25"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
         except OSError:
             self.proc = None
             return
         self.thread = threading.Thread(target=self._read, daemon=True)
         self.thread.start()
+        t_end = time.monotonic() + 5.0      # first sample in = NVML is up; only then does the warm-up begin
+        while not self.rows and time.monotonic() < t_end and self.proc.poll() is None:
+            time.sleep(0.01)
 
     def _read(self):
         for line in self.proc.stdout:
-            self.rows.append(line.strip())
+            self.rows.append((time.monotonic(), line.strip()))
+
+    def mark_begin(self):
+        self.t0 = time.monotonic()
+
+    def mark_end(self):
+        self.t1 = time.monotonic()
 
     def stop(self):
         if self.proc is None:
@@ -90,7 +103,8 @@ class ClockSampler:
         except Exception:
             self.proc.kill()
         sm, mx, pw, reasons = [], [], [], set()
-        for r in self.rows:
+        rows = [r for t, r in self.rows if self.t0 is None or (self.t0 <= t <= (self.t1 or t) + 0.03)]
+        for r in rows:
             f = [x.strip() for x in r.split(",")]
             if len(f) < 7:
                 continue
@@ -382,13 +396,15 @@ def main():
         return float(ms.item())
 
     # ---- device-resident `value`
-    for i in range(a.warmup):
-        step_resident(i)
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
+    for i in range(a.warmup):
+        step_resident(i)
     l0 = arm.launches()
+    sampler.mark_begin()
     ms_total = timed(step_resident, a.steps, a.warmup)
+    sampler.mark_end()
     launches = arm.launches() - l0
     clocks = sampler.stop() if rank == 0 else None
     ms_per_step = ms_total / a.steps

@@ -13,13 +13,14 @@ from concurrent.futures import ThreadPoolExecutor
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "lib", "libgs2d.so")
-SOURCES = ["api.cu", "preprocess.cu", "binning.cu", "footprint.cu", "composite_fwd.cu", "composite_bwd.cu",
+SOURCES = ["api.cu", "preprocess.cu", "binning.cu", "tile_sort.cu", "footprint.cu", "composite_fwd.cu", "composite_bwd.cu",
            "preprocess_bwd.cu", "knn.cu"]
-HEADERS = ["common.cuh", "math.cuh", "exact.cuh", "tma.cuh", "pair.cuh", os.path.join("..", "..", "include", "gs2d.h")]
+HEADERS = ["common.cuh", "math.cuh", "exact.cuh", "tma.cuh", "pair.cuh", "footprint.cuh", os.path.join("..", "..", "include", "gs2d.h")]
 # Kernels whose results only have to meet a tolerance (backward gradients: 1e-3 relative; footprint masks: a
 # superset) may use MUFU division / flush-to-zero; everything that decides bit-exact outputs keeps IEEE math.
 FAST_MATH = {"composite_bwd.cu": ["-ftz=true", "-prec-div=false", "-prec-sqrt=false"],
-             "footprint.cu": ["-ftz=true", "-prec-div=false", "-prec-sqrt=false"]}
+             "footprint.cu": ["-ftz=true", "-prec-div=false", "-prec-sqrt=false"],
+             "tile_sort.cu": ["-ftz=true", "-prec-div=false", "-prec-sqrt=false"]}
 NVCC_FLAGS = ["-std=c++17", "-O3", "-lineinfo", "-Xcompiler", "-fPIC",
               "-gencode", "arch=compute_100a,code=sm_100a"]
 

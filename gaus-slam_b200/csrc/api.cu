@@ -34,7 +34,8 @@ cudaEvent_t prof_event()
 const char* const kKernelNames[K_COUNT] = {
 	"preprocess_forward", "scan_tiles", "duplicate_keys", "histogram", "digit_base", "onesweep_pass",
 	"gather_ranges", "composite_forward", "composite_backward", "preprocess_backward", "mark_visible",
-	"memset", "memcpy", "knn", "footprint", "composite_backward_instances"};
+	"memset", "memcpy", "knn", "footprint", "composite_backward_instances", "tile_offsets", "scatter_pairs",
+	"tile_sort_gather_footprint"};
 }  // namespace
 void prof_mark(int id, cudaStream_t st, bool begin)
 {
@@ -79,6 +80,8 @@ ImageState ImageState::carve(void* base, size_t W, size_t H, size_t* bytes)
 	im.median_depth = c.take<float>(px);
 	im.depth_std = c.take<float>(px);
 	im.ranges = c.take<uint32_t>(2 * tiles);
+	im.tile_count = c.take<uint32_t>(tiles);
+	im.tile_cursor = c.take<uint32_t>(tiles);
 	if (bytes) *bytes = c.total();
 	return im;
 }
@@ -128,12 +131,6 @@ BinningState BinningState::carve(void* base, size_t I, size_t tiles, size_t* byt
 static inline size_t tiles_of(int W, int H)
 {
 	return (size_t)((W + TILE - 1) / TILE) * (size_t)((H + TILE - 1) / TILE);
-}
-
-static inline int end_bit_for(const gs2d_settings& s)
-{
-	const unsigned gx = (s.image_width + TILE - 1) / TILE, gy = (s.image_height + TILE - 1) / TILE;
-	return 32 + (int)higher_msb(gx * gy);
 }
 
 static int check_common(const gs2d_settings* s, const gs2d_inputs* in, const gs2d_buffers* b)
@@ -187,10 +184,16 @@ int gs2d_forward_preprocess(const gs2d_settings* s, const gs2d_inputs* in, const
 	cudaStream_t st = (cudaStream_t)stream;
 	if (num_rendered_host) *num_rendered_host = 0;
 	if (s->P == 0) return GS2D_OK;
-	if (!buffers->geom || !radii) return GS2D_ERR_INVALID;
+	if (!buffers->geom || !radii || !buffers->image) return GS2D_ERR_INVALID;
 	if (buffers->geom_bytes < gs2d_geom_bytes(s->P, s->sh_coeffs)) return GS2D_ERR_CAPACITY;
+	if (buffers->image_bytes < gs2d_image_bytes(s->image_width, s->image_height)) return GS2D_ERR_CAPACITY;
 	GeomState g = GeomState::carve(buffers->geom, (size_t)s->P, nullptr);
-	GS2D_TRY(launch_preprocess_forward(*s, *in, g, radii, st));
+	ImageState im = ImageState::carve(buffers->image, (size_t)s->image_width, (size_t)s->image_height, nullptr);
+	{
+		ProfScope ps(K_MEMSET, st);
+		GS2D_CUDA_OK(cudaMemsetAsync(im.tile_count, 0, sizeof(uint32_t) * tiles_of(s->image_width, s->image_height), st));
+	}
+	GS2D_TRY(launch_preprocess_forward(*s, *in, g, im.tile_count, radii, st));
 	GS2D_TRY(debug_sync(*s, st));
 	GS2D_TRY(launch_scan_tiles(g, s->P, st));
 	GS2D_TRY(debug_sync(*s, st));
@@ -221,25 +224,19 @@ int gs2d_forward_render(const gs2d_settings* s, const gs2d_inputs* in, const gs2
 	GeomState g = GeomState::carve(buffers->geom, (size_t)s->P, nullptr);
 	BinningState b = BinningState::carve(buffers->binning, (size_t)I, tiles_of(s->image_width, s->image_height), nullptr);
 
-	GS2D_TRY(launch_duplicate(*s, g, nullptr, b, I, st));
-	GS2D_TRY(debug_sync(*s, st));
 	if (s->debug) {
-		GS2D_CUDA_OK(cudaMemcpyAsync(b.keys_dbg, b.keys_a, sizeof(uint64_t) * (size_t)I, cudaMemcpyDeviceToDevice, st));
-		GS2D_CUDA_OK(cudaMemcpyAsync(b.vals_dbg, b.vals_a, sizeof(uint32_t) * (size_t)I, cudaMemcpyDeviceToDevice, st));
+		// the reference's unsorted (key, surfel) list, for gs2d_state_view only
+		GS2D_TRY(launch_duplicate(*s, g, nullptr, b, I, st));
+		GS2D_TRY(debug_sync(*s, st));
 	}
-	bool in_b = false;
-	GS2D_TRY(launch_sort_pairs(I, b.keys_a, b.vals_a, b.keys_b, b.vals_b, b.keys_a, b.vals_a, end_bit_for(*s),
-	                           b.sort, &in_b, st));
+	// tile ranges, scatter into tile segments, per-tile sort + instance gather + footprint masks
+	GS2D_TRY(launch_tile_binning(*s, g, im, b, I, st));
 	GS2D_TRY(debug_sync(*s, st));
-	if (!in_b) {
-		// keep the sorted result where gs2d_state_view_get and backward expect it (keys_b / vals_b)
-		GS2D_CUDA_OK(cudaMemcpyAsync(b.keys_b, b.keys_a, sizeof(uint64_t) * (size_t)I, cudaMemcpyDeviceToDevice, st));
-		GS2D_CUDA_OK(cudaMemcpyAsync(b.vals_b, b.vals_a, sizeof(uint32_t) * (size_t)I, cudaMemcpyDeviceToDevice, st));
+	{
+		ProfScope ps(K_MEMSET, st);
+		GS2D_CUDA_OK(cudaMemsetAsync(b.pair_status, 0, (size_t)((char*)(b.pair_counters + 8) - (char*)b.pair_status), st));
 	}
-	GS2D_TRY(launch_gather_ranges(*s, g, b.keys_b, b.vals_b, b.instances, im.ranges, I, st));
-	GS2D_TRY(debug_sync(*s, st));
-	GS2D_TRY(launch_footprint(*s, b.instances, b.keys_b, b.hit_inst, b.hit_count, I, st));
-	GS2D_TRY(launch_scan_u32(b.hit_count, b.pair_incl, I, b.pair_status, b.pair_counters, st));
+	GS2D_TRY(launch_scan_u32(b.hit_count, b.pair_incl, I, b.pair_status, b.pair_counters, st, false));
 	if (num_pairs_host)   // 8 bytes: counters[1] = total, counters[2] = 0 -> a whole int64, before the compositing kernel
 		GS2D_CUDA_OK(cudaMemcpyAsync(num_pairs_host, b.pair_counters + 1, 2 * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
 	GS2D_TRY(debug_sync(*s, st));

@@ -7,6 +7,7 @@
 //
 // All kernels here are HBM-bound integer/byte movers.
 #include "common.cuh"
+#include "pair.cuh"
 
 namespace gs2d {
 
@@ -251,22 +252,6 @@ onesweep_kernel(long long n, const uint64_t* __restrict__ keys_in, const uint32_
 // One warp-quarter... one thread group of 5 lanes would complicate things: keep one thread per
 // sorted instance for the bookkeeping and let 5 consecutive float4 stores per thread carry the
 // record (80 B, contiguous in the output).
-// In-tile footprint box of an instance: the surfel's contribution bounds (preprocess.cu) clipped to the
-// tile and to the image, packed as described in pair.cuh (x0 | y0<<4 | x1<<8 | y1<<12 | valid<<16).
-__device__ __forceinline__ uint32_t tile_box_word(float4 cb, int tx, int ty, int W, int H)
-{
-	const int tx0 = tx * TILE, ty0 = ty * TILE;
-	const int tx1 = min(tx0 + TILE - 1, W - 1), ty1 = min(ty0 + TILE - 1, H - 1);
-	// clamp in float first: the bounds may be +-inf ("no culling")
-	const int x0 = (int)ceilf(fminf(fmaxf(cb.x, (float)tx0), (float)(tx1 + 1)));
-	const int y0 = (int)ceilf(fminf(fmaxf(cb.y, (float)ty0), (float)(ty1 + 1)));
-	const int x1 = (int)floorf(fmaxf(fminf(cb.z, (float)tx1), (float)(tx0 - 1)));
-	const int y1 = (int)floorf(fmaxf(fminf(cb.w, (float)ty1), (float)(ty0 - 1)));
-	if (x0 > x1 || y0 > y1) return 0u;
-	return (uint32_t)(x0 - tx0) | ((uint32_t)(y0 - ty0) << 4) | ((uint32_t)(x1 - tx0) << 8) |
-	       ((uint32_t)(y1 - ty0) << 12) | (1u << 16);
-}
-
 __global__ void __launch_bounds__(256)
 gather_ranges_kernel(long long I, unsigned gx, int W, int H, const uint64_t* __restrict__ keys,
                      const uint32_t* __restrict__ point_list, const float4* __restrict__ splat,
@@ -323,7 +308,7 @@ int launch_duplicate(const gs2d_settings& s, const GeomState& g, const int32_t*,
 	{
 		ProfScope ps(K_DUPLICATE, st);
 		duplicate_kernel<<<(s.P + 255) / 256, 256, 0, st>>>(s.P, gx, g.depths, (const ushort4*)g.rect,
-		                                                    g.tiles_touched, g.point_offsets, b.keys_a, b.vals_a,
+		                                                    g.tiles_touched, g.point_offsets, b.keys_dbg, b.vals_dbg,
 		                                                    b.sort.hist, passes);
 		count_launch();
 	}

@@ -92,6 +92,8 @@ struct ImageState {
 	float* median_depth;      // [H,W]
 	float* depth_std;         // [H,W]
 	uint32_t* ranges;         // [tiles,2]
+	uint32_t* tile_count;     // [tiles] instances per tile (counted by preprocess_forward; zeroed before it)
+	uint32_t* tile_cursor;    // [tiles] write cursor of the scatter (starts at the tile's range start)
 	static __host__ ImageState carve(void* base, size_t W, size_t H, size_t* bytes);
 };
 
@@ -138,7 +140,8 @@ void count_launch(int n = 1);
 // Optional per-kernel CUDA-event timing (gs2d_timing_* in include/gs2d.h) -------------------------
 enum KernelId {
 	K_PREPROCESS_FWD = 0, K_SCAN, K_DUPLICATE, K_HISTOGRAM, K_DIGIT_BASE, K_ONESWEEP, K_GATHER_RANGES,
-	K_COMPOSITE_FWD, K_COMPOSITE_BWD, K_PREPROCESS_BWD, K_MARK_VISIBLE, K_MEMSET, K_MEMCPY, K_KNN, K_FOOTPRINT, K_COMPOSITE_BWD_INST, K_COUNT
+	K_COMPOSITE_FWD, K_COMPOSITE_BWD, K_PREPROCESS_BWD, K_MARK_VISIBLE, K_MEMSET, K_MEMCPY, K_KNN, K_FOOTPRINT, K_COMPOSITE_BWD_INST, K_TILE_OFFSETS,
+	K_SCATTER, K_TILE_SORT, K_COUNT
 };
 extern bool g_timing_on;
 void prof_mark(int id, cudaStream_t st, bool begin);
@@ -150,9 +153,12 @@ struct ProfScope {
 
 // Kernel launchers (each returns a gs2d_status) ------------------------------------------
 int launch_preprocess_forward(const gs2d_settings& s, const gs2d_inputs& in, const GeomState& g,
-                              int32_t* radii, cudaStream_t st);
-int launch_scan_tiles(const GeomState& g, int P, cudaStream_t st);
-int launch_scan_u32(const uint32_t* in, uint32_t* out, long long n, uint64_t* status, uint32_t* counters, cudaStream_t st);
+                              uint32_t* tile_count, int32_t* radii, cudaStream_t st);
+int launch_tile_binning(const gs2d_settings& s, const GeomState& g, const ImageState& im, const BinningState& b,
+                        int64_t I, cudaStream_t st);
+int launch_scan_tiles(const GeomState& g, int P, cudaStream_t st);   // zeroes [scan_status, counters + 8) itself
+int launch_scan_u32(const uint32_t* in, uint32_t* out, long long n, uint64_t* status, uint32_t* counters,
+                    cudaStream_t st, bool clear = true);
 int launch_duplicate(const gs2d_settings& s, const GeomState& g, const int32_t* radii_unused,
                      const BinningState& b, int64_t I, cudaStream_t st);
 int launch_sort_pairs(int64_t n, const uint64_t* keys_a, const uint32_t* vals_a, uint64_t* keys_b,

@@ -39,6 +39,22 @@ __device__ __forceinline__ void box_xy(const TileBox& b, int idx, int& lx, int& 
 // warp k owns rows 2k and 2k+1.  Footprint masks use the same order: word k, bit (ly & 1) * 16 + lx.
 __device__ __forceinline__ int pixel_thread(int lx, int ly) { return (ly << 4) | lx; }
 
+// In-tile footprint box of an instance: the surfel's contribution bounds (preprocess.cu) clipped to the
+// tile and to the image, packed as described in pair.cuh (x0 | y0<<4 | x1<<8 | y1<<12 | valid<<16).
+__device__ __forceinline__ uint32_t tile_box_word(float4 cb, int tx, int ty, int W, int H)
+{
+	const int tx0 = tx * TILE, ty0 = ty * TILE;
+	const int tx1 = min(tx0 + TILE - 1, W - 1), ty1 = min(ty0 + TILE - 1, H - 1);
+	// clamp in float first: the bounds may be +-inf ("no culling")
+	const int x0 = (int)ceilf(fminf(fmaxf(cb.x, (float)tx0), (float)(tx1 + 1)));
+	const int y0 = (int)ceilf(fminf(fmaxf(cb.y, (float)ty0), (float)(ty1 + 1)));
+	const int x1 = (int)floorf(fmaxf(fminf(cb.z, (float)tx1), (float)(tx0 - 1)));
+	const int y1 = (int)floorf(fmaxf(fminf(cb.w, (float)ty1), (float)(ty0 - 1)));
+	if (x0 > x1 || y0 > y1) return 0u;
+	return (uint32_t)(x0 - tx0) | ((uint32_t)(y0 - ty0) << 4) | ((uint32_t)(x1 - tx0) << 8) |
+	       ((uint32_t)(y1 - ty0) << 12) | (1u << 16);
+}
+
 struct PairFront {
 	float3 k, l;      // pixel planes in splat space
 	float pz;         // p.z of k x l

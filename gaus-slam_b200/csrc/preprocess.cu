@@ -108,7 +108,8 @@ preprocess_forward_kernel(int P, int D, int M,
 	const float* __restrict__ viewmatrix, const float* __restrict__ projmatrix,
 	const float* __restrict__ campos, int W, int H, unsigned gx, unsigned gy, int prefiltered,
 	int* __restrict__ radii, float* __restrict__ depths, float4* __restrict__ splat,
-	ushort4* __restrict__ rect, float4* __restrict__ cull, uint32_t* __restrict__ tiles_touched)
+	ushort4* __restrict__ rect, float4* __restrict__ cull, uint32_t* __restrict__ tiles_touched,
+	uint32_t* __restrict__ tile_count)
 {
 	int idx = blockIdx.x * blockDim.x + threadIdx.x;
 	if (idx >= P) return;
@@ -172,6 +173,10 @@ preprocess_forward_kernel(int P, int D, int M,
 	                         (unsigned short)rmax.y);
 	cull[idx] = contribution_bounds(Tu, Tv, Tw, centre, opacity);
 	tiles_touched[idx] = (rmax.y - rmin.y) * (rmax.x - rmin.x);
+	// instances per tile, for the tile-local sort (tile_sort.cu): one RED per instance
+	if (tile_count)
+		for (unsigned y = rmin.y; y < rmax.y; y++)
+			for (unsigned x = rmin.x; x < rmax.x; x++) atomicAdd(&tile_count[y * gx + x], 1u);
 }
 
 // ---- inclusive scan of tiles_touched: single pass, decoupled look-back -----------------------
@@ -266,7 +271,7 @@ __global__ void mark_visible_kernel(int P, const float* __restrict__ means3D,
 }  // namespace
 
 int launch_preprocess_forward(const gs2d_settings& s, const gs2d_inputs& in, const GeomState& g,
-                              int32_t* radii, cudaStream_t st)
+                              uint32_t* tile_count, int32_t* radii, cudaStream_t st)
 {
 	const int P = s.P;
 	const unsigned gx = (s.image_width + TILE - 1) / TILE, gy = (s.image_height + TILE - 1) / TILE;
@@ -277,7 +282,7 @@ int launch_preprocess_forward(const gs2d_settings& s, const gs2d_inputs& in, con
 			(const float4*)in.rotations, in.opacities, in.shs, g.clamped, in.transMat_precomp,
 			in.colors_precomp, in.viewmatrix, in.projmatrix, in.campos, s.image_width, s.image_height,
 			gx, gy, s.prefiltered, radii, g.depths, (float4*)g.splat, (ushort4*)g.rect, (float4*)g.cull,
-			g.tiles_touched);
+			g.tiles_touched, tile_count);
 		count_launch();
 	}
 	GS2D_CUDA_OK(cudaGetLastError());
@@ -286,11 +291,14 @@ int launch_preprocess_forward(const gs2d_settings& s, const gs2d_inputs& in, con
 
 // Inclusive scan of n u32 values (single pass, decoupled look-back).  status: n / SCAN_TILE + 1 u64 words,
 // counters: 8 u32 words (both zeroed here); counters[1] receives the total.
-int launch_scan_u32(const uint32_t* in, uint32_t* out, long long n, uint64_t* status, uint32_t* counters, cudaStream_t st)
+int launch_scan_u32(const uint32_t* in, uint32_t* out, long long n, uint64_t* status, uint32_t* counters,
+                    cudaStream_t st, bool clear)
 {
 	const int blocks = (int)((n + SCAN_TILE - 1) / SCAN_TILE);
-	{ ProfScope ps(K_MEMSET, st); GS2D_CUDA_OK(cudaMemsetAsync(status, 0, sizeof(uint64_t) * (size_t)(blocks + 1), st)); }
-	{ ProfScope ps(K_MEMSET, st); GS2D_CUDA_OK(cudaMemsetAsync(counters, 0, sizeof(uint32_t) * 8, st)); }
+	if (clear) {
+		{ ProfScope ps(K_MEMSET, st); GS2D_CUDA_OK(cudaMemsetAsync(status, 0, sizeof(uint64_t) * (size_t)(blocks + 1), st)); }
+		{ ProfScope ps(K_MEMSET, st); GS2D_CUDA_OK(cudaMemsetAsync(counters, 0, sizeof(uint32_t) * 8, st)); }
+	}
 	if (blocks > 0) {
 		ProfScope ps(K_SCAN, st);
 		scan_tiles_kernel<<<blocks, SCAN_THREADS, 0, st>>>(in, out, (int)n, (unsigned long long*)status, counters);
@@ -302,7 +310,12 @@ int launch_scan_u32(const uint32_t* in, uint32_t* out, long long n, uint64_t* st
 
 int launch_scan_tiles(const GeomState& g, int P, cudaStream_t st)
 {
-	return launch_scan_u32(g.tiles_touched, g.point_offsets, P, g.scan_status, g.counters, st);
+	// status words and counters are adjacent in the geom buffer: one memset
+	{
+		ProfScope ps(K_MEMSET, st);
+		GS2D_CUDA_OK(cudaMemsetAsync(g.scan_status, 0, (size_t)((char*)(g.counters + 8) - (char*)g.scan_status), st));
+	}
+	return launch_scan_u32(g.tiles_touched, g.point_offsets, P, g.scan_status, g.counters, st, false);
 }
 
 int launch_mark_visible(int P, const float* means3D, const float* view, const float* proj,

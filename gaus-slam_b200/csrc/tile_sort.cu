@@ -1,0 +1,270 @@
+// tile_sort.cu -- tile binning without a global sort: count, scatter, sort inside each tile.
+//
+// Replaces duplicateWithKeys + cub::DeviceRadixSort::SortPairs + identifyTileRanges
+// (CR/rasterizer_impl.cu:70-138, :296-323) for the rendering path.  The reference sorts all
+// (tile << 32 | depth bits, surfel) pairs of the frame with a stable global radix sort.  The order that sort
+// produces is a total order that can be stated without the sort: tiles ascending; inside a tile depth bits
+// ascending; equal depths by surfel index ascending (duplicateWithKeys emits surfels in index order and a
+// surfel touches a tile once, so "stable" means exactly that).  Hence:
+//   1. preprocess_forward counts the instances of every tile (one RED per instance, preprocess.cu);
+//   2. tile_offsets_kernel scans the 3 225 counts -> tile ranges (identifyTileRanges's output) + write cursors;
+//   3. scatter_kernel drops every instance's (depth bits << 32 | surfel) word into its tile's segment, in
+//      whatever order the atomics resolve;
+//   4. tile_sort_kernel (one CTA per tile) sorts the segment by that 64-bit word in shared memory -- unique
+//      keys, so the result does not depend on the scatter order and equals the reference's sorted list bit for
+//      bit -- then, while the tile's list is on chip, writes keys / point list, gathers the 80-byte instance
+//      records (binning.cu's gather) and computes the footprint masks (footprint.cuh).
+// Six onesweep passes over 0.8 M pairs, the gather and the footprint launch become one kernel whose sort part
+// works on ~250 keys in shared memory.  Tiles with more than TS_CAP instances sort in place in global memory
+// with the same network (slow, correct).
+#include "common.cuh"
+#include "footprint.cuh"
+
+namespace gs2d {
+
+namespace {
+
+constexpr int TS_CAP = 2048;   // instances of a tile sorted in shared memory (16 KB of keys)
+
+// Exclusive scan of the per-tile counts (one CTA): ranges[t] = (start, end), cursor[t] = start.
+__global__ void __launch_bounds__(1024)
+tile_offsets_kernel(int tiles, const uint32_t* __restrict__ tile_count, uint2* __restrict__ ranges,
+                    uint32_t* __restrict__ cursor)
+{
+	__shared__ uint32_t s_warp[32];
+	__shared__ uint32_t s_total;
+	const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+	uint32_t carry = 0;
+	for (int base = 0; base < tiles; base += 1024) {
+		const int i = base + tid;
+		const uint32_t v = i < tiles ? tile_count[i] : 0u;
+		uint32_t incl = v;
+#pragma unroll
+		for (int o = 1; o < 32; o <<= 1) {
+			const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+			if (lane >= o) incl += t;
+		}
+		if (lane == 31) s_warp[warp] = incl;
+		__syncthreads();
+		if (warp == 0) {
+			const uint32_t w = s_warp[lane];
+			uint32_t wi = w;
+#pragma unroll
+			for (int o = 1; o < 32; o <<= 1) {
+				const uint32_t t = __shfl_up_sync(0xffffffffu, wi, o);
+				if (lane >= o) wi += t;
+			}
+			s_warp[lane] = wi - w;
+			if (lane == 31) s_total = wi;
+		}
+		__syncthreads();
+		const uint32_t start = carry + s_warp[warp] + incl - v;
+		if (i < tiles) {
+			ranges[i] = v ? make_uint2(start, start + v) : make_uint2(0u, 0u);   // empty tiles stay (0, 0) like the reference's memset
+			cursor[i] = start;
+		}
+		carry += s_total;
+		__syncthreads();
+	}
+}
+
+// One thread per surfel, like duplicateWithKeys -- but the destination is the tile's own segment.
+__global__ void __launch_bounds__(256)
+scatter_kernel(int P, unsigned gx, const float* __restrict__ depths, const ushort4* __restrict__ rect,
+               const uint32_t* __restrict__ tiles_touched, uint32_t* __restrict__ cursor,
+               uint64_t* __restrict__ pairs)
+{
+	const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+	if (idx >= P || tiles_touched[idx] == 0) return;
+	const ushort4 r = rect[idx];
+	const uint64_t word = ((uint64_t)__float_as_uint(depths[idx]) << 32) | (uint32_t)idx;
+	for (unsigned y = r.y; y < r.w; y++)
+		for (unsigned x = r.x; x < r.z; x++) pairs[atomicAdd(&cursor[y * gx + x], 1u)] = word;
+}
+
+// Ascending sort of keys[0, n) by 256 threads in memory (the fallback for tiles beyond TS_CAP): bitonic network in its "every exchange puts the smaller key at
+// the lower index" form (first step of a merge mirrors the partner), so the virtual +inf padding up to the next
+// power of two never moves and pairs that reach it are simply skipped.
+__device__ __forceinline__ void cta_sort(uint64_t* keys, int n, int tid)
+{
+	int N = 1;
+	while (N < n) N <<= 1;
+	const int half = N >> 1;
+	for (int k = 2; k <= N; k <<= 1) {
+		const int hk = k >> 1;
+		for (int t = tid; t < half; t += 256) {
+			const int blk = t / hk, off = t - blk * hk;
+			const int i = blk * k + off, j = blk * k + (k - 1 - off);
+			if (j < n) {
+				const uint64_t a = keys[i], b = keys[j];
+				if (a > b) { keys[i] = b; keys[j] = a; }
+			}
+		}
+		__syncthreads();
+		for (int s = hk >> 1; s >= 1; s >>= 1) {
+			for (int t = tid; t < half; t += 256) {
+				const int i = ((t / s) * 2 * s) + (t % s), j = i + s;
+				if (j < n) {
+					const uint64_t a = keys[i], b = keys[j];
+					if (a > b) { keys[i] = b; keys[j] = a; }
+				}
+			}
+			__syncthreads();
+		}
+	}
+}
+
+// Register version for n <= 256 * E: thread t holds the keys at positions r * 256 + t (r < E), padded with
+// +inf.  One exchange step pairs position e with e ^ mask; the position whose `dirbit` is clear keeps the
+// smaller key.  The partner sits in the same thread (mask is a multiple of 256), in the same warp (shuffle) or
+// elsewhere (through shared memory); the network is unrolled at compile time, so every mask is a constant.
+template <int E>
+__device__ __forceinline__ void exchange_step(uint64_t (&key)[E], const int mask, const int dirbit, uint64_t* smem,
+                                              int tid)
+{
+	const int mr = mask >> 8, mt = mask & 255;
+	if (mt == 0) {
+#pragma unroll
+		for (int r = 0; r < E; r++) {
+			if ((r ^ mr) > r) {
+				const uint64_t a = key[r], b = key[r ^ mr];
+				key[r] = a < b ? a : b;
+				key[r ^ mr] = a < b ? b : a;
+			}
+		}
+		return;
+	}
+	uint64_t got[E];
+	if (mt < 32) {
+#pragma unroll
+		for (int r = 0; r < E; r++) got[r] = __shfl_xor_sync(0xffffffffu, key[r ^ mr], mt);
+	} else {
+#pragma unroll
+		for (int r = 0; r < E; r++) smem[r * 256 + tid] = key[r];
+		__syncthreads();
+#pragma unroll
+		for (int r = 0; r < E; r++) got[r] = smem[(r ^ mr) * 256 + (tid ^ mt)];
+		__syncthreads();
+	}
+#pragma unroll
+	for (int r = 0; r < E; r++) {
+		const bool lower = (((r << 8) | tid) & dirbit) == 0;
+		const uint64_t a = key[r], b = got[r];
+		key[r] = (lower == (a < b)) ? a : b;
+	}
+}
+
+// Loads the segment, sorts it, leaves the sorted keys in smem[0, n).
+template <int E>
+__device__ __forceinline__ void cta_sort_regs(const uint64_t* seg, int n, uint64_t* smem, int tid)
+{
+	uint64_t key[E];
+#pragma unroll
+	for (int r = 0; r < E; r++) key[r] = (r * 256 + tid) < n ? seg[r * 256 + tid] : ~0ull;
+#pragma unroll
+	for (int k = 2; k <= 256 * E; k <<= 1) {
+		exchange_step<E>(key, k - 1, k >> 1, smem, tid);
+#pragma unroll
+		for (int s = k >> 2; s >= 1; s >>= 1) exchange_step<E>(key, s, s, smem, tid);
+	}
+#pragma unroll
+	for (int r = 0; r < E; r++) smem[r * 256 + tid] = key[r];
+	__syncthreads();
+}
+
+__global__ void __launch_bounds__(256)
+tile_sort_kernel(int W, int H, unsigned gx, const uint2* __restrict__ ranges, uint64_t* pairs,
+                 const float4* __restrict__ splat, const ushort4* __restrict__ rect,
+                 const float4* __restrict__ cull, const uint32_t* __restrict__ offsets,
+                 uint64_t* __restrict__ keys_sorted, uint32_t* __restrict__ point_list, float4* instances,
+                 uint32_t* __restrict__ hit_words, uint32_t* __restrict__ hit_count)
+{
+	__shared__ uint64_t s_keys[TS_CAP];
+	const int tid = threadIdx.x, lane = tid & 31;
+	const unsigned tile = blockIdx.x;
+	const uint2 range = ranges[tile];
+	const int n = (int)(range.y - range.x);
+	if (n == 0) return;
+	uint64_t* seg = pairs + range.x;
+	uint64_t* kp = seg;
+	if (n <= TS_CAP) {
+		kp = s_keys;
+		if (n <= 256) cta_sort_regs<1>(seg, n, s_keys, tid);
+		else if (n <= 512) cta_sort_regs<2>(seg, n, s_keys, tid);
+		else if (n <= 1024) cta_sort_regs<4>(seg, n, s_keys, tid);
+		else cta_sort_regs<8>(seg, n, s_keys, tid);
+	} else {
+		__syncthreads();
+		cta_sort(seg, n, tid);
+	}
+
+	const int tx = (int)(tile % gx), ty = (int)(tile / gx);
+	// the reference's sorted key / value lists (gs2d_state_view, footprint audit)
+	for (int k = tid; k < n; k += 256) {
+		const uint64_t w = kp[k];
+		keys_sorted[range.x + k] = ((uint64_t)tile << 32) | (w >> 32);
+		point_list[range.x + k] = (uint32_t)w;
+	}
+	// gather: 5 consecutive threads copy the 5 float4 of a record -> the tile's list is written contiguously.
+	// Word 15 = in-tile footprint box, word 19 = the instance's gradient row (surfel-major, see common.cuh).
+	float4* tile_rec = instances + 5 * (size_t)range.x;
+	for (int t = tid; t < 5 * n; t += 256) {
+		const int k = t / 5, part = t - 5 * k;
+		const uint32_t idx = (uint32_t)kp[k];
+		float4 v = splat[5 * (size_t)idx + part];
+		if (part == 3) {
+			v.w = __uint_as_float(tile_box_word(cull[idx], tx, ty, W, H));
+		} else if (part == 4) {
+			const ushort4 r = rect[idx];
+			const uint32_t first = idx == 0 ? 0u : offsets[idx - 1];
+			v.w = __uint_as_float(first + (uint32_t)(ty - r.y) * (uint32_t)(r.z - r.x) + (uint32_t)(tx - r.x));
+		}
+		tile_rec[t] = v;
+	}
+	__syncthreads();   // the records just written are read back below (same CTA)
+	// footprints: a quarter-warp per instance
+	const float ox = (float)(tx * TILE), oy = (float)(ty * TILE);
+	for (int q0 = 0; q0 < n; q0 += 32) {
+		const int k = q0 + (tid >> 3);
+		const bool live = k < n;
+		uint32_t cnt;
+		const uint32_t word = footprint_word(live, tile_rec + 5 * (size_t)(live ? k : 0), ox, oy, lane, cnt);
+		if (live) {
+			hit_words[8 * ((size_t)range.x + k) + (lane & 7)] = word;
+			if ((lane & 7) == 0) hit_count[range.x + k] = cnt;
+		}
+	}
+}
+
+}  // namespace
+
+int launch_tile_binning(const gs2d_settings& s, const GeomState& g, const ImageState& im, const BinningState& b,
+                        int64_t I, cudaStream_t st)
+{
+	const int W = s.image_width, H = s.image_height;
+	const unsigned gx = (W + TILE - 1) / TILE, gy = (H + TILE - 1) / TILE;
+	const int tiles = (int)(gx * gy);
+	if (tiles == 0 || I <= 0) return GS2D_OK;
+	{
+		ProfScope ps(K_TILE_OFFSETS, st);
+		tile_offsets_kernel<<<1, 1024, 0, st>>>(tiles, im.tile_count, (uint2*)im.ranges, im.tile_cursor);
+		count_launch();
+	}
+	{
+		ProfScope ps(K_SCATTER, st);
+		scatter_kernel<<<(s.P + 255) / 256, 256, 0, st>>>(s.P, gx, g.depths, (const ushort4*)g.rect, g.tiles_touched,
+		                                                  im.tile_cursor, b.keys_a);
+		count_launch();
+	}
+	{
+		ProfScope ps(K_TILE_SORT, st);
+		tile_sort_kernel<<<tiles, 256, 0, st>>>(W, H, gx, (const uint2*)im.ranges, b.keys_a, (const float4*)g.splat,
+		                                        (const ushort4*)g.rect, (const float4*)g.cull, g.point_offsets, b.keys_b,
+		                                        b.vals_b, (float4*)b.instances, b.hit_inst, b.hit_count);
+		count_launch();
+	}
+	GS2D_CUDA_OK(cudaGetLastError());
+	return GS2D_OK;
+}
+
+}  // namespace gs2d

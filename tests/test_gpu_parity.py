@@ -189,3 +189,33 @@ def test_footprint_masks_are_a_superset(P, size, scale_mult, view, seed):
     out = gpu_run.run_ours(case, debug=False, backward=False)
     hits, bits, missed = (int(x) for x in out["footprint_audit"])
     assert hits > 0 and missed == 0, (hits, bits, missed)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("P", [1, 7, 250, 300, 600, 1100, 2100, 3000, 6000])
+def test_tile_local_sort_equals_the_stable_global_sort(P):
+    """tile_sort.cu: every size class of the per-tile sort (registers x1/x2/x4/x8, the in-memory fallback beyond
+    2048 instances per tile), with exact depth ties (duplicated surfels), against a stable argsort of the
+    reference-order unsorted list; ranges must partition the list by tile."""
+    import gpu_run
+    case = cases._base(P, cases._intr(32, 32), seed=11 + P, view=0, scale_mult=6.0)
+    if P >= 7:   # exact ties: copies of a few surfels (same depth bits, different index)
+        src = np.arange(0, P // 2, 3)
+        for k in ("means3D", "scales", "rotations"):
+            case[k] = case[k].copy()
+            case[k][src + P // 2] = case[k][src]
+    a = gpu_run.run_ours(case, debug=True)
+    n = int(a["num_rendered"])
+    ks = a["keys_sorted"]
+    order = np.argsort(a["keys_unsorted"], kind="stable")
+    assert np.array_equal(a["keys_unsorted"][order], ks)
+    assert np.array_equal(a["values_unsorted"][order], a["point_list"])
+    tiles = (ks >> np.uint64(32)).astype(np.int64)
+    r = a["ranges"].astype(np.int64)
+    cnt = np.bincount(tiles, minlength=r.shape[0])
+    assert np.array_equal(r[:, 1] - r[:, 0], cnt) and int(cnt.sum()) == n
+    if P >= 3000:
+        assert cnt.max() > 2048, "the fallback size class is not exercised"
+    assert int(a["footprint_audit"][2]) == 0
+    b = gpu_run.run_ours(case, debug=False)
+    assert not compare.check_images(a, b, exact=True)
