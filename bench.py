@@ -73,7 +73,7 @@ class ClockSampler:
         try:
             self.proc = subprocess.Popen(
                 ["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                 "-lms", "25"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+                 "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
         except OSError:
             self.proc = None
             return
@@ -104,6 +104,8 @@ class ClockSampler:
             self.proc.kill()
         sm, mx, pw, reasons = [], [], [], set()
         rows = [r for t, r in self.rows if self.t0 is None or (self.t0 <= t <= (self.t1 or t) + 0.03)]
+        if not rows and self.t0 is not None:   # region shorter than the sampling period: the samples bracketing it
+            rows = [r for t, r in self.rows if self.t0 - 0.15 <= t <= (self.t1 or t) + 0.15]
         for r in rows:
             f = [x.strip() for x in r.split(",")]
             if len(f) < 7:
@@ -174,16 +176,16 @@ def algorithmic_bytes(P, Pv, I, W, H):
     once).  Keys are gs2d kernel names."""
     Px, Tl = W * H, ((W + 15) // 16) * ((H + 15) // 16)
     return {
-        "preprocess_forward": 40 * P + 8 * P + 64 * Pv,
+        "preprocess_forward": 40 * P + 8 * P + 64 * Pv + 4 * I,   # + one RED per instance (tile counts)
         "scan_tiles": 8 * P,
-        "duplicate_keys": 20 * P + 12 * I,
-        "onesweep_pass": 24 * I,                       # per pass: read + write (u64 key, u32 value)
+        "scatter_pairs": 20 * P + 8 * I + 4 * I,       # depth/rect/count in, cursor RED + (depth, surfel) word out
+        # per tile: unsorted words in; sorted keys + point list, gathered 80-byte records, 256-bit masks, pair counts out
+        "tile_sort_gather_footprint": 8 * I + 12 * I + 80 * I + 80 * I + 32 * I + 4 * I + 8 * Tl,
+        "duplicate_keys": 20 * P + 12 * I,             # (debug mode / stand-alone sort only)
+        "onesweep_pass": 24 * I,
         "histogram": 8 * I,
-        "gather_ranges": 8 * I + 8 * Tl + 12 * I + 76 * I,   # sorted pairs in, per-instance records out
-        "footprint": 88 * I + 32 * I,                     # record + key in, 256-bit mask out (new stage)
         "composite_forward": 76 * I + 8 * Tl + 68 * Px,
-        "composite_backward": 76 * I + 8 * Tl + 68 * Px,            # kernel A (per pixel) reads records + pixel state
-        "composite_backward_instances": 76 * I + 64 * I,         # kernel B (per instance) reads records, writes rows
+        "composite_backward": 76 * I + 8 * Tl + 68 * Px + 64 * I,   # records + pixel state in, gradient rows out
         "preprocess_backward": 4 * P + 136 * Pv + 48 * Pv,
     }
 

@@ -195,7 +195,8 @@ int gs2d_forward_preprocess(const gs2d_settings* s, const gs2d_inputs* in, const
 	}
 	GS2D_TRY(launch_preprocess_forward(*s, *in, g, im.tile_count, radii, st));
 	GS2D_TRY(debug_sync(*s, st));
-	GS2D_TRY(launch_scan_tiles(g, s->P, st));
+	GS2D_TRY(launch_scan_tiles(g, s->P, st, (int)tiles_of(s->image_width, s->image_height), im.tile_count, im.ranges,
+	                           im.tile_cursor));
 	GS2D_TRY(debug_sync(*s, st));
 	if (num_rendered_host) {
 		// 4-byte read-back into the low half of the (zeroed) int64

@@ -1,4 +1,5 @@
-// binning.cu -- tile binning: key duplication, onesweep radix sort, tile ranges + instance gather.
+// binning.cu -- key duplication (debug view of the reference's unsorted list) and the onesweep radix sort
+// (stand-alone gs2d_sort_pairs + the Morton sort of distCUDA2).  The rendering path bins per tile: tile_sort.cu.
 //
 // Replaces duplicateWithKeys (CR/rasterizer_impl.cu:70-111), cub::DeviceRadixSort::SortPairs
 // (:309-314) and cudaMemset + identifyTileRanges (:116-138, :316-323).  Keys, sorted order and
@@ -248,46 +249,6 @@ onesweep_kernel(long long n, const uint64_t* __restrict__ keys_in, const uint32_
 	}
 }
 
-// ---- tile ranges + instance gather -----------------------------------------------------------------
-// One warp-quarter... one thread group of 5 lanes would complicate things: keep one thread per
-// sorted instance for the bookkeeping and let 5 consecutive float4 stores per thread carry the
-// record (80 B, contiguous in the output).
-__global__ void __launch_bounds__(256)
-gather_ranges_kernel(long long I, unsigned gx, int W, int H, const uint64_t* __restrict__ keys,
-                     const uint32_t* __restrict__ point_list, const float4* __restrict__ splat,
-                     const ushort4* __restrict__ rect, const float4* __restrict__ cull,
-                     const uint32_t* __restrict__ offsets, float4* __restrict__ instances,
-                     uint32_t* __restrict__ ranges)
-{
-	long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-	if (i >= I) return;
-	const uint64_t key = keys[i];
-	const uint32_t tile = (uint32_t)(key >> 32);
-	if (i == 0) {
-		ranges[2 * tile] = 0;
-	} else {
-		uint32_t prev = (uint32_t)(keys[i - 1] >> 32);
-		if (prev != tile) {
-			ranges[2 * prev + 1] = (uint32_t)i;
-			ranges[2 * tile] = (uint32_t)i;
-		}
-	}
-	if (i == I - 1) ranges[2 * tile + 1] = (uint32_t)I;
-
-	const uint32_t idx = point_list[i];
-	const int tx = tile % gx, ty = tile / gx;
-	const ushort4 r = rect[idx];
-	const uint32_t start = idx == 0 ? 0u : offsets[idx - 1];
-	const uint32_t row = start + (uint32_t)(ty - r.y) * (uint32_t)(r.z - r.x) + (uint32_t)(tx - r.x);
-	const uint32_t mask = tile_box_word(cull[idx], tx, ty, W, H);
-	const float4* src = splat + 5 * (size_t)idx;
-	float4 a = src[0], b = src[1], c = src[2], d = src[3], e = src[4];
-	d.w = __uint_as_float(mask);
-	e.w = __uint_as_float(row);
-	float4* dst = instances + 5 * (size_t)i;
-	dst[0] = a; dst[1] = b; dst[2] = c; dst[3] = d; dst[4] = e;
-}
-
 }  // namespace
 
 uint32_t higher_msb(uint32_t n)
@@ -377,25 +338,6 @@ int launch_sort_pairs(int64_t n, const uint64_t* keys_in, const uint32_t* vals_i
 		}
 	}
 	return sort_passes_run(n, keys_a_rw, vals_a_rw, keys_b, vals_b, end_bit, ss, result_in_b, st);
-}
-
-int launch_gather_ranges(const gs2d_settings& s, const GeomState& g, const uint64_t* keys_sorted,
-                         const uint32_t* point_list, float* instances, uint32_t* ranges, int64_t I,
-                         cudaStream_t st)
-{
-	const unsigned gx = (s.image_width + TILE - 1) / TILE, gy = (s.image_height + TILE - 1) / TILE;
-	{ ProfScope ps(K_MEMSET, st); GS2D_CUDA_OK(cudaMemsetAsync(ranges, 0, sizeof(uint32_t) * 2 * (size_t)gx * gy, st)); }
-	if (I > 0) {
-		{
-			ProfScope ps(K_GATHER_RANGES, st);
-			gather_ranges_kernel<<<(unsigned)((I + 255) / 256), 256, 0, st>>>(
-				I, gx, s.image_width, s.image_height, keys_sorted, point_list, (const float4*)g.splat, (const ushort4*)g.rect,
-				(const float4*)g.cull, g.point_offsets, (float4*)instances, ranges);
-			count_launch();
-		}
-	}
-	GS2D_CUDA_OK(cudaGetLastError());
-	return GS2D_OK;
 }
 
 }  // namespace gs2d

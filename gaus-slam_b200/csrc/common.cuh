@@ -156,19 +156,17 @@ int launch_preprocess_forward(const gs2d_settings& s, const gs2d_inputs& in, con
                               uint32_t* tile_count, int32_t* radii, cudaStream_t st);
 int launch_tile_binning(const gs2d_settings& s, const GeomState& g, const ImageState& im, const BinningState& b,
                         int64_t I, cudaStream_t st);
-int launch_scan_tiles(const GeomState& g, int P, cudaStream_t st);   // zeroes [scan_status, counters + 8) itself
+// zeroes [scan_status, counters + 8) itself; one extra block turns the per-tile counts into ranges + cursors
+int launch_scan_tiles(const GeomState& g, int P, cudaStream_t st, int tiles, const uint32_t* tile_count,
+                      uint32_t* ranges, uint32_t* tile_cursor);
 int launch_scan_u32(const uint32_t* in, uint32_t* out, long long n, uint64_t* status, uint32_t* counters,
-                    cudaStream_t st, bool clear = true);
+                    cudaStream_t st, bool clear = true, int side_n = 0, const uint32_t* side_in = nullptr,
+                    uint32_t* side_ranges = nullptr, uint32_t* side_cursor = nullptr);
 int launch_duplicate(const gs2d_settings& s, const GeomState& g, const int32_t* radii_unused,
                      const BinningState& b, int64_t I, cudaStream_t st);
 int launch_sort_pairs(int64_t n, const uint64_t* keys_a, const uint32_t* vals_a, uint64_t* keys_b,
                       uint32_t* vals_b, uint64_t* keys_a_rw, uint32_t* vals_a_rw, int end_bit,
                       const SortScratch& ss, bool* result_in_b, cudaStream_t st);
-int launch_gather_ranges(const gs2d_settings& s, const GeomState& g, const uint64_t* keys_sorted,
-                         const uint32_t* point_list, float* instances, uint32_t* ranges, int64_t I,
-                         cudaStream_t st);
-int launch_footprint(const gs2d_settings& s, const float* instances, const uint64_t* keys_sorted,
-                     uint32_t* hit_inst, uint32_t* hit_count, int64_t I, cudaStream_t st);
 int launch_footprint_audit(const gs2d_settings& s, const float* instances, const uint64_t* keys_sorted,
                            const uint32_t* hit_inst, int64_t I, unsigned long long* counts, cudaStream_t st);
 int launch_composite_forward(const gs2d_settings& s, const gs2d_inputs& in, const ImageState& im,

@@ -23,28 +23,6 @@ namespace gs2d {
 
 namespace {
 
-__global__ void __launch_bounds__(256)
-footprint_kernel(long long I, unsigned gx, float inv_gx, const float4* __restrict__ instances,
-                 const uint64_t* __restrict__ keys_sorted, uint32_t* __restrict__ hit_words,
-                 uint32_t* __restrict__ hit_count)
-{
-	const int lane = threadIdx.x & 31;
-	const long long i = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 3;
-	const bool live = i < I;
-	float ox = 0.f, oy = 0.f;
-	if (live) {
-		const uint32_t tile = (uint32_t)(keys_sorted[i] >> 32);
-		const uint32_t ty = (uint32_t)(((float)tile + 0.5f) * inv_gx);     // tile / gx, exact for tile < 2^20
-		ox = (float)((tile - ty * gx) * TILE); oy = (float)(ty * TILE);
-	}
-	uint32_t cnt;
-	const uint32_t word = footprint_word(live, instances + 5 * (size_t)(live ? i : 0), ox, oy, lane, cnt);
-	if (live) {
-		hit_words[8 * (size_t)i + (lane & 7)] = word;
-		if ((lane & 7) == 0) hit_count[i] = cnt;
-	}
-}
-
 // Audit (tests only): one thread per instance evaluates the exact tests (pair_front) at all 256 tile pixels
 // and compares with the mask: counts[0] += exact hits, [1] += mask bits, [2] += exact hits MISSING in the mask.
 __global__ void __launch_bounds__(128)
@@ -93,20 +71,6 @@ int launch_footprint_audit(const gs2d_settings& s, const float* instances, const
 	const unsigned gx = (s.image_width + TILE - 1) / TILE;
 	footprint_audit_kernel<<<(unsigned)((I + 127) / 128), 128, 0, st>>>(
 		I, gx, s.image_width, s.image_height, (const float4*)instances, keys_sorted, (const uint16_t*)hit_inst, counts);
-	GS2D_CUDA_OK(cudaGetLastError());
-	return GS2D_OK;
-}
-
-int launch_footprint(const gs2d_settings& s, const float* instances, const uint64_t* keys_sorted,
-                     uint32_t* hit_inst, uint32_t* hit_count, int64_t I, cudaStream_t st)
-{
-	if (I <= 0) return GS2D_OK;
-	const unsigned gx = (s.image_width + TILE - 1) / TILE;
-	const long long threads = I * 8;
-	ProfScope ps(K_FOOTPRINT, st);
-	footprint_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, st>>>(I, gx, 1.0f / (float)gx, (const float4*)instances,
-	                                                                    keys_sorted, hit_inst, hit_count);
-	count_launch();
 	GS2D_CUDA_OK(cudaGetLastError());
 	return GS2D_OK;
 }

@@ -183,9 +183,45 @@ preprocess_forward_kernel(int P, int D, int M,
 // status word: bits 63..62 flag (1 = block aggregate, 2 = inclusive prefix), low 62 bits value.
 constexpr unsigned long long ST_AGG = 1ull << 62, ST_PREFIX = 2ull << 62, ST_MASK = (1ull << 62) - 1;
 
+// Exclusive scan of side_n counts by one CTA of SCAN_THREADS threads: ranges[t] = (start, end) -- (0, 0) for an
+// empty tile, like the reference's memset -- and cursor[t] = start.
+__device__ void side_scan_block(int side_n, const uint32_t* __restrict__ cnt, uint2* __restrict__ ranges,
+                                uint32_t* __restrict__ cursor, uint32_t* s_warp)
+{
+	const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+	uint32_t carry = 0;
+	for (int base = 0; base < side_n; base += SCAN_THREADS) {
+		const int i = base + tid;
+		const uint32_t v = i < side_n ? cnt[i] : 0u;
+		uint32_t incl = v;
+#pragma unroll
+		for (int o = 1; o < 32; o <<= 1) {
+			const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+			if (lane >= o) incl += t;
+		}
+		__syncthreads();   // s_warp of the previous round is consumed
+		if (lane == 31) s_warp[warp] = incl;
+		__syncthreads();
+		uint32_t woff = 0, total = 0;
+#pragma unroll
+		for (int w = 0; w < SCAN_THREADS / 32; w++) {
+			const uint32_t t = s_warp[w];
+			if (w < warp) woff += t;
+			total += t;
+		}
+		const uint32_t start = carry + woff + incl - v;
+		if (i < side_n) {
+			ranges[i] = v ? make_uint2(start, start + v) : make_uint2(0u, 0u);
+			cursor[i] = start;
+		}
+		carry += total;
+	}
+}
+
 __global__ void __launch_bounds__(SCAN_THREADS)
 scan_tiles_kernel(const uint32_t* __restrict__ in, uint32_t* __restrict__ out, int n,
-                  unsigned long long* status, uint32_t* counters)
+                  unsigned long long* status, uint32_t* counters, int side_n, const uint32_t* __restrict__ side_in,
+                  uint2* __restrict__ side_ranges, uint32_t* __restrict__ side_cursor)
 {
 	__shared__ uint32_t s_block;
 	__shared__ uint32_t s_warp[SCAN_THREADS / 32];
@@ -193,6 +229,12 @@ scan_tiles_kernel(const uint32_t* __restrict__ in, uint32_t* __restrict__ out, i
 	if (threadIdx.x == 0) s_block = atomicAdd(&counters[0], 1u);
 	__syncthreads();
 	const uint32_t bid = s_block;
+	if ((long long)bid * SCAN_TILE >= n) {
+		// The one extra block of the launch: exclusive scan of the (few thousand) per-tile instance counts ->
+		// tile ranges + scatter cursors (tile_sort.cu), done beside the big scan instead of in its own launch.
+		side_scan_block(side_n, side_in, side_ranges, side_cursor, s_warp);
+		return;
+	}
 	const int base = bid * SCAN_TILE + threadIdx.x * SCAN_ITEMS;
 
 	uint32_t v[SCAN_ITEMS];
@@ -292,30 +334,35 @@ int launch_preprocess_forward(const gs2d_settings& s, const gs2d_inputs& in, con
 // Inclusive scan of n u32 values (single pass, decoupled look-back).  status: n / SCAN_TILE + 1 u64 words,
 // counters: 8 u32 words (both zeroed here); counters[1] receives the total.
 int launch_scan_u32(const uint32_t* in, uint32_t* out, long long n, uint64_t* status, uint32_t* counters,
-                    cudaStream_t st, bool clear)
+                    cudaStream_t st, bool clear, int side_n, const uint32_t* side_in, uint32_t* side_ranges,
+                    uint32_t* side_cursor)
 {
 	const int blocks = (int)((n + SCAN_TILE - 1) / SCAN_TILE);
 	if (clear) {
 		{ ProfScope ps(K_MEMSET, st); GS2D_CUDA_OK(cudaMemsetAsync(status, 0, sizeof(uint64_t) * (size_t)(blocks + 1), st)); }
 		{ ProfScope ps(K_MEMSET, st); GS2D_CUDA_OK(cudaMemsetAsync(counters, 0, sizeof(uint32_t) * 8, st)); }
 	}
-	if (blocks > 0) {
+	const int extra = side_n > 0 ? 1 : 0;
+	if (blocks + extra > 0) {
 		ProfScope ps(K_SCAN, st);
-		scan_tiles_kernel<<<blocks, SCAN_THREADS, 0, st>>>(in, out, (int)n, (unsigned long long*)status, counters);
+		scan_tiles_kernel<<<blocks + extra, SCAN_THREADS, 0, st>>>(in, out, (int)n, (unsigned long long*)status, counters,
+		                                                          side_n, side_in, (uint2*)side_ranges, side_cursor);
 		count_launch();
 	}
 	GS2D_CUDA_OK(cudaGetLastError());
 	return GS2D_OK;
 }
 
-int launch_scan_tiles(const GeomState& g, int P, cudaStream_t st)
+int launch_scan_tiles(const GeomState& g, int P, cudaStream_t st, int tiles, const uint32_t* tile_count,
+                      uint32_t* ranges, uint32_t* tile_cursor)
 {
 	// status words and counters are adjacent in the geom buffer: one memset
 	{
 		ProfScope ps(K_MEMSET, st);
 		GS2D_CUDA_OK(cudaMemsetAsync(g.scan_status, 0, (size_t)((char*)(g.counters + 8) - (char*)g.scan_status), st));
 	}
-	return launch_scan_u32(g.tiles_touched, g.point_offsets, P, g.scan_status, g.counters, st, false);
+	return launch_scan_u32(g.tiles_touched, g.point_offsets, P, g.scan_status, g.counters, st, false, tiles, tile_count,
+	                       ranges, tile_cursor);
 }
 
 int launch_mark_visible(int P, const float* means3D, const float* view, const float* proj,

@@ -7,7 +7,8 @@
 // ascending; equal depths by surfel index ascending (duplicateWithKeys emits surfels in index order and a
 // surfel touches a tile once, so "stable" means exactly that).  Hence:
 //   1. preprocess_forward counts the instances of every tile (one RED per instance, preprocess.cu);
-//   2. tile_offsets_kernel scans the 3 225 counts -> tile ranges (identifyTileRanges's output) + write cursors;
+//   2. one extra block of the tiles_touched scan (preprocess.cu) scans the 3 225 counts -> tile ranges
+//      (identifyTileRanges's output) + write cursors;
 //   3. scatter_kernel drops every instance's (depth bits << 32 | surfel) word into its tile's segment, in
 //      whatever order the atomics resolve;
 //   4. tile_sort_kernel (one CTA per tile) sorts the segment by that 64-bit word in shared memory -- unique
@@ -25,48 +26,6 @@ namespace gs2d {
 namespace {
 
 constexpr int TS_CAP = 2048;   // instances of a tile sorted in shared memory (16 KB of keys)
-
-// Exclusive scan of the per-tile counts (one CTA): ranges[t] = (start, end), cursor[t] = start.
-__global__ void __launch_bounds__(1024)
-tile_offsets_kernel(int tiles, const uint32_t* __restrict__ tile_count, uint2* __restrict__ ranges,
-                    uint32_t* __restrict__ cursor)
-{
-	__shared__ uint32_t s_warp[32];
-	__shared__ uint32_t s_total;
-	const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-	uint32_t carry = 0;
-	for (int base = 0; base < tiles; base += 1024) {
-		const int i = base + tid;
-		const uint32_t v = i < tiles ? tile_count[i] : 0u;
-		uint32_t incl = v;
-#pragma unroll
-		for (int o = 1; o < 32; o <<= 1) {
-			const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
-			if (lane >= o) incl += t;
-		}
-		if (lane == 31) s_warp[warp] = incl;
-		__syncthreads();
-		if (warp == 0) {
-			const uint32_t w = s_warp[lane];
-			uint32_t wi = w;
-#pragma unroll
-			for (int o = 1; o < 32; o <<= 1) {
-				const uint32_t t = __shfl_up_sync(0xffffffffu, wi, o);
-				if (lane >= o) wi += t;
-			}
-			s_warp[lane] = wi - w;
-			if (lane == 31) s_total = wi;
-		}
-		__syncthreads();
-		const uint32_t start = carry + s_warp[warp] + incl - v;
-		if (i < tiles) {
-			ranges[i] = v ? make_uint2(start, start + v) : make_uint2(0u, 0u);   // empty tiles stay (0, 0) like the reference's memset
-			cursor[i] = start;
-		}
-		carry += s_total;
-		__syncthreads();
-	}
-}
 
 // One thread per surfel, like duplicateWithKeys -- but the destination is the tile's own segment.
 __global__ void __launch_bounds__(256)
@@ -245,11 +204,7 @@ int launch_tile_binning(const gs2d_settings& s, const GeomState& g, const ImageS
 	const unsigned gx = (W + TILE - 1) / TILE, gy = (H + TILE - 1) / TILE;
 	const int tiles = (int)(gx * gy);
 	if (tiles == 0 || I <= 0) return GS2D_OK;
-	{
-		ProfScope ps(K_TILE_OFFSETS, st);
-		tile_offsets_kernel<<<1, 1024, 0, st>>>(tiles, im.tile_count, (uint2*)im.ranges, im.tile_cursor);
-		count_launch();
-	}
+	// (tile ranges and cursors come from the extra block of the tiles_touched scan, preprocess.cu)
 	{
 		ProfScope ps(K_SCATTER, st);
 		scatter_kernel<<<(s.P + 255) / 256, 256, 0, st>>>(s.P, gx, g.depths, (const ushort4*)g.rect, g.tiles_touched,

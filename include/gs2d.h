@@ -99,14 +99,19 @@ size_t gs2d_binning_bytes(int64_t num_rendered, int32_t image_width, int32_t ima
 /* Stage 1 of forward: per-surfel preprocess (world->ray-splat transform, screen bounds,
  * tile counts; CR/forward.cu:150-253) and the inclusive scan of tile counts
  * (CR/rasterizer_impl.cu:283).  Writes `radii` [P] int32 (zero for culled surfels).
+ * Also counts the instances of every tile and turns the counts into the tile ranges
+ * (the output of identifyTileRanges, CR/rasterizer_impl.cu:116-138) for the tile-local sort.
  * Enqueues an async copy of num_rendered to `num_rendered_host` (pinned host int64) when
- * that pointer is not NULL. Needs buffers->geom (gs2d_geom_bytes). */
+ * that pointer is not NULL. Needs buffers->geom (gs2d_geom_bytes) and buffers->image
+ * (gs2d_image_bytes). */
 int gs2d_forward_preprocess(const gs2d_settings* s, const gs2d_inputs* in,
                             const gs2d_buffers* buffers, int32_t* radii,
                             int64_t* num_rendered_host, void* stream);
 
-/* Stage 2 of forward: key duplication, radix sort, tile ranges, per-tile compositing
- * (CR/rasterizer_impl.cu:295-347, CR/forward.cu:258-467).  `num_rendered` is the exact
+/* Stage 2 of forward: binning -- the sorted per-tile instance lists that duplicateWithKeys +
+ * cub::DeviceRadixSort::SortPairs + identifyTileRanges produce (CR/rasterizer_impl.cu:295-323), here by a
+ * scatter into tile segments and a sort inside each tile, same order bit for bit -- and per-tile
+ * compositing (CR/rasterizer_impl.cu:325-347, CR/forward.cu:258-467).  `num_rendered` is the exact
  * instance count read back after stage 1; buffers->binning must hold
  * gs2d_binning_bytes(num_rendered, W, H) and buffers->image gs2d_image_bytes(W, H).
  * out_color [3,H,W], out_others [7,H,W] are fully written (no pre-zeroing needed).
