@@ -367,6 +367,11 @@ def main():
     order = ["means3D", "opacities", "scales", "rotations", "colors"]
 
     from gs2d_b200 import mapping
+    grad_path = {"zero_copy": None}
+    if multi and a.impl == "b200":
+        # gradients of the five parameter groups are written straight into the buffer the all-reduce runs on
+        from gaus_2dgs_rasterization import _C as _gs2d_C
+        _gs2d_C.set_gradient_arena(flat)
 
     def view_of(step):
         return wl["sets"][mapping.view_of(step, rank, world if multi else 1, V)]
@@ -374,6 +379,8 @@ def main():
     def step_resident(step):
         color, others, g = arm.forward_backward(view_of(step))
         if multi:
+            if grad_path["zero_copy"] is None:
+                grad_path["zero_copy"] = mapping.grads_alias_flat(g, flat)
             mapping.allreduce_map_gradient(mapping.pack_grads(g, flat))
         return color
 
@@ -573,7 +580,7 @@ def main():
            "config": {"workload": f"mapping-shaped fwd+bwd of one keyframe view per GPU per step, {W}x{H}, "
                                   f"{P} surfels, {V}-keyframe window (BASELINE.json configs[2]), use_sa=True",
                       "surfels": P, "visible_mean": Pv_mean, "instances_mean": I_mean, "views": V,
-                      "parallelism": f"view-sharded x{world if multi else 1}" + (", NCCL all-reduce of [P,13] map gradients" if multi else ""),
+                      "parallelism": f"view-sharded x{world if multi else 1}" + (", NCCL all-reduce of [P,13] map gradients" + (" written in place by the backward pass" if grad_path["zero_copy"] else " (packed copy)") if multi else ""),
                       "l2": f"inputs rotate over {V} per-view sets ({V} x {(P * 52 + W * H * 56) / 1e6:.1f} MB > 126 MB L2); no explicit flush"},
            "gpu_launches": launches, "clocks": clocks}
     if a.impl == "reference":

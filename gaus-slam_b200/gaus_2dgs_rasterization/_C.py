@@ -19,6 +19,25 @@ _pinned = {}
 _PAIR_RING = 64
 _pair_slots = {}
 _pair_of_binning = {}
+# Optional destination of the five map-parameter gradients (gs2d_b200.mapping.gradient_arena): a flat fp32
+# buffer [13 * P] laid out group by group (xyz | opacity | scale | rotation | rgb).  While set, the backward
+# pass writes those gradients straight into it, so a view-sharded trainer all-reduces the buffer without a
+# packing copy (the "write grads straight into the collective's buffer" item of SURVEY.md 8e).
+_grad_arena = None
+
+
+def set_gradient_arena(flat):
+    global _grad_arena
+    _grad_arena = flat
+
+
+def _arena_views(P, dev):
+    a = _grad_arena
+    if a is None or a.device != dev or a.dtype != torch.float32 or a.numel() != 13 * P or not a.is_contiguous():
+        return None
+    o = [0, 3 * P, 4 * P, 6 * P, 10 * P, 13 * P]
+    return (a[o[0]:o[1]].view(P, 3), a[o[1]:o[2]].view(P, 1), a[o[2]:o[3]].view(P, 2), a[o[3]:o[4]].view(P, 4),
+            a[o[4]:o[5]].view(P, 3))
 
 
 def _stream_ptr(device) -> C.c_void_p:
@@ -146,10 +165,15 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
     M = int(sh.shape[1]) if sh.numel() != 0 and sh.ndim >= 2 else 0
 
     f32 = dict(dtype=torch.float32, device=dev)
-    g_means3D = torch.empty((P, 3), **f32); g_means2D = torch.empty((P, 3), **f32)
-    g_colors = torch.empty((P, 3), **f32); g_opacity = torch.empty((P, 1), **f32)
+    arena = _arena_views(P, dev) if P else None
+    if arena is not None:
+        g_means3D, g_opacity, g_scales, g_rot, g_colors = arena
+    else:
+        g_means3D = torch.empty((P, 3), **f32); g_opacity = torch.empty((P, 1), **f32)
+        g_scales = torch.empty((P, 2), **f32); g_rot = torch.empty((P, 4), **f32)
+        g_colors = torch.empty((P, 3), **f32)
+    g_means2D = torch.empty((P, 3), **f32)
     g_transMat = torch.empty((P, 9), **f32); g_sh = torch.empty((P, M, 3), **f32)
-    g_scales = torch.empty((P, 2), **f32); g_rot = torch.empty((P, 4), **f32)
     if P == 0:
         return g_means2D, g_colors, g_opacity, g_means3D, g_transMat, g_sh, g_scales, g_rot
 

@@ -8,6 +8,8 @@ of the number of ranks.  Works with any torch.distributed backend (NCCL on the G
 """
 from __future__ import annotations
 
+import contextlib
+
 import torch
 import torch.distributed as dist
 
@@ -36,10 +38,34 @@ def flat_sections(P: int):
     return out
 
 
+def grads_alias_flat(grads: dict, flat: torch.Tensor) -> bool:
+    """True when every group gradient already lives in its section of `flat` (gradient_arena)."""
+    P = flat.numel() // FLAT_WIDTH
+    return all(grads[name] is not None and grads[name].data_ptr() == flat.data_ptr() + 4 * a
+               for name, a, _ in flat_sections(P))
+
+
 def pack_grads(grads: dict, flat: torch.Tensor) -> torch.Tensor:
-    """Concatenate the per-group gradients into `flat` (one copy kernel)."""
-    torch.cat([grads[k].reshape(-1) for k in PARAM_ORDER], out=flat)
+    """The per-group gradients as one flat buffer: nothing to do when the backward pass wrote them there
+    (gradient_arena), else one concatenating copy."""
+    if not grads_alias_flat(grads, flat):
+        torch.cat([grads[k].reshape(-1) for k in PARAM_ORDER], out=flat)
     return flat
+
+
+@contextlib.contextmanager
+def gradient_arena(flat: torch.Tensor):
+    """While active, the rasterizer's backward pass writes dL/d(means3D, opacities, scales, rotations, colors)
+    directly into the sections of `flat` ([13 * P] fp32 on the surfels' device): `param.grad` then aliases the
+    buffer the all-reduce runs on, with no packing copy in between.  One backward pass per all-reduce (a second
+    one would overwrite the first: accumulate over views by all-reducing per view or summing into another
+    buffer)."""
+    from gaus_2dgs_rasterization import _C
+    _C.set_gradient_arena(flat)
+    try:
+        yield flat
+    finally:
+        _C.set_gradient_arena(None)
 
 
 def unpack_grads(flat: torch.Tensor, P: int) -> dict:

@@ -219,3 +219,40 @@ def test_tile_local_sort_equals_the_stable_global_sort(P):
     assert int(a["footprint_audit"][2]) == 0
     b = gpu_run.run_ours(case, debug=False)
     assert not compare.check_images(a, b, exact=True)
+
+
+@pytest.mark.gpu
+def test_gradient_arena_is_zero_copy_and_changes_nothing():
+    """gs2d_b200.mapping.gradient_arena: through the public API + autograd, the five parameter gradients land in
+    the flat [13 P] buffer (param.grad aliases it) and equal the gradients of a run without the arena."""
+    import torch
+    import gaus_2dgs_rasterization as G
+    from gs2d_b200 import mapping
+    case = cases.room_sa()
+    dev = torch.device("cuda:0")
+    P, W, H = case["means3D"].shape[0], case["W"], case["H"]
+    t = lambda x: torch.from_numpy(np.ascontiguousarray(x, dtype=np.float32)).to(dev)
+
+    def run():
+        prm = {k: t(case[k]).requires_grad_(True) for k in ("means3D", "opacities", "scales", "rotations", "colors")}
+        means2D = torch.zeros((P, 3), device=dev, requires_grad=True)
+        st = G.GaussianRasterizationSettings(
+            image_height=H, image_width=W, tanfovx=float(case["tanfovx"]), tanfovy=float(case["tanfovy"]), bg=t(case["bg"]),
+            scale_modifier=1.0, viewmatrix=t(case["viewmatrix"]).view(4, 4), projmatrix=t(case["projmatrix"]).view(4, 4),
+            sh_degree=0, campos=t(case["campos"]), use_sa=True, prefiltered=False, debug=False)
+        color, radii, allmap = G.GaussianRasterizer(st)(
+            means3D=prm["means3D"], means2D=means2D, opacities=prm["opacities"], colors_precomp=prm["colors"],
+            scales=prm["scales"], rotations=prm["rotations"])
+        torch.autograd.backward([color, allmap], [t(case["dL_dcolor"]), t(case["dL_dothers"])])
+        return {k: v.grad for k, v in prm.items()}
+
+    plain = run()
+    flat = torch.full((13 * P,), float("nan"), device=dev)
+    with mapping.gradient_arena(flat):
+        inplace = run()
+    assert mapping.grads_alias_flat(inplace, flat), "gradients were copied instead of written in place"
+    assert not mapping.grads_alias_flat(run(), flat), "the arena leaked out of its context"
+    back = mapping.unpack_grads(flat, P)
+    for k in plain:
+        assert torch.equal(back[k], inplace[k])
+        assert compare.grad_rel(inplace[k].cpu().numpy(), plain[k].cpu().numpy()) < 1e-6, k

@@ -89,3 +89,15 @@ def test_allreduce_of_view_sharded_gradients_gloo(tmp_path):
         scale = float(want.abs().max())
         assert scale > 0
         assert torch.allclose(got, want, rtol=1e-4, atol=1e-5 * scale)
+
+
+def test_pack_is_a_noop_when_gradients_alias_the_flat_buffer():
+    flat = torch.zeros(P * mapping.FLAT_WIDTH)
+    views = mapping.unpack_grads(flat, P)
+    for k, v in views.items():
+        v.copy_(torch.randn_like(v))
+    assert mapping.grads_alias_flat(views, flat)
+    before = flat.clone()
+    assert mapping.pack_grads(views, flat) is flat and torch.equal(flat, before)
+    other = {k: v.clone() for k, v in views.items()}
+    assert not mapping.grads_alias_flat(other, flat)
