@@ -47,6 +47,9 @@ def parse_args():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-kernel-timing", action="store_true")
     ap.add_argument("--cpu-frames", type=int, default=2)
+    ap.add_argument("--no-stats", action="store_true",
+                    help="skip the (untimed) scene-statistics renders: for ncu launch lists of the timed steps only")
+    ap.add_argument("--clock-period-ms", type=int, default=100, help="nvidia-smi sampling period; 0 = no sampling (diagnosis)")
     return ap.parse_args()
 
 
@@ -59,8 +62,9 @@ class ClockSampler:
          "clocks_event_reasons.sw_power_cap")
     NAMES = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
 
-    def __init__(self, index: int):
+    def __init__(self, index: int, period_ms: int = 100):
         self.index = index
+        self.period_ms = period_ms
         self.rows = []
         self.proc = None
         self.thread = None
@@ -70,10 +74,12 @@ class ClockSampler:
         and must not fall into the timed region.  Samples are time-stamped as they arrive; stop() keeps those
         taken between mark_begin() and mark_end()."""
         self.t0 = self.t1 = None
+        if self.period_ms <= 0:
+            return
         try:
             self.proc = subprocess.Popen(
                 ["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                 "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+                 "-lms", str(self.period_ms)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
         except OSError:
             self.proc = None
             return
@@ -405,7 +411,7 @@ def main():
         return float(ms.item())
 
     # ---- device-resident `value`
-    sampler = ClockSampler(local_rank)
+    sampler = ClockSampler(local_rank, a.clock_period_ms)
     if rank == 0:
         sampler.start()
     for i in range(a.warmup):
@@ -420,9 +426,9 @@ def main():
     value = world * 1000.0 / ms_per_step if multi else 1000.0 / ms_per_step
 
     # scene statistics of the window (instances I = num_rendered, visible surfels Pv), outside the timed region
-    stats = []
+    stats = [(float("nan"), float("nan"))] if a.no_stats else []
     with torch.no_grad():
-        for v in range(V):
+        for v in range(0 if a.no_stats else V):
             s_ = wl["sets"][v]
             if isinstance(arm, ApiArm):
                 e_ = wl["empty"]

@@ -1,3 +1,5 @@
+import signal
+signal.signal(signal.SIGPIPE, signal.SIG_DFL)
 import json, sys
 for f in sys.argv[1:] or ['gpurun_out/bench_b200.json', 'gpurun_out/bench_ref.json']:
     try:
