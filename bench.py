@@ -472,21 +472,24 @@ def main():
                 k["gbs"] = alg[name] / (avg_ms * 1e-3) / 1e9
                 k["frac_hbm"] = k["gbs"] / peak
             kernels[name] = k
+        traffic = {}
+        try:        # DRAM bytes per launch from the committed ncu --set full captures (profiles/)
+            with open(os.path.join(ROOT, "profiles", "r1_ncu_traffic.json")) as f:
+                traffic = json.load(f)
+        except OSError:
+            pass
+        for n, k in kernels.items():
+            if n in traffic:
+                k["ncu_dram_bytes"] = traffic[n]
         dom = max((n for n in kernels if n in alg), key=lambda n: kernels[n]["ms_per_step"])
         roofline = {"kernel": dom, "bound": "hbm", "achieved": kernels[dom]["gbs"], "peak": peak, "unit": "GB/s",
-                    "frac": kernels[dom]["frac_hbm"], "traffic": None, "peak_source": peak_src,
+                    "frac": kernels[dom]["frac_hbm"], "traffic": traffic.get(dom), "peak_source": peak_src,
                     "avg_launch_us": kernels[dom]["avg_us"], "alg_bytes_per_launch": kernels[dom]["alg_bytes"],
                     "share_of_step": kernels[dom]["ms_per_step"] / (ms_timed_pass / a.steps),
                     "note": "compositing is FP32-issue/MUFU-bound, not HBM-bound (DESIGN.md): the HBM fraction of this "
                             "kernel is small by construction; see `kernels` for the HBM-bound stages",
                     "timed_over": f"second pass of {a.steps} steps with CUDA events around every launch "
                                   f"({ms_timed_pass / a.steps:.3f} ms/step vs {ms_per_step:.3f} untimed)"}
-        traffic_file = os.path.join(ROOT, "profiles", "traffic.json")
-        if os.path.exists(traffic_file):
-            try:
-                roofline["traffic"] = json.load(open(traffic_file)).get(dom)
-            except Exception:
-                pass
 
     # ---- e2e: public API, per-step inputs from pinned host memory, loss read back to the host
     e2e = None
