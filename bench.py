@@ -414,6 +414,16 @@ def main():
     sampler = ClockSampler(local_rank, a.clock_period_ms)
     if rank == 0:
         sampler.start()
+    # Spin-up before the W warm-up steps: an idle B200 sits at ~120 MHz and a handful of millisecond steps is not
+    # enough for it to reach its running clocks; without this the first timed steps are erratic (seen as 0.9 vs
+    # 1.4 ms/step between otherwise identical runs).  Same for both arms.
+    t_spin = time.monotonic()
+    i = 0
+    while time.monotonic() - t_spin < 0.5:
+        step_resident(i)
+        i += 1
+        if i % 8 == 0:
+            torch.cuda.synchronize()
     for i in range(a.warmup):
         step_resident(i)
     l0 = arm.launches()
@@ -563,6 +573,9 @@ def main():
         for ev in freed:
             ev.record(torch.cuda.current_stream(dev))
         prefetch(0)
+        t_spin = time.monotonic()       # spin-up (graph capture above left the GPU idle), then the W warm-up steps
+        while time.monotonic() - t_spin < 0.3:
+            step_e2e(0)
         for i in range(a.warmup):
             step_e2e(i)
         read_pending_loss()

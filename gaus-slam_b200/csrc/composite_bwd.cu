@@ -44,15 +44,16 @@ struct PixelConst {
 	uint32_t median_contributor;
 };
 
+// Back-to-front state of a pixel.  The reference keeps, for each of its 8 blended channels x (rgb, depth,
+// alpha, normal) the running "what lies behind" value acc_x and adds (x - acc_x) * dL/dx to dL/dalpha
+// (CR/backward.cu:336-345, :384-397), plus the same construction for the regulariser weight (last_dL_dT,
+// :370-376).  All nine recurrences are linear with the same coefficients, acc <- alpha * x + (1 - alpha) * acc,
+// so their weighted sum R = sum_x acc_x * dL/dx + last_dL_dT obeys the same recurrence with
+// Y = sum_x x * dL/dx + dL_dweight in the place of x: one scalar instead of 17 (same value up to fp32 summation
+// order; the gradient bar is 1e-3 relative).
 struct PixelBwd {
 	float T;
-	float acc_c0 = 0.f, acc_c1 = 0.f, acc_c2 = 0.f;
-	float last_c0 = 0.f, last_c1 = 0.f, last_c2 = 0.f;
-	float last_alpha = 0.f;
-	float last_depth = 0.f, acc_depth = 0.f, acc_alpha = 0.f;
-	float acc_n0 = 0.f, acc_n1 = 0.f, acc_n2 = 0.f;
-	float last_n0 = 0.f, last_n1 = 0.f, last_n2 = 0.f;
-	float last_dL_dT = 0.f;
+	float behind = 0.f;   // R
 };
 
 struct BwdSmem {
@@ -83,17 +84,6 @@ __device__ __forceinline__ void pixel_step(const float4* __restrict__ rec, float
 	const float T = st.T;
 	const float w = alpha * T;
 
-	float dL_dalpha = 0.0f;
-	st.acc_c0 = st.last_alpha * st.last_c0 + (1.f - st.last_alpha) * st.acc_c0;
-	st.last_c0 = r4.x;
-	dL_dalpha += (r4.x - st.acc_c0) * pc.dpix0;
-	st.acc_c1 = st.last_alpha * st.last_c1 + (1.f - st.last_alpha) * st.acc_c1;
-	st.last_c1 = r4.y;
-	dL_dalpha += (r4.y - st.acc_c1) * pc.dpix1;
-	st.acc_c2 = st.last_alpha * st.last_c2 + (1.f - st.last_alpha) * st.acc_c2;
-	st.last_c2 = r4.z;
-	dL_dalpha += (r4.z - st.acc_c2) * pc.dpix2;
-
 	float conf = 1;
 	if (USE_SA) {
 		// confidence from the FINAL per-pixel statistics, treated as a constant (CR/backward.cu:349)
@@ -104,40 +94,24 @@ __device__ __forceinline__ void pixel_step(const float4* __restrict__ rec, float
 	float dL_dz = 0.0f;
 	float dL_dweight = 0;
 	if (q + 1 == pc.median_contributor) dL_dz += pc.dL_dmedian;
-	float m_d = 0.f, dmd_dd = 0.f;
 	if (USE_SA) {
-		dL_dweight += ((c_d - pc.mm) * (c_d - pc.mm)) * pc.dL_dreg;
-	} else {
-		m_d = GS2D_FAR / (GS2D_FAR - GS2D_NEAR) * (1 - GS2D_NEAR / c_d);
-		dmd_dd = (GS2D_FAR * GS2D_NEAR) / ((GS2D_FAR - GS2D_NEAR) * c_d * c_d);
-		dL_dweight += (pc.final_D2 + m_d * m_d * pc.final_A - 2 * m_d * pc.final_D) * pc.dL_dreg;
-	}
-	dL_dalpha += dL_dweight - st.last_dL_dT;
-	st.last_dL_dT = dL_dweight * alpha + (1 - alpha) * st.last_dL_dT;
-	if (USE_SA) {
+		dL_dweight = ((c_d - pc.mm) * (c_d - pc.mm)) * pc.dL_dreg;
 		dL_dz += conf * 2.0f * w * (c_d - pc.mm) * pc.dL_dreg;
 	} else {
+		const float m_d = GS2D_FAR / (GS2D_FAR - GS2D_NEAR) * (1 - GS2D_NEAR / c_d);
+		const float dmd_dd = (GS2D_FAR * GS2D_NEAR) / ((GS2D_FAR - GS2D_NEAR) * c_d * c_d);
+		dL_dweight = (pc.final_D2 + m_d * m_d * pc.final_A - 2 * m_d * pc.final_D) * pc.dL_dreg;
 		const float dL_dmd = 2.0f * (T * alpha) * (m_d * pc.final_A - pc.final_D) * pc.dL_dreg;
 		dL_dz += dL_dmd * dmd_dd;
 	}
-	st.acc_depth = st.last_alpha * st.last_depth + (1.f - st.last_alpha) * st.acc_depth;
-	st.last_depth = c_d;
-	dL_dalpha += (c_d - st.acc_depth) * pc.dL_ddepth;
-	st.acc_alpha = st.last_alpha * 1.0f + (1.f - st.last_alpha) * st.acc_alpha;
-	dL_dalpha += (1 - st.acc_alpha) * pc.dL_daccum;
-
-	st.acc_n0 = st.last_alpha * st.last_n0 + (1.f - st.last_alpha) * st.acc_n0;
-	st.last_n0 = r3.x;
-	dL_dalpha += (r3.x - st.acc_n0) * pc.dn0;
-	st.acc_n1 = st.last_alpha * st.last_n1 + (1.f - st.last_alpha) * st.acc_n1;
-	st.last_n1 = r3.y;
-	dL_dalpha += (r3.y - st.acc_n1) * pc.dn1;
-	st.acc_n2 = st.last_alpha * st.last_n2 + (1.f - st.last_alpha) * st.acc_n2;
-	st.last_n2 = r3.z;
-	dL_dalpha += (r3.z - st.acc_n2) * pc.dn2;
-
-	dL_dalpha *= T;
-	st.last_alpha = alpha;
+	// Y: this instance's blended values weighted by the pixel's gradients (+ the regulariser weight)
+	float Y = dL_dweight + pc.dL_daccum;
+	Y += r4.x * pc.dpix0; Y += r4.y * pc.dpix1; Y += r4.z * pc.dpix2;
+	Y += r3.x * pc.dn0;   Y += r3.y * pc.dn1;   Y += r3.z * pc.dn2;
+	Y += c_d * pc.dL_ddepth;
+	const float ahead = Y - st.behind;
+	st.behind += alpha * ahead;
+	float dL_dalpha = ahead * T;
 	dL_dalpha += (-pc.T_final * inv_1ma) * pc.bg_dot;
 	dL_dz += conf * alpha * T * pc.dL_ddepth;
 
