@@ -47,6 +47,7 @@ def parse_args():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-kernel-timing", action="store_true")
     ap.add_argument("--cpu-frames", type=int, default=2)
+    ap.add_argument("--torch-loss", action="store_true", help="e2e of the product with the torch-ops loss instead of the fused kernels")
     ap.add_argument("--no-stats", action="store_true",
                     help="skip the (untimed) scene-statistics renders: for ncu launch lists of the timed steps only")
     ap.add_argument("--clock-period-ms", type=int, default=100, help="nvidia-smi sampling period; 0 = no sampling (diagnosis)")
@@ -163,18 +164,20 @@ def build_workload(a, dev):
 
 
 def mapping_loss(color, allmap, gt_color, gt_depth):
-    """Mapping loss of slam/Loss.py:51-58 on one view (masked means of L1 colour, L1 depth, + 0.1 * distortion /
-    depth-variance channel), with the weight-normalised depth of render/__init__.py:46-49.  Mask multiplications
-    instead of boolean indexing so the step has no extra host synchronisation."""
+    """The reference's mapping loss on one view with torch ops: weight-normalised depth with outlier zeroing
+    (render/__init__.py:46-49), nan_to_num, depth mask, masked means of L1 colour / L1 depth / distortion with
+    the shipped weights 0.5 / 1.0 / 0.1 (slam/Loss.py:22-25, :36, :51-63; configs/replica/config.py:101-106).
+    Mask multiplications instead of boolean indexing (same value, no host synchronisation, graph-capturable)."""
     import torch
-    alpha = torch.nan_to_num(allmap[1:2])
-    depth = torch.nan_to_num(allmap[0:1]) / (alpha + 1e-6)
+    depth = allmap[0:1] / (allmap[1:2] + 1e-6)
+    depth = torch.where((depth > 1e2) | (depth < 1e-2), torch.zeros_like(depth), depth)
+    depth = torch.nan_to_num(depth, 0, 0)
     mask = ((gt_depth > 1e-5) & (depth > 1e-5)).to(color.dtype)
-    cnt = mask.sum().clamp(min=1.0)
-    l_color = ((torch.nan_to_num(color) - gt_color).abs() * mask).sum() / (3.0 * cnt)
+    cnt = mask.sum()
+    l_color = ((torch.nan_to_num(color, 0, 0) - gt_color).abs() * mask).sum() / (3.0 * cnt)
     l_depth = ((depth - gt_depth).abs() * mask).sum() / cnt
-    l_dist = (torch.nan_to_num(allmap[6:7]) * mask).sum() / cnt
-    return l_color + l_depth + 0.1 * l_dist
+    l_dist = (torch.nan_to_num(allmap[6:7], 0, 0) * mask).sum() / cnt
+    return 0.5 * l_color + l_depth + 0.1 * l_dist
 
 
 def algorithmic_bytes(P, Pv, I, W, H):
@@ -528,13 +531,19 @@ def main():
         # The loss is ~20 small torch ops (+ their autograd): capture it once as CUDA graphs (forward and backward)
         # so that its launch overhead does not hide the rasterizer; same harness for both arms.
         loss_fn, loss_how = mapping_loss, "eager torch ops"
-        try:
+        if a.impl == "b200" and not a.torch_loss:
+            # product path: the fused loss + image-gradient kernels of libgs2d.so
+            from gs2d_b200 import loss as gs2d_loss
+            loss_fn = gs2d_loss.mapping_loss
+            loss_how = "gs2d_b200.loss.mapping_loss (fused forward / backward kernels of libgs2d.so)"
+        else:
+          try:
             s0 = wl["sets"][0]
             sample = (torch.rand((3, H, W), device=dev, requires_grad=True),
                       torch.rand((7, H, W), device=dev, requires_grad=True), s0["gt_color"].clone(), s0["gt_depth"].clone())
             loss_fn = torch.cuda.make_graphed_callables(mapping_loss, sample)
-            loss_how = "torch ops captured as CUDA graphs (make_graphed_callables)"
-        except Exception as e:      # pragma: no cover
+            loss_how = "the reference's loss as torch ops, captured as CUDA graphs (make_graphed_callables)"
+          except Exception as e:      # pragma: no cover
             loss_fn, loss_how = mapping_loss, f"eager torch ops (graph capture failed: {type(e).__name__})"
 
         def prefetch(step):
@@ -585,7 +594,7 @@ def main():
         e2e = {"value": (world if multi else 1) * 1000.0 / ms_e2e, "unit": UNIT, "h2d_bytes_per_step": h2d,
                "d2h_bytes_per_step": 4 + 4, "ms_per_step": ms_e2e,
                "what": "one mapping iteration through the public python API: GaussianRasterizer(...)(...) -> mapping "
-                       "loss (slam/Loss.py:51-58, torch) -> loss.backward(); the keyframe's camera and RGB-D image "
+                       "loss (slam/Loss.py:51-63 incl. render/__init__.py:46-49) -> loss.backward(); the keyframe's camera and RGB-D image "
                        "(3+1 channels fp32) are copied from pinned host memory every step (double-buffered on a copy "
                        "stream), num_rendered is read back inside every forward and the loss of every step is copied to pinned "
                        "memory and read on the host one step later (the last one before the timer stops); surfel parameters are optimiser "

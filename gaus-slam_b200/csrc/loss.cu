@@ -1,0 +1,238 @@
+// loss.cu -- fused mapping loss + image gradients (the step right after the rasterizer).
+//
+// Replaces, for the mapping branch of get_loss (slam/Loss.py:22-25, :36, :51-63) together with the weight
+// normalisation of the rendered depth that precedes it (render/__init__.py:46-49), about 25 elementwise /
+// reduction launches of torch (+ as many in autograd) by two kernels:
+//
+//   depth  = allmap[0] / (allmap[1] + eps);  depth = 0 where depth > far or depth < near       (render/__init__.py)
+//   x      = nan_to_num(x, 0, 0) for colour, depth, dist (NaN -> 0, +inf -> 0, -inf -> -FLT_MAX)   (Loss.py:22-25)
+//   mask   = gt_depth > 1e-5  and  depth > 1e-5                                                  (Loss.py:36)
+//   loss   = w_color * mean_{mask, 3 channels} |colour - gt_colour|
+//          + w_depth * mean_{mask} |depth - gt_depth|  +  w_dist * mean_{mask} allmap[6]         (Loss.py:52-63)
+//
+// (use_edge_growth = False, use_normal_loss = False, enable_exposure = False: the defaults of every shipped
+// config; the other branches are not built.)  Forward: one pass, per-block partial sums, the last block adds
+// them in a fixed order (deterministic) and leaves {loss, count, the three sums} in device memory.  Backward: one
+// pass that recomputes the mask and writes dL/dcolour [3,H,W] and dL/dallmap [7,H,W] (channels 2..5 get zeros),
+// scaled by the upstream gradient read from device memory -- nothing goes through the host.
+// Both kernels are pure HBM streams: 40 B read per pixel forward, 40 B read + 40 B written backward.
+#include "common.cuh"
+
+#include <cfloat>
+
+namespace gs2d {
+
+namespace {
+
+struct LossPixel {
+	float c[3], depth, dist, gc[3], gd;
+	bool mask, c_ok[3], dist_ok;
+	float inv_a;     // 1 / (alpha + eps)
+};
+
+__device__ __forceinline__ float nan_to_num00(float v, bool& passes)
+{
+	// torch.nan_to_num(v, 0, 0): nan = 0, posinf = 0, neginf = default (lowest finite); gradient passes only
+	// where the value was finite
+	passes = isfinite(v);
+	if (passes) return v;
+	return (v < 0.f) ? -FLT_MAX : 0.f;
+}
+
+__device__ __forceinline__ LossPixel load_pixel(size_t p, size_t HW, const float* __restrict__ color,
+                                                const float* __restrict__ allmap, const float* __restrict__ gt_color,
+                                                const float* __restrict__ gt_depth, int gt_hwc, float eps, float near_,
+                                                float far_)
+{
+	LossPixel px;
+#pragma unroll
+	for (int k = 0; k < 3; k++) {
+		px.c[k] = nan_to_num00(color[k * HW + p], px.c_ok[k]);
+		px.gc[k] = gt_hwc ? gt_color[3 * p + k] : gt_color[k * HW + p];
+	}
+	px.gd = gt_depth[p];
+	const float D = allmap[p], A = allmap[HW + p];
+	px.inv_a = 1.0f / (A + eps);
+	float d = D * px.inv_a;
+	const bool outlier = (d > far_) || (d < near_);
+	if (outlier) d = 0.f;
+	bool d_ok;
+	d = nan_to_num00(d, d_ok);
+	px.depth = d;
+	px.dist = nan_to_num00(allmap[6 * HW + p], px.dist_ok);
+	px.mask = (px.gd > 1e-5f) && (d > 1e-5f);   // implies: finite, not an outlier
+	return px;
+}
+
+constexpr int LOSS_THREADS = 256;
+
+__global__ void __launch_bounds__(LOSS_THREADS)
+mapping_loss_forward_kernel(size_t HW, const float* __restrict__ color, const float* __restrict__ allmap,
+                            const float* __restrict__ gt_color, const float* __restrict__ gt_depth, int gt_hwc,
+                            float w_color, float w_depth, float w_dist, float eps, float near_, float far_,
+                            float* __restrict__ partials, uint32_t* __restrict__ ticket, float* __restrict__ state)
+{
+	float cnt = 0.f, sc = 0.f, sd = 0.f, sr = 0.f;
+	for (size_t p = (size_t)blockIdx.x * LOSS_THREADS + threadIdx.x; p < HW; p += (size_t)gridDim.x * LOSS_THREADS) {
+		const LossPixel px = load_pixel(p, HW, color, allmap, gt_color, gt_depth, gt_hwc, eps, near_, far_);
+		if (px.mask) {
+			cnt += 1.f;
+			sc += fabsf(px.c[0] - px.gc[0]) + fabsf(px.c[1] - px.gc[1]) + fabsf(px.c[2] - px.gc[2]);
+			sd += fabsf(px.depth - px.gd);
+			sr += px.dist;
+		}
+	}
+	__shared__ float s_part[LOSS_THREADS / 32][4];
+	__shared__ bool s_last;
+	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+	for (int o = 16; o >= 1; o >>= 1) {
+		cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
+		sc += __shfl_xor_sync(0xffffffffu, sc, o);
+		sd += __shfl_xor_sync(0xffffffffu, sd, o);
+		sr += __shfl_xor_sync(0xffffffffu, sr, o);
+	}
+	if (lane == 0) { s_part[warp][0] = cnt; s_part[warp][1] = sc; s_part[warp][2] = sd; s_part[warp][3] = sr; }
+	__syncthreads();
+	if (threadIdx.x < 4) {
+		float t = 0.f;
+#pragma unroll
+		for (int w = 0; w < LOSS_THREADS / 32; w++) t += s_part[w][threadIdx.x];
+		partials[4 * blockIdx.x + threadIdx.x] = t;
+	}
+	__threadfence();
+	__syncthreads();
+	if (threadIdx.x == 0) s_last = atomicAdd(ticket, 1u) == gridDim.x - 1;
+	__syncthreads();
+	if (!s_last) return;
+	// last block: add the per-block partials in block order (deterministic), in double
+	__shared__ double s_sum[4];
+	if (threadIdx.x < 4) {
+		double t = 0.0;
+		for (unsigned b = 0; b < gridDim.x; b++) t += (double)__ldcg(&partials[4 * b + threadIdx.x]);
+		s_sum[threadIdx.x] = t;
+	}
+	__syncthreads();
+	if (threadIdx.x == 0) {
+		const double n = s_sum[0];
+		// mean over an empty selection is NaN in torch; kept
+		const double loss = (double)w_color * (s_sum[1] / (3.0 * n)) + (double)w_depth * (s_sum[2] / n) +
+		                    (double)w_dist * (s_sum[3] / n);
+		state[0] = (float)loss;
+		state[1] = (float)n;
+		state[2] = (float)s_sum[1];
+		state[3] = (float)s_sum[2];
+		state[4] = (float)s_sum[3];
+		*ticket = 0u;   // ready for the next call
+	}
+}
+
+__global__ void __launch_bounds__(LOSS_THREADS)
+mapping_loss_backward_kernel(size_t HW, const float* __restrict__ color, const float* __restrict__ allmap,
+                             const float* __restrict__ gt_color, const float* __restrict__ gt_depth, int gt_hwc,
+                             float w_color, float w_depth, float w_dist, float eps, float near_, float far_,
+                             const float* __restrict__ state, const float* __restrict__ grad_out,
+                             float* __restrict__ dL_dcolor, float* __restrict__ dL_dallmap)
+{
+	const float n = state[1];
+	const float g = grad_out ? grad_out[0] : 1.0f;
+	const float gc = n > 0.f ? g * w_color / (3.0f * n) : 0.f;
+	const float gd = n > 0.f ? g * w_depth / n : 0.f;
+	const float gr = n > 0.f ? g * w_dist / n : 0.f;
+	for (size_t p = (size_t)blockIdx.x * LOSS_THREADS + threadIdx.x; p < HW; p += (size_t)gridDim.x * LOSS_THREADS) {
+		const LossPixel px = load_pixel(p, HW, color, allmap, gt_color, gt_depth, gt_hwc, eps, near_, far_);
+		float dc[3] = {0.f, 0.f, 0.f}, dD = 0.f, dA = 0.f, dR = 0.f;
+		if (px.mask) {
+#pragma unroll
+			for (int k = 0; k < 3; k++) {
+				const float e = px.c[k] - px.gc[k];
+				dc[k] = px.c_ok[k] ? (e > 0.f ? gc : (e < 0.f ? -gc : 0.f)) : 0.f;   // sign(0) = 0 like torch.abs
+			}
+			const float e = px.depth - px.gd;
+			const float dd = e > 0.f ? gd : (e < 0.f ? -gd : 0.f);
+			dD = dd * px.inv_a;                       // depth = D / (A + eps)
+			dA = -dd * px.depth * px.inv_a;
+			dR = px.dist_ok ? gr : 0.f;
+		}
+		dL_dcolor[p] = dc[0]; dL_dcolor[HW + p] = dc[1]; dL_dcolor[2 * HW + p] = dc[2];
+		dL_dallmap[p] = dD; dL_dallmap[HW + p] = dA;
+		dL_dallmap[2 * HW + p] = 0.f; dL_dallmap[3 * HW + p] = 0.f; dL_dallmap[4 * HW + p] = 0.f;
+		dL_dallmap[5 * HW + p] = 0.f; dL_dallmap[6 * HW + p] = dR;
+	}
+}
+
+inline int loss_blocks(size_t HW)
+{
+	const size_t want = (HW + LOSS_THREADS - 1) / LOSS_THREADS;
+	const size_t cap = 148 * 8;   // one wave of 8 CTAs per SM
+	return (int)(want < cap ? (want ? want : 1) : cap);
+}
+
+}  // namespace
+
+}  // namespace gs2d
+
+using namespace gs2d;
+
+extern "C" {
+
+size_t gs2d_mapping_loss_scratch_bytes(int32_t, int32_t)
+{
+	// per-block partials (4 floats x 148*8 blocks), the ticket, the 8-float state
+	return sizeof(float) * 4 * 148 * 8 + 128 + sizeof(float) * 8;
+}
+
+static inline void loss_carve(void* scratch, float** partials, uint32_t** ticket, float** state)
+{
+	char* b = (char*)scratch;
+	*partials = (float*)b;
+	*ticket = (uint32_t*)(b + sizeof(float) * 4 * 148 * 8);
+	*state = (float*)(b + sizeof(float) * 4 * 148 * 8 + 128);
+}
+
+int gs2d_mapping_loss_forward(int32_t W, int32_t H, const float* color, const float* allmap, const float* gt_color,
+                              const float* gt_depth, int32_t gt_color_hwc, const gs2d_loss_params* lp, void* scratch,
+                              float* loss_out, void* stream)
+{
+	if (W <= 0 || H <= 0 || !color || !allmap || !gt_color || !gt_depth || !lp || !scratch) return GS2D_ERR_INVALID;
+	cudaStream_t st = (cudaStream_t)stream;
+	float *partials, *state;
+	uint32_t* ticket;
+	loss_carve(scratch, &partials, &ticket, &state);
+	const size_t HW = (size_t)W * H;
+	{
+		ProfScope ps(K_LOSS, st);
+		mapping_loss_forward_kernel<<<loss_blocks(HW), LOSS_THREADS, 0, st>>>(
+			HW, color, allmap, gt_color, gt_depth, gt_color_hwc, lp->w_color, lp->w_depth, lp->w_dist, lp->eps,
+			lp->depth_near, lp->depth_far, partials, ticket, state);
+		count_launch();
+	}
+	GS2D_CUDA_OK(cudaGetLastError());
+	if (loss_out) GS2D_CUDA_OK(cudaMemcpyAsync(loss_out, state, sizeof(float), cudaMemcpyDeviceToDevice, st));
+	return GS2D_OK;
+}
+
+int gs2d_mapping_loss_backward(int32_t W, int32_t H, const float* color, const float* allmap, const float* gt_color,
+                               const float* gt_depth, int32_t gt_color_hwc, const gs2d_loss_params* lp,
+                               const void* scratch, const float* grad_loss, float* dL_dcolor, float* dL_dallmap,
+                               void* stream)
+{
+	if (W <= 0 || H <= 0 || !color || !allmap || !gt_color || !gt_depth || !lp || !scratch || !dL_dcolor || !dL_dallmap)
+		return GS2D_ERR_INVALID;
+	cudaStream_t st = (cudaStream_t)stream;
+	float *partials, *state;
+	uint32_t* ticket;
+	loss_carve(const_cast<void*>(scratch), &partials, &ticket, &state);
+	const size_t HW = (size_t)W * H;
+	{
+		ProfScope ps(K_LOSS, st);
+		mapping_loss_backward_kernel<<<loss_blocks(HW), LOSS_THREADS, 0, st>>>(
+			HW, color, allmap, gt_color, gt_depth, gt_color_hwc, lp->w_color, lp->w_depth, lp->w_dist, lp->eps,
+			lp->depth_near, lp->depth_far, state, grad_loss, dL_dcolor, dL_dallmap);
+		count_launch();
+	}
+	GS2D_CUDA_OK(cudaGetLastError());
+	return GS2D_OK;
+}
+
+}  // extern "C"

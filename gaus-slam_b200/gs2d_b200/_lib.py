@@ -56,6 +56,11 @@ class StateView(C.Structure):
 
 
 # name -> (restype, argtypes); also the list of symbols the header declares (checked by tests).
+class LossParams(C.Structure):
+    _fields_ = [("w_color", C.c_float), ("w_depth", C.c_float), ("w_dist", C.c_float), ("eps", C.c_float),
+                ("depth_near", C.c_float), ("depth_far", C.c_float)]
+
+
 PROTOTYPES = {
     "gs2d_geom_bytes": (C.c_size_t, [C.c_int32, C.c_int32]),
     "gs2d_image_bytes": (C.c_size_t, [C.c_int32, C.c_int32]),
@@ -80,6 +85,12 @@ PROTOTYPES = {
     "gs2d_sort_scratch_bytes": (C.c_size_t, [C.c_int64]),
     "gs2d_sort_pairs": (C.c_int, [C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32,
                                   C.c_void_p, C.c_void_p]),
+    "gs2d_mapping_loss_scratch_bytes": (C.c_size_t, [C.c_int32, C.c_int32]),
+    "gs2d_mapping_loss_forward": (C.c_int, [C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                            C.c_int32, C.POINTER(LossParams), C.c_void_p, C.c_void_p, C.c_void_p]),
+    "gs2d_mapping_loss_backward": (C.c_int, [C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                             C.c_int32, C.POINTER(LossParams), C.c_void_p, C.c_void_p, C.c_void_p,
+                                             C.c_void_p, C.c_void_p]),
     "gs2d_timing_enable": (C.c_int, [C.c_int]),
     "gs2d_num_kernels": (C.c_int, []),
     "gs2d_kernel_name": (C.c_char_p, [C.c_int]),

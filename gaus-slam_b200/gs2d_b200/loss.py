@@ -1,0 +1,88 @@
+"""Fused mapping loss: the mapping branch of the reference's `get_loss`
+(slam/Loss.py:6-64) together with the weight normalisation of the rendered depth that `Renderer_*` applies
+before it (render/__init__.py:46-49), as ONE forward and ONE backward kernel of libgs2d.so instead of ~25 torch
+launches each way.
+
+    loss = mapping_loss(color, allmap, gt_color, gt_depth)          # color [3,H,W], allmap [7,H,W] from the rasterizer
+    loss.backward()
+
+Argument meaning follows the reference's config keys: `weights` = config['loss']['mapping'] (color, depth, dist),
+`eps`, `depth_near`, `depth_far` = config['render'][...].  `gt_color` may be [3,H,W] or the reference's [H,W,3].
+Built for the shipped defaults (use_edge_growth = use_normal_loss = enable_exposure = False); anything else
+raises.  CUDA only: there is no CPU path.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import torch
+
+from . import _lib as L
+
+_scratch = {}
+
+
+def _scratch_for(dev, W, H):
+    key = (str(dev), int(torch.cuda.current_stream(dev).cuda_stream))
+    if key not in _scratch:      # zero-initialised once; the kernels keep it consistent afterwards
+        _scratch[key] = torch.zeros(L.load().gs2d_mapping_loss_scratch_bytes(W, H), dtype=torch.uint8, device=dev)
+    return _scratch[key]
+
+
+def _check(t, name, shape):
+    if not t.is_cuda or t.dtype != torch.float32:
+        raise RuntimeError(f"{name} must be a float32 CUDA tensor")
+    if tuple(t.shape) not in shape:
+        raise RuntimeError(f"{name} has shape {tuple(t.shape)}, expected one of {shape}")
+    return t.contiguous()
+
+
+class _MappingLoss(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, color, allmap, gt_color, gt_depth, params):
+        lib = L.load()
+        H, W = int(color.shape[1]), int(color.shape[2])
+        dev = color.device
+        color = _check(color, "color", [(3, H, W)])
+        allmap = _check(allmap, "allmap", [(7, H, W)])
+        gt_color = _check(gt_color, "gt_color", [(3, H, W), (H, W, 3)])
+        gt_depth = _check(gt_depth, "gt_depth", [(H, W), (1, H, W), (H, W, 1)])
+        hwc = int(tuple(gt_color.shape) == (H, W, 3) and (H, W, 3) != (3, H, W))
+        lp = L.LossParams(*params)
+        with torch.cuda.device(dev):
+            scratch = _scratch_for(dev, W, H)
+            loss = torch.empty((), dtype=torch.float32, device=dev)
+            st = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+            L.check(lib.gs2d_mapping_loss_forward(W, H, color.data_ptr(), allmap.data_ptr(), gt_color.data_ptr(),
+                                                  gt_depth.data_ptr(), hwc, C.byref(lp), scratch.data_ptr(),
+                                                  loss.data_ptr(), st), "gs2d_mapping_loss_forward")
+        ctx.save_for_backward(color, allmap, gt_color, gt_depth)
+        ctx.lp, ctx.hwc, ctx.scratch = lp, hwc, scratch
+        return loss
+
+    @staticmethod
+    def backward(ctx, grad_loss):
+        lib = L.load()
+        color, allmap, gt_color, gt_depth = ctx.saved_tensors
+        H, W = int(color.shape[1]), int(color.shape[2])
+        dev = color.device
+        g = grad_loss.to(torch.float32).contiguous()
+        d_color = torch.empty_like(color)
+        d_allmap = torch.empty_like(allmap)
+        with torch.cuda.device(dev):
+            st = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+            L.check(lib.gs2d_mapping_loss_backward(W, H, color.data_ptr(), allmap.data_ptr(), gt_color.data_ptr(),
+                                                   gt_depth.data_ptr(), ctx.hwc, C.byref(ctx.lp),
+                                                   ctx.scratch.data_ptr(), g.data_ptr(), d_color.data_ptr(),
+                                                   d_allmap.data_ptr(), st), "gs2d_mapping_loss_backward")
+        return d_color, d_allmap, None, None, None
+
+
+def mapping_loss(color, allmap, gt_color, gt_depth, weights=(0.5, 1.0, 0.1), eps=1e-6, depth_near=1e-2,
+                 depth_far=1e2, use_edge_growth=False, use_normal_loss=False):
+    """-> scalar loss tensor (differentiable w.r.t. color and allmap).  One forward pass of the rasterizer per
+    call of backward: the mask count of the forward pass is kept in a per-stream scratch."""
+    if use_edge_growth or use_normal_loss:
+        raise NotImplementedError("only the default mapping loss (no edge growth, no normal loss) is built")
+    params = (float(weights[0]), float(weights[1]), float(weights[2]), float(eps), float(depth_near), float(depth_far))
+    return _MappingLoss.apply(color, allmap, gt_color, gt_depth, params)

@@ -211,6 +211,34 @@ int gs2d_sort_pairs(int64_t n, const uint64_t* keys_in, const uint32_t* values_i
                     uint64_t* keys_out, uint32_t* values_out, int32_t end_bit,
                     void* scratch, void* stream);
 
+/* ---- "next" row f2: fused mapping loss + image gradients --------------------------------
+ * The mapping branch of get_loss (slam/Loss.py:22-25, :36, :51-63) on the rasterizer's outputs, including the
+ * weight normalisation of the depth that Renderer_* applies first (render/__init__.py:46-49):
+ *   depth = allmap[0] / (allmap[1] + eps), zeroed outside [depth_near, depth_far]; NaN/inf -> nan_to_num(x,0,0);
+ *   mask = gt_depth > 1e-5 and depth > 1e-5;
+ *   loss = w_color * mean_mask,3ch |color - gt_color| + w_depth * mean_mask |depth - gt_depth|
+ *        + w_dist * mean_mask allmap[6].
+ * Defaults of every shipped config: use_edge_growth = use_normal_loss = enable_exposure = False (other
+ * branches: not built).  color [3,H,W], allmap [7,H,W], gt_depth [H,W] (or [1,H,W]); gt_color [3,H,W], or
+ * [H,W,3] (the reference's layout) when gt_color_hwc != 0.  `scratch`: gs2d_mapping_loss_scratch_bytes bytes,
+ * ZERO-INITIALISED once by the caller and then reused call after call (forward leaves the mask count there for
+ * backward).  Forward writes the scalar loss to loss_out (device float).  Backward writes dL/dcolor [3,H,W] and
+ * dL/dallmap [7,H,W] entirely (channels 2..5 are zeros), scaled by *grad_loss (device float; NULL = 1). */
+typedef struct gs2d_loss_params {
+	float w_color, w_depth, w_dist;   /* configs: 0.5, 1.0, 0.1                                  */
+	float eps;                        /* render.eps = 1e-6                                        */
+	float depth_near, depth_far;      /* render.depth_near = 1e-2, render.depth_far = 1e2         */
+} gs2d_loss_params;
+
+size_t gs2d_mapping_loss_scratch_bytes(int32_t image_width, int32_t image_height);
+int gs2d_mapping_loss_forward(int32_t image_width, int32_t image_height, const float* color, const float* allmap,
+                              const float* gt_color, const float* gt_depth, int32_t gt_color_hwc,
+                              const gs2d_loss_params* params, void* scratch, float* loss_out, void* stream);
+int gs2d_mapping_loss_backward(int32_t image_width, int32_t image_height, const float* color, const float* allmap,
+                               const float* gt_color, const float* gt_depth, int32_t gt_color_hwc,
+                               const gs2d_loss_params* params, const void* scratch, const float* grad_loss,
+                               float* dL_dcolor, float* dL_dallmap, void* stream);
+
 /* Optional per-kernel timing for bench.py's roofline line: while enabled, every kernel launch
  * (and memset) of this library is bracketed by CUDA events on the launching stream.
  * gs2d_timing_collect() waits for the recorded events, writes the summed device time (ms) and

@@ -1,0 +1,112 @@
+"""Fused mapping loss.  CPU: the two restatements of the reference's loss (torch
+transliteration with autograd, numpy with hand-written gradients) agree.  GPU: the CUDA kernels agree with both,
+through the C ABI (gs2d_b200.loss) -- fp32 tolerance 1e-5 relative on the loss, 1e-6 abs-to-max on gradients."""
+import os
+import sys
+
+import numpy as np
+import pytest
+import torch
+
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "oracle"))
+import loss_ref  # noqa: E402
+
+
+def _inputs(H, W, seed, nasty=True):
+    rng = np.random.default_rng(seed)
+    color = rng.uniform(0, 1, (3, H, W)).astype(np.float32)
+    allmap = rng.normal(0, 1, (7, H, W)).astype(np.float32)
+    alpha = rng.uniform(0.0, 1.0, (H, W)).astype(np.float32)
+    depth = rng.uniform(0.5, 5.0, (H, W)).astype(np.float32)
+    allmap[1] = alpha
+    allmap[0] = depth * alpha
+    allmap[6] = rng.uniform(0, 0.05, (H, W)).astype(np.float32)
+    gt_color = rng.uniform(0, 1, (3, H, W)).astype(np.float32)
+    gt_depth = rng.uniform(0.5, 5.0, (H, W)).astype(np.float32)
+    if nasty:
+        gt_depth[rng.uniform(size=(H, W)) < 0.1] = 0.0           # holes in the sensor depth
+        allmap[1][rng.uniform(size=(H, W)) < 0.05] = 0.0         # nothing rendered: depth = D / eps -> outlier
+        allmap[0][rng.uniform(size=(H, W)) < 0.02] = np.nan
+        allmap[0][rng.uniform(size=(H, W)) < 0.02] = np.inf
+        color[:, rng.uniform(size=(H, W)) < 0.02] = np.nan
+        color[0][rng.uniform(size=(H, W)) < 0.01] = np.inf
+        allmap[6][rng.uniform(size=(H, W)) < 0.02] = np.inf
+        allmap[0][0, :4] = 1e6                                    # beyond depth_far
+        color[1][1, :4] = gt_color[1][1, :4]                      # exact zeros of |c - gt|: sign(0) = 0
+    return color, allmap, gt_color, gt_depth
+
+
+def _close(got, want_torch, rel):
+    """Compare with torch autograd.  One documented divergence: where the rendered depth sum allmap[0] is not
+    finite, autograd back-propagates 0 * inf = NaN into dL/dallmap[1]; the restatements (and the kernels) write 0."""
+    bad = ~np.isfinite(want_torch)
+    assert np.all(got[bad] == 0)
+    w = np.where(bad, 0.0, want_torch)
+    return np.abs(got - w).max() <= rel * np.abs(w).max()
+
+
+def _torch_ref(color, allmap, gt_color, gt_depth, dev="cpu", **kw):
+    c = torch.tensor(color, device=dev, requires_grad=True)
+    a = torch.tensor(allmap, device=dev, requires_grad=True)
+    gc = torch.tensor(gt_color, device=dev).permute(1, 2, 0).contiguous()
+    gd = torch.tensor(gt_depth, device=dev)[..., None]
+    loss = loss_ref.mapping_loss_torch(c, a, gc, gd, **kw)
+    loss.backward()
+    return float(loss.detach()), c.grad.cpu().numpy(), a.grad.cpu().numpy()
+
+
+@pytest.mark.parametrize("H,W,seed", [(24, 40, 0), (17, 33, 1), (64, 96, 2)])
+def test_numpy_restatement_equals_torch_transliteration(H, W, seed):
+    x = _inputs(H, W, seed)
+    l0, dc0, da0 = _torch_ref(*x)
+    l1, dc1, da1 = loss_ref.mapping_loss_numpy(*x)
+    assert abs(l0 - l1) <= 1e-5 * abs(l1)
+    assert _close(dc1, dc0, 1e-6) and _close(da1, da0, 1e-5)
+    assert np.isnan(da0[1]).sum() > 0 and np.all(da1[2:6] == 0)
+
+
+def test_weights_and_upstream_gradient_scale():
+    x = _inputs(20, 28, 5, nasty=False)
+    kw = dict(weights=(0.3, 2.0, 0.7), eps=1e-5, depth_near=0.6, depth_far=4.0)
+    l0, dc0, da0 = _torch_ref(*x, **kw)
+    l1, dc1, da1 = loss_ref.mapping_loss_numpy(*x, **kw)
+    assert abs(l0 - l1) <= 1e-5 * abs(l1)
+    assert np.abs(da0 - da1).max() <= 1e-5 * np.abs(da1).max()
+    _, dc2, _ = loss_ref.mapping_loss_numpy(*x, grad_out=3.0, **kw)
+    assert np.allclose(dc2, 3.0 * dc1)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("H,W,seed,hwc", [(24, 40, 0, False), (17, 33, 1, True), (680, 1200, 2, True)])
+def test_fused_kernels_equal_the_reference_loss(H, W, seed, hwc):
+    from gs2d_b200 import loss as gl
+    dev = torch.device("cuda:0")
+    x = _inputs(H, W, seed)
+    color, allmap, gt_color, gt_depth = x
+    l_np, dc_np, da_np = loss_ref.mapping_loss_numpy(*x)
+    l_t, dc_t, da_t = _torch_ref(*x, dev=dev)
+    c = torch.tensor(color, device=dev, requires_grad=True)
+    a = torch.tensor(allmap, device=dev, requires_grad=True)
+    gc = torch.tensor(gt_color, device=dev)
+    gc = gc.permute(1, 2, 0).contiguous() if hwc else gc
+    gd = torch.tensor(gt_depth, device=dev)
+    for rep in range(2):                      # twice: the scratch must be left ready for the next call
+        c.grad = a.grad = None
+        loss = gl.mapping_loss(c, a, gc, gd)
+        (2.0 * loss).backward()
+        assert abs(float(loss) - l_np) <= 1e-5 * abs(l_np)
+        assert abs(float(loss) - l_t) <= 1e-5 * abs(l_t)
+        for got, want in ((c.grad, 2.0 * dc_np), (a.grad, 2.0 * da_np), (c.grad, 2.0 * dc_t), (a.grad, 2.0 * da_t)):
+            assert _close(got.cpu().numpy(), want, 2e-6)
+        assert float(a.grad[2:6].abs().max()) == 0.0
+
+
+@pytest.mark.gpu
+def test_fused_loss_rejects_what_is_not_built():
+    from gs2d_b200 import loss as gl
+    t = torch.zeros((3, 8, 8), device="cuda:0")
+    with pytest.raises(NotImplementedError):
+        gl.mapping_loss(t, torch.zeros((7, 8, 8), device="cuda:0"), t, torch.zeros((8, 8), device="cuda:0"),
+                        use_normal_loss=True)
+    with pytest.raises(RuntimeError):
+        gl.mapping_loss(t.cpu(), torch.zeros((7, 8, 8)), t.cpu(), torch.zeros((8, 8)))
