@@ -205,8 +205,26 @@ int gs2d_forward_preprocess(const gs2d_settings* s, const gs2d_inputs* in, const
 	return GS2D_OK;
 }
 
+int gs2d_forward_scatter_early(const gs2d_settings* s, const gs2d_buffers* buffers, uint64_t* pairs_arena,
+                               int64_t capacity, void* stream)
+{
+	if (!s || !buffers || !pairs_arena || capacity <= 0) return GS2D_ERR_INVALID;
+	if (s->P <= 0) return GS2D_OK;
+	if (!buffers->geom || !buffers->image) return GS2D_ERR_INVALID;
+	GeomState g = GeomState::carve(buffers->geom, (size_t)s->P, nullptr);
+	ImageState im = ImageState::carve(buffers->image, (size_t)s->image_width, (size_t)s->image_height, nullptr);
+	return launch_scatter(*s, g, im, pairs_arena, true, capacity, (cudaStream_t)stream);
+}
+
 int gs2d_forward_render(const gs2d_settings* s, const gs2d_inputs* in, const gs2d_buffers* buffers,
                         int64_t I, float* out_color, float* out_others, int64_t* num_pairs_host, void* stream)
+{
+	return gs2d_forward_render_scattered(s, in, buffers, I, out_color, out_others, num_pairs_host, nullptr, stream);
+}
+
+int gs2d_forward_render_scattered(const gs2d_settings* s, const gs2d_inputs* in, const gs2d_buffers* buffers,
+                                  int64_t I, float* out_color, float* out_others, int64_t* num_pairs_host,
+                                  uint64_t* scattered_pairs, void* stream)
 {
 	GS2D_TRY(check_common(s, in, buffers));
 	cudaStream_t st = (cudaStream_t)stream;
@@ -230,8 +248,11 @@ int gs2d_forward_render(const gs2d_settings* s, const gs2d_inputs* in, const gs2
 		GS2D_TRY(launch_duplicate(*s, g, nullptr, b, I, st));
 		GS2D_TRY(debug_sync(*s, st));
 	}
-	// tile ranges, scatter into tile segments, per-tile sort + instance gather + footprint masks
-	GS2D_TRY(launch_tile_binning(*s, g, im, b, I, st));
+	// scatter into tile segments (unless gs2d_forward_scatter_early already did), per-tile sort + instance gather +
+	// footprint masks
+	uint64_t* pairs = scattered_pairs ? scattered_pairs : b.keys_a;
+	if (!scattered_pairs) GS2D_TRY(launch_scatter(*s, g, im, pairs, false, I, st));
+	GS2D_TRY(launch_tile_sort(*s, g, im, b, pairs, I, st));
 	GS2D_TRY(debug_sync(*s, st));
 	{
 		ProfScope ps(K_MEMSET, st);

@@ -154,8 +154,10 @@ struct ProfScope {
 // Kernel launchers (each returns a gs2d_status) ------------------------------------------
 int launch_preprocess_forward(const gs2d_settings& s, const gs2d_inputs& in, const GeomState& g,
                               uint32_t* tile_count, int32_t* radii, cudaStream_t st);
-int launch_tile_binning(const gs2d_settings& s, const GeomState& g, const ImageState& im, const BinningState& b,
-                        int64_t I, cudaStream_t st);
+int launch_scatter(const gs2d_settings& s, const GeomState& g, const ImageState& im, uint64_t* pairs, bool early,
+                   int64_t capacity, cudaStream_t st);
+int launch_tile_sort(const gs2d_settings& s, const GeomState& g, const ImageState& im, const BinningState& b,
+                     uint64_t* pairs, int64_t I, cudaStream_t st);
 // zeroes [scan_status, counters + 8) itself; one extra block turns the per-tile counts into ranges + cursors
 int launch_scan_tiles(const GeomState& g, int P, cudaStream_t st, int tiles, const uint32_t* tile_count,
                       uint32_t* ranges, uint32_t* tile_cursor);

@@ -31,8 +31,10 @@ constexpr int TS_CAP = 2048;   // instances of a tile sorted in shared memory (1
 __global__ void __launch_bounds__(256)
 scatter_kernel(int P, unsigned gx, const float* __restrict__ depths, const ushort4* __restrict__ rect,
                const uint32_t* __restrict__ tiles_touched, uint32_t* __restrict__ cursor,
-               uint64_t* __restrict__ pairs)
+               uint64_t* __restrict__ pairs, const uint32_t* __restrict__ total, uint32_t capacity)
 {
+	// early launch (before the host knows num_rendered): only when the caller's arena is large enough
+	if (total && *total > capacity) return;
 	const int idx = blockIdx.x * blockDim.x + threadIdx.x;
 	if (idx >= P || tiles_touched[idx] == 0) return;
 	const ushort4 r = rect[idx];
@@ -197,27 +199,36 @@ tile_sort_kernel(int W, int H, unsigned gx, const uint2* __restrict__ ranges, ui
 
 }  // namespace
 
-int launch_tile_binning(const gs2d_settings& s, const GeomState& g, const ImageState& im, const BinningState& b,
-                        int64_t I, cudaStream_t st)
+// Scatter into `pairs` (capacity words).  With `early`, num_rendered is read on the device (the host has not
+// seen it yet) and the launch is a no-op when it exceeds the capacity.
+int launch_scatter(const gs2d_settings& s, const GeomState& g, const ImageState& im, uint64_t* pairs, bool early,
+                   int64_t capacity, cudaStream_t st)
+{
+	const unsigned gx = (s.image_width + TILE - 1) / TILE;
+	if (s.P <= 0) return GS2D_OK;
+	ProfScope ps(K_SCATTER, st);
+	const uint32_t cap = (uint32_t)(capacity < 0 ? 0 : (capacity > 0xffffffffll ? 0xffffffffll : capacity));
+	scatter_kernel<<<(s.P + 255) / 256, 256, 0, st>>>(s.P, gx, g.depths, (const ushort4*)g.rect, g.tiles_touched,
+	                                                  im.tile_cursor, pairs, early ? g.counters + 1 : nullptr, cap);
+	count_launch();
+	GS2D_CUDA_OK(cudaGetLastError());
+	return GS2D_OK;
+}
+
+// `pairs`: the scattered words (b.keys_a, or the caller's arena when the scatter was launched early).
+int launch_tile_sort(const gs2d_settings& s, const GeomState& g, const ImageState& im, const BinningState& b,
+                     uint64_t* pairs, int64_t I, cudaStream_t st)
 {
 	const int W = s.image_width, H = s.image_height;
 	const unsigned gx = (W + TILE - 1) / TILE, gy = (H + TILE - 1) / TILE;
 	const int tiles = (int)(gx * gy);
 	if (tiles == 0 || I <= 0) return GS2D_OK;
 	// (tile ranges and cursors come from the extra block of the tiles_touched scan, preprocess.cu)
-	{
-		ProfScope ps(K_SCATTER, st);
-		scatter_kernel<<<(s.P + 255) / 256, 256, 0, st>>>(s.P, gx, g.depths, (const ushort4*)g.rect, g.tiles_touched,
-		                                                  im.tile_cursor, b.keys_a);
-		count_launch();
-	}
-	{
-		ProfScope ps(K_TILE_SORT, st);
-		tile_sort_kernel<<<tiles, 256, 0, st>>>(W, H, gx, (const uint2*)im.ranges, b.keys_a, (const float4*)g.splat,
-		                                        (const ushort4*)g.rect, (const float4*)g.cull, g.point_offsets, b.keys_b,
-		                                        b.vals_b, (float4*)b.instances, b.hit_inst, b.hit_count);
-		count_launch();
-	}
+	ProfScope ps(K_TILE_SORT, st);
+	tile_sort_kernel<<<tiles, 256, 0, st>>>(W, H, gx, (const uint2*)im.ranges, pairs, (const float4*)g.splat,
+	                                        (const ushort4*)g.rect, (const float4*)g.cull, g.point_offsets, b.keys_b,
+	                                        b.vals_b, (float4*)b.instances, b.hit_inst, b.hit_count);
+	count_launch();
 	GS2D_CUDA_OK(cudaGetLastError());
 	return GS2D_OK;
 }

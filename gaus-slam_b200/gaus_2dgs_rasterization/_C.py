@@ -82,6 +82,24 @@ def _pair_slot(device):
     return ring[0], i
 
 
+# Scatter arenas (one per device and stream): capacity follows the largest num_rendered seen, so that the scatter of
+# the next forward pass can be launched BEFORE the host has read num_rendered back (the device is busy with it
+# while the host wakes up from its wait, allocates the binning buffer and launches the rest).
+_arenas = {}
+_events = {}
+
+
+def _arena(dev, stream_id):
+    return _arenas.get((str(dev), stream_id))
+
+
+def _grow_arena(dev, stream_id, n):
+    cap = max(1 << 16, int(n * 1.25))
+    cap = (cap + (1 << 18) - 1) >> 18 << 18
+    t = torch.empty((cap,), dtype=torch.int64, device=dev)
+    _arenas[(str(dev), stream_id)] = (t, cap)
+
+
 def _settings(P, W, H, degree, M, use_sa, prefiltered, debug, tan_fovx, tan_fovy, scale_modifier):
     return L.Settings(P=P, image_width=W, image_height=H, sh_degree=int(degree), sh_coeffs=int(M),
                       use_sa=int(bool(use_sa)), prefiltered=int(bool(prefiltered)), debug=int(bool(debug)),
@@ -127,10 +145,25 @@ def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations,
         bufs = L.Buffers(geom=_ptr(geom), geom_bytes=geom.numel(), binning=None, binning_bytes=0,
                          image=_ptr(img), image_bytes=img.numel())
         n_host = _pinned_i64(dev)
+        stream = torch.cuda.current_stream(dev)
+        sid = int(stream.cuda_stream)
         L.check(lib.gs2d_forward_preprocess(C.byref(s), C.byref(i), C.byref(bufs), _ptr(radii),
                                             n_host.data_ptr(), st), "gs2d_forward_preprocess")
-        torch.cuda.current_stream(dev).synchronize()
-        num_rendered = int(n_host[0]) if P else 0
+        ev = _events.get((str(dev), sid))
+        if ev is None:
+            ev = _events[(str(dev), sid)] = torch.cuda.Event()
+        ev.record(stream)
+        arena = _arena(dev, sid) if P and not debug else None
+        if arena is not None:
+            L.check(lib.gs2d_forward_scatter_early(C.byref(s), C.byref(bufs), arena[0].data_ptr(), arena[1], st),
+                    "gs2d_forward_scatter_early")
+        ev.synchronize()                                   # the reference's one host wait (num_rendered)
+        num_rendered = C.c_int64.from_address(n_host.data_ptr()).value if P else 0
+        scattered = None
+        if arena is not None and num_rendered <= arena[1]:
+            scattered = arena[0].data_ptr()
+        elif num_rendered and not debug:
+            _grow_arena(dev, sid, num_rendered)             # for the next frames
         binning = torch.empty((_bucket(lib.gs2d_binning_bytes(num_rendered, W, H)) if num_rendered else 0,), **u8)
         bufs.binning = _ptr(binning)
         bufs.binning_bytes = binning.numel()
@@ -142,8 +175,9 @@ def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations,
             if len(_pair_of_binning) > 4 * _PAIR_RING:
                 _pair_of_binning.clear()
             _pair_of_binning[binning.data_ptr()] = pairs_ptr
-        L.check(lib.gs2d_forward_render(C.byref(s), C.byref(i), C.byref(bufs), num_rendered,
-                                        _ptr(out_color), _ptr(out_others), pairs_ptr, st), "gs2d_forward_render")
+        L.check(lib.gs2d_forward_render_scattered(C.byref(s), C.byref(i), C.byref(bufs), num_rendered, _ptr(out_color),
+                                                  _ptr(out_others), pairs_ptr, scattered, st),
+                "gs2d_forward_render")
     return num_rendered, out_color, out_others, radii, geom, binning, img
 
 

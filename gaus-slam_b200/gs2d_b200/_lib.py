@@ -69,6 +69,9 @@ PROTOTYPES = {
                                           C.c_void_p, C.c_void_p, C.c_void_p]),
     "gs2d_forward_render": (C.c_int, [C.POINTER(Settings), C.POINTER(Inputs), C.POINTER(Buffers),
                                       C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "gs2d_forward_scatter_early": (C.c_int, [C.POINTER(Settings), C.POINTER(Buffers), C.c_void_p, C.c_int64, C.c_void_p]),
+    "gs2d_forward_render_scattered": (C.c_int, [C.POINTER(Settings), C.POINTER(Inputs), C.POINTER(Buffers),
+                                                C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "gs2d_forward": (C.c_int, [C.POINTER(Settings), C.POINTER(Inputs), C.POINTER(Buffers), C.c_void_p,
                                C.POINTER(C.c_int64), C.c_void_p, C.c_void_p, C.c_void_p]),
     "gs2d_forward_pair_count": (C.c_int, [C.POINTER(Settings), C.POINTER(Buffers), C.c_int64, C.c_void_p, C.c_void_p]),

@@ -121,6 +121,20 @@ int gs2d_forward_render(const gs2d_settings* s, const gs2d_inputs* in,
                         const gs2d_buffers* buffers, int64_t num_rendered,
                         float* out_color, float* out_others, int64_t* num_pairs_host, void* stream);
 
+/* Optional overlap of the host read-back with device work: between stage 1 and the host's wait for
+ * num_rendered, gs2d_forward_scatter_early launches the scatter of stage 2 into a caller-owned arena of
+ * `capacity` 8-byte words (sized from earlier frames).  The kernel reads num_rendered on the device and does
+ * nothing when it exceeds the capacity.  Once the host knows num_rendered it calls
+ * gs2d_forward_render_scattered with the arena when num_rendered <= capacity (stage 2 then skips its own
+ * scatter; the arena must stay untouched until that call's kernels have run -- stream order is enough), else
+ * gs2d_forward_render as usual.  (No counterpart in the reference: it blocks at CR/rasterizer_impl.cu:287 with
+ * the device idle.) */
+int gs2d_forward_scatter_early(const gs2d_settings* s, const gs2d_buffers* buffers, uint64_t* pairs_arena,
+                               int64_t capacity, void* stream);
+int gs2d_forward_render_scattered(const gs2d_settings* s, const gs2d_inputs* in, const gs2d_buffers* buffers,
+                                  int64_t num_rendered, float* out_color, float* out_others,
+                                  int64_t* num_pairs_host, uint64_t* scattered_pairs, void* stream);
+
 /* Convenience: stage 1, stream synchronise, stage 2 -- the reference's control flow
  * (CR/rasterizer_impl.cu:287 blocks on the same 4-byte read-back).  On entry
  * *num_rendered_io is the binning capacity (in instances) the caller provisioned; on

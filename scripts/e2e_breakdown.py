@@ -12,9 +12,13 @@ s = wl["sets"][0]
 params = {k: s[k].detach().clone().requires_grad_(True) for k in bench.PARAMS}
 means2D = torch.zeros((wl["P"], 3), device=dev, requires_grad=True)
 H, W = wl["H"], wl["W"]
-loss_fn = torch.cuda.make_graphed_callables(bench.mapping_loss, (
-    torch.rand((3, H, W), device=dev, requires_grad=True), torch.rand((7, H, W), device=dev, requires_grad=True),
-    s["gt_color"].clone(), s["gt_depth"].clone()))
+if len(sys.argv) < 2:
+    from gs2d_b200 import loss as gs2d_loss
+    loss_fn = gs2d_loss.mapping_loss
+else:
+    loss_fn = torch.cuda.make_graphed_callables(bench.mapping_loss, (
+        torch.rand((3, H, W), device=dev, requires_grad=True), torch.rand((7, H, W), device=dev, requires_grad=True),
+        s["gt_color"].clone(), s["gt_depth"].clone()))
 seg = {k: 0.0 for k in ("raster_ctor", "forward", "loss", "backward", "sync")}
 gpu = {k: 0.0 for k in ("forward", "loss", "backward")}
 N = 40

@@ -256,3 +256,27 @@ def test_gradient_arena_is_zero_copy_and_changes_nothing():
     for k in plain:
         assert torch.equal(back[k], inplace[k])
         assert compare.grad_rel(inplace[k].cpu().numpy(), plain[k].cpu().numpy()) < 1e-6, k
+
+
+@pytest.mark.gpu
+def test_early_scatter_paths_give_the_same_frame():
+    """_C.rasterize_gaussians launches the scatter before the host has read num_rendered when its arena is large
+    enough (from earlier frames); without arena, with arena, and with an arena that turns out too small (device
+    skips, host falls back) must give bit-identical binning and images."""
+    import gpu_run
+    from gaus_2dgs_rasterization import _C
+    case = cases.dense_sa()
+    _C._arenas.clear()
+    first = gpu_run.run_ours(case, debug=False)          # no arena yet: scatter inside stage 2
+    assert len(_C._arenas) == 1
+    key = next(iter(_C._arenas))
+    early = gpu_run.run_ours(case, debug=False)          # arena from the first call: early scatter
+    t, cap = _C._arenas[key]
+    assert cap >= int(first["num_rendered"])
+    _C._arenas[key] = (t, 10)                            # pretend the arena is far too small
+    small = gpu_run.run_ours(case, debug=False)
+    assert _C._arenas[key][1] >= int(first["num_rendered"]), "the arena did not grow after the fallback"
+    for other in (early, small):
+        assert not compare.check_binning(other, first, exact_float_state=True)
+        assert not compare.check_images(other, first, exact=True)
+        assert int(other["footprint_audit"][2]) == 0
