@@ -339,18 +339,15 @@ composite_backward_pixels_kernel(int W, int H, unsigned gx, const uint2* __restr
 			constexpr int NG = BWD_BATCH / 32;
 			int g = NG - 1;
 			uint32_t m = foot[NG - 1], u = used[NG - 1];
-			auto next_word = [&]() {
-				while (m == 0u && g > 0) {
+			for (;;) {
+				while (m == 0u && g > 0) {     // advance to the next non-empty word (towards the front)
 					g--;
 #pragma unroll
 					for (int k = 0; k < NG - 1; k++)
 						if (g == k) { m = foot[k]; u = used[k]; }
 				}
-				return m != 0u;
-			};
-			bool has = next_word();
-			while (__any_sync(0xffffffffu, has)) {
-				if (has) {
+				if (!__any_sync(0xffffffffu, m != 0u)) break;
+				if (m != 0u) {
 					const int jl = 31 - __clz(m);
 					m &= ~(1u << jl);
 					const int j = g * 32 + jl;
@@ -364,7 +361,6 @@ composite_backward_pixels_kernel(int W, int H, unsigned gx, const uint2* __restr
 					} else {
 						*dst = empty;
 					}
-					has = next_word();
 				}
 			}
 		}

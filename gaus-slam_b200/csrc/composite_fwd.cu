@@ -191,27 +191,31 @@ composite_forward_kernel(int W, int H, unsigned gx, const uint2* __restrict__ ra
 		// Every pixel walks its own hits of the WHOLE batch front to back, in one loop: a warp iterates as often as
 		// its longest pixel list (lists of 128 instances balance better between the lanes than lists of 32).
 		{
-			int g = 0;
+			int g = done ? FWD_GROUPS - 1 : 0;
 			uint32_t m = done ? 0u : sm.hits[0][tid], used = 0u;
-			// advance to the next non-empty word; false when the pixel has no hit left in this batch
-			auto next_word = [&]() {
-				while (m == 0u && g + 1 < FWD_GROUPS) {
+			for (;;) {
+				// advance to the next non-empty word (finished pixels sit at the last word with m = 0)
+				while (m == 0u && g < FWD_GROUPS - 1) {
 					sm.used[g][tid] = used;
 					used = 0u;
 					g++;
 					m = sm.hits[g][tid];
 				}
-				return m != 0u;
-			};
-			bool has = !done && next_word();
-			while (__any_sync(0xffffffffu, has)) {
-				if (has) {
+				if (!__any_sync(0xffffffffu, m != 0u)) break;
+				if (m != 0u) {
 					const int jl = __ffs(m) - 1;
 					m &= m - 1;
 					const int j = g * 32 + jl;
 					if (eval_pair<USE_SA>(recs + j * 5, pxf, pyf, (uint32_t)(b * FWD_BATCH + j + 1), px, done))
 						used |= 1u << jl;
-					has = !done && next_word();
+					if (done) {   // T < 1e-4: nothing behind this pair counts; park the lane at the last word
+						m = 0u;
+						if (g < FWD_GROUPS - 1) {
+							sm.used[g][tid] = used;
+							used = 0u;
+							g = FWD_GROUPS - 1;
+						}
+					}
 				}
 			}
 			sm.used[g][tid] = used;
