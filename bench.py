@@ -376,8 +376,15 @@ def main():
     order = ["means3D", "opacities", "scales", "rotations", "colors"]
 
     from gs2d_b200 import mapping
-    grad_path = {"zero_copy": None}
+    grad_path = {"zero_copy": None, "collective": "NCCL all-reduce"}
     if multi and a.impl == "b200":
+        # From 4 ranks on, the buffer lives in symmetric memory and is reduced IN the NVSwitch by libgs2d's own
+        # multimem kernel (csrc/collective.cu); with 2 ranks NCCL's direct exchange is as fast.
+        want = os.environ.get("GS2D_ALLREDUCE", "multimem" if world >= 4 else "nccl")
+        sym = mapping.symmetric_gradient_buffer(P, dev) if want == "multimem" else None
+        if sym is not None:
+            flat = sym
+            grad_path["collective"] = "own in-switch all-reduce (multimem.ld_reduce / multimem.st over NVLS)"
         # gradients of the five parameter groups are written straight into the buffer the all-reduce runs on
         from gaus_2dgs_rasterization import _C as _gs2d_C
         _gs2d_C.set_gradient_arena(flat)
@@ -611,7 +618,7 @@ def main():
            "config": {"workload": f"mapping-shaped fwd+bwd of one keyframe view per GPU per step, {W}x{H}, "
                                   f"{P} surfels, {V}-keyframe window (BASELINE.json configs[2]), use_sa=True",
                       "surfels": P, "visible_mean": Pv_mean, "instances_mean": I_mean, "views": V,
-                      "parallelism": f"view-sharded x{world if multi else 1}" + (", NCCL all-reduce of [P,13] map gradients" + (" written in place by the backward pass" if grad_path["zero_copy"] else " (packed copy)") if multi else ""),
+                      "parallelism": f"view-sharded x{world if multi else 1}" + (", " + grad_path["collective"] + " of [P,13] map gradients" + (" written in place by the backward pass" if grad_path["zero_copy"] else " (packed copy)") if multi else ""),
                       "l2": f"inputs rotate over {V} per-view sets ({V} x {(P * 52 + W * H * 56) / 1e6:.1f} MB > 126 MB L2); no explicit flush"},
            "gpu_launches": launches, "clocks": clocks}
     if a.impl == "reference":

@@ -94,6 +94,7 @@ PROTOTYPES = {
     "gs2d_mapping_loss_backward": (C.c_int, [C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                              C.c_int32, C.POINTER(LossParams), C.c_void_p, C.c_void_p, C.c_void_p,
                                              C.c_void_p, C.c_void_p]),
+    "gs2d_allreduce_multimem": (C.c_int, [C.c_void_p, C.c_int64, C.c_int32, C.c_int32, C.c_int32, C.c_void_p]),
     "gs2d_timing_enable": (C.c_int, [C.c_int]),
     "gs2d_num_kernels": (C.c_int, []),
     "gs2d_kernel_name": (C.c_char_p, [C.c_int]),

@@ -72,10 +72,51 @@ def unpack_grads(flat: torch.Tensor, P: int) -> dict:
     return {name: flat[a:b].view(P, PARAM_WIDTH[name]) for name, a, b in flat_sections(P)}
 
 
+_symmetric = {}   # data_ptr of a flat buffer from symmetric_gradient_buffer -> (handle, numel, rank, world)
+
+
+def symmetric_gradient_buffer(P: int, device, group=None):
+    """Flat [13 * P] fp32 gradient buffer in NVLink symmetric memory bound to an NVSwitch multicast object
+    (torch.distributed._symmetric_memory does the allocation and the binding).  allreduce_map_gradient then
+    reduces it IN the switch with libgs2d's own kernel (csrc/collective.cu: multimem.ld_reduce / multimem.st)
+    instead of calling NCCL.  Returns None when symmetric memory or multicast is unavailable (e.g. gloo, one
+    rank, no NVSwitch): the caller falls back to an ordinary tensor and NCCL."""
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) < 2:
+        return None
+    if dist.get_backend(group) != "nccl" or (13 * P) % 4:
+        return None
+    try:
+        import torch.distributed._symmetric_memory as symm_mem
+        g = group if group is not None else dist.group.WORLD
+        flat = symm_mem.empty(FLAT_WIDTH * P, dtype=torch.float32, device=device)
+        hdl = symm_mem.rendezvous(flat, g.group_name)
+        if not getattr(hdl, "multicast_ptr", 0):
+            return None
+    except Exception:      # no symmetric memory on this build / box
+        return None
+    flat.zero_()
+    _symmetric[flat.data_ptr()] = (hdl, flat.numel(), hdl.rank, hdl.world_size)
+    return flat
+
+
 def allreduce_map_gradient(flat: torch.Tensor, group=None, average: bool = False) -> torch.Tensor:
-    """Sum (or mean) of the map gradient over the ranks; a no-op without an initialised process group."""
+    """Sum (or mean) of the map gradient over the ranks; a no-op without an initialised process group.
+    Buffers from symmetric_gradient_buffer go through the in-switch kernel of libgs2d.so, bracketed by two
+    cross-GPU barriers (all gradients written / all slices stored); anything else through the backend's
+    all_reduce (NCCL on GPUs, gloo in the CPU tests)."""
     if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
-        dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=group)
+        sym = _symmetric.get(flat.data_ptr()) if flat.is_cuda else None
+        if sym is not None and sym[1] == flat.numel():
+            import ctypes as C
+            from . import _lib as L
+            hdl, n, rank, world = sym
+            hdl.barrier(channel=0)
+            st = C.c_void_p(torch.cuda.current_stream(flat.device).cuda_stream)
+            L.check(L.load().gs2d_allreduce_multimem(C.c_void_p(hdl.multicast_ptr), n, rank, world, 0, st),
+                    "gs2d_allreduce_multimem")
+            hdl.barrier(channel=1)
+        else:
+            dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=group)
         if average:
             flat /= dist.get_world_size(group)
     return flat

@@ -253,6 +253,16 @@ int gs2d_mapping_loss_backward(int32_t image_width, int32_t image_height, const 
                                const gs2d_loss_params* params, const void* scratch, const float* grad_loss,
                                float* dL_dcolor, float* dL_dallmap, void* stream);
 
+/* ---- multi-GPU (new; the reference is single-GPU) -----------------------------------------
+ * In-switch all-reduce (sum, fp32) of a buffer that lives in symmetric memory bound to an NVLS multicast
+ * object: `multicast_ptr` is the multicast address of the buffer (same offset on every rank), n_floats a
+ * multiple of 4.  Rank r reduces and re-broadcasts the r-th of `world` slices with multimem.ld_reduce /
+ * multimem.st.  The caller must separate the launch from the producers and consumers of the buffer on ALL
+ * ranks with cross-GPU barriers (before: every rank's data is written; after: every slice is stored).
+ * max_blocks <= 0 picks a default grid. */
+int gs2d_allreduce_multimem(void* multicast_ptr, int64_t n_floats, int32_t rank, int32_t world,
+                            int32_t max_blocks, void* stream);
+
 /* Optional per-kernel timing for bench.py's roofline line: while enabled, every kernel launch
  * (and memset) of this library is bracketed by CUDA events on the launching stream.
  * gs2d_timing_collect() waits for the recorded events, writes the summed device time (ms) and
