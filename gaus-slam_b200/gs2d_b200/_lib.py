@@ -61,6 +61,16 @@ class LossParams(C.Structure):
                 ("depth_near", C.c_float), ("depth_far", C.c_float)]
 
 
+class MapState(C.Structure):
+    _fields_ = [("xyz", C.c_void_p), ("opacity", C.c_void_p), ("scaling", C.c_void_p), ("rotation", C.c_void_p),
+                ("rgb", C.c_void_p), ("exp_avg", C.c_void_p * 5), ("exp_avg_sq", C.c_void_p * 5)]
+
+
+class AdamParams(C.Structure):
+    _fields_ = [("lr", C.c_double * 5), ("beta1", C.c_double), ("beta2", C.c_double), ("eps", C.c_double),
+                ("step", C.c_int64)]
+
+
 PROTOTYPES = {
     "gs2d_geom_bytes": (C.c_size_t, [C.c_int32, C.c_int32]),
     "gs2d_image_bytes": (C.c_size_t, [C.c_int32, C.c_int32]),
@@ -94,6 +104,13 @@ PROTOTYPES = {
     "gs2d_mapping_loss_backward": (C.c_int, [C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                              C.c_int32, C.POINTER(LossParams), C.c_void_p, C.c_void_p, C.c_void_p,
                                              C.c_void_p, C.c_void_p]),
+    "gs2d_map_activate": (C.c_int, [C.c_int32, C.c_int32, C.POINTER(MapState), C.c_void_p, C.c_void_p, C.c_void_p,
+                                    C.c_void_p]),
+    "gs2d_map_adam_step": (C.c_int, [C.c_int32, C.c_int32, C.POINTER(MapState), C.c_void_p, C.POINTER(AdamParams),
+                                     C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "gs2d_pose_transform_forward": (C.c_int, [C.c_int32] + [C.c_void_p] * 8),
+    "gs2d_pose_transform_scratch_bytes": (C.c_size_t, []),
+    "gs2d_pose_transform_backward": (C.c_int, [C.c_int32] + [C.c_void_p] * 11),
     "gs2d_allreduce_multimem": (C.c_int, [C.c_void_p, C.c_int64, C.c_int32, C.c_int32, C.c_int32, C.c_void_p]),
     "gs2d_timing_enable": (C.c_int, [C.c_int]),
     "gs2d_num_kernels": (C.c_int, []),

@@ -1,0 +1,97 @@
+"""Fused map optimiser: the host side of gs2d_map_activate / gs2d_map_adam_step.
+
+Mirrors how the reference drives its map parameters: `Gaussians.training_setup` builds
+`torch.optim.Adam(groups, lr=0.0, eps=1e-15)` over the raw tensors `_xyz, _opacity, _scaling, _rotation, _rgb`
+with the learning rates of `config['gaussians']['training_args']` (scene/Gaussians.py:124-137), and
+`get_render_params` renders `sigmoid(_opacity)`, `exp(_scaling)`, `F.normalize(_rotation)` (:336-358).
+
+    opt = MapOptimizer(xyz, opacity_logit, log_scaling, rotation, rgb, training_args)
+    params = opt.render_params()            # means3D / opacities / scales / rotations / colors_precomp (leaves)
+    ... forward, loss, backward inside mapping.gradient_arena(opt.flat_grad) (+ all-reduce) ...
+    opt.step()                              # chain rule of the activations + Adam + next activations: ONE launch
+
+CUDA only: there is no CPU path (the CPU restatement used by the tests lives outside the package).
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import torch
+
+from . import _lib as L
+from .mapping import FLAT_WIDTH
+
+GROUPS = ("xyz", "opacity", "scaling", "rotation", "rgb")
+LR_KEYS = ("xyz_lr", "opacity_lr", "scaling_lr", "rotation_lr", "rgb_lr")
+
+
+class MapOptimizer:
+    def __init__(self, xyz, opacity, scaling, rotation, rgb, training_args, betas=(0.9, 0.999), eps=1e-15,
+                 flat_grad=None):
+        raw = dict(xyz=xyz, opacity=opacity, scaling=scaling, rotation=rotation, rgb=rgb)
+        P = int(xyz.shape[0])
+        want = dict(xyz=[(P, 3)], opacity=[(P, 1)], scaling=[(P, 2), (P, 1)], rotation=[(P, 4)], rgb=[(P, 3)])
+        for k, t in raw.items():
+            if not t.is_cuda or t.dtype != torch.float32:
+                raise RuntimeError(f"{k} must be a float32 CUDA tensor (there is no CPU path)")
+            if tuple(t.shape) not in want[k]:
+                raise RuntimeError(f"{k} has shape {tuple(t.shape)}, expected one of {want[k]}")
+        self.P, self.dev = P, xyz.device
+        self.scale_cols = int(scaling.shape[1])
+        self.raw = {k: t.detach().contiguous() for k, t in raw.items()}
+        self.exp_avg = {k: torch.zeros_like(t) for k, t in self.raw.items()}
+        self.exp_avg_sq = {k: torch.zeros_like(t) for k, t in self.raw.items()}
+        self.lr = [float(training_args[k]) for k in LR_KEYS]
+        self.betas, self.eps, self.step_count = (float(betas[0]), float(betas[1])), float(eps), 0
+        self.flat_grad = flat_grad if flat_grad is not None else torch.zeros(FLAT_WIDTH * P, device=self.dev)
+        if self.flat_grad.numel() != FLAT_WIDTH * P or not self.flat_grad.is_cuda:
+            raise RuntimeError("flat_grad must be a CUDA tensor of 13 * P floats")
+        self.opacities = torch.empty((P, 1), device=self.dev)
+        self.scales = torch.empty((P, 2), device=self.dev)
+        self.rotations = torch.empty((P, 4), device=self.dev)
+        self._state = L.MapState()
+        self._bind()
+        self.activate()
+
+    def _bind(self):
+        s = self._state
+        for k in GROUPS:
+            setattr(s, k, self.raw[k].data_ptr())
+        for i, k in enumerate(GROUPS):
+            s.exp_avg[i] = self.exp_avg[k].data_ptr()
+            s.exp_avg_sq[i] = self.exp_avg_sq[k].data_ptr()
+
+    def _stream(self):
+        return C.c_void_p(torch.cuda.current_stream(self.dev).cuda_stream)
+
+    def activate(self):
+        """Render parameters of the current raw parameters (get_render_params)."""
+        with torch.cuda.device(self.dev):
+            L.check(L.load().gs2d_map_activate(self.P, self.scale_cols, C.byref(self._state), self.opacities.data_ptr(),
+                                               self.scales.data_ptr(), self.rotations.data_ptr(), self._stream()),
+                    "gs2d_map_activate")
+
+    def render_params(self, requires_grad=True):
+        """The keyword arguments `render()` of render/render_2dgs.py passes on: fresh leaves over the optimiser's
+        own buffers (no copies)."""
+        def leaf(t):
+            t = t.detach()
+            t.requires_grad_(requires_grad)
+            return t
+        return dict(means3D=leaf(self.raw["xyz"]), opacities=leaf(self.opacities), scales=leaf(self.scales),
+                    rotations=leaf(self.rotations), colors_precomp=leaf(self.raw["rgb"]))
+
+    def step(self, flat_grad=None):
+        """One Adam step from the gradient w.r.t. the render parameters in the flat [13 * P] layout."""
+        g = self.flat_grad if flat_grad is None else flat_grad
+        if g.numel() != FLAT_WIDTH * self.P or not g.is_cuda or g.dtype != torch.float32:
+            raise RuntimeError("flat_grad must be a float32 CUDA tensor of 13 * P elements")
+        self.step_count += 1
+        ap = L.AdamParams()
+        for i, v in enumerate(self.lr):
+            ap.lr[i] = v
+        ap.beta1, ap.beta2, ap.eps, ap.step = self.betas[0], self.betas[1], self.eps, self.step_count
+        with torch.cuda.device(self.dev):
+            L.check(L.load().gs2d_map_adam_step(self.P, self.scale_cols, C.byref(self._state), g.data_ptr(), C.byref(ap),
+                                                self.opacities.data_ptr(), self.scales.data_ptr(),
+                                                self.rotations.data_ptr(), self._stream()), "gs2d_map_adam_step")

@@ -253,6 +253,64 @@ int gs2d_mapping_loss_backward(int32_t image_width, int32_t image_height, const 
                                const gs2d_loss_params* params, const void* scratch, const float* grad_loss,
                                float* dL_dcolor, float* dL_dallmap, void* stream);
 
+/* ---- "next" row f3: fused map optimiser step -------------------------------------------------
+ * The reference's map optimiser: five raw parameter tensors (scene/Gaussians.py:106-114), rendered through
+ * sigmoid / exp / F.normalize (get_render_params, :336-358) and stepped by torch.optim.Adam(eps=1e-15) with one
+ * learning rate per group (training_setup, :124-137).  gs2d_map_adam_step is one launch for: the chain rule of
+ * the three activations, the Adam update of all five groups (torch/optim/adam.py, no amsgrad / weight decay)
+ * and the activations of the updated parameters for the next forward pass.
+ * Group order everywhere: xyz, opacity, scaling, rotation, rgb.  `flat_grad` is the gradient w.r.t. the RENDER
+ * parameters in the flat [13 * P] layout of the view-sharded all-reduce (gs2d_b200/mapping.py):
+ * means3D 3P | opacities P | scales 2P | rotations 4P | colors 3P.  scale_cols = 2 (anisotropic, every shipped
+ * config) or 1 (isotropic: _scaling is [P,1] and the render scales are exp(s) in both columns). */
+typedef struct gs2d_map_state {
+	float* xyz;             /* [P,3]  _xyz                                   */
+	float* opacity;         /* [P,1]  _opacity (logit)                       */
+	float* scaling;         /* [P,scale_cols] _scaling (log)                 */
+	float* rotation;        /* [P,4]  _rotation (unnormalised, w first)      */
+	float* rgb;             /* [P,3]  _rgb                                   */
+	float* exp_avg[5];      /* Adam first moments, shapes as above           */
+	float* exp_avg_sq[5];   /* Adam second moments                           */
+} gs2d_map_state;
+
+typedef struct gs2d_adam_params {
+	double lr[5];           /* xyz_lr, opacity_lr, scaling_lr, rotation_lr, rgb_lr        */
+	double beta1, beta2;    /* 0.9, 0.999                                                  */
+	double eps;             /* 1e-15 (scene/Gaussians.py:137)                              */
+	int64_t step;           /* 1 for the first update (torch increments before using it)   */
+} gs2d_adam_params;
+
+/* Render parameters of the current raw parameters: opacities [P,1] = sigmoid, scales [P,2] = exp,
+ * rotations [P,4] = q / max(|q|, 1e-12).  (means3D and colors are the raw tensors themselves.)  The moments of
+ * `ms` are not touched and may be NULL. */
+int gs2d_map_activate(int32_t P, int32_t scale_cols, const gs2d_map_state* ms, float* opacities, float* scales,
+                      float* rotations, void* stream);
+/* One optimiser step in place; opacities / scales / rotations (all three or none) receive the activations of the
+ * updated parameters. */
+int gs2d_map_adam_step(int32_t P, int32_t scale_cols, const gs2d_map_state* ms, const float* flat_grad,
+                       const gs2d_adam_params* params, float* opacities, float* scales, float* rotations,
+                       void* stream);
+
+/* ---- "next" row f1: fused pose transform + pose-gradient reduction ---------------------------
+ * Renderer_tracking / Renderer_BA move the map into the camera frame before rendering with an identity camera
+ * (render/__init__.py:35-36, :97-98):
+ *   means3D'   = (w2c[:3,:3] @ means3D.T + w2c[:3,3:]).T
+ *   rotations' = quaternion_multiply(matrix_to_quaternion(w2c[None,:3,:3]), rotations)        (no gradient)
+ * The pose is given EITHER as the optimiser's own scalars (scene/Frame.py:66-67, :87-96: cam_rot [4] unnormalised
+ * quaternion, real first; cam_trans [3]; w2c = [quaternion_to_matrix(normalize(cam_rot)) | cam_trans]) OR as a
+ * row-major 4x4 `w2c` (fix_w2c / LocalMap.get_frame_w2c) -- the other form's pointers NULL.  All device pointers.
+ * rotations / rotations_out may both be NULL (means only); when given they must be 16-byte aligned.
+ * Backward: g = dL/dmeans3D' [P,3] -> dL/dcam_rot [4] + dL/dcam_trans [3] (quaternion form) or dL/dw2c [16]
+ * (matrix form; last row zero), and, when dL_dxyz is not NULL, dL/dmeans3D = R^T g [P,3] (bundle adjustment).
+ * `scratch`: gs2d_pose_transform_scratch_bytes() bytes, ZERO-INITIALISED once by the caller, then reusable. */
+int gs2d_pose_transform_forward(int32_t P, const float* xyz, const float* rotations, const float* cam_rot,
+                                const float* cam_trans, const float* w2c, float* means3D_out, float* rotations_out,
+                                void* stream);
+size_t gs2d_pose_transform_scratch_bytes(void);
+int gs2d_pose_transform_backward(int32_t P, const float* xyz, const float* cam_rot, const float* cam_trans,
+                                 const float* w2c, const float* dL_dmeans3D, void* scratch, float* dL_dcam_rot,
+                                 float* dL_dcam_trans, float* dL_dw2c, float* dL_dxyz, void* stream);
+
 /* ---- multi-GPU (new; the reference is single-GPU) -----------------------------------------
  * In-switch all-reduce (sum, fp32) of a buffer that lives in symmetric memory bound to an NVLS multicast
  * object: `multicast_ptr` is the multicast address of the buffer (same offset on every rank), n_floats a

@@ -1,0 +1,97 @@
+"""TEST INFRASTRUCTURE ONLY (never imported by the product): the reference's map optimiser step, restated.
+
+`MapTorch` is the reference's own machinery run on the CPU: raw parameters as nn.Parameters, the activations of
+`Gaussians.get_render_params` (scene/Gaussians.py:17-21, :336-358: sigmoid / exp / F.normalize, exp tiled to two
+columns when isotropic) and `torch.optim.Adam(groups, lr=0.0, eps=1e-15)` with the per-group learning rates of
+`training_setup` (:124-137).  torch.optim.Adam IS the reference's optimiser, so this pins the parity of the fused
+kernel against outputs of the reference's implementation run here.  `map_step_numpy` is a float64 restatement of
+the same step with hand-written activation gradients (checks the derivation the CUDA kernel uses).
+"""
+import numpy as np
+
+GROUPS = ("xyz", "opacity", "scaling", "rotation", "rgb")
+LR_KEYS = ("xyz_lr", "opacity_lr", "scaling_lr", "rotation_lr", "rgb_lr")
+# flat [13 * P] gradient layout of the render parameters (gs2d_b200/mapping.py)
+FLAT = (("means3D", 3), ("opacities", 1), ("scales", 2), ("rotations", 4), ("colors", 3))
+
+
+def split_flat(flat, P):
+    out, off = {}, 0
+    for name, w in FLAT:
+        out[name] = flat[off:off + w * P].reshape(P, w)
+        off += w * P
+    return out
+
+
+class MapTorch:
+    """The reference's parameter handling, on whatever device the tensors live on (CPU in the tests here)."""
+
+    def __init__(self, raw, training_args, betas=(0.9, 0.999), eps=1e-15):
+        import torch
+        self.torch = torch
+        self.p = {k: torch.nn.Parameter(torch.as_tensor(raw[k]).clone().requires_grad_(True)) for k in GROUPS}
+        groups = [{"params": [self.p[k]], "lr": training_args[lk], "name": k} for k, lk in zip(GROUPS, LR_KEYS)]
+        self.optimizer = torch.optim.Adam(groups, lr=0.0, eps=eps, betas=betas)      # scene/Gaussians.py:137
+
+    def render_params(self):
+        torch = self.torch
+        scales = torch.exp(self.p["scaling"])
+        if scales.shape[1] == 1:
+            scales = torch.tile(scales, (1, 2))                                      # :340-341
+        return dict(means3D=self.p["xyz"], opacities=torch.sigmoid(self.p["opacity"]), scales=scales,
+                    rotations=torch.nn.functional.normalize(self.p["rotation"]), colors=self.p["rgb"])
+
+    def step(self, flat_grad):
+        """Back-propagate a given gradient of the render parameters and step (what loss.backward() +
+        optimizer.step() do in Frontend.mapping, slam/Frontend.py:116-128)."""
+        torch = self.torch
+        self.optimizer.zero_grad(set_to_none=True)
+        rp = self.render_params()
+        g = split_flat(torch.as_tensor(flat_grad), self.p["xyz"].shape[0])
+        torch.autograd.backward([rp[k] for k, _ in FLAT], [g[k] for k, _ in FLAT])
+        self.optimizer.step()
+
+    def state(self):
+        out = {k: self.p[k].detach().cpu().numpy() for k in GROUPS}
+        for k in GROUPS:
+            st = self.optimizer.state[self.p[k]]
+            out["m_" + k] = st["exp_avg"].cpu().numpy()
+            out["v_" + k] = st["exp_avg_sq"].cpu().numpy()
+        with self.torch.no_grad():
+            rp = self.render_params()
+        for k in ("opacities", "scales", "rotations"):
+            out[k] = rp[k].detach().cpu().numpy()
+        return out
+
+
+def activate_numpy(raw):
+    q = raw["rotation"].astype(np.float64)
+    n = np.maximum(np.sqrt((q * q).sum(1, keepdims=True)), 1e-12)
+    s = np.exp(raw["scaling"].astype(np.float64))
+    if s.shape[1] == 1:
+        s = np.tile(s, (1, 2))
+    return dict(opacities=1.0 / (1.0 + np.exp(-raw["opacity"].astype(np.float64))), scales=s, rotations=q / n)
+
+
+def map_step_numpy(raw, m, v, flat_grad, lr, step, betas=(0.9, 0.999), eps=1e-15):
+    """float64.  raw / m / v: dicts over GROUPS; returns the updated (raw, m, v) and the new activations."""
+    P = raw["xyz"].shape[0]
+    g = {k: x.astype(np.float64) for k, x in split_flat(np.asarray(flat_grad), P).items()}
+    x = {k: raw[k].astype(np.float64) for k in GROUPS}
+    act = activate_numpy(raw)
+    graw = {"xyz": g["means3D"], "rgb": g["colors"]}
+    o = act["opacities"]
+    graw["opacity"] = g["opacities"] * (1.0 - o) * o
+    gs = g["scales"] if x["scaling"].shape[1] == 2 else g["scales"].sum(1, keepdims=True)
+    graw["scaling"] = gs * np.exp(x["scaling"])
+    qh = act["rotations"]
+    n = np.maximum(np.sqrt((x["rotation"] ** 2).sum(1, keepdims=True)), 1e-12)
+    graw["rotation"] = (g["rotations"] - qh * (qh * g["rotations"]).sum(1, keepdims=True)) / n
+    b1, b2 = betas
+    bc1, bc2 = 1.0 - b1 ** step, 1.0 - b2 ** step
+    nr, nm, nv = {}, {}, {}
+    for k, l in zip(GROUPS, lr):
+        nm[k] = m[k].astype(np.float64) + (graw[k] - m[k]) * (1.0 - b1)
+        nv[k] = v[k].astype(np.float64) * b2 + (1.0 - b2) * graw[k] * graw[k]
+        nr[k] = x[k] - (l / bc1) * nm[k] / (np.sqrt(nv[k]) / np.sqrt(bc2) + eps)
+    return nr, nm, nv, activate_numpy(nr)
