@@ -50,6 +50,8 @@ def parse_args():
     ap.add_argument("--torch-loss", action="store_true", help="e2e of the product with the torch-ops loss instead of the fused kernels")
     ap.add_argument("--no-stats", action="store_true",
                     help="skip the (untimed) scene-statistics renders: for ncu launch lists of the timed steps only")
+    ap.add_argument("--no-loops", action="store_true",
+                    help="skip the whole-iteration loops (mapping_iteration / tracking_iteration keys, bench_loops.py)")
     ap.add_argument("--clock-period-ms", type=int, default=100, help="nvidia-smi sampling period; 0 = no sampling (diagnosis)")
     return ap.parse_args()
 
@@ -607,6 +609,14 @@ def main():
                        "memory and read on the host one step later (the last one before the timer stops); surfel parameters are optimiser "
                        "state and stay in HBM; loss = " + loss_how}
 
+    # ---- whole-iteration loops (extra keys; N = 1 only): mapping with the optimiser step, pose tracking
+    loops = {}
+    if e2e is not None and not a.no_loops and not multi:
+        import bench_loops
+        loops["mapping_iteration"] = bench_loops.mapping_iteration(arm, wl, dev, timed, a.steps, a.warmup, view_of,
+                                                                   loss_fn, a.impl, multi, None)
+        loops["tracking_iteration"] = bench_loops.tracking_iteration(arm, dev, timed, a.steps, a.warmup, a.impl)
+
     if rank != 0:
         if multi:
             dist.destroy_process_group()
@@ -635,6 +645,7 @@ def main():
             out["cpu_baseline"] = cpu_baseline(wl, a.cpu_frames)
     if e2e is not None:
         out["e2e"] = e2e
+    out.update(loops)
     print(json.dumps(out))
     if multi:
         dist.destroy_process_group()
