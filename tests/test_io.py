@@ -1,0 +1,76 @@
+"""Map formats: gaussians.ply in the reference's attribute order and w2cs.npz.npy.
+plyfile is not installed here, so the file is checked byte for byte against the layout plyfile's
+PlyData([el]).write produces for the reference's structured array (known-answer header + packed float32 rows), and
+read back with the selection rules of Gaussians.load_ply."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from gs2d_b200 import io as gio
+
+
+def _params(P, S, seed):
+    rng = np.random.default_rng(seed)
+    return dict(xyz=rng.normal(0, 2, (P, 3)).astype(np.float32), opacity=rng.normal(0, 1, (P, 1)).astype(np.float32),
+                scaling=rng.normal(-4, 1, (P, S)).astype(np.float32), rotation=rng.normal(0, 1, (P, 4)).astype(np.float32),
+                rgb=rng.uniform(0, 1, (P, 3)).astype(np.float32))
+
+
+def test_attribute_order_matches_the_reference():
+    # scene/Gaussians.py:435-450 with use_sh False
+    assert gio.ply_attributes(2) == ["x", "y", "z", "nx", "ny", "nz", "opacity", "scale_0", "scale_1", "rot_0", "rot_1",
+                                     "rot_2", "rot_3", "r", "g", "b"]
+    assert gio.ply_attributes(1)[6:9] == ["opacity", "scale_0", "rot_0"]
+
+
+@pytest.mark.parametrize("P,S,as_torch", [(5, 2, True), (1000, 2, False), (17, 1, True), (0, 2, False)])
+def test_ply_bytes_and_round_trip(tmp_path, P, S, as_torch):
+    p = _params(P, S, P + S)
+    args = {k: (torch.tensor(v) if as_torch else v) for k, v in p.items()}
+    path = os.path.join(tmp_path, "sub", "gaussians.ply")
+    gio.save_ply(path, **args)
+    raw = open(path, "rb").read()
+    names = gio.ply_attributes(S)
+    header = ("ply\nformat binary_little_endian 1.0\nelement vertex %d\n" % P +
+              "".join("property float %s\n" % n for n in names) + "end_header\n").encode()
+    assert raw.startswith(header)
+    body = np.frombuffer(raw[len(header):], dtype="<f4").reshape(P, len(names))
+    want = np.concatenate([p["xyz"], np.zeros_like(p["xyz"]), p["opacity"], p["scaling"], p["rotation"], p["rgb"]], axis=1)
+    assert body.tobytes() == want.astype("<f4").tobytes()
+    back = gio.load_ply(path)
+    for k in p:
+        assert back[k].dtype == np.float32 and back[k].shape == p[k].shape and np.array_equal(back[k], p[k])
+
+
+def test_reader_accepts_ascii_big_endian_and_shuffled_properties(tmp_path):
+    p = _params(6, 2, 3)
+    names = ["rot_3", "x", "y", "z", "opacity", "scale_1", "scale_0", "rot_0", "rot_1", "rot_2", "b", "g", "r", "extra"]
+    cols = dict(x=p["xyz"][:, 0], y=p["xyz"][:, 1], z=p["xyz"][:, 2], opacity=p["opacity"][:, 0], scale_0=p["scaling"][:, 0],
+                scale_1=p["scaling"][:, 1], rot_0=p["rotation"][:, 0], rot_1=p["rotation"][:, 1], rot_2=p["rotation"][:, 2],
+                rot_3=p["rotation"][:, 3], r=p["rgb"][:, 0], g=p["rgb"][:, 1], b=p["rgb"][:, 2], extra=np.arange(6, dtype=np.float32))
+    table = np.stack([cols[n] for n in names], axis=1)
+    hdr = "ply\nformat %s 1.0\ncomment made by a test\nelement vertex 6\n" + "".join("property float %s\n" % n for n in names) + \
+        "element face 0\nproperty list uchar int vertex_indices\nend_header\n"
+    a = os.path.join(tmp_path, "a.ply")
+    with open(a, "w") as f:
+        f.write(hdr % "ascii")
+        for row in table:
+            f.write(" ".join(repr(float(x)) for x in row) + "\n")
+    b = os.path.join(tmp_path, "b.ply")
+    with open(b, "wb") as f:
+        f.write((hdr % "binary_big_endian").encode())
+        f.write(table.astype(">f4").tobytes())
+    for path in (a, b):
+        back = gio.load_ply(path)
+        for k in p:
+            assert np.array_equal(back[k], p[k]), (path, k)
+
+
+def test_w2cs_file_name_and_content(tmp_path):
+    w = [torch.eye(4) * (i + 1) for i in range(3)]
+    path = gio.save_w2cs(str(tmp_path), w)
+    assert os.path.basename(path) == "w2cs.npz.npy" and os.path.exists(path)      # scene/__init__.py:33
+    back = gio.load_w2cs(str(tmp_path))
+    assert back.shape == (3, 4, 4) and back.dtype == np.float32 and np.array_equal(back[2], 3 * np.eye(4, dtype=np.float32))
