@@ -135,7 +135,9 @@ def tracking_iteration(arm, dev, timed, steps, warmup, impl, surfels=300_000):
 
         def to_camera():
             return tracking.pose_transform(xyz, rot, cam_rot=cam_rot, cam_trans=cam_trans)
-        how = "gs2d_b200.tracking.pose_transform (one kernel each way, pose chain rule inside)"
+        from gs2d_b200 import loss as gs2d_loss
+        loss_fn = gs2d_loss.tracking_loss
+        how = "gs2d_b200.tracking.pose_transform (one kernel each way, pose chain rule inside) + fused tracking loss"
     else:
         sys.path.insert(0, os.path.join(ROOT, "oracle"))
         import pose_ref
@@ -143,7 +145,8 @@ def tracking_iteration(arm, dev, timed, steps, warmup, impl, surfels=300_000):
         def to_camera():
             w2c = pose_ref.get_transform_matrix(cam_rot, cam_trans)
             return pose_ref.pose_transform_torch(xyz, rot, w2c)
-        how = "the reference's torch expressions (render/__init__.py:35-36, scene/Frame.py:87-96; pytorch3d algebra restated)"
+        loss_fn = tracking_loss
+        how = "the reference's torch expressions (render/__init__.py:35-36, scene/Frame.py:87-96; pytorch3d algebra restated) + tracking loss as eager torch ops"
     rast = arm.rasterizer(s)
 
     def step(i):
@@ -152,7 +155,7 @@ def tracking_iteration(arm, dev, timed, steps, warmup, impl, surfels=300_000):
         means2D = torch.zeros_like(xyz, requires_grad=True)
         color, radii, allmap = rast(means3D=means_c, means2D=means2D, opacities=opa, colors_precomp=rgb, scales=scl,
                                     rotations=rots_c)
-        loss = tracking_loss(color, allmap, s["gt_color"], s["gt_depth"])
+        loss = loss_fn(color, allmap, s["gt_color"], s["gt_depth"])
         loss.backward()
         with torch.no_grad():
             optimizer.step()
@@ -167,5 +170,4 @@ def tracking_iteration(arm, dev, timed, steps, warmup, impl, surfels=300_000):
     ms = timed(run, steps, warmup) / steps
     return {"value": 1000.0 / ms, "unit": "iterations/s", "ms_per_iteration": ms, "surfels": surfels,
             "frames_per_s_at_40_iters": 1000.0 / ms / 40.0, "final_loss": float(last["loss"].detach()),
-            "what": "pose -> camera-frame map -> render (identity camera) -> tracking loss (torch ops, eager, both "
-                    "arms) -> backward -> Adam on 7 pose scalars (slam/Frontend.py:80-92, BASELINE.json configs[1]); " + how}
+            "what": "pose -> camera-frame map -> render (identity camera) -> tracking loss -> backward -> Adam on 7 pose scalars (slam/Frontend.py:80-92, BASELINE.json configs[1]); " + how}

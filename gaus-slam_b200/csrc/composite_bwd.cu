@@ -196,8 +196,11 @@ __device__ __forceinline__ void oct_reduce24(float (&g)[24], int lane)
 	}
 }
 
+#ifndef GS2D_BWD_MIN_BLOCKS
+#define GS2D_BWD_MIN_BLOCKS 4
+#endif
 template <bool USE_SA>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, GS2D_BWD_MIN_BLOCKS)
 composite_backward_pixels_kernel(int W, int H, unsigned gx, const uint2* __restrict__ ranges,
                                  const float4* __restrict__ instances, const uint32_t* __restrict__ hit_inst,
                                  const uint32_t* __restrict__ hit_pix, const uint32_t* __restrict__ pair_incl,
@@ -212,8 +215,10 @@ composite_backward_pixels_kernel(int W, int H, unsigned gx, const uint2* __restr
 	const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 	const unsigned tile = blockIdx.x;
 	const unsigned tx = tile % gx, ty = tile / gx;
-	const unsigned pix_x = tx * TILE + (tid & 15);       // thread t <-> tile pixel (t & 15, t >> 4), pair.cuh
-	const unsigned pix_y = ty * TILE + (tid >> 4);
+	const int lx = thread_lx<GS2D_BWD_BLOCK>(tid), ly = thread_ly<GS2D_BWD_BLOCK>(tid);   // thread <-> tile pixel: pair.cuh
+	const int ptid = pixel_thread(lx, ly);               // row-major pixel index: this pixel's words in hit_pix
+	const unsigned pix_x = tx * TILE + lx;
+	const unsigned pix_y = ty * TILE + ly;
 	const bool inside = pix_x < (unsigned)W && pix_y < (unsigned)H;
 	const float pxf = (float)pix_x, pyf = (float)pix_y;
 	const size_t HW = (size_t)H * W;
@@ -310,8 +315,8 @@ composite_backward_pixels_kernel(int W, int H, unsigned gx, const uint2* __restr
 		uint32_t used[BWD_BATCH / 32], foot[BWD_BATCH / 32];
 #pragma unroll
 		for (int g = 0; g < BWD_BATCH / 32; g++) {
-			used[g] = pix_words[(size_t)((b * (BWD_BATCH / 32) + g) * 2 + 0) * TILE_PIXELS + tid];
-			foot[g] = pix_words[(size_t)((b * (BWD_BATCH / 32) + g) * 2 + 1) * TILE_PIXELS + tid];
+			used[g] = pix_words[(size_t)((b * (BWD_BATCH / 32) + g) * 2 + 0) * TILE_PIXELS + ptid];
+			foot[g] = pix_words[(size_t)((b * (BWD_BATCH / 32) + g) * 2 + 1) * TILE_PIXELS + ptid];
 		}
 		if (tid < cnt) {
 			const size_t gi = (size_t)range.x + (size_t)b * BWD_BATCH + tid;
@@ -322,6 +327,16 @@ composite_backward_pixels_kernel(int W, int H, unsigned gx, const uint2* __restr
 
 		const float4* recs = &sm.rec[stage][0];
 		const uint32_t* masks = &sm.mask[stage][0];
+#if GS2D_BWD_BLOCK
+		// re-order every mask in place from row-pair words to warp-block words (pair.cuh): word pair (2m, 2m+1) holds
+		// tile rows 4m..4m+3, i.e. exactly the two 8 x 4 blocks of block row m
+		for (int e = tid; e < cnt * 4; e += 256) {
+			uint2* w2 = reinterpret_cast<uint2*>(&sm.mask[stage][0]) + e;
+			const uint2 rows = *w2;
+			*w2 = make_uint2(__byte_perm(rows.x, rows.y, 0x6420), __byte_perm(rows.x, rows.y, 0x7531));
+		}
+		__syncthreads();
+#endif
 		if (tid < cnt) {
 			uint32_t run = 0, lo = 0, hi = 0;
 #pragma unroll
@@ -386,7 +401,7 @@ composite_backward_pixels_kernel(int W, int H, unsigned gx, const uint2* __restr
 				const float4 sl = slots[k];
 				const int p = __float_as_int(sl.w);
 				if (p >= 0)
-					instance_step(r0, r1, r2, (float)(tx * TILE + (p & 15)), (float)(ty * TILE + (p >> 4)), sl.x, sl.y,
+					instance_step(r0, r1, r2, (float)(tx * TILE + thread_lx<GS2D_BWD_BLOCK>(p)), (float)(ty * TILE + thread_ly<GS2D_BWD_BLOCK>(p)), sl.x, sl.y,
 					              sl.z, &sm.pix[0][0], p, g);
 			}
 		}

@@ -115,8 +115,11 @@ __device__ __forceinline__ bool eval_pair(const float4* __restrict__ rec, float 
 	return true;
 }
 
+#ifndef GS2D_FWD_MIN_BLOCKS
+#define GS2D_FWD_MIN_BLOCKS 4
+#endif
 template <bool USE_SA>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, GS2D_FWD_MIN_BLOCKS)
 composite_forward_kernel(int W, int H, unsigned gx, const uint2* __restrict__ ranges,
                          const float4* __restrict__ instances, const uint32_t* __restrict__ hit_inst,
                          uint32_t* __restrict__ hit_pix, const float* __restrict__ bg, float* __restrict__ final_T,
@@ -133,8 +136,10 @@ composite_forward_kernel(int W, int H, unsigned gx, const uint2* __restrict__ ra
 	const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 	const unsigned tile = blockIdx.x;
 	const unsigned tx = tile % gx, ty = tile / gx;
-	const unsigned pix_x = tx * TILE + (tid & 15);       // thread t <-> tile pixel (t & 15, t >> 4), pair.cuh
-	const unsigned pix_y = ty * TILE + (tid >> 4);
+	const int lx = thread_lx<GS2D_FWD_BLOCK>(tid), ly = thread_ly<GS2D_FWD_BLOCK>(tid);   // thread <-> tile pixel: pair.cuh
+	const int ptid = pixel_thread(lx, ly);               // row-major pixel index: where this pixel's words go in hit_pix
+	const unsigned pix_x = tx * TILE + lx;
+	const unsigned pix_y = ty * TILE + ly;
 	const bool inside = pix_x < (unsigned)W && pix_y < (unsigned)H;
 	const float pxf = (float)pix_x, pyf = (float)pix_y;
 
@@ -183,7 +188,7 @@ composite_forward_kernel(int W, int H, unsigned gx, const uint2* __restrict__ ra
 #pragma unroll
 		for (int g = 0; g < FWD_GROUPS; g++) {
 			const int j = g * 32 + lane;
-			const uint32_t mine = j < cnt ? masks[j * 8 + warp] : 0u;
+			const uint32_t mine = j < cnt ? warp_word<GS2D_FWD_BLOCK>(masks + j * 8, warp) : 0u;
 			sm.hits[g][tid] = __any_sync(0xffffffffu, mine != 0u) ? transpose32(mine, lane) : 0u;
 			sm.used[g][tid] = 0u;
 		}
@@ -224,8 +229,8 @@ composite_forward_kernel(int W, int H, unsigned gx, const uint2* __restrict__ ra
 		// and the pairs of the footprint masks (they own a gradient-pair slot each)
 #pragma unroll
 		for (int g = 0; g < FWD_GROUPS; g++) {
-			pix_words[(size_t)((b * FWD_GROUPS + g) * 2 + 0) * TILE_PIXELS + tid] = sm.used[g][tid];
-			pix_words[(size_t)((b * FWD_GROUPS + g) * 2 + 1) * TILE_PIXELS + tid] = sm.hits[g][tid];
+			pix_words[(size_t)((b * FWD_GROUPS + g) * 2 + 0) * TILE_PIXELS + ptid] = sm.used[g][tid];
+			pix_words[(size_t)((b * FWD_GROUPS + g) * 2 + 1) * TILE_PIXELS + ptid] = sm.hits[g][tid];
 		}
 	}
 

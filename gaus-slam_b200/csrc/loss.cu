@@ -42,7 +42,7 @@ __device__ __forceinline__ float nan_to_num00(float v, bool& passes)
 __device__ __forceinline__ LossPixel load_pixel(size_t p, size_t HW, const float* __restrict__ color,
                                                 const float* __restrict__ allmap, const float* __restrict__ gt_color,
                                                 const float* __restrict__ gt_depth, int gt_hwc, float eps, float near_,
-                                                float far_)
+                                                float far_, float silmask_th = -1.f)
 {
 	LossPixel px;
 #pragma unroll
@@ -61,6 +61,8 @@ __device__ __forceinline__ LossPixel load_pixel(size_t p, size_t HW, const float
 	px.depth = d;
 	px.dist = nan_to_num00(allmap[6 * HW + p], px.dist_ok);
 	px.mask = (px.gd > 1e-5f) && (d > 1e-5f);   // implies: finite, not an outlier
+	// tracking branch (slam/Loss.py:42-43): nan_to_num(alpha, 0, 0) > silmask_th as well
+	if (silmask_th >= 0.f) px.mask = px.mask && isfinite(A) && (A > silmask_th);
 	return px;
 }
 
@@ -70,11 +72,12 @@ __global__ void __launch_bounds__(LOSS_THREADS)
 mapping_loss_forward_kernel(size_t HW, const float* __restrict__ color, const float* __restrict__ allmap,
                             const float* __restrict__ gt_color, const float* __restrict__ gt_depth, int gt_hwc,
                             float w_color, float w_depth, float w_dist, float eps, float near_, float far_,
+                            int tracking, float silmask_th,
                             float* __restrict__ partials, uint32_t* __restrict__ ticket, float* __restrict__ state)
 {
 	float cnt = 0.f, sc = 0.f, sd = 0.f, sr = 0.f;
 	for (size_t p = (size_t)blockIdx.x * LOSS_THREADS + threadIdx.x; p < HW; p += (size_t)gridDim.x * LOSS_THREADS) {
-		const LossPixel px = load_pixel(p, HW, color, allmap, gt_color, gt_depth, gt_hwc, eps, near_, far_);
+		const LossPixel px = load_pixel(p, HW, color, allmap, gt_color, gt_depth, gt_hwc, eps, near_, far_, tracking ? silmask_th : -1.f);
 		if (px.mask) {
 			cnt += 1.f;
 			sc += fabsf(px.c[0] - px.gc[0]) + fabsf(px.c[1] - px.gc[1]) + fabsf(px.c[2] - px.gc[2]);
@@ -116,8 +119,10 @@ mapping_loss_forward_kernel(size_t HW, const float* __restrict__ color, const fl
 	if (threadIdx.x == 0) {
 		const double n = s_sum[0];
 		// mean over an empty selection is NaN in torch; kept
-		const double loss = (double)w_color * (s_sum[1] / (3.0 * n)) + (double)w_depth * (s_sum[2] / n) +
-		                    (double)w_dist * (s_sum[3] / n);
+		// mapping: masked means (slam/Loss.py:52-58); tracking: masked sums, no distortion term (:46-47)
+		const double loss = tracking ? (double)w_color * s_sum[1] + (double)w_depth * s_sum[2]
+		                             : (double)w_color * (s_sum[1] / (3.0 * n)) + (double)w_depth * (s_sum[2] / n) +
+		                                   (double)w_dist * (s_sum[3] / n);
 		state[0] = (float)loss;
 		state[1] = (float)n;
 		state[2] = (float)s_sum[1];
@@ -131,16 +136,17 @@ __global__ void __launch_bounds__(LOSS_THREADS)
 mapping_loss_backward_kernel(size_t HW, const float* __restrict__ color, const float* __restrict__ allmap,
                              const float* __restrict__ gt_color, const float* __restrict__ gt_depth, int gt_hwc,
                              float w_color, float w_depth, float w_dist, float eps, float near_, float far_,
+                             int tracking, float silmask_th,
                              const float* __restrict__ state, const float* __restrict__ grad_out,
                              float* __restrict__ dL_dcolor, float* __restrict__ dL_dallmap)
 {
 	const float n = state[1];
 	const float g = grad_out ? grad_out[0] : 1.0f;
-	const float gc = n > 0.f ? g * w_color / (3.0f * n) : 0.f;
-	const float gd = n > 0.f ? g * w_depth / n : 0.f;
-	const float gr = n > 0.f ? g * w_dist / n : 0.f;
+	const float gc = tracking ? g * w_color : (n > 0.f ? g * w_color / (3.0f * n) : 0.f);
+	const float gd = tracking ? g * w_depth : (n > 0.f ? g * w_depth / n : 0.f);
+	const float gr = tracking ? 0.f : (n > 0.f ? g * w_dist / n : 0.f);
 	for (size_t p = (size_t)blockIdx.x * LOSS_THREADS + threadIdx.x; p < HW; p += (size_t)gridDim.x * LOSS_THREADS) {
-		const LossPixel px = load_pixel(p, HW, color, allmap, gt_color, gt_depth, gt_hwc, eps, near_, far_);
+		const LossPixel px = load_pixel(p, HW, color, allmap, gt_color, gt_depth, gt_hwc, eps, near_, far_, tracking ? silmask_th : -1.f);
 		float dc[3] = {0.f, 0.f, 0.f}, dD = 0.f, dA = 0.f, dR = 0.f;
 		if (px.mask) {
 #pragma unroll
@@ -204,7 +210,7 @@ int gs2d_mapping_loss_forward(int32_t W, int32_t H, const float* color, const fl
 		ProfScope ps(K_LOSS, st);
 		mapping_loss_forward_kernel<<<loss_blocks(HW), LOSS_THREADS, 0, st>>>(
 			HW, color, allmap, gt_color, gt_depth, gt_color_hwc, lp->w_color, lp->w_depth, lp->w_dist, lp->eps,
-			lp->depth_near, lp->depth_far, partials, ticket, state);
+			lp->depth_near, lp->depth_far, lp->tracking, lp->silmask_th, partials, ticket, state);
 		count_launch();
 	}
 	GS2D_CUDA_OK(cudaGetLastError());
@@ -228,7 +234,7 @@ int gs2d_mapping_loss_backward(int32_t W, int32_t H, const float* color, const f
 		ProfScope ps(K_LOSS, st);
 		mapping_loss_backward_kernel<<<loss_blocks(HW), LOSS_THREADS, 0, st>>>(
 			HW, color, allmap, gt_color, gt_depth, gt_color_hwc, lp->w_color, lp->w_depth, lp->w_dist, lp->eps,
-			lp->depth_near, lp->depth_far, state, grad_loss, dL_dcolor, dL_dallmap);
+			lp->depth_near, lp->depth_far, lp->tracking, lp->silmask_th, state, grad_loss, dL_dcolor, dL_dallmap);
 		count_launch();
 	}
 	GS2D_CUDA_OK(cudaGetLastError());

@@ -25,7 +25,8 @@ namespace gs2d {
 namespace {
 
 constexpr int POSE_THREADS = 256;
-constexpr int POSE_MAX_BLOCKS = 148 * 8;
+constexpr int POSE_MAX_BLOCKS = 148 * 4;
+constexpr int POSE_CHUNKS = 20;           // the last block sums the per-block partials as 12 columns x 20 chunks
 
 struct Pose {
 	float R[9];      // row-major
@@ -180,9 +181,18 @@ __global__ void __launch_bounds__(POSE_THREADS) pose_transform_backward_kernel(
 	__threadfence();
 	// the last block: fixed-order sum of the per-block partials, then the chain rule of the pose parametrisation
 	__shared__ float G[12];
+	__shared__ float red[POSE_CHUNKS][12];
+	if (threadIdx.x < 12 * POSE_CHUNKS) {
+		const unsigned col = threadIdx.x % 12, chunk = threadIdx.x / 12;
+		float v = 0.f;
+		for (unsigned b = chunk; b < gridDim.x; b += POSE_CHUNKS) v += __ldcg(&partials[12 * b + col]);
+		red[chunk][col] = v;
+	}
+	__syncthreads();
 	if (threadIdx.x < 12) {
 		float v = 0.f;
-		for (unsigned b = 0; b < gridDim.x; b++) v += __ldcg(&partials[12 * b + threadIdx.x]);
+#pragma unroll
+		for (int c = 0; c < POSE_CHUNKS; c++) v += red[c][threadIdx.x];
 		G[threadIdx.x] = v;
 	}
 	__syncthreads();

@@ -25,6 +25,9 @@ namespace gs2d {
 
 namespace {
 
+#ifndef GS2D_SCATTER_UNROLL
+#define GS2D_SCATTER_UNROLL 1
+#endif
 constexpr int TS_CAP = 2048;   // instances of a tile sorted in shared memory (16 KB of keys)
 
 // One thread per surfel, like duplicateWithKeys -- but the destination is the tile's own segment.
@@ -39,8 +42,27 @@ scatter_kernel(int P, unsigned gx, const float* __restrict__ depths, const ushor
 	if (idx >= P || tiles_touched[idx] == 0) return;
 	const ushort4 r = rect[idx];
 	const uint64_t word = ((uint64_t)__float_as_uint(depths[idx]) << 32) | (uint32_t)idx;
+#if GS2D_SCATTER_UNROLL
+	// four cursor atomics in flight per thread: the returned slot is only needed by the store that follows
+	const unsigned w = r.z - r.x, cnt = w * (r.w - r.y);
+	for (unsigned e0 = 0; e0 < cnt; e0 += 4) {
+		uint32_t slot[4];
+#pragma unroll
+		for (int k = 0; k < 4; k++) {
+			const unsigned e = e0 + k;
+			if (e < cnt) {
+				const unsigned yy = e / w;
+				slot[k] = atomicAdd(&cursor[(r.y + yy) * gx + r.x + (e - yy * w)], 1u);
+			}
+		}
+#pragma unroll
+		for (int k = 0; k < 4; k++)
+			if (e0 + k < cnt) pairs[slot[k]] = word;
+	}
+#else
 	for (unsigned y = r.y; y < r.w; y++)
 		for (unsigned x = r.x; x < r.z; x++) pairs[atomicAdd(&cursor[y * gx + x], 1u)] = word;
+#endif
 }
 
 // Ascending sort of keys[0, n) by 256 threads in memory (the fallback for tiles beyond TS_CAP): bitonic network in its "every exchange puts the smaller key at

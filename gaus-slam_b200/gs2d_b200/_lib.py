@@ -58,7 +58,7 @@ class StateView(C.Structure):
 # name -> (restype, argtypes); also the list of symbols the header declares (checked by tests).
 class LossParams(C.Structure):
     _fields_ = [("w_color", C.c_float), ("w_depth", C.c_float), ("w_dist", C.c_float), ("eps", C.c_float),
-                ("depth_near", C.c_float), ("depth_far", C.c_float)]
+                ("depth_near", C.c_float), ("depth_far", C.c_float), ("tracking", C.c_int32), ("silmask_th", C.c_float)]
 
 
 class MapState(C.Structure):

@@ -84,5 +84,18 @@ def mapping_loss(color, allmap, gt_color, gt_depth, weights=(0.5, 1.0, 0.1), eps
     call of backward: the mask count of the forward pass is kept in a per-stream scratch."""
     if use_edge_growth or use_normal_loss:
         raise NotImplementedError("only the default mapping loss (no edge growth, no normal loss) is built")
-    params = (float(weights[0]), float(weights[1]), float(weights[2]), float(eps), float(depth_near), float(depth_far))
+    params = (float(weights[0]), float(weights[1]), float(weights[2]), float(eps), float(depth_near), float(depth_far),
+              0, 0.0)
+    return _MappingLoss.apply(color, allmap, gt_color, gt_depth, params)
+
+
+def tracking_loss(color, allmap, gt_color, gt_depth, weights=(0.5, 1.0), eps=1e-6, depth_near=1e-2, depth_far=1e2,
+                  silmask_th=0.9, ignore_outliners=False, use_normal_loss=False):
+    """The tracking branch of get_loss (slam/Loss.py:35-47) with the shipped defaults (ignore_outliners = False,
+    use_normal_loss = False): mask = depth mask & nan_to_num(alpha) > silmask_th, loss = weights[0] * SUM |color -
+    gt_color| + weights[1] * SUM |depth - gt_depth| over the mask.  Same two kernels as mapping_loss."""
+    if ignore_outliners or use_normal_loss:
+        raise NotImplementedError("only the default tracking loss (no median outlier mask, no normal loss) is built")
+    params = (float(weights[0]), float(weights[1]), 0.0, float(eps), float(depth_near), float(depth_far), 1,
+              float(silmask_th))
     return _MappingLoss.apply(color, allmap, gt_color, gt_depth, params)

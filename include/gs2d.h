@@ -242,6 +242,10 @@ typedef struct gs2d_loss_params {
 	float w_color, w_depth, w_dist;   /* configs: 0.5, 1.0, 0.1                                  */
 	float eps;                        /* render.eps = 1e-6                                        */
 	float depth_near, depth_far;      /* render.depth_near = 1e-2, render.depth_far = 1e2         */
+	int32_t tracking;                 /* 1: the tracking branch (slam/Loss.py:35-47, ignore_outliners = False):
+	                                   * mask also needs nan_to_num(alpha) > silmask_th; loss = w_color * SUM |dc|
+	                                   * + w_depth * SUM |dd| over the mask (sums, not means; no distortion term) */
+	float silmask_th;                 /* loss.silmask_th = 0.9 (tracking only)                    */
 } gs2d_loss_params;
 
 size_t gs2d_mapping_loss_scratch_bytes(int32_t image_width, int32_t image_height);

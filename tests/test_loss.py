@@ -101,6 +101,49 @@ def test_fused_kernels_equal_the_reference_loss(H, W, seed, hwc):
         assert float(a.grad[2:6].abs().max()) == 0.0
 
 
+def _torch_tracking(color, allmap, gt_color, gt_depth, dev="cpu"):
+    c = torch.tensor(color, device=dev, requires_grad=True)
+    a = torch.tensor(allmap, device=dev, requires_grad=True)
+    gc = torch.tensor(gt_color, device=dev).permute(1, 2, 0).contiguous()
+    gd = torch.tensor(gt_depth, device=dev)[..., None]
+    loss = loss_ref.tracking_loss_torch(c, a, gc, gd)
+    loss.backward()
+    return float(loss.detach()), c.grad.cpu().numpy(), a.grad.cpu().numpy()
+
+
+@pytest.mark.parametrize("H,W,seed", [(24, 40, 0), (33, 17, 4)])
+def test_tracking_restatement_equals_torch_transliteration(H, W, seed):
+    x = _inputs(H, W, seed)
+    x[1][1][np.random.default_rng(seed).uniform(size=(H, W)) < 0.5] = 0.95      # half the pixels pass the silhouette mask
+    l0, dc0, da0 = _torch_tracking(*x)
+    l1, dc1, da1 = loss_ref.mapping_loss_numpy(*x, weights=(0.5, 1.0, 0.0), tracking=True)
+    assert l1 > 0 and abs(l0 - l1) <= 1e-5 * abs(l1)
+    assert _close(dc1, dc0, 1e-6) and _close(da1, da0, 1e-5)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("H,W,seed,hwc", [(24, 40, 0, False), (680, 1200, 3, True)])
+def test_fused_tracking_loss_equals_the_reference_loss(H, W, seed, hwc):
+    from gs2d_b200 import loss as gl
+    dev = torch.device("cuda:0")
+    x = _inputs(H, W, seed)
+    x[1][1][np.random.default_rng(seed).uniform(size=(H, W)) < 0.5] = 0.95
+    color, allmap, gt_color, gt_depth = x
+    l_np, dc_np, da_np = loss_ref.mapping_loss_numpy(*x, weights=(0.5, 1.0, 0.0), tracking=True)
+    l_t, dc_t, da_t = _torch_tracking(*x, dev=dev)
+    c = torch.tensor(color, device=dev, requires_grad=True)
+    a = torch.tensor(allmap, device=dev, requires_grad=True)
+    gc = torch.tensor(gt_color, device=dev)
+    gc = gc.permute(1, 2, 0).contiguous() if hwc else gc
+    loss = gl.tracking_loss(c, a, gc, torch.tensor(gt_depth, device=dev))
+    loss.backward()
+    assert abs(float(loss.detach()) - l_np) <= 1e-5 * abs(l_np) and abs(float(loss.detach()) - l_t) <= 2e-5 * abs(l_t)
+    for got, want in ((c.grad, dc_np), (a.grad, da_np), (c.grad, dc_t), (a.grad, da_t)):
+        assert _close(got.cpu().numpy(), want, 2e-6)
+    with pytest.raises(NotImplementedError):
+        gl.tracking_loss(c, a, gc, torch.tensor(gt_depth, device=dev), ignore_outliners=True)
+
+
 @pytest.mark.gpu
 def test_fused_loss_rejects_what_is_not_built():
     from gs2d_b200 import loss as gl
