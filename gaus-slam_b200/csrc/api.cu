@@ -254,10 +254,7 @@ int gs2d_forward_render_scattered(const gs2d_settings* s, const gs2d_inputs* in,
 	if (!scattered_pairs) GS2D_TRY(launch_scatter(*s, g, im, pairs, false, I, st));
 	GS2D_TRY(launch_tile_sort(*s, g, im, b, pairs, I, st));
 	GS2D_TRY(debug_sync(*s, st));
-	{
-		ProfScope ps(K_MEMSET, st);
-		GS2D_CUDA_OK(cudaMemsetAsync(b.pair_status, 0, (size_t)((char*)(b.pair_counters + 8) - (char*)b.pair_status), st));
-	}
+	// (pair_status / pair_counters were zeroed by tile_sort_kernel)
 	GS2D_TRY(launch_scan_u32(b.hit_count, b.pair_incl, I, b.pair_status, b.pair_counters, st, false));
 	if (num_pairs_host)   // 8 bytes: counters[1] = total, counters[2] = 0 -> a whole int64, before the compositing kernel
 		GS2D_CUDA_OK(cudaMemcpyAsync(num_pairs_host, b.pair_counters + 1, 2 * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));

@@ -158,7 +158,7 @@ int launch_scatter(const gs2d_settings& s, const GeomState& g, const ImageState&
                    int64_t capacity, cudaStream_t st);
 int launch_tile_sort(const gs2d_settings& s, const GeomState& g, const ImageState& im, const BinningState& b,
                      uint64_t* pairs, int64_t I, cudaStream_t st);
-// zeroes [scan_status, counters + 8) itself; one extra block turns the per-tile counts into ranges + cursors
+// [scan_status, counters + 8) must be zero (preprocess_forward_kernel clears them); one extra block turns the per-tile counts into ranges + cursors
 int launch_scan_tiles(const GeomState& g, int P, cudaStream_t st, int tiles, const uint32_t* tile_count,
                       uint32_t* ranges, uint32_t* tile_cursor);
 int launch_scan_u32(const uint32_t* in, uint32_t* out, long long n, uint64_t* status, uint32_t* counters,

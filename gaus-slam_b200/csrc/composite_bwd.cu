@@ -32,6 +32,9 @@ namespace gs2d {
 
 namespace {
 
+#ifndef GS2D_BWD_DISCARD
+#define GS2D_BWD_DISCARD 1
+#endif
 constexpr int BWD_BATCH = 128;
 constexpr int BWD_STAGES = 2;
 
@@ -412,6 +415,19 @@ composite_backward_pixels_kernel(int W, int H, unsigned gx, const uint2* __restr
 			dst[0] = g[0]; dst[1] = g[1]; dst[2] = g[2];
 		}
 	}
+#if GS2D_BWD_DISCARD
+	// The tile's pair slots are dead now (written in phase A, read back once in phase B): tell L2 to drop the lines
+	// that lie wholly inside this tile's slot range instead of writing them back to HBM (16 B x ~15 M pairs a frame).
+	__syncthreads();
+	{
+		const size_t gi0 = (size_t)range.x;
+		const uint32_t t0 = gi0 ? pair_incl[gi0 - 1] : 0u, t1 = pair_incl[gi0 + n_done - 1];
+		const uintptr_t a0 = (reinterpret_cast<uintptr_t>(slots + t0) + 127) & ~(uintptr_t)127;
+		const uintptr_t a1 = reinterpret_cast<uintptr_t>(slots + t1) & ~(uintptr_t)127;
+		for (uintptr_t a = a0 + (uintptr_t)tid * 128; a < a1; a += 256 * 128)
+			asm volatile("discard.global.L2 [%0], 128;" ::"l"(a) : "memory");
+	}
+#endif
 }
 
 }  // namespace

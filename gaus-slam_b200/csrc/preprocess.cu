@@ -109,15 +109,25 @@ preprocess_forward_kernel(int P, int D, int M,
 	const float* __restrict__ campos, int W, int H, unsigned gx, unsigned gy, int prefiltered,
 	int* __restrict__ radii, float* __restrict__ depths, float4* __restrict__ splat,
 	ushort4* __restrict__ rect, float4* __restrict__ cull, uint32_t* __restrict__ tiles_touched,
-	uint32_t* __restrict__ tile_count)
+	uint32_t* __restrict__ tile_count, uint32_t* __restrict__ zero_words, int n_zero_words)
 {
 	int idx = blockIdx.x * blockDim.x + threadIdx.x;
+	// status words + counters of the tiles_touched scan that follows (instead of a memset launch)
+	for (int i = idx; i < n_zero_words; i += gridDim.x * blockDim.x) zero_words[i] = 0u;
 	if (idx >= P) return;
 
 	radii[idx] = 0;
 	tiles_touched[idx] = 0;
 
 	const float3 p_orig = make_float3(means3D[3 * idx], means3D[3 * idx + 1], means3D[3 * idx + 2]);
+	// all per-surfel inputs are requested up front (one memory round trip; the kernel is latency-bound)
+	const bool own_transform = transMat_precomp == nullptr;
+	const float2 scale_in = own_transform ? scales[idx] : make_float2(1.f, 1.f);
+	const float4 rot_in = own_transform ? rotations[idx] : make_float4(1.f, 0.f, 0.f, 0.f);
+	const float opacity = opacities[idx];
+	float3 rgb = make_float3(0.f, 0.f, 0.f);
+	if (colors_precomp != nullptr)
+		rgb = make_float3(colors_precomp[3 * idx], colors_precomp[3 * idx + 1], colors_precomp[3 * idx + 2]);
 	const float3 p_view = xform_point_exact(p_orig, viewmatrix);
 	if (p_view.z <= 0.2f) {
 		if (prefiltered) __trap();
@@ -126,7 +136,7 @@ preprocess_forward_kernel(int P, int D, int M,
 
 	float3 Tu, Tv, Tw, normal;
 	if (transMat_precomp == nullptr) {
-		const SplatFrame fr = splat_frame_exact(p_orig, scales[idx], scale_modifier, rotations[idx], projmatrix, W, H);
+		const SplatFrame fr = splat_frame_exact(p_orig, scale_in, scale_modifier, rot_in, projmatrix, W, H);
 		Tu = fr.Tu; Tv = fr.Tv; Tw = fr.Tw;
 		normal = xform_vec_exact(fr.L2, viewmatrix);
 	} else {
@@ -152,15 +162,11 @@ preprocess_forward_kernel(int P, int D, int M,
 	tile_rect_exact(centre.x, centre.y, (int)radius, gx, gy, rmin, rmax);
 	if ((rmax.x - rmin.x) * (rmax.y - rmin.y) == 0) return;
 
-	float3 rgb;
 	if (colors_precomp == nullptr) {
 		float3 cp = make_float3(campos[0], campos[1], campos[2]);
 		rgb = sh_to_rgb(idx, D, M, p_orig, cp, shs, clamped);
-	} else {
-		rgb = make_float3(colors_precomp[3 * idx], colors_precomp[3 * idx + 1], colors_precomp[3 * idx + 2]);
 	}
 
-	const float opacity = opacities[idx];
 	depths[idx] = p_view.z;
 	radii[idx] = (int)radius;
 	float4* rec = splat + 5 * (size_t)idx;
@@ -324,7 +330,8 @@ int launch_preprocess_forward(const gs2d_settings& s, const gs2d_inputs& in, con
 			(const float4*)in.rotations, in.opacities, in.shs, g.clamped, in.transMat_precomp,
 			in.colors_precomp, in.viewmatrix, in.projmatrix, in.campos, s.image_width, s.image_height,
 			gx, gy, s.prefiltered, radii, g.depths, (float4*)g.splat, (ushort4*)g.rect, (float4*)g.cull,
-			g.tiles_touched, tile_count);
+			g.tiles_touched, tile_count, (uint32_t*)g.scan_status,
+			(int)(((char*)(g.counters + 8) - (char*)g.scan_status) / sizeof(uint32_t)));
 		count_launch();
 	}
 	GS2D_CUDA_OK(cudaGetLastError());
@@ -356,11 +363,7 @@ int launch_scan_u32(const uint32_t* in, uint32_t* out, long long n, uint64_t* st
 int launch_scan_tiles(const GeomState& g, int P, cudaStream_t st, int tiles, const uint32_t* tile_count,
                       uint32_t* ranges, uint32_t* tile_cursor)
 {
-	// status words and counters are adjacent in the geom buffer: one memset
-	{
-		ProfScope ps(K_MEMSET, st);
-		GS2D_CUDA_OK(cudaMemsetAsync(g.scan_status, 0, (size_t)((char*)(g.counters + 8) - (char*)g.scan_status), st));
-	}
+	// status words and counters (adjacent in the geom buffer) were zeroed by preprocess_forward_kernel
 	return launch_scan_u32(g.tiles_touched, g.point_offsets, P, g.scan_status, g.counters, st, false, tiles, tile_count,
 	                       ranges, tile_cursor);
 }

@@ -160,11 +160,15 @@ tile_sort_kernel(int W, int H, unsigned gx, const uint2* __restrict__ ranges, ui
                  const float4* __restrict__ splat, const ushort4* __restrict__ rect,
                  const float4* __restrict__ cull, const uint32_t* __restrict__ offsets,
                  uint64_t* __restrict__ keys_sorted, uint32_t* __restrict__ point_list, float4* instances,
-                 uint32_t* __restrict__ hit_words, uint32_t* __restrict__ hit_count)
+                 uint32_t* __restrict__ hit_words, uint32_t* __restrict__ hit_count,
+                 uint32_t* __restrict__ zero_words, int n_zero_words)
 {
 	__shared__ uint64_t s_keys[TS_CAP];
 	const int tid = threadIdx.x, lane = tid & 31;
 	const unsigned tile = blockIdx.x;
+	// status words + counters of the pair-count scan that follows (instead of a memset launch)
+	if (tile == 0)
+		for (int i = tid; i < n_zero_words; i += 256) zero_words[i] = 0u;
 	const uint2 range = ranges[tile];
 	const int n = (int)(range.y - range.x);
 	if (n == 0) return;
@@ -249,7 +253,9 @@ int launch_tile_sort(const gs2d_settings& s, const GeomState& g, const ImageStat
 	ProfScope ps(K_TILE_SORT, st);
 	tile_sort_kernel<<<tiles, 256, 0, st>>>(W, H, gx, (const uint2*)im.ranges, pairs, (const float4*)g.splat,
 	                                        (const ushort4*)g.rect, (const float4*)g.cull, g.point_offsets, b.keys_b,
-	                                        b.vals_b, (float4*)b.instances, b.hit_inst, b.hit_count);
+	                                        b.vals_b, (float4*)b.instances, b.hit_inst, b.hit_count,
+	                                        (uint32_t*)b.pair_status,
+	                                        (int)(((char*)(b.pair_counters + 8) - (char*)b.pair_status) / sizeof(uint32_t)));
 	count_launch();
 	GS2D_CUDA_OK(cudaGetLastError());
 	return GS2D_OK;
