@@ -8,7 +8,8 @@
 //   * one CTA per 16x16 tile, one thread per pixel, warp k owns tile rows 2k and 2k+1;
 //   * the tile's instance records (80 B each, sorted, contiguous in HBM) and their footprint masks
 //     (32 B each, footprint.cu) are staged by TMA bulk copies, 128 instances per batch, into a
-//     two-stage shared-memory ring guarded by mbarriers: batch b+1 lands while batch b is blended;
+//     three-stage shared-memory ring guarded by mbarriers; the first three batches are requested at once and every
+//     thread waits on the mbarrier itself, so lists of up to 384 instances need no CTA barrier at all;
 //   * per batch the instance-major footprint masks are transposed into per-PIXEL hit words with warp
 //     ballots (registers only: word k of a mask is exactly warp k's 32 pixels), and every pixel thread
 //     then walks only ITS OWN set bits in depth order.  A pixel visits ~17 instances per tile instead of ~250; lanes of a
@@ -28,7 +29,10 @@ namespace {
 #endif
 constexpr int FWD_BATCH = GS2D_FWD_BATCH;   // instances per staged batch (a multiple of 32)
 constexpr int FWD_GROUPS = FWD_BATCH / 32;  // hit words per pixel per batch
-constexpr int FWD_STAGES = 2;
+#ifndef GS2D_FWD_STAGES
+#define GS2D_FWD_STAGES 3
+#endif
+constexpr int FWD_STAGES = GS2D_FWD_STAGES;
 static_assert(FWD_BATCH % 32 == 0 && FWD_BATCH / 32 <= HIT_PIX_PAD, "hit_pix padding");
 
 struct FwdSmem {
@@ -160,25 +164,30 @@ composite_forward_kernel(int W, int H, unsigned gx, const uint2* __restrict__ ra
 		tma_load_1d(&s_rec[stage][0], tile_rec + 5 * (size_t)b * FWD_BATCH, cnt * 80u, &s_bar[stage]);
 		tma_load_1d(&s_mask[stage][0], tile_mask + 8 * (size_t)b * FWD_BATCH, cnt * 32u, &s_bar[stage]);
 	};
-	if (tid == 0 && nb > 0) issue(0, 0);
+	// The first FWD_STAGES batches are requested at once: tiles of up to FWD_STAGES * FWD_BATCH instances (most of
+	// them) run without a single CTA barrier -- every thread waits on the batch's mbarrier itself, so the 8 warps of
+	// a tile drift apart freely instead of waiting for the slowest one at every batch (the barrier was the top stall
+	// of this kernel).  Longer lists reuse the stages: one barrier per batch, which is also the CTA-wide exit vote.
+	if (tid == 0)
+		for (int b = 0; b < min(nb, FWD_STAGES); b++) issue(b, b);
 
 	uint32_t* pix_words = hit_pix + ((size_t)(range.x >> 5) + HIT_PIX_PAD * (size_t)tile) * 2 * TILE_PIXELS;
 
 	PixelFwd px;
 	bool done = !inside;
+	int first_unwaited = 0;       // batches below this index have been waited for by every thread
 
 	for (int b = 0; b < nb; b++) {
-		const int stage = b & 1;
-		const uint32_t parity = (uint32_t)(b >> 1) & 1u;
-		// everyone is finished with batch b-1 (its stage and s_hit may be reused); CTA-wide exit vote
-		const int num_done = __syncthreads_count(done);
-		if (num_done == TILE_PIXELS) {
-			mbar_wait(&s_bar[stage], parity);   // do not exit with a bulk copy in flight
-			break;
+		const int stage = b % FWD_STAGES;
+		const uint32_t parity = (uint32_t)(b / FWD_STAGES) & 1u;
+		if (b >= 1 && b + FWD_STAGES - 1 < nb) {
+			// batch b-1 is consumed by everyone -> its stage takes batch b + FWD_STAGES - 1; CTA-wide exit vote
+			const int num_done = __syncthreads_count(done);
+			if (num_done == TILE_PIXELS) break;
+			if (tid == 0) issue(b + FWD_STAGES - 1, (b + FWD_STAGES - 1) % FWD_STAGES);
 		}
-		if (tid == 0 && b + 1 < nb) issue(b + 1, stage ^ 1);
-		if (warp == 0) mbar_wait(&s_bar[stage], parity);
-		__syncthreads();   // warp 0 observed the copy; the barrier publishes it to the other warps
+		mbar_wait(&s_bar[stage], parity);
+		first_unwaited = b + 1;
 
 		const int cnt = min(n - b * FWD_BATCH, FWD_BATCH);
 		const float4* recs = &s_rec[stage][0];
@@ -233,6 +242,11 @@ composite_forward_kernel(int W, int H, unsigned gx, const uint2* __restrict__ ra
 			pix_words[(size_t)((b * FWD_GROUPS + g) * 2 + 1) * TILE_PIXELS + ptid] = sm.hits[g][tid];
 		}
 	}
+
+	// early exit: no bulk copy may still be in flight when the CTA retires (requested but never consumed batches)
+	if (tid == 0)
+		for (int bb = first_unwaited; bb < min(nb, first_unwaited + FWD_STAGES - 1); bb++)
+			mbar_wait(&s_bar[bb % FWD_STAGES], (uint32_t)(bb / FWD_STAGES) & 1u);
 
 	if (inside) {
 		const size_t HW = (size_t)H * W;
