@@ -35,6 +35,9 @@ namespace {
 #ifndef GS2D_BWD_DISCARD
 #define GS2D_BWD_DISCARD 1
 #endif
+#ifndef GS2D_BWD_PREFETCH
+#define GS2D_BWD_PREFETCH 1
+#endif
 constexpr int BWD_BATCH = 128;
 constexpr int BWD_STAGES = 2;
 
@@ -400,8 +403,17 @@ composite_backward_pixels_kernel(int W, int H, unsigned gx, const uint2* __restr
 			row = __float_as_uint(rec[4].w);
 			const size_t gi = (size_t)range.x + q;
 			const uint32_t s0 = gi ? pair_incl[gi - 1] : 0u, s1 = pair_incl[gi];
+#if GS2D_BWD_PREFETCH
+			// the next slot is requested before the current one is worked on (phase B waits on L2 otherwise)
+			float4 nx = (s0 + gl < s1) ? slots[s0 + gl] : make_float4(0.f, 0.f, 0.f, __int_as_float(-1));
+#endif
 			for (uint32_t k = s0 + gl; k < s1; k += 8) {
+#if GS2D_BWD_PREFETCH
+				const float4 sl = nx;
+				if (k + 8 < s1) nx = slots[k + 8];
+#else
 				const float4 sl = slots[k];
+#endif
 				const int p = __float_as_int(sl.w);
 				if (p >= 0)
 					instance_step(r0, r1, r2, (float)(tx * TILE + thread_lx<GS2D_BWD_BLOCK>(p)), (float)(ty * TILE + thread_ly<GS2D_BWD_BLOCK>(p)), sl.x, sl.y,
