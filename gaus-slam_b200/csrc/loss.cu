@@ -109,10 +109,19 @@ mapping_loss_forward_kernel(size_t HW, const float* __restrict__ color, const fl
 	__syncthreads();
 	if (!s_last) return;
 	// last block: add the per-block partials in block order (deterministic), in double
+	// (4 columns x 64 chunks in parallel, then the chunks in order: the order of additions is fixed)
 	__shared__ double s_sum[4];
+	__shared__ double s_chunk[LOSS_THREADS / 4][4];
+	{
+		const unsigned col = threadIdx.x & 3, chunk = threadIdx.x >> 2;
+		double t = 0.0;
+		for (unsigned b = chunk; b < gridDim.x; b += LOSS_THREADS / 4) t += (double)__ldcg(&partials[4 * b + col]);
+		s_chunk[chunk][col] = t;
+	}
+	__syncthreads();
 	if (threadIdx.x < 4) {
 		double t = 0.0;
-		for (unsigned b = 0; b < gridDim.x; b++) t += (double)__ldcg(&partials[4 * b + threadIdx.x]);
+		for (int c = 0; c < LOSS_THREADS / 4; c++) t += s_chunk[c][threadIdx.x];
 		s_sum[threadIdx.x] = t;
 	}
 	__syncthreads();
