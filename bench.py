@@ -363,6 +363,16 @@ def main():
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     multi = world > 1 and a.impl == "b200"
+    if world > 1:
+        # a multi-rank run that does not finish (a lost rank, a mismatched collective) must not block the box:
+        # after GS2D_BENCH_WATCHDOG_S seconds every rank gives up, rank 0 says so on stdout
+        def _watchdog(limit=float(os.environ.get("GS2D_BENCH_WATCHDOG_S", "420"))):
+            time.sleep(limit)
+            if rank == 0:
+                print(json.dumps({"metric": METRIC, "value": None, "unit": UNIT, "n_gpus": world,
+                                  "error": f"bench did not finish within {limit:.0f} s (watchdog)"}), flush=True)
+            os._exit(3)
+        threading.Thread(target=_watchdog, daemon=True).start()
     if multi:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=dev)
@@ -382,7 +392,9 @@ def main():
     if multi and a.impl == "b200":
         # From 4 ranks on, the buffer lives in symmetric memory and is reduced IN the NVSwitch by libgs2d's own
         # multimem kernel (csrc/collective.cu); with 2 ranks NCCL's direct exchange is as fast.
-        want = os.environ.get("GS2D_ALLREDUCE", "multimem" if world >= 4 else "nccl")
+        # NCCL is the default: the in-switch kernel is opt-in (GS2D_ALLREDUCE=multimem) until the bench has been
+        # re-validated with it at 4 and 8 ranks
+        want = os.environ.get("GS2D_ALLREDUCE", "nccl")
         sym = mapping.symmetric_gradient_buffer(P, dev) if want == "multimem" else None
         if sym is not None:
             flat = sym
@@ -394,9 +406,9 @@ def main():
     def view_of(step):
         return wl["sets"][mapping.view_of(step, rank, world if multi else 1, V)]
 
-    def step_resident(step):
+    def step_resident(step, collective=True):
         color, others, g = arm.forward_backward(view_of(step))
-        if multi:
+        if multi and collective:
             if grad_path["zero_copy"] is None:
                 grad_path["zero_copy"] = mapping.grads_alias_flat(g, flat)
             mapping.allreduce_map_gradient(mapping.pack_grads(g, flat))
@@ -432,7 +444,8 @@ def main():
     t_spin = time.monotonic()
     i = 0
     while time.monotonic() - t_spin < 0.5:
-        step_resident(i)
+        # local work only: the number of spin-up steps is time-based and differs between ranks, so no collective here
+        step_resident(i, collective=False)
         i += 1
         if i % 8 == 0:
             torch.cuda.synchronize()
@@ -564,7 +577,7 @@ def main():
                     slots[sl][k].copy_(v, non_blocking=True)
                 ready[sl].record(copy_stream)
 
-        def step_e2e(step):
+        def step_e2e(step, collective=True):
             sl = step & 1
             cur = torch.cuda.current_stream(dev)
             cur.wait_event(ready[sl])
@@ -579,7 +592,7 @@ def main():
                                         rotations=params["rotations"])
             loss = loss_fn(color, allmap, s["gt_color"], s["gt_depth"])
             loss.backward()
-            if multi:
+            if multi and collective:
                 mapping.allreduce_map_gradient(mapping.pack_grads({k: params[k].grad for k in order}, flat))
             freed[sl].record(cur)
             loss_host[sl].copy_(loss.detach().reshape(1), non_blocking=True)
@@ -593,7 +606,7 @@ def main():
         prefetch(0)
         t_spin = time.monotonic()       # spin-up (graph capture above left the GPU idle), then the W warm-up steps
         while time.monotonic() - t_spin < 0.3:
-            step_e2e(0)
+            step_e2e(0, collective=False)      # time-based count: local work only (see the spin-up above)
         for i in range(a.warmup):
             step_e2e(i)
         read_pending_loss()
