@@ -390,9 +390,8 @@ def main():
     from gs2d_b200 import mapping
     grad_path = {"zero_copy": None, "collective": "NCCL all-reduce"}
     if multi and a.impl == "b200":
-        # From 4 ranks on, the buffer lives in symmetric memory and is reduced IN the NVSwitch by libgs2d's own
-        # multimem kernel (csrc/collective.cu); with 2 ranks NCCL's direct exchange is as fast.
-        # NCCL is the default: the in-switch kernel is opt-in (GS2D_ALLREDUCE=multimem) until the bench has been
+        # With GS2D_ALLREDUCE=multimem the buffer lives in symmetric memory and is reduced IN the NVSwitch by libgs2d's
+        # own multimem kernel (csrc/collective.cu).  NCCL is the default: the in-switch kernel is opt-in (GS2D_ALLREDUCE=multimem) until the bench has been
         # re-validated with it at 4 and 8 ranks
         want = os.environ.get("GS2D_ALLREDUCE", "nccl")
         sym = mapping.symmetric_gradient_buffer(P, dev) if want == "multimem" else None
