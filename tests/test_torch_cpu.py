@@ -1,0 +1,79 @@
+"""CPU: the pure-PyTorch transliteration of the reference rasterizer (oracle/torch_cpu.py, forward + hand-written
+backward) against the golden fixtures of the UNMODIFIED reference CUDA rasterizer (tests/golden/*.npz) and against
+the C restatement.  Plain fp32 torch ops do not reproduce the compiled kernel's FMA placement, so a bounding box may
+round differently once in a while: instance lists are compared exactly where they have the same length and otherwise
+only by count (<= 0.1 %), images and gradients at the oracle tolerances of tests/compare.py."""
+import numpy as np
+import pytest
+
+import cases
+import compare
+import cpu as O
+import torch_cpu as T
+
+# the golden cases that use the call pattern of gaus-slam (colors_precomp, scales + rotations, no SH)
+TORCH_CASES = [n for n in cases.GOLDEN_CASES if n not in ("sh_deg2", "transmat_pre")]
+
+
+def _np(d):
+    return {k: (v.numpy() if hasattr(v, "numpy") else v) for k, v in d.items()}
+
+
+def _run(mod, case):
+    a = (case["means3D"], case["opacities"], case["viewmatrix"], case["projmatrix"], case["W"], case["H"], case["bg"])
+    st = mod.forward(*a, scales=case["scales"], rotations=case["rotations"], colors=case["colors"], campos=case["campos"],
+                     scale_modifier=float(case["scale_modifier"]), use_sa=case["use_sa"])
+    g = mod.backward(st, case["means3D"], case["viewmatrix"], case["projmatrix"], case["W"], case["H"],
+                     float(case["tanfovx"]), float(case["tanfovy"]), case["bg"], case["dL_dcolor"], case["dL_dothers"],
+                     scales=case["scales"], rotations=case["rotations"], campos=case["campos"], use_sa=case["use_sa"])
+    out = _np(st)
+    out.update({"grad_" + k: v for k, v in _np(g).items()})
+    return out
+
+
+def _check(got, ref, use_sa):
+    n_ref, n_got = int(ref["num_rendered"]), int(got["num_rendered"])
+    assert abs(n_got - n_ref) <= max(1, n_ref // 1000), (n_got, n_ref)
+    if n_got == n_ref and n_ref:
+        assert np.array_equal(np.asarray(got["point_list"], np.int64), np.asarray(ref["point_list"], np.int64))
+        assert np.array_equal(np.asarray(got["ranges"], np.int64), np.asarray(ref["ranges"], np.int64))
+        assert np.array_equal(np.asarray(got["radii"], np.int64), np.asarray(ref["radii"], np.int64))
+    # depth / variance channels at the loose oracle tolerance in both modes: they are differences of O(10) terms and
+    # plain torch ops round them differently from the compiled kernel's fused multiply-adds
+    fails = compare.check_images_oracle(got, ref, True)
+    # gradients: 1e-3 (BASELINE bar) without SA; with SA the confidence exp(-(d - md)^2 / (4 var)) amplifies fp32
+    # rounding of var ~ 1e-6 (tests/compare.py) -- whole-tensor error 1e-2, single worst element 3e-2 of the largest
+    for k in compare.GRADS:
+        a, b = got.get("grad_" + k), ref.get("grad_" + k)
+        if a is None or b is None or np.asarray(b).size == 0:
+            continue
+        r, e = compare.grad_rel(a, b), compare.grad_elem_rel(a, b)
+        if not (r <= (1e-2 if use_sa else 1e-3) and e <= (3e-2 if use_sa else 1e-3)):
+            fails.append(f"grad_{k}: rel_l2 {r:.3e}, worst element/absmax {e:.3e}")
+    assert not fails, "\n".join(fails)
+
+
+@pytest.mark.parametrize("name", TORCH_CASES)
+def test_torch_transliteration_matches_reference_outputs(name):
+    g = cases.load_golden(name)
+    assert g is not None, f"tests/golden/{name}.npz missing"
+    case = cases.case_from_golden(g)
+    ref = {k[4:]: v for k, v in g.items() if k.startswith("ref_")}
+    _check(_run(T, case), ref, case["use_sa"])
+
+
+@pytest.mark.parametrize("name", ["room_sa", "room_dist"])
+def test_torch_transliteration_matches_c_restatement(name):
+    case = getattr(cases, name)()
+    want = _run(O, case)
+    want["transMat"] = want["transMat_used"]
+    _check(_run(T, case), want, case["use_sa"])
+
+
+def test_cold_branches_are_refused():
+    case = cases.room_sa()
+    a = (case["means3D"], case["opacities"], case["viewmatrix"], case["projmatrix"], case["W"], case["H"], case["bg"])
+    with pytest.raises(NotImplementedError):
+        T.forward(*a, scales=case["scales"], rotations=case["rotations"], colors=None, shs=np.zeros((3000, 1, 3), np.float32))
+    with pytest.raises(NotImplementedError):
+        T.forward(*a, transMat=np.zeros((3000, 9), np.float32), colors=case["colors"])
