@@ -50,6 +50,7 @@ def parse_args():
     ap.add_argument("--torch-loss", action="store_true", help="e2e of the product with the torch-ops loss instead of the fused kernels")
     ap.add_argument("--no-stats", action="store_true",
                     help="skip the (untimed) scene-statistics renders: for ncu launch lists of the timed steps only")
+    ap.add_argument("--no-torch-cpu", action="store_true", help="skip the pure-PyTorch CPU transliteration in cpu_baseline")
     ap.add_argument("--no-loops", action="store_true",
                     help="skip the whole-iteration loops (mapping_iteration / tracking_iteration keys, bench_loops.py)")
     ap.add_argument("--clock-period-ms", type=int, default=100, help="nvidia-smi sampling period; 0 = no sampling (diagnosis)")
@@ -327,7 +328,7 @@ class ReferenceArm:
 # ----------------------------------------------------------------------------------------------------
 # CPU baseline: the C restatement (oracle/gs2d_oracle.c, OpenMP over tiles/surfels) on the host cores
 # ----------------------------------------------------------------------------------------------------
-def cpu_baseline(wl, frames):
+def cpu_baseline(wl, frames, torch_cpu=True):
     sys.path.insert(0, os.path.join(ROOT, "oracle"))
     import cpu as O
     sc, cam = wl["scene"], wl["cams"][0]
@@ -342,10 +343,50 @@ def cpu_baseline(wl, frames):
         O.backward(st, sc["means3D"], cam.viewmatrix, cam.projmatrix, W, H, cam.tanfovx, cam.tanfovy, bg, gc, go,
                    scales=sc["scales"], rotations=sc["rotations"], campos=cam.campos)
     dt = time.perf_counter() - t0
-    return {"value": frames / dt, "unit": UNIT, "cores": O.num_threads(), "kind": "port",
-            "sample": f"{frames} whole fwd+bwd frame(s) of view 0 of the same workload (P={wl['P']}, {W}x{H}, "
-                      f"I={int(st['num_rendered'])}), C restatement oracle/gs2d_oracle.c, OpenMP",
-            "seconds": dt}
+    out = {"value": frames / dt, "unit": UNIT, "cores": O.num_threads(), "kind": "port",
+           "sample": f"{frames} whole fwd+bwd frame(s) of view 0 of the same workload (P={wl['P']}, {W}x{H}, "
+                     f"I={int(st['num_rendered'])}), C restatement oracle/gs2d_oracle.c, OpenMP",
+           "seconds": dt}
+    if torch_cpu:
+        try:
+            out["torch_cpu"] = torch_cpu_baseline()
+        except Exception as e:      # a reported extra: never lose the bench line over it
+            out["torch_cpu"] = {"error": f"{type(e).__name__}: {e}"}
+    return out
+
+
+def torch_cpu_baseline(surfels=100_000):
+    """BASELINE.md baseline B1: the pure-PyTorch CPU transliteration of the reference's forward + backward
+    (oracle/torch_cpu.py) on the host cores, on a bounded sample: ONE frame of BASELINE.json configs[0] (1200x680,
+    100k surfels, identity view) -- the 500k-surfel frames of the bench workload would take about a minute each --
+    with the C restatement timed on the same frame beside it."""
+    import torch
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    sys.path.insert(0, os.path.join(ROOT, "gaus-slam_b200"))
+    import cpu as O
+    import torch_cpu as T
+    from gs2d_b200 import scene
+    intr = scene.REPLICA
+    W, H = intr["W"], intr["H"]
+    sc = scene.room_scene(surfels, intr, seed=0)
+    cam = scene.view_sweep(1, intr, seed=0)[0]
+    gc, go = scene.image_grads(W, H, seed=0)
+    bg = np.zeros(3, np.float32)
+    torch.set_num_threads(os.cpu_count() or 1)
+
+    def frame(mod):
+        t0 = time.perf_counter()
+        st = mod.forward(sc["means3D"], sc["opacities"], cam.viewmatrix, cam.projmatrix, W, H, bg, scales=sc["scales"],
+                         rotations=sc["rotations"], colors=sc["colors"], campos=cam.campos)
+        mod.backward(st, sc["means3D"], cam.viewmatrix, cam.projmatrix, W, H, cam.tanfovx, cam.tanfovy, bg, gc, go,
+                     scales=sc["scales"], rotations=sc["rotations"], campos=cam.campos)
+        return time.perf_counter() - t0, int(st["num_rendered"])
+    dt_t, n = frame(T)
+    dt_c, _ = frame(O)
+    return {"value": 1.0 / dt_t, "unit": UNIT, "cores": torch.get_num_threads(), "kind": "port", "seconds": dt_t,
+            "sample": f"1 whole fwd+bwd frame of BASELINE.json configs[0] ({W}x{H}, P={surfels}, I={n}), pure-PyTorch "
+                      f"CPU transliteration oracle/torch_cpu.py (fp32, hand-written backward)",
+            "c_restatement_same_frame": {"value": 1.0 / dt_c, "seconds": dt_c, "cores": O.num_threads()}}
 
 
 # ----------------------------------------------------------------------------------------------------
@@ -654,7 +695,7 @@ def main():
         out["roofline"] = roofline
         out["kernels"] = kernels
         if not a.no_cpu_baseline and not multi:
-            out["cpu_baseline"] = cpu_baseline(wl, a.cpu_frames)
+            out["cpu_baseline"] = cpu_baseline(wl, a.cpu_frames, torch_cpu=not a.no_torch_cpu)
     if e2e is not None:
         out["e2e"] = e2e
     out.update(loops)

@@ -77,3 +77,13 @@ def test_cold_branches_are_refused():
         T.forward(*a, scales=case["scales"], rotations=case["rotations"], colors=None, shs=np.zeros((3000, 1, 3), np.float32))
     with pytest.raises(NotImplementedError):
         T.forward(*a, transMat=np.zeros((3000, 9), np.float32), colors=case["colors"])
+
+
+def test_bench_torch_cpu_baseline_runs():
+    """The cpu_baseline extra of bench.py, at a small size."""
+    import os
+    import sys
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    import bench
+    r = bench.torch_cpu_baseline(surfels=3000)
+    assert r["value"] > 0 and r["cores"] >= 1 and "configs[0]" in r["sample"] and r["c_restatement_same_frame"]["value"] > 0
