@@ -110,3 +110,46 @@ def test_product_never_touches_the_oracle():
                 txt = open(os.path.join(d, f), errors="ignore").read()
                 m = bad.search(txt)
                 assert m is None, f"{os.path.join(d, f)} references the oracle: {m.group(0)!r}"
+
+
+def test_next_row_entry_points_validate_their_arguments():
+    """gs2d_map_* / gs2d_pose_transform_* / loss: invalid calls are rejected before anything is launched."""
+    lib = L.load()
+    ms, ap = L.MapState(), L.AdamParams()
+    assert lib.gs2d_map_activate(4, 3, C.byref(ms), None, None, None, None) == L.GS2D_ERR_INVALID      # scale_cols
+    assert lib.gs2d_map_activate(0, 2, C.byref(ms), None, None, None, None) == L.GS2D_OK               # nothing to do
+    assert lib.gs2d_map_activate(4, 2, C.byref(ms), None, None, None, None) == L.GS2D_ERR_INVALID      # NULL tensors
+    assert lib.gs2d_map_adam_step(4, 2, C.byref(ms), None, C.byref(ap), None, None, None, None) == L.GS2D_ERR_INVALID
+    assert lib.gs2d_map_adam_step(-1, 2, None, None, None, None, None, None, None) == L.GS2D_ERR_INVALID
+    assert lib.gs2d_pose_transform_scratch_bytes() >= 12 * 4 * 148
+    # exactly one pose parametrisation: none given / both given
+    one = C.c_void_p(16)          # any non-NULL value: validation happens before a launch
+    assert lib.gs2d_pose_transform_forward(4, one, None, None, None, None, one, None, None) == L.GS2D_ERR_INVALID
+    assert lib.gs2d_pose_transform_forward(4, one, None, one, one, one, one, None, None) == L.GS2D_ERR_INVALID
+    assert lib.gs2d_pose_transform_forward(4, one, one, one, one, None, one, None, None) == L.GS2D_ERR_INVALID   # rotations w/o output
+    assert lib.gs2d_pose_transform_forward(0, None, None, None, None, None, None, None, None) == L.GS2D_OK
+    assert lib.gs2d_pose_transform_backward(4, one, one, one, None, one, None, one, one, None, None, None) == L.GS2D_ERR_INVALID  # no scratch
+    assert lib.gs2d_pose_transform_backward(4, one, one, one, None, one, one, None, one, None, None, None) == L.GS2D_ERR_INVALID  # no dL_dcam_rot
+    assert lib.gs2d_mapping_loss_forward(0, 8, None, None, None, None, 0, None, None, None, None) == L.GS2D_ERR_INVALID
+
+
+def test_next_row_wrappers_refuse_cpu_tensors_and_unbuilt_branches():
+    """No CPU path anywhere in the product: the python wrappers raise before touching CUDA."""
+    import torch
+    from gs2d_b200 import loss, optim, tracking
+    P = 8
+    raw = [torch.zeros((P, 3)), torch.zeros((P, 1)), torch.zeros((P, 2)), torch.ones((P, 4)), torch.zeros((P, 3))]
+    args = dict(xyz_lr=1e-4, opacity_lr=5e-2, scaling_lr=1e-3, rotation_lr=1e-3, rgb_lr=2.5e-3)
+    with pytest.raises(RuntimeError, match="CUDA"):
+        optim.MapOptimizer(*raw, args)
+    with pytest.raises(RuntimeError, match="CUDA"):
+        tracking.pose_transform(raw[0], raw[3], cam_rot=torch.tensor([1.0, 0, 0, 0]), cam_trans=torch.zeros(3))
+    with pytest.raises(Exception, match="exactly one"):
+        tracking.pose_transform(raw[0], raw[3])
+    img, am = torch.zeros((3, 8, 8)), torch.zeros((7, 8, 8))
+    with pytest.raises(NotImplementedError):
+        loss.tracking_loss(img, am, img, torch.zeros((8, 8)), ignore_outliners=True)
+    with pytest.raises(NotImplementedError):
+        loss.mapping_loss(img, am, img, torch.zeros((8, 8)), use_edge_growth=True)
+    with pytest.raises(RuntimeError):
+        loss.mapping_loss(img, am, img, torch.zeros((8, 8)))
