@@ -3,8 +3,9 @@
 `mapping_loss_torch` follows slam/Loss.py:22-25, :36, :51-63 and render/__init__.py:46-49 line by line with the
 same torch calls (so torch autograd gives the gradients the reference would get); `mapping_loss_numpy` is a
 loop-free float64 restatement with hand-written gradients, used to check the torch transliteration itself.
-Parity pin: the reference has no tests for this function and cannot be imported here (pytorch3d etc. missing,
-SURVEY.md 8c) -- the torch transliteration uses the reference's own expressions; "parity unpinned" beyond that.
+Parity pin: tests/golden/loss_*.npz hold what the reference's own get_loss (slam/Loss.py imported unmodified, CPU)
+computes for both branches (tests/golden/make_loss_golden.py); tests/test_loss.py checks both restatements against
+them.
 """
 import numpy as np
 

@@ -153,3 +153,53 @@ def test_fused_loss_rejects_what_is_not_built():
                         use_normal_loss=True)
     with pytest.raises(RuntimeError):
         gl.mapping_loss(t.cpu(), torch.zeros((7, 8, 8)), t.cpu(), torch.zeros((8, 8)))
+
+
+# ---- golden vectors from the reference's OWN get_loss (tests/golden/make_loss_golden.py: slam/Loss.py imported
+# unmodified in the authoring container, run on the CPU) --------------------------------------------------------
+GOLDEN_LOSS = ["small", "ragged", "clean"]
+
+
+def _golden(name):
+    p = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", f"loss_{name}.npz")
+    with np.load(p) as z:
+        return {k: z[k] for k in z.files}
+
+
+@pytest.mark.parametrize("name", GOLDEN_LOSS)
+@pytest.mark.parametrize("mode", ["mapping", "tracking"])
+def test_restatements_match_the_reference_get_loss(name, mode):
+    """Pins oracle/loss_ref.py: both restatements against what the reference's code computed."""
+    g = _golden(name)
+    color, allmap = g["in_color"], g["in_allmap"]
+    gt_chw = np.ascontiguousarray(g["in_gt_color"].transpose(2, 0, 1))
+    gt_depth = g["in_gt_depth"][..., 0]
+    want = float(g[f"ref_loss_{mode}"]), g[f"ref_dcolor_{mode}"], g[f"ref_dallmap_{mode}"]
+    if mode == "mapping":
+        got_np = loss_ref.mapping_loss_numpy(color, allmap, gt_chw, gt_depth)
+        got_t = _torch_ref(color, allmap, gt_chw, gt_depth)
+    else:
+        got_np = loss_ref.mapping_loss_numpy(color, allmap, gt_chw, gt_depth, weights=(0.5, 1.0, 0.0), tracking=True)
+        got_t = _torch_tracking(color, allmap, gt_chw, gt_depth)
+    for got in (got_np, got_t):
+        assert abs(got[0] - want[0]) <= 1e-5 * abs(want[0])
+        assert _close(np.asarray(got[1]), want[1], 2e-6) and _close(np.asarray(got[2]), want[2], 1e-5)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", GOLDEN_LOSS)
+@pytest.mark.parametrize("mode", ["mapping", "tracking"])
+def test_fused_kernels_match_the_reference_get_loss(name, mode):
+    from gs2d_b200 import loss as gl
+    dev = torch.device("cuda:0")
+    g = _golden(name)
+    c = torch.tensor(g["in_color"], device=dev, requires_grad=True)
+    a = torch.tensor(g["in_allmap"], device=dev, requires_grad=True)
+    gc = torch.tensor(g["in_gt_color"], device=dev)               # [H,W,3], the reference's layout
+    gd = torch.tensor(g["in_gt_depth"], device=dev)               # [H,W,1]
+    loss = gl.mapping_loss(c, a, gc, gd) if mode == "mapping" else gl.tracking_loss(c, a, gc, gd)
+    loss.backward()
+    want = float(g[f"ref_loss_{mode}"])
+    assert abs(float(loss.detach()) - want) <= 2e-5 * abs(want)
+    assert _close(c.grad.cpu().numpy(), g[f"ref_dcolor_{mode}"], 5e-6)
+    assert _close(a.grad.cpu().numpy(), g[f"ref_dallmap_{mode}"], 1e-5)
