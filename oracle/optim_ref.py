@@ -6,6 +6,10 @@ columns when isotropic) and `torch.optim.Adam(groups, lr=0.0, eps=1e-15)` with t
 `training_setup` (:124-137).  torch.optim.Adam IS the reference's optimiser, so this pins the parity of the fused
 kernel against outputs of the reference's implementation run here.  `map_step_numpy` is a float64 restatement of
 the same step with hand-written activation gradients (checks the derivation the CUDA kernel uses).
+
+Pinned: tests/golden/optim_*.npz are the states the reference's own `Gaussians` class (scene/Gaussians.py, imported
+unmodified by tests/golden/make_optim_golden.py) reaches over 4 steps; MapTorch reproduces them bit for bit
+(tests/test_optim.py).
 """
 import numpy as np
 

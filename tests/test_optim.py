@@ -1,7 +1,11 @@
 """Fused map optimiser step.  CPU: the float64 restatement with hand-written activation
 gradients agrees with the reference's own machinery (torch activations + torch.optim.Adam, run on the CPU).  GPU:
 gs2d_map_activate / gs2d_map_adam_step through the C ABI (gs2d_b200.optim.MapOptimizer) agree with both over several
-steps -- fp32 tolerances written at each assert."""
+steps -- fp32 tolerances written at each assert.  Golden: tests/golden/optim_*.npz hold the states the reference's own
+`Gaussians.training_setup()` / `get_render_params` / `optimizer.step()` produced (scene/Gaussians.py imported
+unmodified, tests/golden/make_optim_golden.py); the restatements (CPU) and the fused kernel (GPU) are held to them."""
+import os
+
 import numpy as np
 import pytest
 import torch
@@ -24,6 +28,19 @@ def _grad(P, seed, step):
     g = (rng.normal(0, 1, 13 * P) * 10.0 ** rng.uniform(-6, -2, 13 * P)).astype(np.float32)
     g[rng.uniform(size=13 * P) < 0.3] = 0.0        # surfels a view does not see get exactly zero gradient
     return g
+
+
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+GOLDEN_CASES = ("aniso", "iso", "aligned")
+
+
+def _golden(name):
+    path = os.path.join(GOLDEN, f"optim_{name}.npz")
+    assert os.path.exists(path), f"{path} missing (tests/golden/make_optim_golden.py)"
+    g = dict(np.load(path))
+    raw = {k: g["in_" + k] for k in R.GROUPS}
+    args = dict(zip(R.LR_KEYS, (float(x) for x in g["in_lr"])))
+    return g, raw, args
 
 
 def _rel(a, b):
@@ -49,6 +66,55 @@ def test_numpy_restatement_equals_torch_adam(P, scale_cols, seed):
             assert _rel(st["v_" + k], v[k]) <= 1e-5, (step, k)
         for k in ("opacities", "scales", "rotations"):
             assert _rel(st[k], act[k]) <= 1e-6, (step, k)
+
+
+@pytest.mark.parametrize("name", GOLDEN_CASES)
+def test_restatements_match_the_reference_gaussians_class(name):
+    """MapTorch (torch ops, fp32) must reproduce the reference's states BIT FOR BIT -- same torch, same ops, same
+    order; the float64 numpy restatement to fp32 rounding."""
+    g, raw, args = _golden(name)
+    ref = R.MapTorch(raw, args)
+    x = {k: raw[k].astype(np.float64) for k in R.GROUPS}
+    m = {k: np.zeros_like(x[k]) for k in R.GROUPS}
+    v = {k: np.zeros_like(x[k]) for k in R.GROUPS}
+    lr = [args[k] for k in R.LR_KEYS]
+    for step in range(1, g["in_grad"].shape[0] + 1):
+        grad = g["in_grad"][step - 1]
+        ref.step(grad)
+        x, m, v, act = R.map_step_numpy(x, m, v, grad, lr, step)
+        st = ref.state()
+        for k in R.GROUPS:
+            assert np.array_equal(st[k], g[f"ref_{k}_{step}"]), (step, k)
+            assert np.array_equal(st["m_" + k], g[f"ref_m_{k}_{step}"]), (step, k)
+            assert np.array_equal(st["v_" + k], g[f"ref_v_{k}_{step}"]), (step, k)
+            assert _rel(g[f"ref_{k}_{step}"], x[k]) <= 2e-6, (step, k)
+            assert _rel(g[f"ref_m_{k}_{step}"], m[k]) <= 1e-5, (step, k)
+            assert _rel(g[f"ref_v_{k}_{step}"], v[k]) <= 1e-5, (step, k)
+        for k in ("opacities", "scales", "rotations"):
+            assert np.array_equal(st[k], g[f"ref_{k}_{step}"]), (step, k)
+            assert _rel(g[f"ref_{k}_{step}"], act[k]) <= 1e-6, (step, k)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", GOLDEN_CASES)
+def test_fused_step_matches_the_reference_gaussians_class(name):
+    from gs2d_b200 import optim
+    dev = torch.device("cuda:0")
+    g, raw, args = _golden(name)
+    opt = optim.MapOptimizer(*[torch.tensor(raw[k], device=dev) for k in R.GROUPS], args)
+    for step in range(1, g["in_grad"].shape[0] + 1):
+        opt.flat_grad.copy_(torch.from_numpy(g["in_grad"][step - 1]))
+        opt.step()
+        for k in R.GROUPS:
+            assert _rel(opt.raw[k].cpu().numpy(), g[f"ref_{k}_{step}"].astype(np.float64)) <= 2e-6, (step, k)
+            assert _rel(opt.exp_avg[k].cpu().numpy(), g[f"ref_m_{k}_{step}"].astype(np.float64)) <= 1e-5, (step, k)
+            assert _rel(opt.exp_avg_sq[k].cpu().numpy(), g[f"ref_v_{k}_{step}"].astype(np.float64)) <= 1e-5, (step, k)
+        for k in ("opacities", "scales", "rotations"):
+            assert _rel(getattr(opt, k).cpu().numpy(), g[f"ref_{k}_{step}"].astype(np.float64)) <= 2e-6, (step, k)
+    last = g["in_grad"].shape[0]
+    moved = opt.raw["opacity"].cpu().numpy() - raw["opacity"]
+    want = g[f"ref_opacity_{last}"] - raw["opacity"]
+    assert np.abs(moved - want).max() <= 1e-4 * np.abs(want).max() + 1e-7
 
 
 @pytest.mark.gpu
