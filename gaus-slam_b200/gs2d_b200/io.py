@@ -13,7 +13,8 @@ reference's evaluation / visualisation scripts and vice versa.
 The reference fills its structured array through `list(map(tuple, attributes))` (a Python loop over surfels); here
 the [P,K] matrix is packed on the device with one concatenation, crosses PCIe once and is written with one
 `tofile`.  plyfile is not installed in this image, so the reader/writer are written against the PLY specification
-and plyfile's documented header; parity with plyfile itself is unpinned.
+and plyfile's documented header; the rows written and the arrays read back are pinned by tests/golden/ply_*.npz
+(the reference's own save_ply / load_ply run against a recording stand-in for plyfile), the header text is not.
 """
 from __future__ import annotations
 

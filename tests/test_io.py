@@ -74,3 +74,48 @@ def test_w2cs_file_name_and_content(tmp_path):
     assert os.path.basename(path) == "w2cs.npz.npy" and os.path.exists(path)      # scene/__init__.py:33
     back = gio.load_w2cs(str(tmp_path))
     assert back.shape == (3, 4, 4) and back.dtype == np.float32 and np.array_equal(back[2], 3 * np.eye(4, dtype=np.float32))
+
+
+# ---- golden: what the reference's own save_ply hands to plyfile / load_ply makes of a file (make_ply_golden.py) ----
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+GROUPS = ("xyz", "opacity", "scaling", "rotation", "rgb")
+_PLY_NAME = {"<f4": "float", "<f8": "double"}
+
+
+def _golden(name):
+    path = os.path.join(GOLDEN, f"ply_{name}.npz")
+    assert os.path.exists(path), f"{path} missing (tests/golden/make_ply_golden.py)"
+    return dict(np.load(path))
+
+
+@pytest.mark.parametrize("name", ["aniso", "iso", "empty"])
+def test_save_ply_writes_the_rows_the_reference_hands_to_plyfile(tmp_path, name):
+    g = _golden(name)
+    path = os.path.join(tmp_path, "gaussians.ply")
+    gio.save_ply(path, **{k: torch.tensor(g["in_" + k]) for k in GROUPS})
+    raw = open(path, "rb").read()
+    end = raw.index(b"end_header\n") + len(b"end_header\n")
+    props = [line.split() for line in raw[:end].decode().splitlines() if line.startswith("property")]
+    assert [p[2] for p in props] == [str(n) for n in g["ref_names"]]                  # names, in the reference's order
+    assert [p[1] for p in props] == [_PLY_NAME[str(f)] for f in g["ref_formats"]]     # every property is float32
+    assert raw[end:] == g["ref_rows"].tobytes()                                       # the reference's structured array
+    assert f"element vertex {g['in_xyz'].shape[0]}\n".encode() in raw[:end]
+
+
+@pytest.mark.parametrize("name", ["aniso", "iso"])
+def test_load_ply_selects_what_the_reference_load_ply_selects(tmp_path, name):
+    """A file with shuffled, extra and float64 properties: same arrays as Gaussians.load_ply builds from it."""
+    g = _golden(name)
+    names, formats = [str(n) for n in g["file_names"]], [str(f) for f in g["file_formats"]]
+    P = g["in_xyz"].shape[0]
+    path = os.path.join(tmp_path, "other_tool.ply")
+    with open(path, "wb") as f:
+        f.write(("ply\nformat binary_little_endian 1.0\nelement vertex %d\n" % P +
+                 "".join("property %s %s\n" % (_PLY_NAME[t], n) for n, t in zip(names, formats)) + "end_header\n").encode())
+        f.write(g["file_rows"].tobytes())
+    back = gio.load_ply(path)
+    for k in GROUPS:
+        want = g["ref_load_" + k]
+        assert back[k].dtype == want.dtype == np.float32 and back[k].shape == want.shape, k
+        assert np.array_equal(back[k], want), k
+        assert np.array_equal(back[k], g["in_" + k]), k
