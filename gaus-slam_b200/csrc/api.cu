@@ -35,7 +35,7 @@ const char* const kKernelNames[K_COUNT] = {
 	"preprocess_forward", "scan_tiles", "duplicate_keys", "histogram", "digit_base", "onesweep_pass",
 	"gather_ranges", "composite_forward", "composite_backward", "preprocess_backward", "mark_visible",
 	"memset", "memcpy", "knn", "footprint", "composite_backward_instances", "tile_offsets", "scatter_pairs",
-	"tile_sort_gather_footprint", "mapping_loss", "allreduce_multimem", "map_adam_step", "pose_transform"};
+	"tile_sort_gather_footprint", "mapping_loss", "allreduce_multimem", "map_adam_step", "pose_transform", "map_compact"};
 }  // namespace
 void prof_mark(int id, cudaStream_t st, bool begin)
 {

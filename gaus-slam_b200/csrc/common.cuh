@@ -141,7 +141,7 @@ void count_launch(int n = 1);
 enum KernelId {
 	K_PREPROCESS_FWD = 0, K_SCAN, K_DUPLICATE, K_HISTOGRAM, K_DIGIT_BASE, K_ONESWEEP, K_GATHER_RANGES,
 	K_COMPOSITE_FWD, K_COMPOSITE_BWD, K_PREPROCESS_BWD, K_MARK_VISIBLE, K_MEMSET, K_MEMCPY, K_KNN, K_FOOTPRINT, K_COMPOSITE_BWD_INST, K_TILE_OFFSETS,
-	K_SCATTER, K_TILE_SORT, K_LOSS, K_ALLREDUCE, K_MAP_STEP, K_POSE, K_COUNT
+	K_SCATTER, K_TILE_SORT, K_LOSS, K_ALLREDUCE, K_MAP_STEP, K_POSE, K_MAP_COMPACT, K_COUNT
 };
 extern bool g_timing_on;
 void prof_mark(int id, cudaStream_t st, bool begin);

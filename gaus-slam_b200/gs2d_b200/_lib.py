@@ -108,6 +108,10 @@ PROTOTYPES = {
                                     C.c_void_p]),
     "gs2d_map_adam_step": (C.c_int, [C.c_int32, C.c_int32, C.POINTER(MapState), C.c_void_p, C.POINTER(AdamParams),
                                      C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "gs2d_map_compact_scratch_bytes": (C.c_size_t, [C.c_int32]),
+    "gs2d_map_compact_plan": (C.c_int, [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "gs2d_map_compact_move": (C.c_int, [C.c_int32, C.c_int32, C.c_void_p, C.POINTER(MapState), C.POINTER(MapState),
+                                        C.c_void_p, C.c_void_p]),
     "gs2d_pose_transform_forward": (C.c_int, [C.c_int32] + [C.c_void_p] * 8),
     "gs2d_pose_transform_scratch_bytes": (C.c_size_t, []),
     "gs2d_pose_transform_backward": (C.c_int, [C.c_int32] + [C.c_void_p] * 11),

@@ -43,23 +43,28 @@ class MapOptimizer:
         self.exp_avg_sq = {k: torch.zeros_like(t) for k, t in self.raw.items()}
         self.lr = [float(training_args[k]) for k in LR_KEYS]
         self.betas, self.eps, self.step_count = (float(betas[0]), float(betas[1])), float(eps), 0
-        self.flat_grad = flat_grad if flat_grad is not None else torch.zeros(FLAT_WIDTH * P, device=self.dev)
-        if self.flat_grad.numel() != FLAT_WIDTH * P or not self.flat_grad.is_cuda:
+        if flat_grad is not None and (flat_grad.numel() != FLAT_WIDTH * P or not flat_grad.is_cuda):
             raise RuntimeError("flat_grad must be a CUDA tensor of 13 * P floats")
+        self._state = L.MapState()
+        self._resize(flat_grad)
+
+    def _resize(self, flat_grad=None):
+        """(Re)create what depends on P after the raw tensors changed: gradient buffer, activations, bindings."""
+        P = self.P = int(self.raw["xyz"].shape[0])
+        self.flat_grad = flat_grad if flat_grad is not None else torch.zeros(FLAT_WIDTH * P, device=self.dev)
         self.opacities = torch.empty((P, 1), device=self.dev)
         self.scales = torch.empty((P, 2), device=self.dev)
         self.rotations = torch.empty((P, 4), device=self.dev)
-        self._state = L.MapState()
-        self._bind()
+        self._bind(self._state, self.raw, self.exp_avg, self.exp_avg_sq)
         self.activate()
 
-    def _bind(self):
-        s = self._state
+    @staticmethod
+    def _bind(s, raw, exp_avg, exp_avg_sq):
         for k in GROUPS:
-            setattr(s, k, self.raw[k].data_ptr())
+            setattr(s, k, raw[k].data_ptr())
         for i, k in enumerate(GROUPS):
-            s.exp_avg[i] = self.exp_avg[k].data_ptr()
-            s.exp_avg_sq[i] = self.exp_avg_sq[k].data_ptr()
+            s.exp_avg[i] = exp_avg[k].data_ptr()
+            s.exp_avg_sq[i] = exp_avg_sq[k].data_ptr()
 
     def _stream(self):
         return C.c_void_p(torch.cuda.current_stream(self.dev).cuda_stream)
@@ -95,3 +100,56 @@ class MapOptimizer:
             L.check(L.load().gs2d_map_adam_step(self.P, self.scale_cols, C.byref(self._state), g.data_ptr(), C.byref(ap),
                                                 self.opacities.data_ptr(), self.scales.data_ptr(),
                                                 self.rotations.data_ptr(), self._stream()), "gs2d_map_adam_step")
+
+    # ---- densification: the optimiser surgery of scene/Gaussians.py:143-184, :419-433 ------------------------
+    def prune(self, keep):
+        """`prune_optimizer(mask)` (scene/Gaussians.py:143-160): keep the surfels where `keep` [P] (bool) is set, in
+        order, with their Adam moments; the step counter stays.  One plan (count + scan) and ONE move kernel for
+        all 15 arrays instead of 15 boolean-index launches.  Returns the number of surfels kept."""
+        if keep.dtype != torch.bool or not keep.is_cuda or tuple(keep.shape) != (self.P,):
+            raise RuntimeError("keep must be a bool CUDA tensor of P elements")
+        keep = keep.contiguous()
+        lib = L.load()
+        with torch.cuda.device(self.dev):
+            scratch = torch.empty(lib.gs2d_map_compact_scratch_bytes(self.P) // 4, dtype=torch.int32, device=self.dev)
+            L.check(lib.gs2d_map_compact_plan(self.P, keep.data_ptr(), scratch.data_ptr(), self._stream()),
+                    "gs2d_map_compact_plan")
+            n = int(scratch[0].item())          # the host has to size the new tensors: one 4-byte read-back
+            new = [{k: torch.empty((n, t.shape[1]), device=self.dev) for k, t in d.items()}
+                   for d in (self.raw, self.exp_avg, self.exp_avg_sq)]
+            if n:
+                dst = L.MapState()
+                self._bind(dst, *new)
+                L.check(lib.gs2d_map_compact_move(self.P, self.scale_cols, keep.data_ptr(), C.byref(self._state),
+                                                  C.byref(dst), scratch.data_ptr(), self._stream()),
+                        "gs2d_map_compact_move")
+        self.raw, self.exp_avg, self.exp_avg_sq = new
+        self._resize()
+        return n
+
+    def extend(self, xyz, opacity, scaling, rotation, rgb):
+        """`cat_tensors_to_optimizer` (scene/Gaussians.py:162-184): append new surfels (raw parameters) with zero
+        moments; the step counter (hence the bias correction) stays that of the existing surfels."""
+        ext = dict(xyz=xyz, opacity=opacity, scaling=scaling, rotation=rotation, rgb=rgb)
+        n = int(xyz.shape[0])
+        for k, t in ext.items():
+            if not t.is_cuda or t.dtype != torch.float32 or tuple(t.shape) != (n, self.raw[k].shape[1]):
+                raise RuntimeError(f"{k}: expected a float32 CUDA tensor of shape {(n, self.raw[k].shape[1])}")
+        for k, t in ext.items():
+            self.raw[k] = torch.cat((self.raw[k], t.detach()), dim=0)
+            self.exp_avg[k] = torch.cat((self.exp_avg[k], torch.zeros_like(t)), dim=0)
+            self.exp_avg_sq[k] = torch.cat((self.exp_avg_sq[k], torch.zeros_like(t)), dim=0)
+        self._resize()
+        return self.P
+
+    def replace(self, name, tensor):
+        """`replace_tensor_to_optimizer(tensor, name)` (scene/Gaussians.py:419-433; reset_opacity :399-406,
+        transform_gaussians :408-417): new raw values for one group, its moments reset to zero."""
+        if name not in GROUPS:
+            raise KeyError(name)
+        if not tensor.is_cuda or tensor.dtype != torch.float32 or tuple(tensor.shape) != tuple(self.raw[name].shape):
+            raise RuntimeError(f"{name}: expected a float32 CUDA tensor of shape {tuple(self.raw[name].shape)}")
+        self.raw[name].copy_(tensor.detach())
+        self.exp_avg[name].zero_()
+        self.exp_avg_sq[name].zero_()
+        self.activate()

@@ -295,6 +295,20 @@ int gs2d_map_adam_step(int32_t P, int32_t scale_cols, const gs2d_map_state* ms, 
                        const gs2d_adam_params* params, float* opacities, float* scales, float* rotations,
                        void* stream);
 
+/* Stream compaction of the map state: what Gaussians.prune_optimizer(mask) does to the five parameter tensors and
+ * their Adam moments (scene/Gaussians.py:143-160; remove_gaussians_from_mask :280-297), in two steps so that the
+ * caller can size the destination exactly:
+ *   plan:  keep [P] bytes (torch.bool storage: 0 / non-zero) -> scratch (gs2d_map_compact_scratch_bytes(P) bytes,
+ *          need not be initialised): int32 scratch[0] = number of kept surfels, the rest are per-block offsets;
+ *   move:  every array of `src` -> the same array of `dst` (row r of dst = the r-th kept row of src, order
+ *          preserved as in tensor[mask]).  Out of place.  A moment pointer may be NULL on BOTH sides (optimiser that
+ *          has not stepped); parameters are required.  `dst` arrays hold at least scratch[0] rows.
+ * The Adam step counter is not touched (the reference keeps the state dict's "step"). */
+size_t gs2d_map_compact_scratch_bytes(int32_t P);
+int gs2d_map_compact_plan(int32_t P, const uint8_t* keep, void* scratch, void* stream);
+int gs2d_map_compact_move(int32_t P, int32_t scale_cols, const uint8_t* keep, const gs2d_map_state* src,
+                          const gs2d_map_state* dst, const void* scratch, void* stream);
+
 /* ---- "next" row f1: fused pose transform + pose-gradient reduction ---------------------------
  * Renderer_tracking / Renderer_BA move the map into the camera frame before rendering with an identity camera
  * (render/__init__.py:35-36, :97-98):

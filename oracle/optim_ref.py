@@ -55,6 +55,49 @@ class MapTorch:
         torch.autograd.backward([rp[k] for k, _ in FLAT], [g[k] for k, _ in FLAT])
         self.optimizer.step()
 
+    # ---- densification surgery, restated from scene/Gaussians.py (pinned by tests/golden/optim_surgery.npz) ----
+    def _swap(self, k, new_param, exp_avg=None, exp_avg_sq=None):
+        """Replace group k's Parameter, carrying the optimiser state over (its "step" included)."""
+        torch = self.torch
+        group = next(g for g in self.optimizer.param_groups if g["name"] == k)
+        stored = self.optimizer.state.get(group["params"][0], None)
+        if stored is not None:
+            stored["exp_avg"], stored["exp_avg_sq"] = exp_avg(stored["exp_avg"]), exp_avg_sq(stored["exp_avg_sq"])
+            del self.optimizer.state[group["params"][0]]
+        group["params"][0] = torch.nn.Parameter(new_param.requires_grad_(True))
+        if stored is not None:
+            self.optimizer.state[group["params"][0]] = stored
+        self.p[k] = group["params"][0]
+
+    def prune(self, keep):
+        """prune_optimizer(mask) (:143-160): parameters and both moments indexed with the same boolean mask."""
+        keep = self.torch.as_tensor(keep)
+        for k in GROUPS:
+            self._swap(k, self.p[k].detach()[keep], lambda m: m[keep], lambda v: v[keep])
+
+    def extend(self, new):
+        """cat_tensors_to_optimizer (:162-184): new rows appended, their moments zero."""
+        torch = self.torch
+        for k in GROUPS:
+            ext = torch.as_tensor(new[k])
+            self._swap(k, torch.cat((self.p[k].detach(), ext), dim=0),
+                       lambda m: torch.cat((m, torch.zeros_like(ext)), dim=0),
+                       lambda v: torch.cat((v, torch.zeros_like(ext)), dim=0))
+
+    def replace(self, k, tensor):
+        """replace_tensor_to_optimizer (:419-433): new values, moments reset to zero."""
+        torch = self.torch
+        tensor = torch.as_tensor(tensor).clone()
+        self._swap(k, tensor, lambda m: torch.zeros_like(tensor), lambda v: torch.zeros_like(tensor))
+
+    def reset_opacity_values(self):
+        """What reset_opacity (:399-406) hands to replace_tensor_to_optimizer: the ACTIVATED opacities, min'ed with
+        logit(0.01) -- which is always logit(0.01), since sigmoid > 0 > logit(0.01); kept as the reference has it."""
+        torch = self.torch
+        new = torch.sigmoid(self.p["opacity"]).detach()
+        cap = 0.01 * torch.ones_like(new)
+        return torch.min(new, torch.log(cap / (1 - cap)))
+
     def state(self):
         out = {k: self.p[k].detach().cpu().numpy() for k in GROUPS}
         for k in GROUPS:

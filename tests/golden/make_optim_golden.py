@@ -53,6 +53,23 @@ def import_reference_gaussians():
     spec = importlib.util.spec_from_file_location("reference_gaussians", os.path.join(REFERENCE, "scene", "Gaussians.py"))
     mod = importlib.util.module_from_spec(spec)
     spec.loader.exec_module(mod)
+
+    class TorchOnCpu:
+        """The module's `torch`, with the `device="cuda"` of zeros / tensor redirected to the CPU (the per-surfel
+        statistics re-created after pruning / densification, scene/Gaussians.py:295-297, :527-529)."""
+        def __getattr__(self, name):
+            return getattr(torch, name)
+
+        @staticmethod
+        def zeros(*a, **kw):
+            kw.pop("device", None)
+            return torch.zeros(*a, **kw)
+
+        @staticmethod
+        def tensor(*a, **kw):
+            kw.pop("device", None)
+            return torch.tensor(*a, **kw)
+    mod.torch = TorchOnCpu()
     return mod.Gaussians
 
 
@@ -102,6 +119,80 @@ def run_reference(Gaussians, raw, grads, distribution):
     return out
 
 
+def snapshot(gs, out, tag):
+    for k in GROUPS:
+        p = getattr(gs, "_" + k)
+        st = gs.optimizer.state[p]
+        out[f"ref_{k}_{tag}"] = p.detach().numpy().copy()
+        out[f"ref_m_{k}_{tag}"] = st["exp_avg"].numpy().copy()
+        out[f"ref_v_{k}_{tag}"] = st["exp_avg_sq"].numpy().copy()
+    with torch.no_grad():
+        rp = gs.get_render_params
+        for k in ("opacities", "scales", "rotations"):
+            out[f"ref_{k}_{tag}"] = rp[k].numpy().copy()
+
+
+def one_step(gs, flat):
+    P = gs._xyz.shape[0]
+    rp = gs.get_render_params
+    outs, gts, off = [], [], 0
+    for name, w in FLAT:
+        outs.append(rp[name])
+        gts.append(torch.tensor(flat[off:off + w * P].reshape(P, w)))
+        off += w * P
+    torch.autograd.backward(outs, gts)
+    gs.optimizer.step()
+    gs.optimizer.zero_grad(set_to_none=True)
+
+
+def run_surgery(Gaussians, P=300, n_new=77, seed=5):
+    """step, step, remove_gaussians_from_mask, step, densification_postfix, step, reset_opacity, step -- the
+    optimiser surgery of densification (scene/Gaussians.py:143-184, :280-297, :399-406, :419-433, :513-529), all of it
+    the reference's own code."""
+    rng = np.random.default_rng(seed)
+    raw = raw_parameters(P, 2, seed)
+    config = dict(render=dict(method="2dgs"), gaussians=dict(gaussian_distribution="anisotropic", training_args=TRAINING_ARGS))
+    gs = Gaussians(config)
+    for k in GROUPS:
+        setattr(gs, "_" + k, torch.nn.Parameter(torch.tensor(raw[k]).requires_grad_(True)))
+    gs.training_setup()
+    out = {"in_" + k: raw[k] for k in GROUPS}
+    out["in_lr"] = np.array([TRAINING_ARGS[k] for k in LR_KEYS], np.float64)
+
+    def grad(tag):
+        n = gs._xyz.shape[0]
+        g = (rng.normal(0, 1, 13 * n) * 10.0 ** rng.uniform(-6, -2, 13 * n)).astype(np.float32)
+        g[rng.uniform(size=g.shape) < 0.3] = 0.0
+        out[f"in_grad_{tag}"] = g
+        return g
+
+    for tag in ("1", "2"):
+        one_step(gs, grad(tag))
+        snapshot(gs, out, tag)
+    remove = rng.uniform(size=P) < 0.4
+    remove[:3] = True                                   # the first surfels and a whole 256-block boundary region go
+    remove[250:262] = True
+    out["in_remove_mask"] = remove
+    gs.remove_gaussians_from_mask(torch.tensor(remove))
+    snapshot(gs, out, "pruned")
+    one_step(gs, grad("3"))
+    snapshot(gs, out, "3")
+    new = raw_parameters(n_new, 2, seed + 1)
+    for k in GROUPS:
+        out["in_new_" + k] = new[k]
+    t = {k: torch.tensor(v) for k, v in new.items()}
+    gs.densification_postfix(t["xyz"], t["rgb"], t["opacity"], t["scaling"], t["rotation"])
+    snapshot(gs, out, "extended")
+    one_step(gs, grad("4"))
+    snapshot(gs, out, "4")
+    gs.reset_opacity()
+    snapshot(gs, out, "reset")
+    one_step(gs, grad("5"))
+    snapshot(gs, out, "5")
+    np.savez_compressed(os.path.join(HERE, "optim_surgery.npz"), **out)
+    print("surgery", P, "->", int((~remove).sum()), "->", gs._xyz.shape[0], "surfels")
+
+
 # name: (P, columns of the raw scaling, gaussian_distribution, seed).  P odd: the sections of the flat gradient are
 # not 16-byte aligned (scalar path of the kernel); P % 4 == 0: 128-bit path.
 CASES = dict(aniso=(257, 2, "anisotropic", 0), iso=(64, 1, "isotropic", 1), aligned=(512, 2, "anisotropic", 2))
@@ -117,6 +208,7 @@ def main():
         out.update(run_reference(Gaussians, raw, grads, dist))
         np.savez_compressed(os.path.join(HERE, f"optim_{name}.npz"), **out)
         print(name, P, dist, "opacity moved by", float(np.abs(out[f"ref_opacity_{STEPS}"] - raw["opacity"]).max()))
+    run_surgery(Gaussians)
 
 
 if __name__ == "__main__":

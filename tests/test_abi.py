@@ -131,6 +131,24 @@ def test_next_row_entry_points_validate_their_arguments():
     assert lib.gs2d_pose_transform_backward(4, one, one, one, None, one, None, one, one, None, None, None) == L.GS2D_ERR_INVALID  # no scratch
     assert lib.gs2d_pose_transform_backward(4, one, one, one, None, one, one, None, one, None, None, None) == L.GS2D_ERR_INVALID  # no dL_dcam_rot
     assert lib.gs2d_mapping_loss_forward(0, 8, None, None, None, None, 0, None, None, None, None) == L.GS2D_ERR_INVALID
+    # map compaction: scratch = one total + one offset per 256-surfel block
+    assert lib.gs2d_map_compact_scratch_bytes(0) == 4 and lib.gs2d_map_compact_scratch_bytes(257) == 4 * 3
+    assert lib.gs2d_map_compact_scratch_bytes(-5) == 0
+    assert lib.gs2d_map_compact_plan(-1, one, one, None) == L.GS2D_ERR_INVALID
+    assert lib.gs2d_map_compact_plan(4, one, None, None) == L.GS2D_ERR_INVALID                             # no scratch
+    assert lib.gs2d_map_compact_plan(4, None, one, None) == L.GS2D_ERR_INVALID                             # no mask
+    dst = L.MapState()
+    assert lib.gs2d_map_compact_move(0, 2, None, C.byref(ms), C.byref(dst), one, None) == L.GS2D_OK        # nothing to do
+    assert lib.gs2d_map_compact_move(4, 3, one, C.byref(ms), C.byref(dst), one, None) == L.GS2D_ERR_INVALID
+    assert lib.gs2d_map_compact_move(4, 2, one, C.byref(ms), C.byref(dst), one, None) == L.GS2D_ERR_INVALID  # NULL parameters
+    for st in (ms, dst):
+        for k in ("xyz", "opacity", "scaling", "rotation", "rgb"):
+            setattr(st, k, 16 if st is ms else 32)
+    dst.exp_avg[2] = 32                                                                                    # moment on one side only
+    assert lib.gs2d_map_compact_move(4, 2, one, C.byref(ms), C.byref(dst), one, None) == L.GS2D_ERR_INVALID
+    dst.exp_avg[2] = 0
+    dst.rgb = ms.rgb                                                                                       # in place
+    assert lib.gs2d_map_compact_move(4, 2, one, C.byref(ms), C.byref(dst), one, None) == L.GS2D_ERR_INVALID
 
 
 def test_next_row_wrappers_refuse_cpu_tensors_and_unbuilt_branches():
