@@ -171,3 +171,33 @@ def test_next_row_wrappers_refuse_cpu_tensors_and_unbuilt_branches():
         loss.mapping_loss(img, am, img, torch.zeros((8, 8)), use_edge_growth=True)
     with pytest.raises(RuntimeError):
         loss.mapping_loss(img, am, img, torch.zeros((8, 8)))
+
+
+def test_header_is_plain_c_and_a_c_client_links(tmp_path):
+    """The boundary is a C ABI: include/gs2d.h compiles as strict C99 (no C++ / torch / CUDA types in a signature),
+    a C program that references EVERY declared entry point links against libgs2d.so, and the calls that need no
+    GPU answer (version, sizes, argument validation)."""
+    import shutil
+    import subprocess
+    if shutil.which("gcc") is None:
+        pytest.skip("needs gcc")
+    names = _header_functions()
+    src = os.path.join(tmp_path, "client.c")
+    with open(src, "w") as f:
+        f.write('#include <stdio.h>\n#include "gs2d.h"\n')
+        f.write("typedef void (*fn)(void);\nstatic const fn table[] = {\n")
+        f.write("".join(f"\t(fn){n},\n" for n in names))
+        f.write("};\nint main(void) {\n"
+                "\tif (sizeof(table) / sizeof(table[0]) != %d) return 2;\n"
+                "\tif (gs2d_abi_version() != 2) return 3;\n"
+                "\tif (gs2d_map_compact_scratch_bytes(257) != 12) return 4;\n"
+                "\tif (gs2d_map_activate(4, 3, 0, 0, 0, 0, 0) == GS2D_OK) return 5;\n"
+                '\tprintf("%%s\\n", gs2d_strerror(GS2D_ERR_INVALID));\n\treturn 0;\n}\n' % len(names))
+    exe = os.path.join(tmp_path, "client")
+    libdir = os.path.dirname(L.LIB_PATH)
+    r = subprocess.run(["gcc", "-std=c99", "-pedantic", "-Wall", "-Wextra", "-Werror",
+                        "-I", os.path.join(ROOT, "include"), src, "-o", exe, "-L", libdir, "-lgs2d",
+                        "-Wl,-rpath," + libdir], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr[-3000:]
+    r = subprocess.run([exe], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0 and r.stdout.strip(), (r.returncode, r.stdout, r.stderr)
