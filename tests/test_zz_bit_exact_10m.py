@@ -1,0 +1,43 @@
+"""SURVEY.md 7.3 trap 7: "test on >= 10 M random surfels that integer outputs match exactly".
+
+20 different 500 k-surfel rooms, each under a different camera of its own sweep (10 M surfels in total), through the
+product and through the UNMODIFIED compiled reference (oracle/_ref) on the same GPU: radii, tiles touched, offsets,
+keys, sort order, tile ranges and the per-surfel float state (depth, transMat, means2D, normal) must agree BIT FOR
+BIT, and so must the images.
+
+Sorts last and is marked as a first run: it was written after this round's GPU budget was spent.  Every size that HAS
+been run on a B200 (tests/test_gpu_parity.py, profiles/r1_parity_vs_reference_P100k_P500k.log: about 5 M surfels over
+the round) was bit-identical; this case only widens the sample."""
+import numpy as np
+import pytest
+
+import compare
+
+FIRST_RUN = pytest.mark.xfail(strict=False, reason="widened bit-exactness sample: not yet run on a B200 (passes -> XPASS)")
+
+
+@pytest.mark.gpu
+@FIRST_RUN
+def test_integer_outputs_are_bit_exact_on_10m_random_surfels():
+    import refgpu
+    if not refgpu.available():
+        pytest.skip("oracle/_ref/libgs2d_ref.so not on this box")
+    import gpu_run
+    from gs2d_b200 import scene
+    intr = scene.REPLICA
+    gc, go = scene.image_grads(intr["W"], intr["H"], seed=3)
+    total, report = 0, []
+    for seed in range(10, 30):
+        sc = scene.room_scene(500_000, intr, seed=seed)
+        cam = scene.view_sweep(8, intr, seed=seed)[seed % 8]
+        case = dict(W=intr["W"], H=intr["H"], tanfovx=np.float32(cam.tanfovx), tanfovy=np.float32(cam.tanfovy),
+                    viewmatrix=cam.viewmatrix.reshape(16), projmatrix=cam.projmatrix.reshape(16), campos=cam.campos,
+                    bg=np.zeros(3, np.float32), use_sa=True, scale_modifier=np.float32(1.0), sh_degree=0, shs=None,
+                    transMat=None, dL_dcolor=gc, dL_dothers=go, **sc)
+        ref = gpu_run.run_ref(case)
+        ours = gpu_run.run_ours(case, debug=True, backward=False)
+        fails = compare.check_binning(ours, ref, exact_float_state=True) + compare.check_images(ours, ref, exact=True)
+        report += [f"seed {seed}: {f}" for f in fails]
+        total += sc["means3D"].shape[0]
+    assert total >= 10_000_000
+    assert not report, "\n".join(report[:40])
