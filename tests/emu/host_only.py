@@ -1,0 +1,59 @@
+"""TEST INFRASTRUCTURE: run the product's Python wrappers (gs2d_b200.optim / loss / tracking) on HOST tensors against
+the host build of their kernels (tests/emu/build_emu.py).
+
+The product refuses CPU tensors and has no CPU path; that stays true.  For these tests only, a wrapper module's source
+is loaded with (a) its `is_cuda` argument checks textually removed, (b) `torch.cuda.device / current_stream` replaced
+by no-ops, (c) `_lib.load()` returning the emulated library.  Everything else in the wrapper -- shapes, strides,
+scratch handling, ctypes marshalling, the autograd bridge -- runs unchanged, and below it the kernels' own source text.
+"""
+from __future__ import annotations
+
+import contextlib
+import ctypes as C
+import os
+import re
+import sys
+import types
+
+import torch
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+sys.path.insert(0, HERE)
+import build_emu  # noqa: E402
+from gs2d_b200 import _lib as L  # noqa: E402
+
+_lib = None
+
+
+def emulated_library():
+    """libgs2d_emu.so with the prototypes of the product's ctypes mirror (for the entry points it has)."""
+    global _lib
+    if _lib is None:
+        lib = C.CDLL(build_emu.build())
+        for name, (restype, argtypes) in L.PROTOTYPES.items():
+            if hasattr(lib, name):
+                fn = getattr(lib, name)
+                fn.restype, fn.argtypes = restype, argtypes
+        _lib = lib
+    return _lib
+
+
+def load(module: str):
+    """gs2d_b200.<module> as a host-only module bound to the emulated library."""
+    src = open(os.path.join(ROOT, "gaus-slam_b200", "gs2d_b200", module + ".py")).read()
+    src, n1 = re.subn(r"not (\w+)\.is_cuda or ", "", src)
+    src, n2 = re.subn(r" or not (\w+)\.is_cuda", "", src)
+    assert n1 + n2 >= 1 and "is_cuda" not in src, f"{module}: unexpected CUDA checks left"
+    src = src.replace("from . import _lib as L", "L = None").replace("from .mapping import FLAT_WIDTH", "FLAT_WIDTH = 13")
+    assert "from ." not in src, f"{module}: relative import not handled"
+    mod = types.ModuleType(f"gs2d_b200_host_only_{module}")
+    exec(compile(src, f"<host-only {module}.py>", "exec"), mod.__dict__)
+    ns = types.SimpleNamespace(**{k: getattr(L, k) for k in dir(L) if not k.startswith("__")})
+    ns.load = emulated_library
+    mod.L = ns
+    fake_torch = types.SimpleNamespace(**{k: getattr(torch, k) for k in dir(torch) if not k.startswith("__")})
+    fake_torch.cuda = types.SimpleNamespace(device=lambda d: contextlib.nullcontext(),
+                                            current_stream=lambda d=None: types.SimpleNamespace(cuda_stream=0))
+    mod.torch = fake_torch
+    return mod
