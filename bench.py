@@ -407,7 +407,7 @@ def main():
     if world > 1:
         # a multi-rank run that does not finish (a lost rank, a mismatched collective) must not block the box:
         # after GS2D_BENCH_WATCHDOG_S seconds every rank gives up, rank 0 says so on stdout
-        def _watchdog(limit=float(os.environ.get("GS2D_BENCH_WATCHDOG_S", "420"))):
+        def _watchdog(limit=float(os.environ.get("GS2D_BENCH_WATCHDOG_S", "300"))):
             time.sleep(limit)
             if rank == 0:
                 print(json.dumps({"metric": METRIC, "value": None, "unit": UNIT, "n_gpus": world,
