@@ -125,6 +125,36 @@ def main():
     if kp:      # forward (56 B) and backward (24 B) launches averaged together
         kp["gbs"] = 40 * P / kp["avg_us"] / 1e3
         kp["frac_hbm"] = kp["gbs"] / peak
+    # ---- f3, second half: prune 30 % of the map (plan + move of 15 arrays) vs 15 boolean-index launches in torch
+    try:
+        keep = torch.rand(P, device=dev) < 0.7
+        kept = int(keep.sum())
+        state = {k: (opt.raw[k].clone(), opt.exp_avg[k].clone(), opt.exp_avg_sq[k].clone()) for k in bench_loops.GROUPS}
+
+        def ours_prune():
+            for k in bench_loops.GROUPS:
+                opt.raw[k], opt.exp_avg[k], opt.exp_avg_sq[k] = (t.clone() for t in state[k])
+            opt._resize()
+            opt.prune(keep)
+
+        def torch_prune():
+            for k in bench_loops.GROUPS:
+                _ = [t[keep] for t in state[k]]
+
+        def restore_only():
+            for k in bench_loops.GROUPS:
+                opt.raw[k], opt.exp_avg[k], opt.exp_avg_sq[k] = (t.clone() for t in state[k])
+            opt._resize()
+        n = max(3, a.iters // 4)
+        t_ours, t_restore, t_torch = timed(ours_prune, n), timed(restore_only, n), timed(torch_prune, n)
+        alg = 2 * P + 312 * kept
+        out["map_compact_prune"] = {"us": t_ours - t_restore, "kept": kept, "alg_bytes": alg,
+                                    "gbs": alg / max(t_ours - t_restore, 1e-3) / 1e3,
+                                    "note": "MapOptimizer.prune incl. allocation of the new tensors, the 4-byte "
+                                            "read-back and re-activation; restore cost subtracted"}
+        out["torch_boolean_index_x15"] = {"us": t_torch}
+    except Exception as e:      # first GPU run of the compaction kernels: report, do not lose the other numbers
+        out["map_compact_prune"] = {"error": f"{type(e).__name__}: {e}"}
     print(json.dumps(out))
 
 
