@@ -201,3 +201,12 @@ def test_header_is_plain_c_and_a_c_client_links(tmp_path):
     assert r.returncode == 0, r.stderr[-3000:]
     r = subprocess.run([exe], capture_output=True, text=True, timeout=120)
     assert r.returncode == 0 and r.stdout.strip(), (r.returncode, r.stdout, r.stderr)
+
+
+def test_every_kernel_id_has_a_name():
+    """bench.py indexes its per-kernel table by these names: the name table must cover the whole id range."""
+    lib = L.load()
+    n = lib.gs2d_num_kernels()
+    names = [lib.gs2d_kernel_name(i) for i in range(n)]
+    assert n >= 20 and all(names) and len(set(names)) == n
+    assert lib.gs2d_kernel_name(n) == b"?" and lib.gs2d_kernel_name(-1) == b"?"
