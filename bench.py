@@ -556,13 +556,26 @@ def main():
         for n, k in kernels.items():
             if n in traffic:
                 k["ncu_dram_bytes"] = traffic[n]
+        issue = {}
+        try:        # issue-slot utilisation per kernel from the same committed captures: what bounds the compositing kernels
+            with open(os.path.join(ROOT, "profiles", "r1_ncu_issue.json")) as f:
+                issue = json.load(f)
+        except (OSError, ValueError):
+            pass
+        for n, k in kernels.items():
+            if isinstance(issue.get(n), dict):
+                k["ncu_issue_active_pct"] = issue[n].get("issue_active_pct")
+                k["ncu_active_lanes_per_inst"] = issue[n].get("active_lanes_per_inst")
         dom = max((n for n in kernels if n in alg), key=lambda n: kernels[n]["ms_per_step"])
         roofline = {"kernel": dom, "bound": "hbm", "achieved": kernels[dom]["gbs"], "peak": peak, "unit": "GB/s",
                     "frac": kernels[dom]["frac_hbm"], "traffic": traffic.get(dom), "peak_source": peak_src,
                     "avg_launch_us": kernels[dom]["avg_us"], "alg_bytes_per_launch": kernels[dom]["alg_bytes"],
                     "share_of_step": kernels[dom]["ms_per_step"] / (ms_timed_pass / a.steps),
+                    "issue_slot_frac": (issue[dom]["issue_active_pct"] / 100.0) if isinstance(issue.get(dom), dict) else None,
+                    "active_lanes_per_inst": issue[dom].get("active_lanes_per_inst") if isinstance(issue.get(dom), dict) else None,
                     "note": "compositing is FP32-issue/MUFU-bound, not HBM-bound (DESIGN.md): the HBM fraction of this "
-                            "kernel is small by construction; see `kernels` for the HBM-bound stages",
+                            "kernel is small by construction; issue_slot_frac (ncu smsp__issue_active of the committed "
+                            "capture) is the fraction of the bound that does apply; see `kernels` for the HBM-bound stages",
                     "timed_over": f"second pass of {a.steps} steps with CUDA events around every launch "
                                   f"({ms_timed_pass / a.steps:.3f} ms/step vs {ms_per_step:.3f} untimed)"}
 
