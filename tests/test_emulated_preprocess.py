@@ -123,3 +123,75 @@ def test_look_back_scan_over_many_blocks_and_oracle_agreement(lib):
                    scale_modifier=float(case["scale_modifier"]), use_sa=case["use_sa"])
     nd = int((np.asarray(st["radii"]) != got["radii"]).sum())
     assert nd <= 20, nd
+
+
+# ---- backward preprocess (csrc/preprocess_bwd.cu) ----------------------------------------------------------------------
+def _backward(lib, case, fwd, rows):
+    f32 = lambda a: None if a is None else np.ascontiguousarray(a, np.float32)
+    P, W, H = case["means3D"].shape[0], case["W"], case["H"]
+    s = L.Settings(P=P, image_width=W, image_height=H, sh_degree=0, sh_coeffs=0, use_sa=int(case["use_sa"]), prefiltered=0,
+                   debug=0, tanfovx=float(case["tanfovx"]), tanfovy=float(case["tanfovy"]),
+                   scale_modifier=float(case["scale_modifier"]), reserved_=0.0)
+    keep = {k: f32(case[k]) for k in ("bg", "means3D", "colors", "opacities", "scales", "rotations", "viewmatrix",
+                                      "projmatrix", "campos")}
+    inp = L.Inputs(background=_ptr(keep["bg"]), means3D=_ptr(keep["means3D"]), shs=None, colors_precomp=_ptr(keep["colors"]),
+                   opacities=_ptr(keep["opacities"]), scales=_ptr(keep["scales"]), rotations=_ptr(keep["rotations"]),
+                   transMat_precomp=None, viewmatrix=_ptr(keep["viewmatrix"]), projmatrix=_ptr(keep["projmatrix"]),
+                   campos=_ptr(keep["campos"]))
+    out = dict(means2D=np.zeros((P, 3), np.float32), colors=np.zeros((P, 3), np.float32), opacity=np.zeros((P, 1), np.float32),
+               means3D=np.zeros((P, 3), np.float32), transMat=np.zeros((P, 9), np.float32), scales=np.zeros((P, 2), np.float32),
+               rotations=np.zeros((P, 4), np.float32))
+    gr = L.Grads(dL_dmeans2D=_ptr(out["means2D"]), dL_dcolors=_ptr(out["colors"]), dL_dopacity=_ptr(out["opacity"]),
+                 dL_dmeans3D=_ptr(out["means3D"]), dL_dtransMat=_ptr(out["transMat"]), dL_dsh=None,
+                 dL_dscales=_ptr(out["scales"]), dL_drotations=_ptr(out["rotations"]))
+    lib.emu_backward_preprocess.restype = C.c_int
+    lib.emu_backward_preprocess.argtypes = [C.POINTER(L.Settings), C.POINTER(L.Inputs)] + [C.c_void_p] * 5 + [C.POINTER(L.Grads)]
+    rows = np.ascontiguousarray(rows, np.float32)
+    rc = lib.emu_backward_preprocess(C.byref(s), C.byref(inp), _ptr(fwd["radii"]), _ptr(fwd["splat"]), _ptr(fwd["tiles_touched"]),
+                                     _ptr(fwd["point_offsets"]), _ptr(rows), C.byref(gr))
+    assert rc == L.GS2D_OK
+    return out
+
+
+@pytest.mark.parametrize("name", ["room_sa", "room_dist", "scale_mod"])
+def test_backward_preprocess_kernel_text_equals_the_transliteration(lib, name):
+    """The per-surfel sums of the compositing backward pass (taken from the pure-PyTorch transliteration, which is
+    pinned by the golden gradients of the compiled reference: tests/test_torch_cpu.py) are spread over each surfel's
+    gradient rows; the kernel text must reduce them and finish the chain rule (CR/backward.cu:466-664) like the
+    transliteration of the same lines does: 2e-5 of the largest magnitude per tensor, fp32 on both sides."""
+    import torch
+    import torch_cpu as T
+    g = cases.load_golden(name)
+    case = cases.case_from_golden(g)
+    fwd = _run(lib, case)
+    W, H = case["W"], case["H"]
+    a = (case["means3D"], case["opacities"], case["viewmatrix"], case["projmatrix"], W, H, case["bg"])
+    st = T.forward(*a, scales=case["scales"], rotations=case["rotations"], colors=case["colors"], campos=case["campos"],
+                   scale_modifier=float(case["scale_modifier"]), use_sa=case["use_sa"])
+    assert np.array_equal(st["radii"].numpy(), fwd["radii"])                   # same surfels, same rows
+    with torch.no_grad():
+        acc = T.render_backward(W, H, st, case["bg"], case["dL_dcolor"], case["dL_dothers"], case["use_sa"])
+        fx = np.float32(W) / (np.float32(2.0) * np.float32(case["tanfovx"]))
+        fy = np.float32(H) / (np.float32(2.0) * np.float32(case["tanfovy"]))
+        Wb, Hb = int(np.float32(fx) * np.float32(case["tanfovx"]) * np.float32(2)), int(np.float32(fy) * np.float32(case["tanfovy"]) * np.float32(2))
+        want = T.preprocess_backward(st, acc, case["means3D"], case["scales"], case["rotations"], case["viewmatrix"],
+                                     case["projmatrix"], Wb, Hb)
+    # rows: [0:9] dL/dT, [9:11] dL/dmean2D, [11] dL/dopacity, [12:15] dL/dnormal, [15:18] dL/dcolor (csrc/common.cuh)
+    P = case["means3D"].shape[0]
+    per = np.zeros((P, 20), np.float32)
+    per[:, 0:9] = acc["transMat"].numpy(); per[:, 9:11] = acc["means2D"].numpy()[:, :2]; per[:, 11] = acc["opacity"].numpy()[:, 0]
+    per[:, 12:15] = acc["normal3D"].numpy(); per[:, 15:18] = acc["colors"].numpy()
+    rows = np.zeros((fwd["num_rendered"], 20), np.float32)
+    tt = fwd["tiles_touched"].astype(np.int64)
+    first = fwd["point_offsets"].astype(np.int64) - tt
+    for i in np.nonzero(tt)[0]:
+        if tt[i] == 1:
+            rows[first[i]] = per[i]
+        else:                                   # two exact halves, first and last row of the surfel
+            rows[first[i]] = 0.5 * per[i]
+            rows[first[i] + tt[i] - 1] = 0.5 * per[i]
+    got = _backward(lib, case, fwd, rows)
+    for k in ("means3D", "scales", "rotations", "transMat", "colors", "opacity", "means2D"):
+        w = want[k].numpy().reshape(got[k].shape)
+        scale = float(np.abs(w).max())
+        assert scale > 0 and float(np.abs(got[k] - w).max()) <= 2e-5 * scale, k
