@@ -5,7 +5,7 @@
 // thread; __syncthreads* are a block-wide std::barrier; warp intrinsics (__shfl_up_sync, __shfl_down_sync,
 // __shfl_sync, __shfl_xor_sync, __ballot_sync, __any_sync, __all_sync) exchange through a per-warp buffer with a
 // per-warp barrier (full masks only: all 32 lanes must call); `__shared__` variables become function-local statics
-// (one block runs at a time).  What it does NOT model: memory ordering, bank conflicts, partial warps at a
+// (one block runs at a time), `extern __shared__` arrays a per-block buffer.  What it does NOT model: memory ordering, bank conflicts, partial warps at a
 // divergent call site, timing.  It checks arithmetic and indexing -- not performance, not hardware semantics.
 //
 // Restrictions on the kernels: every thread of a block reaches the same barriers (a thread may return early only
@@ -34,10 +34,15 @@ struct Warp {
 };
 
 struct Block {
-	explicit Block(int threads) : bar(threads), warps((threads + 31) / 32) {}
+	explicit Block(int threads, size_t dyn_smem = 0) : bar(threads), warps((threads + 31) / 32), smem_raw(dyn_smem + 256)
+	{
+		smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw.data()) + 255) & ~(uintptr_t)255);
+	}
 	std::barrier<> bar;
 	std::atomic<int> acc{0};
 	std::vector<Warp> warps;
+	std::vector<unsigned char> smem_raw;     // `extern __shared__` storage of this block (the launch's third argument)
+	unsigned char* smem;
 };
 
 inline thread_local Dim t_threadIdx, t_blockIdx;
@@ -47,13 +52,15 @@ inline thread_local Block* t_block = nullptr;
 inline Warp& warp() { return t_block->warps[t_threadIdx.x >> 5]; }
 inline int lane() { return (int)(t_threadIdx.x & 31u); }
 
-template <class F> void launch(unsigned grid, unsigned block, F&& kernel)
+inline unsigned char* dynamic_smem() { return t_block->smem; }
+
+template <class F> void launch(unsigned grid, unsigned block, size_t dyn_smem, F&& kernel)
 {
 	assert(block % 32 == 0 && block <= 1024);
 	g_blockDim = Dim{block, 1, 1};
 	g_gridDim = Dim{grid, 1, 1};
 	for (unsigned b = 0; b < grid; b++) {
-		Block ctx((int)block);
+		Block ctx((int)block, dyn_smem);
 		std::vector<std::thread> th;
 		th.reserve(block);
 		for (unsigned t = 0; t < block; t++)
@@ -66,6 +73,8 @@ template <class F> void launch(unsigned grid, unsigned block, F&& kernel)
 		for (auto& x : th) x.join();
 	}
 }
+
+template <class F> void launch(unsigned grid, unsigned block, F&& kernel) { launch(grid, block, (size_t)0, static_cast<F&&>(kernel)); }
 
 inline void syncthreads() { t_block->bar.arrive_and_wait(); }
 
@@ -111,6 +120,17 @@ inline unsigned ballot(int pred)
 	return r;
 }
 
+inline unsigned match_any(unsigned v)
+{
+	Warp& w = warp();
+	w.slot[lane()] = (long long)v;
+	w.bar.arrive_and_wait();
+	unsigned r = 0;
+	for (int l = 0; l < 32; l++) r |= (unsigned)(w.slot[l] == (long long)v) << l;
+	w.bar.arrive_and_wait();
+	return r;
+}
+
 }  // namespace cuda_emu
 
 // ---- the CUDA spellings the kernel text uses ------------------------------------------------------------------------
@@ -121,6 +141,7 @@ inline unsigned ballot(int pred)
 #define __restrict__
 #define __launch_bounds__(...)
 #define __shared__ static
+#define __constant__ static
 #define threadIdx cuda_emu::t_threadIdx
 #define blockIdx cuda_emu::t_blockIdx
 #define blockDim cuda_emu::g_blockDim
@@ -138,4 +159,5 @@ template <class T> T __shfl_xor_sync(unsigned mask, T v, int m) { EMU_FULL(mask)
 template <class T> T __shfl_sync(unsigned mask, T v, int s) { EMU_FULL(mask); return cuda_emu::shfl_idx(v, s); }
 inline unsigned __ballot_sync(unsigned mask, int p) { EMU_FULL(mask); return cuda_emu::ballot(p); }
 inline int __any_sync(unsigned mask, int p) { EMU_FULL(mask); return cuda_emu::ballot(p) != 0; }
+inline unsigned __match_any_sync(unsigned mask, unsigned v) { EMU_FULL(mask); return cuda_emu::match_any(v); }
 inline int __all_sync(unsigned mask, int p) { EMU_FULL(mask); return cuda_emu::ballot(p) == 0xffffffffu; }

@@ -61,6 +61,15 @@ inline float __int_as_float(int v) { float f; std::memcpy(&f, &v, 4); return f; 
 inline int __float_as_int(float f) { int v; std::memcpy(&v, &f, 4); return v; }
 inline unsigned __float_as_uint(float f) { unsigned v; std::memcpy(&v, &f, 4); return v; }
 inline float __uint_as_float(unsigned v) { float f; std::memcpy(&f, &v, 4); return f; }
+inline unsigned __byte_perm(unsigned x, unsigned y, unsigned s)
+{
+	const unsigned long long src = ((unsigned long long)y << 32) | x;
+	unsigned r = 0;
+	for (int i = 0; i < 4; i++) r |= (unsigned)((src >> (8 * ((s >> (4 * i)) & 7u))) & 0xffu) << (8 * i);
+	return r;
+}
+inline unsigned __brev(unsigned x) { unsigned r = 0; for (int i = 0; i < 32; i++) r |= ((x >> i) & 1u) << (31 - i); return r; }
+inline float __saturatef(float x) { return std::fmin(std::fmax(x, 0.0f), 1.0f); }
 inline int __ffs(unsigned x) { return __builtin_ffs((int)x); }
 [[noreturn]] inline void __trap() { std::abort(); }
 template <class T> inline T __ldg(const T* p) { return *p; }
@@ -77,6 +86,27 @@ inline int atomicAdd(int* p, int v) { return __atomic_fetch_add(p, v, __ATOMIC_S
 inline unsigned long long atomicAdd(unsigned long long* p, unsigned long long v) { return __atomic_fetch_add(p, v, __ATOMIC_SEQ_CST); }
 inline unsigned long long atomicExch(unsigned long long* p, unsigned long long v) { return __atomic_exchange_n(p, v, __ATOMIC_SEQ_CST); }
 inline unsigned atomicExch(unsigned* p, unsigned v) { return __atomic_exchange_n(p, v, __ATOMIC_SEQ_CST); }
+template <class T, class Op> inline T atomic_rmw_emu(T* p, Op op)
+{
+	T old = __atomic_load_n(p, __ATOMIC_SEQ_CST);
+	while (!__atomic_compare_exchange_n(p, &old, op(old), false, __ATOMIC_SEQ_CST, __ATOMIC_SEQ_CST)) {}
+	return old;
+}
+inline unsigned atomicMin(unsigned* p, unsigned v) { return atomic_rmw_emu(p, [v](unsigned o) { return o < v ? o : v; }); }
+inline unsigned atomicMax(unsigned* p, unsigned v) { return atomic_rmw_emu(p, [v](unsigned o) { return o > v ? o : v; }); }
+inline int atomicMin(int* p, int v) { return atomic_rmw_emu(p, [v](int o) { return o < v ? o : v; }); }
+inline int atomicMax(int* p, int v) { return atomic_rmw_emu(p, [v](int o) { return o > v ? o : v; }); }
+inline unsigned atomicOr(unsigned* p, unsigned v) { return __atomic_fetch_or(p, v, __ATOMIC_SEQ_CST); }
+inline unsigned atomicAnd(unsigned* p, unsigned v) { return __atomic_fetch_and(p, v, __ATOMIC_SEQ_CST); }
+inline float atomicAdd(float* p, float v)
+{
+	unsigned* u = reinterpret_cast<unsigned*>(p);
+	unsigned old = __atomic_load_n(u, __ATOMIC_SEQ_CST), upd;
+	float f;
+	do { std::memcpy(&f, &old, 4); f += v; std::memcpy(&upd, &f, 4); } while (!__atomic_compare_exchange_n(u, &old, upd, false, __ATOMIC_SEQ_CST, __ATOMIC_SEQ_CST));
+	std::memcpy(&f, &old, 4);
+	return f;
+}
 inline void __threadfence() { std::atomic_thread_fence(std::memory_order_seq_cst); }
 
 // ---- runtime ----------------------------------------------------------------------------------------------------------
@@ -89,3 +119,10 @@ inline cudaError_t cudaGetLastError() { return cudaSuccess; }
 inline cudaError_t cudaMemsetAsync(void* p, int v, size_t n, cudaStream_t) { std::memset(p, v, n); return cudaSuccess; }
 inline cudaError_t cudaMemcpyAsync(void* d, const void* s, size_t n, cudaMemcpyKind, cudaStream_t) { std::memcpy(d, s, n); return cudaSuccess; }
 inline cudaError_t cudaStreamSynchronize(cudaStream_t) { return cudaSuccess; }
+inline cudaError_t cudaEventCreate(cudaEvent_t* e) { *e = nullptr; return cudaSuccess; }
+inline cudaError_t cudaEventRecord(cudaEvent_t, cudaStream_t) { return cudaSuccess; }
+inline cudaError_t cudaEventSynchronize(cudaEvent_t) { return cudaSuccess; }
+inline cudaError_t cudaEventElapsedTime(float* ms, cudaEvent_t, cudaEvent_t) { *ms = 0.f; return cudaSuccess; }
+inline cudaError_t cudaMemset(void* p, int v, size_t n) { std::memset(p, v, n); return cudaSuccess; }
+enum cudaFuncAttribute { cudaFuncAttributeMaxDynamicSharedMemorySize };
+template <class K> inline cudaError_t cudaFuncSetAttribute(K, cudaFuncAttribute, int) { return cudaSuccess; }
