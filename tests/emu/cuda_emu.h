@@ -59,19 +59,23 @@ template <class F> void launch(unsigned grid, unsigned block, size_t dyn_smem, F
 	assert(block % 32 == 0 && block <= 1024);
 	g_blockDim = Dim{block, 1, 1};
 	g_gridDim = Dim{grid, 1, 1};
-	for (unsigned b = 0; b < grid; b++) {
-		Block ctx((int)block, dyn_smem);
-		std::vector<std::thread> th;
-		th.reserve(block);
-		for (unsigned t = 0; t < block; t++)
-			th.emplace_back([&, t, b] {
-				t_threadIdx = Dim{t, 0, 0};
+	if (grid == 0) return;
+	// one set of host threads per launch; they walk the blocks together (a barrier after every block)
+	Block ctx((int)block, dyn_smem);
+	std::barrier<> block_done((std::ptrdiff_t)block);
+	std::vector<std::thread> th;
+	th.reserve(block);
+	for (unsigned t = 0; t < block; t++)
+		th.emplace_back([&, t] {
+			t_threadIdx = Dim{t, 0, 0};
+			t_block = &ctx;
+			for (unsigned b = 0; b < grid; b++) {
 				t_blockIdx = Dim{b, 0, 0};
-				t_block = &ctx;
 				kernel();
-			});
-		for (auto& x : th) x.join();
-	}
+				block_done.arrive_and_wait();
+			}
+		});
+	for (auto& x : th) x.join();
 }
 
 template <class F> void launch(unsigned grid, unsigned block, F&& kernel) { launch(grid, block, (size_t)0, static_cast<F&&>(kernel)); }
