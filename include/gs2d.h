@@ -217,7 +217,9 @@ int gs2d_state_view_get(const gs2d_settings* s, const gs2d_buffers* buffers,
 int gs2d_footprint_audit(const gs2d_settings* s, const gs2d_buffers* buffers, int64_t num_rendered,
                          uint64_t* counts_host, void* stream);
 
-/* Stand-alone stable LSD radix sort of (u64 key, u32 value) pairs on bits [0, end_bit):
+/* Stand-alone stable LSD radix sort of (u64 key, u32 value) pairs on bits [0, end_bit) -- sorted in whole 8-bit
+ * digits, i.e. on bits [0, 8 * ceil(end_bit / 8)): keys must have no bit set at or above end_bit (the rasterizer's
+ * and the Morton keys do not) for the result to equal a sort on [0, end_bit) --:
  * the hand-written onesweep that replaces cub::DeviceRadixSort::SortPairs
  * (CR/rasterizer_impl.cu:309-314).  scratch: gs2d_sort_scratch_bytes(n). */
 size_t gs2d_sort_scratch_bytes(int64_t n);

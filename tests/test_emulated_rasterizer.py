@@ -67,3 +67,50 @@ def test_release_path_equals_debug_path():
     for k in compare.GRADS:
         if a["grad_" + k].size:
             assert compare.grad_rel(b["grad_" + k], a["grad_" + k]) < 1e-5, k
+
+
+# ---- the rest of the rasterizer's API surface on the host build --------------------------
+def test_mark_visible_matches_the_reference():
+    import ctypes as C
+    import emu_run
+    lib = emu_run.library()
+    g = cases.load_golden("mark_visible")
+    pts = np.ascontiguousarray(g["in_means3D"], np.float32)
+    view, proj = np.ascontiguousarray(g["in_viewmatrix"], np.float32), np.ascontiguousarray(g["in_projmatrix"], np.float32)
+    present = np.full(pts.shape[0], 7, np.uint8)
+    assert lib.gs2d_mark_visible(pts.shape[0], emu_run._ptr(pts), emu_run._ptr(view), emu_run._ptr(proj),
+                                 emu_run._ptr(present), None) == 0
+    assert np.array_equal(present.astype(bool), g["ref_present"])
+
+
+@pytest.mark.parametrize("name", cases.KNN_CASES)
+def test_dist2_matches_the_reference_simple_knn(name):
+    """distCUDA2 (Morton sort by the hand-written onesweep, box search): bit for bit against the reference's output --
+    squared distances are sums of products with no approximate device instruction in them."""
+    import emu_run
+    lib = emu_run.library()
+    g = cases.load_golden(name)
+    pts = np.ascontiguousarray(g["in_points"], np.float32)
+    P = pts.shape[0]
+    out = np.full(P, np.nan, np.float32)
+    scratch = emu_run._garbage(lib.gs2d_dist2_scratch_bytes(P))
+    assert lib.gs2d_dist2(P, emu_run._ptr(pts), emu_run._ptr(out), emu_run._ptr(scratch), None) == 0
+    assert compare.bits_differ(out, g["ref_dist2"]) == 0, f"max abs {np.abs(out - g['ref_dist2']).max():.3e}"
+
+
+@pytest.mark.parametrize("n,end_bit", [(1, 40), (2047, 44), (2049, 44), (10000, 45), (5000, 17)])
+def test_onesweep_sort_is_the_stable_sort_of_the_low_bits(n, end_bit):
+    """gs2d_sort_pairs = cub::DeviceRadixSort::SortPairs(begin_bit 0, end_bit) (CR/rasterizer_impl.cu:309-314)."""
+    import emu_run
+    lib = emu_run.library()
+    rng = np.random.default_rng(n)
+    # keys as the rasterizer makes them: nothing set at or above end_bit (whole 8-bit digits are sorted, include/gs2d.h)
+    keys = rng.integers(0, 1 << end_bit, n, dtype=np.uint64)
+    keys[rng.uniform(size=n) < 0.3] &= np.uint64(0xFF)                         # many equal keys: stability matters
+    vals = np.arange(n, dtype=np.uint32)
+    ko, vo = np.zeros(n, np.uint64), np.zeros(n, np.uint32)
+    scratch = emu_run._garbage(lib.gs2d_sort_scratch_bytes(n))
+    assert lib.gs2d_sort_pairs(n, emu_run._ptr(keys), emu_run._ptr(vals), emu_run._ptr(ko), emu_run._ptr(vo), end_bit,
+                               emu_run._ptr(scratch), None) == 0
+    order = np.argsort(keys, kind="stable")
+    assert np.array_equal(vo, vals[order]) and np.array_equal(ko, keys[order])
