@@ -137,8 +137,11 @@ static int check_common(const gs2d_settings* s, const gs2d_inputs* in, const gs2
 {
 	if (!s || !in || !b) return GS2D_ERR_INVALID;
 	if (s->P < 0 || s->image_width <= 0 || s->image_height <= 0) return GS2D_ERR_INVALID;
-	if (!in->means3D || !in->opacities || !in->viewmatrix || !in->projmatrix || !in->background)
-		return GS2D_ERR_INVALID;
+	if (!in->viewmatrix || !in->projmatrix || !in->background) return GS2D_ERR_INVALID;
+	// an empty map (P == 0) has empty per-surfel tensors, which arrive as NULL: nothing to check, the image is the
+	// background (the reference short-circuits too, RAST/rasterize_points.cu:101)
+	if (s->P == 0) return GS2D_OK;
+	if (!in->means3D || !in->opacities) return GS2D_ERR_INVALID;
 	if ((in->shs == nullptr) == (in->colors_precomp == nullptr)) return GS2D_ERR_INVALID;
 	const bool have_sr = in->scales != nullptr && in->rotations != nullptr;
 	if (have_sr == (in->transMat_precomp != nullptr)) return GS2D_ERR_INVALID;

@@ -114,3 +114,49 @@ def test_onesweep_sort_is_the_stable_sort_of_the_low_bits(n, end_bit):
                                emu_run._ptr(scratch), None) == 0
     order = np.argsort(keys, kind="stable")
     assert np.array_equal(vo, vals[order]) and np.array_equal(ko, keys[order])
+
+
+# ---- edge shapes against the C restatement (the reference has no golden for them) ---------------------------------------
+def _oracle(case):
+    import cpu as O
+    a = (case["means3D"], case["opacities"], case["viewmatrix"], case["projmatrix"], case["W"], case["H"], case["bg"])
+    st = O.forward(*a, scales=case["scales"], rotations=case["rotations"], colors=case["colors"], campos=case["campos"],
+                   scale_modifier=float(case["scale_modifier"]), use_sa=case["use_sa"])
+    g = O.backward(st, case["means3D"], case["viewmatrix"], case["projmatrix"], case["W"], case["H"], float(case["tanfovx"]),
+                   float(case["tanfovy"]), case["bg"], case["dL_dcolor"], case["dL_dothers"], scales=case["scales"],
+                   rotations=case["rotations"], campos=case["campos"], use_sa=case["use_sa"])
+    out = {k: np.asarray(v) for k, v in st.items()}
+    out.update({"grad_" + k: np.asarray(v) for k, v in g.items()})
+    out["transMat"] = out["transMat_used"]
+    return out
+
+
+@pytest.mark.parametrize("P,size,seed,use_sa", [
+    (1, (16, 16), 0, True), (5, (1, 1), 1, True), (300, (33, 17), 2, True), (300, (17, 33), 3, False),
+    (800, (250, 3), 4, True), (500, (15, 15), 5, False), (300, (129, 65), 8, False), (50, (1200, 8), 9, True)])
+def test_ragged_and_tiny_images_against_the_c_restatement(P, size, seed, use_sa):
+    """One surfel, one pixel, images narrower than a tile, one tile row of 75 tiles, non-zero background; debug and
+    release paths alternate.  The oracle may place a radius across an integer boundary for a handful of surfels
+    (oracle/gs2d_oracle.c header): binning is compared only when the radii agree, images and gradients always."""
+    import emu_run
+    case = cases._base(P, cases._intr(*size), seed=seed, view=seed % 3, use_sa=use_sa,
+                       bg=(0.1, 0.2, 0.3) if seed % 2 else (0.0, 0.0, 0.0))
+    out = emu_run.run_ours(case, debug=bool(seed % 2), backward=True)
+    want = _oracle(case)
+    fails = compare.check_images_oracle(out, want, use_sa)
+    fails += compare.check_grads(out, want, rtol=compare.ORACLE_SA_GRAD_RTOL if use_sa else compare.GRAD_RTOL)
+    if np.array_equal(out["radii"], want["radii"]):
+        fails += compare.check_binning(out, want)
+    assert not fails, "\n".join(fails)
+    assert int(out["footprint_audit"][2]) == 0
+
+
+def test_empty_map_through_the_abi():
+    """P = 0: nothing is launched that reads a surfel; the image is the background, alpha 0 (rasterize_points.cu:101)."""
+    import emu_run
+    case = cases._base(4, cases._intr(40, 24), seed=0, view=0, bg=(0.25, 0.5, 0.75))
+    for k in ("means3D", "scales", "rotations", "opacities", "colors"):
+        case[k] = case[k][:0]
+    out = emu_run.run_ours(case, debug=False, backward=True)
+    assert int(out["num_rendered"]) == 0
+    assert np.allclose(out["color"], np.array([0.25, 0.5, 0.75], np.float32)[:, None, None]) and not out["others"][1].any()
