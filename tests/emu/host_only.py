@@ -57,3 +57,44 @@ def load(module: str):
                                             current_stream=lambda d=None: types.SimpleNamespace(cuda_stream=0))
     mod.torch = fake_torch
     return mod
+
+
+class _FakeEvent:
+    def record(self, stream=None):
+        pass
+
+    def synchronize(self):
+        pass
+
+
+def _fake_torch():
+    fake = types.SimpleNamespace(**{k: getattr(torch, k) for k in dir(torch) if not k.startswith("__")})
+    fake.cuda = types.SimpleNamespace(device=lambda d: contextlib.nullcontext(), Event=_FakeEvent,
+                                      current_stream=lambda d=None: types.SimpleNamespace(cuda_stream=0))
+    return fake
+
+
+def load_rasterizer():
+    """The drop-in package gaus_2dgs_rasterization (its _C glue and its autograd bridge) as host-only modules over
+    libgs2d_emu_full.so: `is_cuda` checks and `.pin_memory()` removed textually, torch.cuda replaced by no-ops."""
+    sys.path.insert(0, HERE)
+    import emu_run
+    pkg = os.path.join(ROOT, "gaus-slam_b200", "gaus_2dgs_rasterization")
+    src = open(os.path.join(pkg, "_C.py")).read()
+    src, n = re.subn(r"    if not t\.is_cuda:\n        raise RuntimeError\([^\n]*\)\n", "", src)
+    assert n == 1 and "is_cuda" not in src
+    src = src.replace(".pin_memory()", "")
+    src = src.replace("from gs2d_b200 import _lib as L", "L = None")
+    glue = types.ModuleType("gaus_2dgs_rasterization_host_only._C")
+    exec(compile(src, "<host-only _C.py>", "exec"), glue.__dict__)
+    ns = types.SimpleNamespace(**{k: getattr(L, k) for k in dir(L) if not k.startswith("__")})
+    ns.load = emu_run.library
+    glue.L, glue.torch = ns, _fake_torch()
+    src = open(os.path.join(pkg, "__init__.py")).read()
+    assert "from . import _C" in src
+    src = src.replace("from . import _C", "_C = None")
+    mod = types.ModuleType("gaus_2dgs_rasterization_host_only")
+    mod.__file__ = os.path.join(pkg, "__init__.py")
+    exec(compile(src, "<host-only gaus_2dgs_rasterization/__init__.py>", "exec"), mod.__dict__)
+    mod._C = glue
+    return mod
