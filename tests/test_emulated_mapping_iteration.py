@@ -100,3 +100,50 @@ def test_one_mapping_iteration_end_to_end():
     for k in R.GROUPS:
         assert float((opt.raw[k] - before[k]).abs().max()) > 0, k
         assert np.abs(opt.raw[k].numpy() - st[k]).max() <= 2e-6 * max(np.abs(st[k]).max(), 1e-30), k
+
+
+def test_one_tracking_iteration_end_to_end():
+    """Frontend.tracking's body (render/__init__.py:22-50, slam/Loss.py:35-47): pose scalars -> fused pose transform ->
+    rasterizer with an identity camera -> fused tracking loss -> backward down to dL/dcam_rot, dL/dcam_trans.
+    Reference pipeline: the torch transliteration of the pose path, the C restatement of the rasterizer, the
+    transliterated tracking loss."""
+    import host_only
+    import pose_ref
+    G, tracking, loss = host_only.load_rasterizer(), host_only.load("tracking"), host_only.load("loss")
+    case = cases.room_sa()
+    P, W, H = case["means3D"].shape[0], case["W"], case["H"]
+    rng = np.random.default_rng(11)
+    gt_color = rng.uniform(0, 1, (H, W, 3)).astype(np.float32)
+    gt_depth = rng.uniform(0.5, 4.0, (H, W, 1)).astype(np.float32)
+    t = lambda a, rg=False: torch.tensor(np.ascontiguousarray(a, np.float32), requires_grad=rg)      # noqa: E731
+    # the golden view as the pose: w2c = viewmatrix^T (column-major storage), camera at identity afterwards
+    w2c = np.ascontiguousarray(case["viewmatrix"].reshape(4, 4).T)
+    q0 = pose_ref.matrix_to_quaternion(torch.tensor(w2c[None, :3, :3], dtype=torch.float64))[0].numpy() * 1.3   # unnormalised
+    t0 = w2c[:3, 3]
+    ident = dict(case, viewmatrix=np.eye(4, dtype=np.float32).reshape(16), campos=np.zeros(3, np.float32))
+    proj = case["projmatrix"].reshape(4, 4).T @ np.linalg.inv(w2c.astype(np.float64))              # P V -> P (identity view)
+    ident["projmatrix"] = np.ascontiguousarray(proj.T.astype(np.float32)).reshape(16)
+    xyz, rot = t(case["means3D"]), t(case["rotations"])
+
+    q, tr = t(q0, True), t(t0, True)
+    means, rots = tracking.pose_transform(xyz, rot, cam_rot=q, cam_trans=tr)
+    rs = G.GaussianRasterizationSettings(image_height=H, image_width=W, tanfovx=float(case["tanfovx"]), tanfovy=float(case["tanfovy"]),
+                                         bg=t(case["bg"]), scale_modifier=1.0, viewmatrix=t(ident["viewmatrix"]).view(4, 4),
+                                         projmatrix=t(ident["projmatrix"]).view(4, 4), sh_degree=0, campos=t(ident["campos"]),
+                                         use_sa=True, prefiltered=False, debug=False)
+    color, radii, allmap = G.GaussianRasterizer(rs)(means3D=means, means2D=torch.zeros((P, 3), requires_grad=True),
+                                                    opacities=t(case["opacities"]), colors_precomp=t(case["colors"]),
+                                                    scales=t(case["scales"]), rotations=rots)
+    value = loss.tracking_loss(color, allmap, t(gt_color), t(gt_depth), silmask_th=0.5)
+    value.backward()
+
+    rq, rt = t(q0, True), t(t0, True)
+    rm, rr = pose_ref.pose_transform_torch(xyz, rot, pose_ref.get_transform_matrix(rq, rt))
+    rc, ro = _OracleRasterizer.apply(rm, t(case["opacities"]), t(case["scales"]), rr, t(case["colors"]), ident)
+    rv = loss_ref.tracking_loss_torch(rc, ro, t(gt_color), t(gt_depth), silmask_th=0.5)
+    rv.backward()
+    assert int((radii > 0).sum()) > P // 2                                  # the scene is in view under the pose
+    assert abs(float(value.detach()) - float(rv.detach())) <= 1e-3 * abs(float(rv.detach()))
+    for got, want in ((q.grad, rq.grad), (tr.grad, rt.grad)):
+        scale = float(want.abs().max())
+        assert scale > 0 and float((got - want).abs().max()) <= 3 * compare.ORACLE_SA_GRAD_RTOL * scale
