@@ -7,6 +7,7 @@
 // through one mutex; waiters poll and yield.
 #pragma once
 #include <cstdint>
+#include <chrono>
 #include <cstring>
 #include <mutex>
 #include <thread>
@@ -53,7 +54,11 @@ inline void mbar_arrive_expect_tx(uint64_t* bar, uint32_t bytes)
 // try_wait.parity(p): true once the phase of parity p has completed, i.e. the current phase has the other parity
 inline void mbar_wait(uint64_t* bar, uint32_t parity)
 {
-	while (tma_emu::load(bar).phase == (uint8_t)(parity & 1u)) std::this_thread::yield();
+	// hundreds of waiters share a few host cores with the one thread that issues the copies: back off quickly
+	for (int spins = 0; tma_emu::load(bar).phase == (uint8_t)(parity & 1u); spins++) {
+		if (spins < 4) std::this_thread::yield();
+		else std::this_thread::sleep_for(std::chrono::microseconds(spins < 64 ? 20 : 200));
+	}
 }
 
 inline void tma_load_1d(void* smem_dst, const void* gmem_src, uint32_t bytes, uint64_t* bar)

@@ -49,7 +49,7 @@ class _OracleRasterizer(torch.autograd.Function):
 def test_one_mapping_iteration_end_to_end():
     import host_only
     G, optim, loss = host_only.load_rasterizer(), host_only.load("optim"), host_only.load("loss")
-    case = cases.room_sa()
+    case = cases._base(1200, cases._intr(96, 64), seed=1, view=1)          # room_sa's view at a size the emulator walks in seconds
     P, W, H = case["means3D"].shape[0], case["W"], case["H"]
     rng = np.random.default_rng(5)
     raw = dict(xyz=case["means3D"], opacity=np.log(case["opacities"] / (1 - case["opacities"])).astype(np.float32),
@@ -110,7 +110,7 @@ def test_one_tracking_iteration_end_to_end():
     import host_only
     import pose_ref
     G, tracking, loss = host_only.load_rasterizer(), host_only.load("tracking"), host_only.load("loss")
-    case = cases.room_sa()
+    case = cases._base(1200, cases._intr(96, 64), seed=1, view=1)          # room_sa's view at a size the emulator walks in seconds
     P, W, H = case["means3D"].shape[0], case["W"], case["H"]
     rng = np.random.default_rng(11)
     gt_color = rng.uniform(0, 1, (H, W, 3)).astype(np.float32)

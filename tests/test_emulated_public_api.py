@@ -36,7 +36,7 @@ def _settings(G, case, debug=False):
         use_sa=case["use_sa"], prefiltered=False, debug=debug)
 
 
-@pytest.mark.parametrize("name", ["room_sa", "sh_deg2", "transmat_pre"])
+@pytest.mark.parametrize("name", cases.GOLDEN_CASES if os.environ.get("GS2D_EMU_ALL") else ["sh_deg2", "transmat_pre"])
 def test_public_api_forward_and_autograd_match_the_compiled_reference(G, name):
     g = cases.load_golden(name)
     case = cases.case_from_golden(g)

@@ -14,7 +14,7 @@ mbarrier / bulk-copy PTX is replaced by tests/emu/tma_emu.cuh, the L2 discard hi
 arithmetic, indexing and control flow of the kernels as written -- a gate for kernel edits where there is no GPU --
 not performance, memory ordering or hardware behaviour; the GPU tests remain the parity tests proper.
 
-The default run takes the cases that cover every branch in about a minute and a half; GS2D_EMU_ALL=1 runs all of them."""
+The default run takes the cases that cover every branch (about a minute); GS2D_EMU_ALL=1 runs all of them."""
 import os
 import shutil
 import sys
@@ -30,7 +30,7 @@ sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "emu
 pytestmark = pytest.mark.skipif(shutil.which("g++") is None, reason="needs g++ (C++20) for the host build of the kernels")
 
 # surface-aware, 2DGS distortion branch, SH colours, precomputed transform, nothing visible
-DEFAULT = ["room_sa", "room_dist", "sh_deg2", "transmat_pre", "behind"]
+DEFAULT = ["room_sa", "room_dist", "sh_deg2", "behind"]          # transmat_pre: tests/test_emulated_public_api.py
 CASES = cases.GOLDEN_CASES if os.environ.get("GS2D_EMU_ALL") else DEFAULT
 
 
