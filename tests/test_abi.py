@@ -100,10 +100,11 @@ def test_rasterizer_argument_errors():
 
 
 def test_product_never_touches_the_oracle():
-    """The shipped package must not import, link or execute anything under oracle/."""
+    """The shipped package must not import, link or execute anything under oracle/ -- nor the host emulation of its
+    own kernels under tests/emu (a CPU pre-check for the tests, never a fallback)."""
     pkg = os.path.join(ROOT, "gaus-slam_b200")
     bad = re.compile(r"libgs2d_oracle|libgs2d_ref|gs2d_oracle\.c|import\s+refgpu|import\s+cpu\b|from\s+oracle|oracle[/\\]|"
-                     r"[\"']oracle[\"']")
+                     r"[\"']oracle[\"']|libgs2d_emu|cuda_emu|build_emu|host_only|tests[/\\]emu")
     for d, _, files in os.walk(pkg):
         for f in files:
             if f.endswith((".py", ".cu", ".cuh", ".h", ".cpp")):
