@@ -93,3 +93,27 @@ def test_argument_errors_are_the_reference_ones(G):
         rast(means3D=m3, means2D=m2, opacities=op, colors_precomp=col)
     with pytest.raises(RuntimeError, match="num_points, 3"):
         rast(means3D=m3[:, :2], means2D=m2, opacities=op, colors_precomp=col, scales=sc, rotations=rot)
+
+
+def test_early_scatter_arena_paths_give_the_same_frame(G):
+    """Release mode overlaps the host's wait for num_rendered with the scatter into an arena sized from earlier frames
+    (gs2d_forward_scatter_early / _render_scattered).  Three paths -- no arena yet, arena too small (a bigger scene
+    arrives), arena large enough -- must produce the same frame bit for bit."""
+    def frame(case):
+        P = case["means3D"].shape[0]
+        color, radii, allmap = G.GaussianRasterizer(_settings(G, case))(
+            means3D=_t(case["means3D"]), means2D=torch.zeros((P, 3)), opacities=_t(case["opacities"]),
+            colors_precomp=_t(case["colors"]), scales=_t(case["scales"]), rotations=_t(case["rotations"]))
+        return color.numpy().copy(), allmap.numpy().copy(), radii.numpy().copy()
+    G._C._arenas.clear()
+    small = cases._base(300, cases._intr(64, 48), seed=3, view=0)
+    big = cases._base(1500, cases._intr(64, 48), seed=4, view=1, scale_mult=2.0)
+    frame(small)                                   # no arena yet -> one is sized from this frame
+    assert len(G._C._arenas) == 1
+    key = next(iter(G._C._arenas))
+    G._C._arenas[key] = (G._C._arenas[key][0][:64], 64)     # the smallest real arena holds 2^18 words: shrink it by hand
+    a = frame(big)                                 # arena too small: scatter after the wait, arena grows
+    assert G._C._arenas[key][1] > 64
+    b = frame(big)                                 # early scatter into the arena
+    for x, y in zip(a, b):
+        assert np.array_equal(x.view(np.uint32) if x.dtype == np.float32 else x, y.view(np.uint32) if y.dtype == np.float32 else y)
