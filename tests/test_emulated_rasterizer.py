@@ -160,3 +160,42 @@ def test_empty_map_through_the_abi():
     out = emu_run.run_ours(case, debug=False, backward=True)
     assert int(out["num_rendered"]) == 0
     assert np.allclose(out["color"], np.array([0.25, 0.5, 0.75], np.float32)[:, None, None]) and not out["others"][1].any()
+
+
+def test_one_call_forward_and_its_capacity_protocol():
+    """gs2d_forward (the reference's control flow for a plain-C caller): *num_rendered_io carries the provisioned
+    capacity in and the count out; GS2D_ERR_CAPACITY when it does not fit, then the same frame as the staged calls."""
+    import ctypes as C
+    import emu_run
+    from gs2d_b200 import _lib as L
+    lib = emu_run.library()
+    case = cases.case_from_golden(cases.load_golden("sh_deg2"))
+    staged = emu_run.run_ours(case, debug=False, backward=False)
+    n = int(staged["num_rendered"])
+    P, W, H, M = case["means3D"].shape[0], case["W"], case["H"], case["shs"].shape[1]
+    f32 = lambda a: None if a is None else np.ascontiguousarray(a, np.float32)      # noqa: E731
+    k = {x: f32(case[x]) for x in ("bg", "means3D", "shs", "opacities", "scales", "rotations", "viewmatrix", "projmatrix", "campos")}
+    s = L.Settings(P=P, image_width=W, image_height=H, sh_degree=int(case["sh_degree"]), sh_coeffs=M, use_sa=int(case["use_sa"]),
+                   prefiltered=0, debug=0, tanfovx=float(case["tanfovx"]), tanfovy=float(case["tanfovy"]),
+                   scale_modifier=float(case["scale_modifier"]), reserved_=0.0)
+    p = emu_run._ptr
+    inp = L.Inputs(background=p(k["bg"]), means3D=p(k["means3D"]), shs=p(k["shs"]), colors_precomp=None, opacities=p(k["opacities"]),
+                   scales=p(k["scales"]), rotations=p(k["rotations"]), transMat_precomp=None, viewmatrix=p(k["viewmatrix"]),
+                   projmatrix=p(k["projmatrix"]), campos=p(k["campos"]))
+    geom, img = emu_run._garbage(lib.gs2d_geom_bytes(P, M)), emu_run._garbage(lib.gs2d_image_bytes(W, H))
+    radii = np.zeros(P, np.int32)
+    color, others = np.full((3, H, W), np.nan, np.float32), np.full((7, H, W), np.nan, np.float32)
+
+    def call(capacity):
+        binning = emu_run._garbage(lib.gs2d_binning_bytes(capacity, W, H))
+        bufs = L.Buffers(geom=p(geom), geom_bytes=geom.size, binning=p(binning), binning_bytes=binning.size, image=p(img),
+                         image_bytes=img.size)
+        io = C.c_int64(capacity)
+        rc = lib.gs2d_forward(C.byref(s), C.byref(inp), C.byref(bufs), p(radii), C.byref(io), p(color), p(others), None)
+        return rc, int(io.value)
+    rc, count = call(n // 2)
+    assert rc == L.GS2D_ERR_CAPACITY and count == n
+    rc, count = call(n + 100)
+    assert rc == L.GS2D_OK and count == n
+    assert np.array_equal(radii, staged["radii"])
+    assert not compare.check_images(dict(color=color, others=others), staged, exact=True)
