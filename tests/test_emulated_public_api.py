@@ -117,3 +117,24 @@ def test_early_scatter_arena_paths_give_the_same_frame(G):
     b = frame(big)                                 # early scatter into the arena
     for x, y in zip(a, b):
         assert np.array_equal(x.view(np.uint32) if x.dtype == np.float32 else x, y.view(np.uint32) if y.dtype == np.float32 else y)
+
+
+def test_debug_mode_dumps_the_arguments_on_failure_like_the_reference(G, tmp_path, monkeypatch):
+    """debug=True: a failing forward leaves `snapshot_fw.dump` (the CPU copy of its arguments) in the working
+    directory and re-raises (RAST/gaus_2dgs_rasterization/__init__.py:83-93)."""
+    monkeypatch.chdir(tmp_path)
+    case = cases.room_sa()
+    P = case["means3D"].shape[0]
+    rast = G.GaussianRasterizer(_settings(G, case, debug=True))
+    with pytest.raises(RuntimeError, match="num_points, 3"):
+        rast(means3D=_t(case["means3D"])[:, :2], means2D=torch.zeros((P, 3)), opacities=_t(case["opacities"]),
+             colors_precomp=_t(case["colors"]), scales=_t(case["scales"]), rotations=_t(case["rotations"]))
+    dump = torch.load(os.path.join(tmp_path, "snapshot_fw.dump"), weights_only=False)
+    assert isinstance(dump, tuple) and len(dump) == 20 and dump[1].shape == (P, 2) and dump[13] == case["W"]
+    # and a healthy debug frame (per-stage checks on) equals the release frame
+    a = rast(means3D=_t(case["means3D"]), means2D=torch.zeros((P, 3)), opacities=_t(case["opacities"]),
+             colors_precomp=_t(case["colors"]), scales=_t(case["scales"]), rotations=_t(case["rotations"]))
+    b = G.GaussianRasterizer(_settings(G, case))(means3D=_t(case["means3D"]), means2D=torch.zeros((P, 3)),
+                                                 opacities=_t(case["opacities"]), colors_precomp=_t(case["colors"]),
+                                                 scales=_t(case["scales"]), rotations=_t(case["rotations"]))
+    assert torch.equal(a[0], b[0]) and torch.equal(a[2], b[2]) and torch.equal(a[1], b[1])
