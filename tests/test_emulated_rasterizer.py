@@ -199,3 +199,19 @@ def test_one_call_forward_and_its_capacity_protocol():
     assert rc == L.GS2D_OK and count == n
     assert np.array_equal(radii, staged["radii"])
     assert not compare.check_images(dict(color=color, others=others), staged, exact=True)
+
+
+@pytest.mark.skipif(not os.environ.get("GS2D_EMU_ALL"), reason="about a minute and a half under emulation: GS2D_EMU_ALL=1")
+def test_stress_resolution_of_baseline_config_5_against_the_c_restatement():
+    """1752 x 1168 (BASELINE.json configs[4]: 8030 tiles, 45 sort bits) with a sparse map: tile indices beyond 2^12,
+    thousands of empty tiles, the multi-CTA tile-count scan.  Last run by hand at the end of round 1: radii, keys,
+    ranges exact; images, gradients and the footprint audit clean."""
+    import emu_run
+    case = cases._base(400, cases._intr(1752, 1168, f=1000.0), seed=7, view=1, use_sa=True)
+    out = emu_run.run_ours(case, debug=False, backward=True)
+    want = _oracle(case)
+    assert np.array_equal(out["radii"], want["radii"])
+    fails = compare.check_binning(out, want) + compare.check_images_oracle(out, want, True)
+    fails += compare.check_grads(out, want, rtol=compare.ORACLE_SA_GRAD_RTOL)
+    assert not fails, "\n".join(fails)
+    assert int(out["footprint_audit"][2]) == 0
