@@ -37,13 +37,14 @@ struct GroupArgs {
 	float* activated;        // render parameter out (NULL: not written; xyz / rgb are their own activation)
 	long long n;             // number of raw floats
 	float step_size;         // lr / (1 - beta1^t), computed in double like torch/optim/adam.py
+	float bc2_sqrt;          // sqrt(1 - beta2^t); t is per group (torch keeps one step counter per parameter)
 	int vec;                 // all of the above 16-byte aligned
 	int block0;              // first block of this group
 };
 
 struct StepArgs {
 	GroupArgs g[G_COUNT];
-	float beta1, beta2, w1, w2, eps, bc2_sqrt;   // w_k = 1 - beta_k (rounded from double, as torch's scalars are)
+	float beta1, beta2, w1, w2, eps;             // w_k = 1 - beta_k (rounded from double, as torch's scalars are)
 	int scale_cols;          // S: 2 (anisotropic) or 1 (isotropic: exp(s) tiled to both render columns)
 	int update;              // 0: activation only
 };
@@ -133,7 +134,7 @@ __global__ void __launch_bounds__(OPT_THREADS) map_step_kernel(const StepArgs a)
 			// exp_avg_sq.mul_(beta2).addcmul_(grad, grad, value=1 - beta2)
 			v[k] = v[k] * a.beta2 + a.w2 * g[k] * g[k];
 			// denom = exp_avg_sq.sqrt() / sqrt(bc2) + eps;  param.addcdiv_(exp_avg, denom, value=-step_size)
-			const float denom = sqrtf(v[k]) / a.bc2_sqrt + a.eps;
+			const float denom = sqrtf(v[k]) / G.bc2_sqrt + a.eps;
 			p[k] = p[k] - G.step_size * (m[k] / denom);
 		}
 		st4(G.exp_avg, i, G.n, vec, m);
@@ -173,8 +174,6 @@ int launch_map_step(int P, int scale_cols, const gs2d_map_state* ms, const float
                     float* opacities, float* scales, float* rotations, bool update, cudaStream_t st)
 {
 	StepArgs a{};
-	const double bc1 = update ? 1.0 - pow(ap->beta1, (double)ap->step) : 1.0;
-	const double bc2 = update ? 1.0 - pow(ap->beta2, (double)ap->step) : 1.0;
 	float* param[G_COUNT] = {ms->xyz, ms->opacity, ms->scaling, ms->rotation, ms->rgb};
 	const long long width[G_COUNT] = {3, 1, scale_cols, 4, 3};
 	const long long gsec[G_COUNT] = {0, 3, 4, 6, 10};      // flat-buffer section starts, in units of P floats
@@ -188,19 +187,26 @@ int launch_map_step(int P, int scale_cols, const gs2d_map_state* ms, const float
 		G.grad = update ? flat_grad + gsec[k] * (long long)P : nullptr;
 		G.activated = act[k];
 		G.n = width[k] * (long long)P;
+		// torch counts steps per parameter: a group that was skipped before (no gradient) is behind the others
+		const double t = update ? (double)(ap->group_step[k] > 0 ? ap->group_step[k] : ap->step) : 1.0;
+		const double bc1 = update ? 1.0 - pow(ap->beta1, t) : 1.0;
+		const double bc2 = update ? 1.0 - pow(ap->beta2, t) : 1.0;
 		G.step_size = update ? (float)(ap->lr[k] / bc1) : 0.f;
+		G.bc2_sqrt = (float)sqrt(bc2);
 		G.vec = aligned16(G.param) && aligned16(G.exp_avg) && aligned16(G.exp_avg_sq) && aligned16(G.grad) &&
 		        aligned16(G.activated);
 		G.block0 = blocks;
-		// activation-only launches skip the groups that are their own activation
-		const bool skip = !update && G.activated == nullptr;
+		// activation-only launches skip the groups that are their own activation; an update skips the groups the
+		// caller marks with a negative learning rate: "this parameter has no gradient" -- torch.optim.Adam leaves
+		// parameters whose .grad is None untouched, moments included (Renderer_BA / Renderer_tracking detach the
+		// rotations, render/__init__.py:36, :98, so _rotation.grad stays None in those steps)
+		const bool skip = (!update && G.activated == nullptr) || (update && ap->lr[k] < 0.0);
 		const long long items = skip ? 0 : (G.n + 3) / 4;
 		blocks += (int)((items + OPT_THREADS - 1) / OPT_THREADS);
 	}
 	if (update) {
 		a.beta1 = (float)ap->beta1; a.beta2 = (float)ap->beta2; a.eps = (float)ap->eps;
 		a.w1 = (float)(1.0 - ap->beta1); a.w2 = (float)(1.0 - ap->beta2);
-		a.bc2_sqrt = (float)sqrt(bc2);
 	}
 	a.scale_cols = scale_cols;
 	a.update = update ? 1 : 0;
@@ -239,6 +245,8 @@ int gs2d_map_adam_step(int32_t P, int32_t scale_cols, const gs2d_map_state* ms, 
 	if (!flat_grad || !ms->xyz || !ms->opacity || !ms->scaling || !ms->rotation || !ms->rgb) return GS2D_ERR_INVALID;
 	for (int k = 0; k < 5; k++)
 		if (!ms->exp_avg[k] || !ms->exp_avg_sq[k]) return GS2D_ERR_INVALID;
+	for (int k = 0; k < 5; k++)
+		if (ap->group_step[k] < 0) return GS2D_ERR_INVALID;
 	if (ap->step < 1 || !(ap->beta1 >= 0.0 && ap->beta1 < 1.0) || !(ap->beta2 >= 0.0 && ap->beta2 < 1.0)) return GS2D_ERR_INVALID;
 	// the three activation outputs are optional, but all or none
 	const int n_act = (opacities != nullptr) + (scales != nullptr) + (rotations != nullptr);

@@ -68,7 +68,7 @@ class MapState(C.Structure):
 
 class AdamParams(C.Structure):
     _fields_ = [("lr", C.c_double * 5), ("beta1", C.c_double), ("beta2", C.c_double), ("eps", C.c_double),
-                ("step", C.c_int64)]
+                ("step", C.c_int64), ("group_step", C.c_int64 * 5)]
 
 
 PROTOTYPES = {

@@ -43,6 +43,7 @@ class MapOptimizer:
         self.exp_avg_sq = {k: torch.zeros_like(t) for k, t in self.raw.items()}
         self.lr = [float(training_args[k]) for k in LR_KEYS]
         self.betas, self.eps, self.step_count = (float(betas[0]), float(betas[1])), float(eps), 0
+        self.group_steps = [0] * len(GROUPS)
         if flat_grad is not None and (flat_grad.numel() != FLAT_WIDTH * P or not flat_grad.is_cuda):
             raise RuntimeError("flat_grad must be a CUDA tensor of 13 * P floats")
         self._state = L.MapState()
@@ -86,15 +87,24 @@ class MapOptimizer:
         return dict(means3D=leaf(self.raw["xyz"]), opacities=leaf(self.opacities), scales=leaf(self.scales),
                     rotations=leaf(self.rotations), colors_precomp=leaf(self.raw["rgb"]))
 
-    def step(self, flat_grad=None):
-        """One Adam step from the gradient w.r.t. the render parameters in the flat [13 * P] layout."""
+    def step(self, flat_grad=None, skip=()):
+        """One Adam step from the gradient w.r.t. the render parameters in the flat [13 * P] layout.
+        `skip`: groups that have NO gradient in this step -- left untouched, moments included, as torch.optim.Adam
+        leaves a parameter whose .grad is None (in Renderer_BA / Renderer_tracking the rotations are detached,
+        render/__init__.py:36, :98: pass skip=("rotation",) there)."""
+        for k in skip:
+            if k not in GROUPS:
+                raise KeyError(k)
         g = self.flat_grad if flat_grad is None else flat_grad
         if g.numel() != FLAT_WIDTH * self.P or not g.is_cuda or g.dtype != torch.float32:
             raise RuntimeError("flat_grad must be a float32 CUDA tensor of 13 * P elements")
         self.step_count += 1
         ap = L.AdamParams()
         for i, v in enumerate(self.lr):
-            ap.lr[i] = v
+            ap.lr[i] = -1.0 if GROUPS[i] in skip else v
+            if GROUPS[i] not in skip:         # torch keeps one step counter per parameter
+                self.group_steps[i] += 1
+            ap.group_step[i] = self.group_steps[i]
         ap.beta1, ap.beta2, ap.eps, ap.step = self.betas[0], self.betas[1], self.eps, self.step_count
         with torch.cuda.device(self.dev):
             L.check(L.load().gs2d_map_adam_step(self.P, self.scale_cols, C.byref(self._state), g.data_ptr(), C.byref(ap),

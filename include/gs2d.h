@@ -280,10 +280,14 @@ typedef struct gs2d_map_state {
 } gs2d_map_state;
 
 typedef struct gs2d_adam_params {
-	double lr[5];           /* xyz_lr, opacity_lr, scaling_lr, rotation_lr, rgb_lr        */
+	double lr[5];           /* xyz_lr, opacity_lr, scaling_lr, rotation_lr, rgb_lr; a NEGATIVE value = "this group
+	                         * has no gradient in this step": parameter, moments and activation are left untouched,
+	                         * as torch.optim.Adam does for a parameter whose .grad is None                       */
 	double beta1, beta2;    /* 0.9, 0.999                                                  */
 	double eps;             /* 1e-15 (scene/Gaussians.py:137)                              */
 	int64_t step;           /* 1 for the first update (torch increments before using it)   */
+	int64_t group_step[5];  /* per-group step counts (torch keeps one per parameter: a group skipped in earlier
+	                         * steps is behind the others); 0 = use `step`                 */
 } gs2d_adam_params;
 
 /* Render parameters of the current raw parameters: opacities [P,1] = sigmoid, scales [P,2] = exp,

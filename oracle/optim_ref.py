@@ -45,14 +45,17 @@ class MapTorch:
         return dict(means3D=self.p["xyz"], opacities=torch.sigmoid(self.p["opacity"]), scales=scales,
                     rotations=torch.nn.functional.normalize(self.p["rotation"]), colors=self.p["rgb"])
 
-    def step(self, flat_grad):
+    def step(self, flat_grad, detached=()):
         """Back-propagate a given gradient of the render parameters and step (what loss.backward() +
-        optimizer.step() do in Frontend.mapping, slam/Frontend.py:116-128)."""
+        optimizer.step() do in Frontend.mapping, slam/Frontend.py:116-128).  `detached`: render parameters that
+        are detached before rendering (rotations in Renderer_BA, render/__init__.py:98): their raw parameter gets
+        no gradient and torch.optim.Adam skips it."""
         torch = self.torch
         self.optimizer.zero_grad(set_to_none=True)
         rp = self.render_params()
         g = split_flat(torch.as_tensor(flat_grad), self.p["xyz"].shape[0])
-        torch.autograd.backward([rp[k] for k, _ in FLAT], [g[k] for k, _ in FLAT])
+        keys = [k for k, _ in FLAT if k not in detached]
+        torch.autograd.backward([rp[k] for k in keys], [g[k] for k in keys])
         self.optimizer.step()
 
     # ---- densification surgery, restated from scene/Gaussians.py (pinned by tests/golden/optim_surgery.npz) ----
@@ -102,6 +105,9 @@ class MapTorch:
         out = {k: self.p[k].detach().cpu().numpy() for k in GROUPS}
         for k in GROUPS:
             st = self.optimizer.state[self.p[k]]
+            if "exp_avg" not in st:          # a parameter that never had a gradient has no state yet
+                out["m_" + k] = out["v_" + k] = np.zeros_like(out[k])
+                continue
             out["m_" + k] = st["exp_avg"].cpu().numpy()
             out["v_" + k] = st["exp_avg_sq"].cpu().numpy()
         with self.torch.no_grad():

@@ -172,3 +172,25 @@ def test_pose_kernel_text_equals_the_reference_path(tracking, P, pose):
     ref2 = TP._torch_path(xyz, rot, g, w2c=ref["w2c"])
     assert TP._rel(got2["means"], ref2["means"]) <= 1e-6 and TP._rot_err(got2["rots"], ref2["rots"]) <= 2e-6
     assert TP._rel(got2["dw2c"], ref2["dw2c"]) <= 5e-4 and np.all(got2["dw2c"][3] == 0)
+
+
+def test_groups_without_gradient_are_left_untouched_like_torch_adam(optim):
+    """Renderer_BA / Renderer_tracking detach the rotations: `_rotation.grad` is None and torch.optim.Adam skips the
+    parameter (moments and step included).  MapOptimizer.step(skip=("rotation",)) must do the same, step after step."""
+    g, raw, args = TO._golden("aniso")
+    opt = optim.MapOptimizer(*[torch.tensor(raw[k]) for k in R.GROUPS], args)
+    ref = R.MapTorch(raw, args)
+    for step in (1, 2, 3):
+        grad = g["in_grad"][step - 1]
+        skip = ("rotation",) if step != 2 else ()                     # with, without, with again
+        ref.step(grad, detached=("rotations",) if skip else ())
+        opt.step(torch.from_numpy(grad.copy()), skip=skip)
+        st = ref.state()
+        for k in R.GROUPS:
+            assert TO._rel(opt.raw[k].numpy(), st[k].astype(np.float64)) <= 2e-6, (step, k)
+            assert TO._rel(opt.exp_avg[k].numpy(), st["m_" + k].astype(np.float64)) <= 1e-5 or not st["m_" + k].any(), (step, k)
+        assert TO._rel(opt.rotations.numpy(), st["rotations"].astype(np.float64)) <= 2e-6
+        if step == 1:
+            assert np.array_equal(opt.raw["rotation"].numpy(), raw["rotation"]) and not opt.exp_avg["rotation"].any()
+    with pytest.raises(KeyError):
+        opt.step(torch.zeros(13 * opt.P), skip=("f_dc",))
