@@ -147,3 +147,64 @@ def test_one_tracking_iteration_end_to_end():
     for got, want in ((q.grad, rq.grad), (tr.grad, rt.grad)):
         scale = float(want.abs().max())
         assert scale > 0 and float((got - want).abs().max()) <= 3 * compare.ORACLE_SA_GRAD_RTOL * scale
+
+
+def test_one_bundle_adjustment_step_end_to_end():
+    """Renderer_BA's shape (render/__init__.py:84-111): map AND pose get gradients through the fused pose transform,
+    rotations are detached, so the optimiser step skips the rotation group as torch.optim.Adam skips .grad = None."""
+    import host_only
+    import pose_ref
+    G, tracking, loss, optim = (host_only.load_rasterizer(), host_only.load("tracking"), host_only.load("loss"),
+                                host_only.load("optim"))
+    case = cases._base(1200, cases._intr(96, 64), seed=1, view=1)
+    P, W, H = case["means3D"].shape[0], case["W"], case["H"]
+    rng = np.random.default_rng(23)
+    gt_color = rng.uniform(0, 1, (H, W, 3)).astype(np.float32)
+    gt_depth = rng.uniform(0.5, 4.0, (H, W, 1)).astype(np.float32)
+    t = lambda a, rg=False: torch.tensor(np.ascontiguousarray(a, np.float32), requires_grad=rg)      # noqa: E731
+    raw = dict(xyz=case["means3D"], opacity=np.log(case["opacities"] / (1 - case["opacities"])).astype(np.float32),
+               scaling=np.log(case["scales"]).astype(np.float32), rotation=case["rotations"], rgb=case["colors"])
+    w2c = np.ascontiguousarray(case["viewmatrix"].reshape(4, 4).T)
+    q0 = pose_ref.matrix_to_quaternion(torch.tensor(w2c[None, :3, :3], dtype=torch.float64))[0].numpy()
+    t0 = w2c[:3, 3]
+    ident = dict(case, viewmatrix=np.eye(4, dtype=np.float32).reshape(16), campos=np.zeros(3, np.float32))
+    proj = case["projmatrix"].reshape(4, 4).T @ np.linalg.inv(w2c.astype(np.float64))
+    ident["projmatrix"] = np.ascontiguousarray(proj.T.astype(np.float32)).reshape(16)
+
+    opt = optim.MapOptimizer(*[t(raw[k]) for k in R.GROUPS], ARGS)
+    rp = opt.render_params()
+    q, tr = t(q0, True), t(t0, True)
+    means, rots = tracking.pose_transform(rp["means3D"], rp["rotations"], cam_rot=q, cam_trans=tr)
+    rs = G.GaussianRasterizationSettings(image_height=H, image_width=W, tanfovx=float(case["tanfovx"]), tanfovy=float(case["tanfovy"]),
+                                         bg=t(case["bg"]), scale_modifier=1.0, viewmatrix=t(ident["viewmatrix"]).view(4, 4),
+                                         projmatrix=t(ident["projmatrix"]).view(4, 4), sh_degree=0, campos=t(ident["campos"]),
+                                         use_sa=True, prefiltered=False, debug=False)
+    color, radii, allmap = G.GaussianRasterizer(rs)(means3D=means, means2D=torch.zeros((P, 3), requires_grad=True),
+                                                    opacities=rp["opacities"], colors_precomp=rp["colors_precomp"],
+                                                    scales=rp["scales"], rotations=rots)
+    loss.mapping_loss(color, allmap, t(gt_color), t(gt_depth)).backward()
+    assert rp["rotations"].grad is None                                   # detached inside pose_transform, like the reference
+    flat = torch.cat([rp["means3D"].grad.reshape(-1), rp["opacities"].grad.reshape(-1), rp["scales"].grad.reshape(-1),
+                      torch.zeros(4 * P), rp["colors_precomp"].grad.reshape(-1)])
+    rot_before = opt.raw["rotation"].clone()
+    opt.step(flat, skip=("rotation",))
+    assert torch.equal(opt.raw["rotation"], rot_before) and not opt.exp_avg["rotation"].any()
+
+    ref = R.MapTorch(raw, ARGS)
+    rrp = ref.render_params()
+    rq, rt = t(q0, True), t(t0, True)
+    rm, rr = pose_ref.pose_transform_torch(rrp["means3D"], rrp["rotations"], pose_ref.get_transform_matrix(rq, rt))
+    rc, ro = _OracleRasterizer.apply(rm, rrp["opacities"], rrp["scales"], rr, rrp["colors"], ident)
+    loss_ref.mapping_loss_torch(rc, ro, t(gt_color), t(gt_depth)).backward()
+    assert ref.p["rotation"].grad is None
+    got = R.split_flat(flat.numpy(), P)
+    # gradients w.r.t. the RAW parameters on the reference side -> compare where raw = render (xyz, rgb) and the poses
+    for k, leaf in (("means3D", ref.p["xyz"]), ("colors", ref.p["rgb"])):
+        r = compare.grad_rel(got[k], leaf.grad.numpy())
+        assert r <= compare.ORACLE_SA_GRAD_RTOL, (k, r)
+    for a, b in ((q.grad, rq.grad), (tr.grad, rt.grad)):
+        assert float((a - b).abs().max()) <= 3 * compare.ORACLE_SA_GRAD_RTOL * float(b.abs().max())
+    ref.step(flat.numpy(), detached=("rotations",))
+    st = ref.state()
+    for k in R.GROUPS:
+        assert np.abs(opt.raw[k].numpy() - st[k]).max() <= 2e-6 * max(np.abs(st[k]).max(), 1e-30), k
