@@ -71,6 +71,8 @@ class AdamParams(C.Structure):
                 ("step", C.c_int64), ("group_step", C.c_int64 * 5)]
 
 
+ABI_VERSION = 3      # GS2D_ABI_VERSION of the include/gs2d.h these structs mirror (checked when the library is loaded)
+
 PROTOTYPES = {
     "gs2d_geom_bytes": (C.c_size_t, [C.c_int32, C.c_int32]),
     "gs2d_image_bytes": (C.c_size_t, [C.c_int32, C.c_int32]),
@@ -143,6 +145,9 @@ def load():
         fn = getattr(lib, name)
         fn.restype = res
         fn.argtypes = args
+    if lib.gs2d_abi_version() != ABI_VERSION:
+        raise RuntimeError(f"{LIB_PATH} has ABI version {lib.gs2d_abi_version()}, this package mirrors version "
+                           f"{ABI_VERSION} of include/gs2d.h: rebuild it (python gaus-slam_b200/build.py --force)")
     _lib = lib
     return lib
 

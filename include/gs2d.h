@@ -33,7 +33,8 @@
 extern "C" {
 #endif
 
-#define GS2D_ABI_VERSION 2
+/* 3: gs2d_adam_params gained group_step[5] (and negative lr = "no gradient"); gs2d_map_compact_* added */
+#define GS2D_ABI_VERSION 3
 
 typedef enum gs2d_status {
 	GS2D_OK = 0,

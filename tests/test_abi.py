@@ -29,7 +29,7 @@ def test_library_exports_every_declared_symbol():
 
 def test_abi_version_and_strerror():
     lib = L.load()
-    assert lib.gs2d_abi_version() == 2
+    assert lib.gs2d_abi_version() == 3
     assert lib.gs2d_strerror(0).decode().lower().startswith("ok") or lib.gs2d_strerror(0)
     for code in (-1, -2, -3, -4):
         assert lib.gs2d_strerror(code).decode()
@@ -190,7 +190,7 @@ def test_header_is_plain_c_and_a_c_client_links(tmp_path):
         f.write("".join(f"\t(fn){n},\n" for n in names))
         f.write("};\nint main(void) {\n"
                 "\tif (sizeof(table) / sizeof(table[0]) != %d) return 2;\n"
-                "\tif (gs2d_abi_version() != 2) return 3;\n"
+                "\tif (gs2d_abi_version() != GS2D_ABI_VERSION) return 3;\n"
                 "\tif (gs2d_map_compact_scratch_bytes(257) != 12) return 4;\n"
                 "\tif (gs2d_map_activate(4, 3, 0, 0, 0, 0, 0) == GS2D_OK) return 5;\n"
                 '\tprintf("%%s\\n", gs2d_strerror(GS2D_ERR_INVALID));\n\treturn 0;\n}\n' % len(names))
