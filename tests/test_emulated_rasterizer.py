@@ -215,3 +215,18 @@ def test_stress_resolution_of_baseline_config_5_against_the_c_restatement():
     fails += compare.check_grads(out, want, rtol=compare.ORACLE_SA_GRAD_RTOL)
     assert not fails, "\n".join(fails)
     assert int(out["footprint_audit"][2]) == 0
+
+
+def test_one_tile_with_six_thousand_instances():
+    """The tile-local sort, the staged compositing ring and the pair-slot scan on a list far longer than the usual
+    ~250 instances per tile: 6000 large surfels over a single 16 x 16 tile, against the C restatement."""
+    import emu_run
+    case = cases._base(6000, cases._intr(16, 16), seed=3, view=0, use_sa=False, scale_mult=4.0)
+    out = emu_run.run_ours(case, debug=False, backward=True)
+    want = _oracle(case)
+    assert np.array_equal(out["radii"], want["radii"])
+    r = out["ranges"].astype(np.int64)
+    assert int((r[:, 1] - r[:, 0]).max()) > 5000
+    fails = compare.check_binning(out, want) + compare.check_images_oracle(out, want, False) + compare.check_grads(out, want)
+    assert not fails, "\n".join(fails)
+    assert int(out["footprint_audit"][2]) == 0
