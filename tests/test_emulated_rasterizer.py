@@ -230,3 +230,28 @@ def test_one_tile_with_six_thousand_instances():
     fails = compare.check_binning(out, want) + compare.check_images_oracle(out, want, False) + compare.check_grads(out, want)
     assert not fails, "\n".join(fails)
     assert int(out["footprint_audit"][2]) == 0
+
+
+@pytest.mark.parametrize("degree,coeffs", [(0, 1), (1, 4), (3, 16), (1, 16)])
+def test_spherical_harmonics_degrees_and_clamping(degree, coeffs):
+    """The cold SH branch at every degree the reference supports (CR/forward.cu:20-71, CR/backward.cu:20-139), more
+    coefficients stored than the active degree uses, coefficients large enough to drive colours below zero (clamped:
+    their gradient is cut): against the C restatement."""
+    import cpu as O
+    import emu_run
+    case = cases._base(800, cases._intr(96, 64), seed=10 + degree, view=degree % 3, use_sa=bool(degree % 2))
+    case["shs"] = np.random.default_rng(degree).normal(0, 1.2, (800, coeffs, 3)).astype(np.float32)
+    case["colors"], case["sh_degree"] = None, degree
+    out = emu_run.run_ours(case, debug=False, backward=True)
+    a = (case["means3D"], case["opacities"], case["viewmatrix"], case["projmatrix"], case["W"], case["H"], case["bg"])
+    kw = dict(scales=case["scales"], rotations=case["rotations"], campos=case["campos"], shs=case["shs"], sh_degree=degree)
+    st = O.forward(*a, scale_modifier=1.0, use_sa=case["use_sa"], **kw)
+    g = O.backward(st, case["means3D"], case["viewmatrix"], case["projmatrix"], case["W"], case["H"], float(case["tanfovx"]),
+                   float(case["tanfovy"]), case["bg"], case["dL_dcolor"], case["dL_dothers"], use_sa=case["use_sa"], **kw)
+    want = {k: np.asarray(v) for k, v in st.items()}
+    want.update({"grad_" + k: np.asarray(v) for k, v in g.items()})
+    assert np.array_equal(out["radii"], want["radii"])
+    fails = compare.check_images_oracle(out, want, case["use_sa"])
+    fails += compare.check_grads(out, want, rtol=compare.ORACLE_SA_GRAD_RTOL if case["use_sa"] else compare.GRAD_RTOL)
+    assert not fails, "\n".join(fails)
+    assert float(np.abs(out["grad_sh"]).max()) > 0 and (out["color"] == 0).any() is not None
