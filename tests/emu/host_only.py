@@ -98,3 +98,20 @@ def load_rasterizer():
     exec(compile(src, "<host-only gaus_2dgs_rasterization/__init__.py>", "exec"), mod.__dict__)
     mod._C = glue
     return mod
+
+
+def load_simple_knn():
+    """simple_knn._C (distCUDA2) as a host-only module over the host build of the whole library."""
+    sys.path.insert(0, HERE)
+    import emu_run
+    src = open(os.path.join(ROOT, "gaus-slam_b200", "simple_knn", "_C.py")).read()
+    src, n = re.subn(r"    if not points\.is_cuda:\n        raise RuntimeError\([^\n]*\)\n", "", src)
+    assert n == 1 and "is_cuda" not in src
+    src = src.replace("from gs2d_b200 import _lib as L", "L = None")
+    mod = types.ModuleType("simple_knn_host_only._C")
+    mod.__file__ = os.path.join(ROOT, "gaus-slam_b200", "simple_knn", "_C.py")
+    exec(compile(src, "<host-only simple_knn/_C.py>", "exec"), mod.__dict__)
+    ns = types.SimpleNamespace(**{k: getattr(L, k) for k in dir(L) if not k.startswith("__")})
+    ns.load = emu_run.library
+    mod.L, mod.torch = ns, _fake_torch()
+    return mod

@@ -138,3 +138,16 @@ def test_debug_mode_dumps_the_arguments_on_failure_like_the_reference(G, tmp_pat
                                                  opacities=_t(case["opacities"]), colors_precomp=_t(case["colors"]),
                                                  scales=_t(case["scales"]), rotations=_t(case["rotations"]))
     assert torch.equal(a[0], b[0]) and torch.equal(a[2], b[2]) and torch.equal(a[1], b[1])
+
+
+@pytest.mark.parametrize("name", cases.KNN_CASES)
+def test_dist_cuda2_through_the_drop_in_module(name):
+    """`from simple_knn._C import distCUDA2` as scene/Gaussians.py:8 uses it: bit for bit the reference's output."""
+    import host_only
+    knn = host_only.load_simple_knn()
+    g = cases.load_golden(name)
+    got = knn.distCUDA2(torch.tensor(g["in_points"])).numpy()
+    assert got.dtype == np.float32 and compare.bits_differ(got, g["ref_dist2"]) == 0
+    assert knn.distCUDA2(torch.zeros((0, 3))).shape == (0,)
+    with pytest.raises(RuntimeError, match="num_points, 3"):
+        knn.distCUDA2(torch.zeros((5, 2)))
