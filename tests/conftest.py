@@ -13,9 +13,15 @@ for p in (HERE, os.path.join(ROOT, "gaus-slam_b200"), os.path.join(ROOT, "oracle
 
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box with -m gpu)")
+    config.addinivalue_line("markers", "timeout: per-test time limit (pytest-timeout)")
 
 
 def pytest_collection_modifyitems(config, items):
+    # the host emulation runs real threads: bound every such test (pytest-timeout, when installed) so that a lost
+    # wake-up can only ever be a failure, never a hung run
+    for item in items:
+        if "emulat" in os.path.basename(str(item.fspath)):
+            item.add_marker(pytest.mark.timeout(900))
     try:
         import torch
         have = torch.cuda.is_available()
