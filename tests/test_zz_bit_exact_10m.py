@@ -13,11 +13,9 @@ import pytest
 
 import compare
 
-FIRST_RUN = pytest.mark.xfail(strict=False, reason="widened bit-exactness sample: not yet run on a B200 (passes -> XPASS)")
 
 
 @pytest.mark.gpu
-@FIRST_RUN
 def test_integer_outputs_are_bit_exact_on_10m_random_surfels():
     import refgpu
     if not refgpu.available():

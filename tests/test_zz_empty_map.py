@@ -1,16 +1,13 @@
 """An empty map (P = 0) through the public API on the GPU: the reference short-circuits (RAST/rasterize_points.cu:101,
 :202) and returns the background image and empty gradients.  The C side of this case is covered on the CPU
 (tests/test_emulated_rasterizer.py::test_empty_map_through_the_abi, which found that the argument check refused the
-NULL pointers empty tensors arrive as); the Python glue around it has not run on a B200 yet, hence the first-run mark."""
+NULL pointers empty tensors arrive as); ran green on the B200 at the end of round 1, an ordinary test since)."""
 import pytest
 import torch
 
-FIRST_RUN = pytest.mark.xfail(strict=False, reason="empty-map path fixed after the round's GPU budget was spent: "
-                                                   "not yet run on a B200 (passes -> XPASS)")
 
 
 @pytest.mark.gpu
-@FIRST_RUN
 def test_empty_map_renders_the_background_and_has_empty_gradients():
     from gaus_2dgs_rasterization import GaussianRasterizationSettings, GaussianRasterizer
     dev = torch.device("cuda:0")

@@ -18,8 +18,6 @@ import torch
 import optim_ref as R
 
 GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "optim_surgery.npz")
-FIRST_RUN = pytest.mark.xfail(strict=False, reason="compaction kernels: written after the round's GPU budget was spent, "
-                                                   "not yet run on a B200 (passes -> XPASS)")
 
 
 def _golden():
@@ -69,7 +67,6 @@ def _check(opt, g, tag, exact):
 
 
 @pytest.mark.gpu
-@FIRST_RUN
 def test_map_optimizer_surgery_matches_the_reference():
     from gs2d_b200 import optim
     dev = torch.device("cuda:0")
@@ -106,7 +103,6 @@ def test_map_optimizer_surgery_matches_the_reference():
 
 
 @pytest.mark.gpu
-@FIRST_RUN
 @pytest.mark.parametrize("P,frac,seed", [(1, 1.0, 0), (1, 0.0, 1), (255, 0.5, 2), (256, 0.5, 3), (257, 0.99, 4),
                                          (100003, 0.7, 5), (300000, 0.01, 6), (2000, 0.0, 7), (2000, 1.0, 8)])
 def test_prune_equals_boolean_indexing(P, frac, seed):
@@ -132,7 +128,6 @@ def test_prune_equals_boolean_indexing(P, frac, seed):
 
 
 @pytest.mark.gpu
-@FIRST_RUN
 def test_surgery_argument_checks():
     from gs2d_b200 import optim
     dev = torch.device("cuda:0")
