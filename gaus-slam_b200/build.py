@@ -14,7 +14,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "lib", "libgs2d.so")
 SOURCES = ["api.cu", "preprocess.cu", "binning.cu", "tile_sort.cu", "footprint.cu", "composite_fwd.cu", "composite_bwd.cu",
-           "preprocess_bwd.cu", "knn.cu", "loss.cu", "collective.cu", "optim.cu", "pose.cu", "compact.cu"]
+           "preprocess_bwd.cu", "knn.cu", "loss.cu", "collective.cu", "optim.cu", "pose.cu", "compact.cu", "no_alloc.cu"]
 HEADERS = ["common.cuh", "math.cuh", "exact.cuh", "tma.cuh", "pair.cuh", "footprint.cuh", os.path.join("..", "..", "include", "gs2d.h")]
 # Kernels whose results only have to meet a tolerance (backward gradients: 1e-3 relative; footprint masks: a
 # superset) may use MUFU division / flush-to-zero; everything that decides bit-exact outputs keeps IEEE math.

@@ -100,6 +100,8 @@ PROTOTYPES = {
     "gs2d_sort_scratch_bytes": (C.c_size_t, [C.c_int64]),
     "gs2d_sort_pairs": (C.c_int, [C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32,
                                   C.c_void_p, C.c_void_p]),
+    "gs2d_sort_pairs_static": (C.c_int, [C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32,
+                                         C.c_void_p]),
     "gs2d_mapping_loss_scratch_bytes": (C.c_size_t, [C.c_int32, C.c_int32]),
     "gs2d_mapping_loss_forward": (C.c_int, [C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                             C.c_int32, C.POINTER(LossParams), C.c_void_p, C.c_void_p, C.c_void_p]),

@@ -228,6 +228,19 @@ int gs2d_sort_pairs(int64_t n, const uint64_t* keys_in, const uint32_t* values_i
                     uint64_t* keys_out, uint32_t* values_out, int32_t end_bit,
                     void* scratch, void* stream);
 
+/* gs2d_sort_pairs without a scratch argument and without any allocation.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops,
+ * harnesses that forbid it).  The scratch is a static device array inside the library
+ * (GS2D_SORT_STATIC_SCRATCH_BYTES, held by every GPU that loads the library until exit); the call issues only kernel
+ * launches, cudaMemsetAsync and cudaMemcpyAsync on `stream`.  n > GS2D_SORT_STATIC_MAX_PAIRS returns
+ * GS2D_ERR_CAPACITY ("workspace too small") and launches nothing.  All calls on a device share the array: what must
+ * start at zero is cleared on the stream at the start of every call, and calls that overlap on the GPU (different
+ * streams without ordering between them) race -- serialise them.  Same result as gs2d_sort_pairs, bit for bit. */
+#define GS2D_SORT_STATIC_MAX_PAIRS (1 << 18)
+#define GS2D_SORT_STATIC_SCRATCH_BYTES (4718592u) /* 4.5 MiB >= gs2d_sort_scratch_bytes(GS2D_SORT_STATIC_MAX_PAIRS) */
+int gs2d_sort_pairs_static(int64_t n, const uint64_t* keys_in, const uint32_t* values_in,
+                           uint64_t* keys_out, uint32_t* values_out, int32_t end_bit, void* stream);
+
 /* ---- "next" row f2: fused mapping loss + image gradients --------------------------------
  * The mapping branch of get_loss (slam/Loss.py:22-25, :36, :51-63) on the rasterizer's outputs, including the
  * weight normalisation of the depth that Renderer_* applies first (render/__init__.py:46-49):
