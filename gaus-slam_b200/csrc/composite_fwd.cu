@@ -3,19 +3,29 @@
 // Replaces FORWARD::render / renderCUDA<3> (CR/forward.cu:258-467): ray-splat intersection,
 // low-pass filter, alpha, early ray termination, surface-aware (SA) depth or 2DGS distortion,
 // normals, median depth.  The per-(pixel, instance) arithmetic keeps the reference's operation
-// order, so a pixel's result is the same sequence of fp32 operations (images are bit-identical to
-// the reference build).  What changes is which pairs are visited and how the data is fed:
-//   * one CTA per 16x16 tile, one thread per pixel, warp k owns tile rows 2k and 2k+1;
+// order, so a pixel's result is the same sequence of fp32 operations.  What changes is which pairs
+// are visited and how the data is fed:
+//   * one CTA per 16x16 tile, one thread per pixel (warp k owns an 8 x 4 pixel block, pair.cuh);
 //   * the tile's instance records (80 B each, sorted, contiguous in HBM) and their footprint masks
-//     (32 B each, footprint.cu) are staged by TMA bulk copies, 128 instances per batch, into a
-//     three-stage shared-memory ring guarded by mbarriers; the first three batches are requested at once and every
-//     thread waits on the mbarrier itself, so lists of up to 384 instances need no CTA barrier at all;
-//   * per batch the instance-major footprint masks are transposed into per-PIXEL hit words with warp
-//     ballots (registers only: word k of a mask is exactly warp k's 32 pixels), and every pixel thread
-//     then walks only ITS OWN set bits in depth order.  A pixel visits ~17 instances per tile instead of ~250; lanes of a
-//     warp run independent lists (the trip count of a warp is the longest list among its 32 pixels);
-//   * a pixel stops at T < 1e-4 like the reference; the CTA stops staging when all 256 have.
-// Bound by FP32 issue + MUFU on the visited pairs; HBM traffic is 112 B per instance + 68 B per pixel.
+//     (32 B each, footprint.cu) arrive by TMA bulk copies in chunks of 128 instances; FWD_CHUNKS chunks
+//     (384 instances: all of a tile for 99.9 % / 83 % of the tiles of the bench views) are requested AT ONCE
+//     and stay resident together ("super-batch");
+//   * the instance-major footprint masks are transposed into per-PIXEL hit words with warp shuffles,
+//     and every pixel thread then walks ITS OWN set bits of the WHOLE super-batch front to back in ONE
+//     loop.  A pixel visits ~18 instances per tile instead of ~300.  Lanes of a warp run independent
+//     lists and the warp iterates as often as its longest list -- measured (scripts/pair_stats.py) 0.60 - 0.63
+//     of the lanes busy when the lanes re-synchronise after every 128 instances (round 1), 0.75 when they
+//     only do so per tile: short and long stretches of a pixel's list average out over the tile;
+//   * a pixel stops at T < 1e-4 like the reference; the CTA stops staging when all 256 have;
+//   * the pairs that really contributed (what the backward pass needs to know about visibility and
+//     termination) are the footprint bits minus the rejected ones, in front of the termination point:
+//     rejected bits are cleared in the pixel's own hit words, no second set of words is kept.
+// The arithmetic stays IEEE throughout (division, expf): the SA variance D2 - 2 md D + md^2 (1 - T) is a catastrophic
+// cancellation (~1e-6 from terms ~10) that the backward pass divides by, so even a 1e-6 relative change of one blend
+// weight (measured: MUFU ex2 for the confidence exponent) moves gradients by more than the 1e-3 bar.  Images are
+// bit-identical to the reference build.
+#include <atomic>
+
 #include "common.cuh"
 #include "tma.cuh"
 #include "pair.cuh"
@@ -24,23 +34,20 @@ namespace gs2d {
 
 namespace {
 
-#ifndef GS2D_FWD_BATCH
-#define GS2D_FWD_BATCH 128
+constexpr int FWD_BATCH = 128;              // instances per TMA chunk
+#ifndef GS2D_FWD_CHUNKS
+#define GS2D_FWD_CHUNKS 3
 #endif
-constexpr int FWD_BATCH = GS2D_FWD_BATCH;   // instances per staged batch (a multiple of 32)
-constexpr int FWD_GROUPS = FWD_BATCH / 32;  // hit words per pixel per batch
-#ifndef GS2D_FWD_STAGES
-#define GS2D_FWD_STAGES 3
-#endif
-constexpr int FWD_STAGES = GS2D_FWD_STAGES;
-static_assert(FWD_BATCH % 32 == 0 && FWD_BATCH / 32 <= HIT_PIX_PAD, "hit_pix padding");
+constexpr int FWD_CHUNKS = GS2D_FWD_CHUNKS;
+constexpr int FWD_SUPER = FWD_BATCH * FWD_CHUNKS;   // instances resident at once
+constexpr int FWD_WORDS = FWD_SUPER / 32;           // hit words per pixel per super-batch
+static_assert(FWD_BATCH / 32 <= HIT_PIX_PAD, "hit_pix padding");
 
 struct FwdSmem {
-	float4 rec[FWD_STAGES][FWD_BATCH * 5];
-	uint32_t mask[FWD_STAGES][FWD_BATCH * 8];
-	uint32_t hits[FWD_GROUPS][TILE_PIXELS];   // per-pixel hit words of the current batch
-	uint32_t used[FWD_GROUPS][TILE_PIXELS];   // the pairs that really contributed
-	uint64_t bar[FWD_STAGES];
+	float4 rec[FWD_CHUNKS][FWD_BATCH * 5];    // contiguous: instance i of the super-batch is rec[0][5 * i]
+	uint32_t mask[FWD_CHUNKS][FWD_BATCH * 8];
+	uint32_t hits[FWD_WORDS][TILE_PIXELS];    // per-pixel hit words (live pixels; rejected pairs get cleared)
+	uint64_t bar[FWD_CHUNKS];
 };
 
 struct PixelFwd {
@@ -69,18 +76,17 @@ __device__ __forceinline__ uint32_t transpose32(uint32_t x, int lane)
 	return x;
 }
 
+// The order-dependent half of the reference's loop body (CR/forward.cu:388-441) for one accepted pair:
+// termination test, median depth, SA confidence blend or 2DGS distortion, the weighted sums.  Sets `done`
+// (and adds nothing) when the pair would push the transmittance below 1e-4.
 template <bool USE_SA>
-__device__ __forceinline__ bool eval_pair(const float4* __restrict__ rec, float pxf, float pyf,
-                                          uint32_t contributor, PixelFwd& px, bool& done)
+__device__ __forceinline__ void blend_pair(const float alpha, float depth, const float4 r3, const float4 r4,
+                                           const uint32_t contributor, PixelFwd& px, bool& done)
 {
-	PairFront f;
-	if (!pair_front(rec[0], rec[1], rec[2], pxf, pyf, f)) return false;
-	const float alpha = f.alpha;
-	float depth = f.depth;
 	const float test_T = px.T * (1 - alpha);
 	if (test_T < 0.0001f) {
 		done = true;
-		return false;
+		return;
 	}
 	const float w = alpha * px.T;
 	const bool is_median = px.T > 0.5f;   // the reference compares in double; 0.5 is exact, so the float compare decides the same
@@ -88,16 +94,15 @@ __device__ __forceinline__ bool eval_pair(const float4* __restrict__ rec, float 
 		px.median_depth = depth;
 		px.median_contributor = contributor;
 	}
-
 	if (USE_SA) {
 		// While the pixel is still in front of its median the expected depth IS this depth: error = 0, conf =
 		// expf(-0) = 1 and the blend returns `depth` unchanged, so the block is skipped (it would send 0 / x
 		// through the division's slow path for every such pair).
 		if (px.D > 0 && !is_median) {
 			const float exp_depth = px.median_depth;
+			const float error = (exp_depth - depth) * (exp_depth - depth);
 			float exp_std = (px.D2 - 2 * px.D * exp_depth) / (1 - px.T) + exp_depth * exp_depth;
 			exp_std = fmaxf(exp_std, 1e-7f);
-			const float error = (exp_depth - depth) * (exp_depth - depth);
 			const float conf = expf(-error / (4 * exp_std));
 			depth = conf * depth + (1 - conf) * exp_depth;
 		}
@@ -111,13 +116,14 @@ __device__ __forceinline__ bool eval_pair(const float4* __restrict__ rec, float 
 		px.M1 += m * w;
 		px.M2 += m * m * w;
 	}
-	const float4 r3 = rec[3], r4 = rec[4];
 	px.N0 += r3.x * w; px.N1 += r3.y * w; px.N2 += r3.z * w;
 	px.C0 += r4.x * w; px.C1 += r4.y * w; px.C2 += r4.z * w;
 	px.T = test_T;
 	px.last_contributor = contributor;
-	return true;
 }
+
+__device__ __forceinline__ uint32_t bits_below(int k) { return k <= 0 ? 0u : (k >= 32 ? 0xffffffffu : ((1u << k) - 1u)); }
+
 
 #ifndef GS2D_FWD_MIN_BLOCKS
 #define GS2D_FWD_MIN_BLOCKS 4
@@ -133,14 +139,12 @@ composite_forward_kernel(int W, int H, unsigned gx, const uint2* __restrict__ ra
 {
 	extern __shared__ __align__(128) unsigned char fwd_smem_raw[];
 	FwdSmem& sm = *reinterpret_cast<FwdSmem*>(fwd_smem_raw);
-	float4 (*s_rec)[FWD_BATCH * 5] = sm.rec;
-	uint32_t (*s_mask)[FWD_BATCH * 8] = sm.mask;
 	uint64_t* s_bar = sm.bar;
 
 	const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 	const unsigned tile = blockIdx.x;
 	const unsigned tx = tile % gx, ty = tile / gx;
-	const int lx = thread_lx<GS2D_FWD_BLOCK>(tid), ly = thread_ly<GS2D_FWD_BLOCK>(tid);   // thread <-> tile pixel: pair.cuh
+	const int lx = thread_lx<1>(tid), ly = thread_ly<1>(tid);   // thread <-> tile pixel: 8 x 4 block per warp (pair.cuh)
 	const int ptid = pixel_thread(lx, ly);               // row-major pixel index: where this pixel's words go in hit_pix
 	const unsigned pix_x = tx * TILE + lx;
 	const unsigned pix_y = ty * TILE + ly;
@@ -149,69 +153,70 @@ composite_forward_kernel(int W, int H, unsigned gx, const uint2* __restrict__ ra
 
 	const uint2 range = ranges[tile];
 	const int n = (int)(range.y - range.x);
-	const int nb = (n + FWD_BATCH - 1) / FWD_BATCH;
+	const int nsb = (n + FWD_SUPER - 1) / FWD_SUPER;
 
 	if (tid == 0) {
-		for (int s = 0; s < FWD_STAGES; s++) mbar_init(&s_bar[s], 1);
+		for (int s = 0; s < FWD_CHUNKS; s++) mbar_init(&s_bar[s], 1);
 		mbar_fence_init();
 	}
 	__syncthreads();
 	const float4* tile_rec = instances + 5 * (size_t)range.x;
 	const uint32_t* tile_mask = hit_inst + 8 * (size_t)range.x;
-	auto issue = [&](int b, int stage) {
-		const uint32_t cnt = (uint32_t)min(n - b * FWD_BATCH, FWD_BATCH);
-		mbar_arrive_expect_tx(&s_bar[stage], cnt * (80u + 32u));
-		tma_load_1d(&s_rec[stage][0], tile_rec + 5 * (size_t)b * FWD_BATCH, cnt * 80u, &s_bar[stage]);
-		tma_load_1d(&s_mask[stage][0], tile_mask + 8 * (size_t)b * FWD_BATCH, cnt * 32u, &s_bar[stage]);
-	};
-	// The first FWD_STAGES batches are requested at once: tiles of up to FWD_STAGES * FWD_BATCH instances (most of
-	// them) run without a single CTA barrier -- every thread waits on the batch's mbarrier itself, so the 8 warps of
-	// a tile drift apart freely instead of waiting for the slowest one at every batch (the barrier was the top stall
-	// of this kernel).  Longer lists reuse the stages: one barrier per batch, which is also the CTA-wide exit vote.
-	if (tid == 0)
-		for (int b = 0; b < min(nb, FWD_STAGES); b++) issue(b, b);
-
 	uint32_t* pix_words = hit_pix + ((size_t)(range.x >> 5) + HIT_PIX_PAD * (size_t)tile) * 2 * TILE_PIXELS;
+	const float4* recs = &sm.rec[0][0];
 
 	PixelFwd px;
 	bool done = !inside;
-	int first_unwaited = 0;       // batches below this index have been waited for by every thread
 
-	for (int b = 0; b < nb; b++) {
-		const int stage = b % FWD_STAGES;
-		const uint32_t parity = (uint32_t)(b / FWD_STAGES) & 1u;
-		if (b >= 1 && b + FWD_STAGES - 1 < nb) {
-			// batch b-1 is consumed by everyone -> its stage takes batch b + FWD_STAGES - 1; CTA-wide exit vote
+	for (int sb = 0; sb < nsb; sb++) {
+		if (sb > 0) {
+			// the previous super-batch is consumed by everyone -> its memory takes the next one; CTA-wide exit vote
 			const int num_done = __syncthreads_count(done);
 			if (num_done == TILE_PIXELS) break;
-			if (tid == 0) issue(b + FWD_STAGES - 1, (b + FWD_STAGES - 1) % FWD_STAGES);
 		}
-		mbar_wait(&s_bar[stage], parity);
-		first_unwaited = b + 1;
-
-		const int cnt = min(n - b * FWD_BATCH, FWD_BATCH);
-		const float4* recs = &s_rec[stage][0];
-		const uint32_t* masks = &s_mask[stage][0];
-		// Transpose in registers: word `warp` of instance j holds this warp's 32 pixels; a 32x32 bit transpose turns
-		// the words of 32 instances into one hit word per pixel (bit j <-> instance g*32 + j).
+		const int first = sb * FWD_SUPER;                       // first instance of the super-batch (in the tile)
+		const int cnt_sb = min(n - first, FWD_SUPER);
+		const int nch = (cnt_sb + FWD_BATCH - 1) / FWD_BATCH;   // chunks in flight: all requested at once
+		if (tid == 0) {
+			for (int c = 0; c < nch; c++) {
+				const uint32_t cnt = (uint32_t)min(cnt_sb - c * FWD_BATCH, FWD_BATCH);
+				const size_t at = (size_t)first + (size_t)c * FWD_BATCH;
+				mbar_arrive_expect_tx(&s_bar[c], cnt * (80u + 32u));
+				tma_load_1d(&sm.rec[c][0], tile_rec + 5 * at, cnt * 80u, &s_bar[c]);
+				tma_load_1d(&sm.mask[c][0], tile_mask + 8 * at, cnt * 32u, &s_bar[c]);
+			}
+		}
+		const uint32_t parity = (uint32_t)sb & 1u;              // every chunk barrier completes one phase per super-batch
+		const int nw = nch * (FWD_BATCH / 32);                  // hit words per pixel in this super-batch
+		const bool done_before = done;
+		// Transpose in registers, chunk by chunk as the chunks land: this warp's byte-gathered word of instance j
+		// holds its 32 pixels; a 32x32 bit transpose turns the words of 32 instances into one hit word per pixel
+		// (bit j <-> instance 32 g + j).  The raw words are the footprint (a gradient-pair slot each in the backward
+		// pass) and go out at once; the copy in shared memory is what the walk consumes and edits.
+		for (int c = 0; c < nch; c++) {
+			mbar_wait(&s_bar[c], parity);
+			const int cnt = min(cnt_sb - c * FWD_BATCH, FWD_BATCH);
+			const uint32_t* masks = &sm.mask[c][0];
 #pragma unroll
-		for (int g = 0; g < FWD_GROUPS; g++) {
-			const int j = g * 32 + lane;
-			const uint32_t mine = j < cnt ? warp_word<GS2D_FWD_BLOCK>(masks + j * 8, warp) : 0u;
-			sm.hits[g][tid] = __any_sync(0xffffffffu, mine != 0u) ? transpose32(mine, lane) : 0u;
-			sm.used[g][tid] = 0u;
+			for (int g = 0; g < FWD_BATCH / 32; g++) {
+				const int j = g * 32 + lane;
+				const uint32_t mine = j < cnt ? warp_word<1>(masks + j * 8, warp) : 0u;
+				const uint32_t raw = __any_sync(0xffffffffu, mine != 0u) ? transpose32(mine, lane) : 0u;
+				const int w = c * (FWD_BATCH / 32) + g;
+				sm.hits[w][tid] = done ? 0u : raw;
+				pix_words[(size_t)((sb * FWD_WORDS + w) * 2 + 1) * TILE_PIXELS + ptid] = raw;
+			}
 		}
 
-		// Every pixel walks its own hits of the WHOLE batch front to back, in one loop: a warp iterates as often as
-		// its longest pixel list (lists of 128 instances balance better between the lanes than lists of 32).
+		// Every pixel walks its own hits of the WHOLE super-batch front to back, in one loop: a warp iterates as
+		// often as its longest pixel list.
+		int stop = FWD_SUPER;          // instance (in the super-batch) at which this pixel terminated
 		{
-			int g = done ? FWD_GROUPS - 1 : 0;
-			uint32_t m = done ? 0u : sm.hits[0][tid], used = 0u;
+			int g = 0;
+			uint32_t m = sm.hits[0][tid];
 			for (;;) {
 				// advance to the next non-empty word (finished pixels sit at the last word with m = 0)
-				while (m == 0u && g < FWD_GROUPS - 1) {
-					sm.used[g][tid] = used;
-					used = 0u;
+				while (m == 0u && g < nw - 1) {
 					g++;
 					m = sm.hits[g][tid];
 				}
@@ -220,33 +225,27 @@ composite_forward_kernel(int W, int H, unsigned gx, const uint2* __restrict__ ra
 					const int jl = __ffs(m) - 1;
 					m &= m - 1;
 					const int j = g * 32 + jl;
-					if (eval_pair<USE_SA>(recs + j * 5, pxf, pyf, (uint32_t)(b * FWD_BATCH + j + 1), px, done))
-						used |= 1u << jl;
-					if (done) {   // T < 1e-4: nothing behind this pair counts; park the lane at the last word
-						m = 0u;
-						if (g < FWD_GROUPS - 1) {
-							sm.used[g][tid] = used;
-							used = 0u;
-							g = FWD_GROUPS - 1;
+					const float4* rec = recs + j * 5;
+					PairFront f;
+					if (pair_front(rec[0], rec[1], rec[2], pxf, pyf, f)) {
+						blend_pair<USE_SA>(f.alpha, f.depth, rec[3], rec[4], (uint32_t)(first + j + 1), px, done);
+						if (done) {   // T < 1e-4: nothing behind this pair counts; park the lane at the last word
+							stop = j;
+							m = 0u;
+							g = nw - 1;
 						}
+					} else {
+						sm.hits[g][tid] &= ~(1u << jl);   // in the footprint, not a contributor (1.4 % of the pairs)
 					}
 				}
 			}
-			sm.used[g][tid] = used;
 		}
-		// for the backward pass (coalesced, one word per pixel thread): the pairs that really contributed,
-		// and the pairs of the footprint masks (they own a gradient-pair slot each)
-#pragma unroll
-		for (int g = 0; g < FWD_GROUPS; g++) {
-			pix_words[(size_t)((b * FWD_GROUPS + g) * 2 + 0) * TILE_PIXELS + ptid] = sm.used[g][tid];
-			pix_words[(size_t)((b * FWD_GROUPS + g) * 2 + 1) * TILE_PIXELS + ptid] = sm.hits[g][tid];
+		// for the backward pass (coalesced, one word per pixel thread): the pairs that really contributed
+		for (int w = 0; w < nw; w++) {
+			const uint32_t used = done_before ? 0u : (sm.hits[w][tid] & bits_below(stop - 32 * w));
+			pix_words[(size_t)((sb * FWD_WORDS + w) * 2 + 0) * TILE_PIXELS + ptid] = used;
 		}
 	}
-
-	// early exit: no bulk copy may still be in flight when the CTA retires (requested but never consumed batches)
-	if (tid == 0)
-		for (int bb = first_unwaited; bb < min(nb, first_unwaited + FWD_STAGES - 1); bb++)
-			mbar_wait(&s_bar[bb % FWD_STAGES], (uint32_t)(bb / FWD_STAGES) & 1u);
 
 	if (inside) {
 		const size_t HW = (size_t)H * W;
@@ -276,6 +275,26 @@ composite_forward_kernel(int W, int H, unsigned gx, const uint2* __restrict__ ra
 	}
 }
 
+template <bool USE_SA>
+int launch_variant(const gs2d_settings& s, const gs2d_inputs& in, const ImageState& im, const float* instances,
+                   const uint32_t* hit_inst, uint32_t* hit_pix, float* out_color, float* out_others, unsigned gx,
+                   unsigned gy, cudaStream_t st)
+{
+	// the opt-in to > 48 KB of dynamic shared memory is per device: made once for every device this variant runs on
+	static std::atomic<unsigned long long> opted_in{0};
+	int dev = 0;
+	GS2D_CUDA_OK(cudaGetDevice(&dev));
+	if (dev >= 64 || !((opted_in.load(std::memory_order_relaxed) >> dev) & 1ull)) {
+		GS2D_CUDA_OK(cudaFuncSetAttribute(composite_forward_kernel<USE_SA>,
+		                                  cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(FwdSmem)));
+		if (dev < 64) opted_in.fetch_or(1ull << dev, std::memory_order_relaxed);
+	}
+	composite_forward_kernel<USE_SA><<<gx * gy, 256, sizeof(FwdSmem), st>>>(
+		s.image_width, s.image_height, gx, (const uint2*)im.ranges, (const float4*)instances, hit_inst, hit_pix,
+		in.background, im.final_T, im.n_contrib, im.median_depth, im.depth_std, out_color, out_others);
+	return GS2D_OK;
+}
+
 }  // namespace
 
 int launch_composite_forward(const gs2d_settings& s, const gs2d_inputs& in, const ImageState& im,
@@ -285,21 +304,10 @@ int launch_composite_forward(const gs2d_settings& s, const gs2d_inputs& in, cons
 	const int W = s.image_width, H = s.image_height;
 	const unsigned gx = (W + TILE - 1) / TILE, gy = (H + TILE - 1) / TILE;
 	if (gx * gy == 0) return GS2D_OK;
-	static bool attr_set = false;
-	if (!attr_set) {
-		GS2D_CUDA_OK(cudaFuncSetAttribute(composite_forward_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(FwdSmem)));
-		GS2D_CUDA_OK(cudaFuncSetAttribute(composite_forward_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(FwdSmem)));
-		attr_set = true;
-	}
 	ProfScope ps(K_COMPOSITE_FWD, st);
-	if (s.use_sa)
-		composite_forward_kernel<true><<<gx * gy, 256, sizeof(FwdSmem), st>>>(
-			W, H, gx, (const uint2*)im.ranges, (const float4*)instances, hit_inst, hit_pix, in.background, im.final_T,
-			im.n_contrib, im.median_depth, im.depth_std, out_color, out_others);
-	else
-		composite_forward_kernel<false><<<gx * gy, 256, sizeof(FwdSmem), st>>>(
-			W, H, gx, (const uint2*)im.ranges, (const float4*)instances, hit_inst, hit_pix, in.background, im.final_T,
-			im.n_contrib, im.median_depth, im.depth_std, out_color, out_others);
+	const int rc = s.use_sa ? launch_variant<true>(s, in, im, instances, hit_inst, hit_pix, out_color, out_others, gx, gy, st)
+	                        : launch_variant<false>(s, in, im, instances, hit_inst, hit_pix, out_color, out_others, gx, gy, st);
+	if (rc != GS2D_OK) return rc;
 	count_launch();
 	GS2D_CUDA_OK(cudaGetLastError());
 	return GS2D_OK;

@@ -70,7 +70,8 @@ def main():
     for k in (128, 256, 384):
         out["tile_n"][f"frac_le{k}"] = float((nt <= k).mean())
     tot_foot = tot_used = 0
-    walk = {"rows": 0, "blk8x4": 0, "sorted": 0, "sorted_tile": 0, "ideal": 0}
+    walk = {"rows": 0, "blk8x4": 0, "sorted": 0, "sorted_tile": 0, "tileperm_batch128": 0, "tileperm_batch256": 0,
+            "blk8x4_batch256": 0, "blk8x4_tile": 0, "ideal": 0}
     per_pixel_len, batch_pairs = [], []
     lane = np.arange(256)
     # thread -> row-major pixel id of the 8x4 block layout (pair.cuh thread_lx / thread_ly with BLOCK = 1)
@@ -92,6 +93,14 @@ def main():
         walk["blk8x4"] += int(fb[:, blk_pix].reshape(nb, 8, 32).max(2).sum()) * 32
         walk["sorted"] += int(np.sort(fb, axis=1).reshape(nb, 8, 32).max(2).sum()) * 32
         walk["sorted_tile"] += int(np.sort(fb.sum(0)).reshape(8, 32).max(1).sum()) * 32
+        # one pixel -> thread permutation per tile (by whole-tile list length), walk still in lockstep per batch
+        order = np.argsort(fb.sum(0), kind="stable")
+        walk["tileperm_batch128"] += int(fb[:, order].reshape(nb, 8, 32).max(2).sum()) * 32
+        fb2 = fb if nb % 2 == 0 else np.concatenate([fb, np.zeros((1, 256), fb.dtype)])
+        fb2 = fb2.reshape(-1, 2, 256).sum(1)
+        walk["tileperm_batch256"] += int(fb2[:, order].reshape(-1, 8, 32).max(2).sum()) * 32
+        walk["blk8x4_batch256"] += int(fb2[:, blk_pix].reshape(-1, 8, 32).max(2).sum()) * 32
+        walk["blk8x4_tile"] += int(fb.sum(0)[blk_pix].reshape(8, 32).max(1).sum()) * 32
         walk["ideal"] += int(fb.sum())
     bp = np.array(batch_pairs)
     out.update(footprint_pairs=tot_foot, used_pairs=tot_used, used_over_footprint=tot_used / max(tot_foot, 1),
