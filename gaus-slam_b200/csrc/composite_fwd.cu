@@ -42,12 +42,15 @@ constexpr int FWD_CHUNKS = GS2D_FWD_CHUNKS;
 constexpr int FWD_SUPER = FWD_BATCH * FWD_CHUNKS;   // instances resident at once
 constexpr int FWD_WORDS = FWD_SUPER / 32;           // hit words per pixel per super-batch
 static_assert(FWD_BATCH / 32 <= HIT_PIX_PAD, "hit_pix padding");
+constexpr int FWD_SORT_BINS = 64;                   // list lengths 0 .. 62, 63 = longer
 
 struct FwdSmem {
 	float4 rec[FWD_CHUNKS][FWD_BATCH * 5];    // contiguous: instance i of the super-batch is rec[0][5 * i]
 	uint32_t mask[FWD_CHUNKS][FWD_BATCH * 8];
 	uint32_t hits[FWD_WORDS][TILE_PIXELS];    // per-pixel hit words (live pixels; rejected pairs get cleared)
 	uint64_t bar[FWD_CHUNKS];
+	uint32_t bins[FWD_SORT_BINS];             // counting sort of the pixels by list length
+	uint8_t order[TILE_PIXELS];               // thread -> natural owner of the pixel it walks
 };
 
 struct PixelFwd {
@@ -144,13 +147,10 @@ composite_forward_kernel(int W, int H, unsigned gx, const uint2* __restrict__ ra
 	const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 	const unsigned tile = blockIdx.x;
 	const unsigned tx = tile % gx, ty = tile / gx;
-	const int lx = thread_lx<1>(tid), ly = thread_ly<1>(tid);   // thread <-> tile pixel: 8 x 4 block per warp (pair.cuh)
-	const int ptid = pixel_thread(lx, ly);               // row-major pixel index: where this pixel's words go in hit_pix
-	const unsigned pix_x = tx * TILE + lx;
-	const unsigned pix_y = ty * TILE + ly;
-	const bool inside = pix_x < (unsigned)W && pix_y < (unsigned)H;
-	const float pxf = (float)pix_x, pyf = (float)pix_y;
-
+	// The transposition below hands thread t the hit words of its NATURAL pixel (warp k = 8 x 4 block k, pair.cuh).
+	// The walk is done by another thread: pixels are sorted by list length once per tile, so that the 32 lists of a
+	// warp are alike (lanes busy: 0.75 natural -> 0.93 sorted, scripts/pair_stats.py).
+	const int nat_ptid = pixel_thread(thread_lx<1>(tid), thread_ly<1>(tid));   // row-major index of the natural pixel
 	const uint2 range = ranges[tile];
 	const int n = (int)(range.y - range.x);
 	const int nsb = (n + FWD_SUPER - 1) / FWD_SUPER;
@@ -166,6 +166,11 @@ composite_forward_kernel(int W, int H, unsigned gx, const uint2* __restrict__ ra
 	const float4* recs = &sm.rec[0][0];
 
 	PixelFwd px;
+	int o = tid;                   // natural owner of the pixel this thread walks (sorted at the first super-batch)
+	int ptid = nat_ptid;
+	unsigned pix_x = tx * TILE + thread_lx<1>(tid), pix_y = ty * TILE + thread_ly<1>(tid);
+	bool inside = pix_x < (unsigned)W && pix_y < (unsigned)H;
+	float pxf = (float)pix_x, pyf = (float)pix_y;
 	bool done = !inside;
 
 	for (int sb = 0; sb < nsb; sb++) {
@@ -188,7 +193,6 @@ composite_forward_kernel(int W, int H, unsigned gx, const uint2* __restrict__ ra
 		}
 		const uint32_t parity = (uint32_t)sb & 1u;              // every chunk barrier completes one phase per super-batch
 		const int nw = nch * (FWD_BATCH / 32);                  // hit words per pixel in this super-batch
-		const bool done_before = done;
 		// Transpose in registers, chunk by chunk as the chunks land: this warp's byte-gathered word of instance j
 		// holds its 32 pixels; a 32x32 bit transpose turns the words of 32 instances into one hit word per pixel
 		// (bit j <-> instance 32 g + j).  The raw words are the footprint (a gradient-pair slot each in the backward
@@ -203,22 +207,59 @@ composite_forward_kernel(int W, int H, unsigned gx, const uint2* __restrict__ ra
 				const uint32_t mine = j < cnt ? warp_word<1>(masks + j * 8, warp) : 0u;
 				const uint32_t raw = __any_sync(0xffffffffu, mine != 0u) ? transpose32(mine, lane) : 0u;
 				const int w = c * (FWD_BATCH / 32) + g;
-				sm.hits[w][tid] = done ? 0u : raw;
-				pix_words[(size_t)((sb * FWD_WORDS + w) * 2 + 1) * TILE_PIXELS + ptid] = raw;
+				sm.hits[w][tid] = raw;
+				pix_words[(size_t)((sb * FWD_WORDS + w) * 2 + 1) * TILE_PIXELS + nat_ptid] = raw;
 			}
+		}
+
+		if (sb == 0) {
+			// counting sort of the 256 pixels by the length of their list, longest first
+			int c = 0;
+			for (int w = 0; w < nw; w++) c += __popc(sm.hits[w][tid]);
+			c = (FWD_SORT_BINS - 1) - min(c, FWD_SORT_BINS - 1);
+			if (tid < FWD_SORT_BINS) sm.bins[tid] = 0u;
+			__syncthreads();
+			const uint32_t rank = atomicAdd(&sm.bins[c], 1u);
+			__syncthreads();
+			if (warp == 0) {
+				const uint32_t a = sm.bins[2 * lane], b = sm.bins[2 * lane + 1];
+				uint32_t incl = a + b;
+#pragma unroll
+				for (int d = 1; d < 32; d <<= 1) {
+					const uint32_t t = __shfl_up_sync(0xffffffffu, incl, d);
+					if (lane >= d) incl += t;
+				}
+				sm.bins[2 * lane] = incl - a - b;
+				sm.bins[2 * lane + 1] = incl - b;
+			}
+			__syncthreads();
+			sm.order[sm.bins[c] + rank] = (uint8_t)tid;
+			__syncthreads();
+			o = sm.order[tid];
+			const int lx = thread_lx<1>(o), ly = thread_ly<1>(o);
+			ptid = pixel_thread(lx, ly);
+			pix_x = tx * TILE + lx;
+			pix_y = ty * TILE + ly;
+			inside = pix_x < (unsigned)W && pix_y < (unsigned)H;
+			pxf = (float)pix_x;
+			pyf = (float)pix_y;
+			done = !inside;
+		} else {
+			__syncthreads();           // the hit words were written by the pixels' natural owners
 		}
 
 		// Every pixel walks its own hits of the WHOLE super-batch front to back, in one loop: a warp iterates as
 		// often as its longest pixel list.
+		const bool done_before = done;
 		int stop = FWD_SUPER;          // instance (in the super-batch) at which this pixel terminated
 		{
 			int g = 0;
-			uint32_t m = sm.hits[0][tid];
+			uint32_t m = done ? 0u : sm.hits[0][o];
 			for (;;) {
 				// advance to the next non-empty word (finished pixels sit at the last word with m = 0)
 				while (m == 0u && g < nw - 1) {
 					g++;
-					m = sm.hits[g][tid];
+					m = done ? 0u : sm.hits[g][o];
 				}
 				if (!__any_sync(0xffffffffu, m != 0u)) break;
 				if (m != 0u) {
@@ -235,14 +276,14 @@ composite_forward_kernel(int W, int H, unsigned gx, const uint2* __restrict__ ra
 							g = nw - 1;
 						}
 					} else {
-						sm.hits[g][tid] &= ~(1u << jl);   // in the footprint, not a contributor (1.4 % of the pairs)
+						sm.hits[g][o] &= ~(1u << jl);   // in the footprint, not a contributor (1.4 % of the pairs)
 					}
 				}
 			}
 		}
 		// for the backward pass (coalesced, one word per pixel thread): the pairs that really contributed
 		for (int w = 0; w < nw; w++) {
-			const uint32_t used = done_before ? 0u : (sm.hits[w][tid] & bits_below(stop - 32 * w));
+			const uint32_t used = done_before ? 0u : (sm.hits[w][o] & bits_below(stop - 32 * w));
 			pix_words[(size_t)((sb * FWD_WORDS + w) * 2 + 0) * TILE_PIXELS + ptid] = used;
 		}
 	}

@@ -21,6 +21,13 @@ __device__ __forceinline__ void mbar_fence_init()
 	asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
 }
 
+// Orders earlier generic-proxy accesses of shared memory (ordinary loads / stores) before later async-proxy ones
+// (bulk copies): needed before a bulk copy overwrites shared memory that ordinary stores wrote.
+__device__ __forceinline__ void fence_proxy_async()
+{
+	asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+
 __device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t* bar, uint32_t bytes)
 {
 	asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_addr(bar)), "r"(bytes)

@@ -40,6 +40,7 @@ inline void mbar_init(uint64_t* bar, uint32_t count)
 }
 
 inline void mbar_fence_init() { __threadfence(); }
+inline void fence_proxy_async() { __threadfence(); }
 
 inline void mbar_arrive_expect_tx(uint64_t* bar, uint32_t bytes)
 {
