@@ -328,6 +328,20 @@ int gs2d_backward(const gs2d_settings* s, const gs2d_inputs* in, const gs2d_buff
 	return GS2D_OK;
 }
 
+int gs2d_backward_overflowed(const gs2d_settings* s, const gs2d_buffers* buffers, int64_t I, int32_t* flag_host,
+                             void* stream)
+{
+	if (!s || !buffers || !flag_host) return GS2D_ERR_INVALID;
+	*flag_host = 0;
+	if (I <= 0) return GS2D_OK;
+	if (!buffers->binning) return GS2D_ERR_INVALID;
+	cudaStream_t st = (cudaStream_t)stream;
+	BinningState b = BinningState::carve(buffers->binning, (size_t)I, tiles_of(s->image_width, s->image_height), nullptr);
+	GS2D_CUDA_OK(cudaMemcpyAsync(flag_host, b.pair_counters + 3, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+	GS2D_CUDA_OK(cudaStreamSynchronize(st));
+	return GS2D_OK;
+}
+
 int gs2d_mark_visible(int32_t P, const float* means3D, const float* viewmatrix, const float* projmatrix,
                       uint8_t* present, void* stream)
 {

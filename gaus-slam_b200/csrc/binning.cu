@@ -7,6 +7,8 @@
 // bits), same emission order (tile rows outer, columns inner), stable LSD sort.
 //
 // All kernels here are HBM-bound integer/byte movers.
+#include <atomic>
+
 #include "common.cuh"
 #include "pair.cuh"
 
@@ -285,11 +287,16 @@ static int sort_passes_run(int64_t n, uint64_t* keys_a, uint32_t* vals_a, uint64
 {
 	const int passes = sort_passes(end_bit);
 	if (passes > SORT_MAX_PASSES) return GS2D_ERR_INVALID;
-	static bool attr_set = false;
-	if (!attr_set) {
-		GS2D_CUDA_OK(cudaFuncSetAttribute(onesweep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-		                                  (int)sizeof(SortSmem)));
-		attr_set = true;
+	{
+		// the dynamic shared-memory opt-in is per device: made once for every device the sort runs on
+		static std::atomic<unsigned long long> opted_in{0};
+		int dev = 0;
+		GS2D_CUDA_OK(cudaGetDevice(&dev));
+		if (dev >= 64 || !((opted_in.load(std::memory_order_relaxed) >> dev) & 1ull)) {
+			GS2D_CUDA_OK(cudaFuncSetAttribute(onesweep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+			                                  (int)sizeof(SortSmem)));
+			if (dev < 64) opted_in.fetch_or(1ull << dev, std::memory_order_relaxed);
+		}
 	}
 	{
 		ProfScope ps(K_DIGIT_BASE, st);

@@ -214,7 +214,7 @@ composite_backward_pixels_kernel(int W, int H, unsigned gx, const uint2* __restr
                                  const uint32_t* __restrict__ n_contrib, const float* __restrict__ median_depth,
                                  const float* __restrict__ depth_std, const float* __restrict__ dL_dpix,
                                  const float* __restrict__ dL_dothers, float4* __restrict__ slots,
-                                 float* __restrict__ grad_rows)
+                                 float* __restrict__ grad_rows, uint32_t slot_cap, uint32_t* __restrict__ overflow)
 {
 	__shared__ BwdSmem sm;
 
@@ -232,6 +232,12 @@ composite_backward_pixels_kernel(int W, int H, unsigned gx, const uint2* __restr
 
 	const uint2 range = ranges[tile];
 	const int n = (int)(range.y - range.x);
+	// Memory safety against a wrong pair count from the caller (it sized `slots`): a tile whose slots would end beyond
+	// the scratch writes nothing and raises the flag (pair_counters[3] of the binning state) instead.
+	if (n > 0 && pair_incl[(size_t)range.x + n - 1] > slot_cap) {
+		if (threadIdx.x == 0) *overflow = 1u;
+		return;
+	}
 
 	PixelConst pc;
 	pc.T_final = inside ? final_T[pid] : 0.f;
@@ -470,12 +476,12 @@ int launch_composite_backward(const gs2d_settings& s, const gs2d_inputs& in, con
 			composite_backward_pixels_kernel<true><<<gx * gy, 256, 0, st>>>(
 				W, H, gx, (const uint2*)im.ranges, (const float4*)b.instances, b.hit_inst, b.hit_pix, b.pair_incl,
 				in.background, im.final_T, im.n_contrib, im.median_depth, im.depth_std, dL_dcolor, dL_dothers, slots,
-				rows);
+				rows, (uint32_t)(pairs > 0 ? pairs : 0), b.pair_counters + 3);
 		else
 			composite_backward_pixels_kernel<false><<<gx * gy, 256, 0, st>>>(
 				W, H, gx, (const uint2*)im.ranges, (const float4*)b.instances, b.hit_inst, b.hit_pix, b.pair_incl,
 				in.background, im.final_T, im.n_contrib, im.median_depth, im.depth_std, dL_dcolor, dL_dothers, slots,
-				rows);
+				rows, (uint32_t)(pairs > 0 ? pairs : 0), b.pair_counters + 3);
 		count_launch();
 	}
 	GS2D_CUDA_OK(cudaGetLastError());

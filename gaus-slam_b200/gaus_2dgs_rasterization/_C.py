@@ -14,11 +14,48 @@ import torch
 from gs2d_b200 import _lib as L
 
 _pinned = {}
-# Pair-slot counts of recent forward passes (a by-product like num_rendered, needed to size the backward
-# scratch): ring of pinned int64 slots per device, looked up by the binning buffer's address.
-_PAIR_RING = 64
-_pair_slots = {}
-_pair_of_binning = {}
+
+
+class _PairCount:
+    """The pair-slot count of ONE forward pass (a by-product like num_rendered, needed to size the backward scratch):
+    its own pinned int64 cell, written by a device-to-host copy enqueued right after the footprint scan, and an event
+    recorded after the forward's last launch.  The cell goes back to a free list when the holder dies."""
+    __slots__ = ("cell", "event")
+    _free = []
+
+    def __init__(self):
+        self.cell, self.event = _PairCount._free.pop() if _PairCount._free else (torch.zeros(1, dtype=torch.int64).pin_memory(), torch.cuda.Event())
+        C.c_int64.from_address(self.cell.data_ptr()).value = -1      # "not there yet"
+
+    def __del__(self):
+        try:
+            _PairCount._free.append((self.cell, self.event))
+        except Exception:       # interpreter shutdown
+            pass
+
+    def ptr(self):
+        return self.cell.data_ptr()
+
+    def wait(self):
+        """The count, as soon as its copy has landed (long before the forward pass ends).  Bounded: once the forward's
+        event has completed the copy must be there; a CUDA error of the forward surfaces through the event query."""
+        cell = C.c_int64.from_address(self.cell.data_ptr())
+        spins = 0
+        while cell.value < 0:
+            spins += 1
+            if spins % 256 == 0 and self.event.query():
+                if cell.value < 0:
+                    raise RuntimeError("rasterize_gaussians_backward: the forward pass finished without delivering its "
+                                       "pair count")
+        return int(cell.value)
+
+
+class _NumRendered(int):
+    """num_rendered as the reference returns it (an int), carrying the forward's pair count for the backward pass:
+    the autograd bridge keeps this object in ctx and hands it back as `R`."""
+    pairs = None
+
+
 # Optional destination of the five map-parameter gradients (gs2d_b200.mapping.gradient_arena): a flat fp32
 # buffer [13 * P] laid out group by group (xyz | opacity | scale | rotation | rgb).  While set, the backward
 # pass writes those gradients straight into it, so a view-sharded trainer all-reduces the buffer without a
@@ -58,8 +95,10 @@ def _ptr(t):
     return t.data_ptr()
 
 
-def _pinned_i64(device) -> torch.Tensor:
-    key = str(device)
+def _pinned_i64(device, stream_id) -> torch.Tensor:
+    """One pinned num_rendered cell per device AND stream: two streams of one process (frontend + backend) do not
+    share it."""
+    key = (str(device), stream_id)
     if key not in _pinned:
         _pinned[key] = torch.zeros(1, dtype=torch.int64).pin_memory()
     return _pinned[key]
@@ -70,16 +109,6 @@ def _bucket(nbytes: int) -> int:
     identical sizes let torch's caching allocator reuse the block instead of calling cudaMalloc."""
     g = 1 << 25
     return nbytes if nbytes < g else (nbytes + g - 1) // g * g
-
-
-def _pair_slot(device):
-    key = str(device)
-    if key not in _pair_slots:
-        _pair_slots[key] = [torch.zeros(_PAIR_RING, dtype=torch.int64).pin_memory(), 0]
-    ring = _pair_slots[key]
-    i = ring[1]
-    ring[1] = (i + 1) % _PAIR_RING
-    return ring[0], i
 
 
 # Scatter arenas (one per device and stream): capacity follows the largest num_rendered seen, so that the scatter of
@@ -144,9 +173,9 @@ def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations,
                     viewmatrix, projmatrix, campos)
         bufs = L.Buffers(geom=_ptr(geom), geom_bytes=geom.numel(), binning=None, binning_bytes=0,
                          image=_ptr(img), image_bytes=img.numel())
-        n_host = _pinned_i64(dev)
         stream = torch.cuda.current_stream(dev)
         sid = int(stream.cuda_stream)
+        n_host = _pinned_i64(dev, sid)
         L.check(lib.gs2d_forward_preprocess(C.byref(s), C.byref(i), C.byref(bufs), _ptr(radii),
                                             n_host.data_ptr(), st), "gs2d_forward_preprocess")
         ev = _events.get((str(dev), sid))
@@ -167,17 +196,16 @@ def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations,
         binning = torch.empty((_bucket(lib.gs2d_binning_bytes(num_rendered, W, H)) if num_rendered else 0,), **u8)
         bufs.binning = _ptr(binning)
         bufs.binning_bytes = binning.numel()
+        num_rendered = _NumRendered(num_rendered)
         pairs_ptr = None
         if num_rendered:
-            ring, slot = _pair_slot(dev)
-            pairs_ptr = ring.data_ptr() + 8 * slot
-            C.c_int64.from_address(pairs_ptr).value = -1      # "not there yet"
-            if len(_pair_of_binning) > 4 * _PAIR_RING:
-                _pair_of_binning.clear()
-            _pair_of_binning[binning.data_ptr()] = pairs_ptr
-        L.check(lib.gs2d_forward_render_scattered(C.byref(s), C.byref(i), C.byref(bufs), num_rendered, _ptr(out_color),
+            num_rendered.pairs = _PairCount()
+            pairs_ptr = num_rendered.pairs.ptr()
+        L.check(lib.gs2d_forward_render_scattered(C.byref(s), C.byref(i), C.byref(bufs), int(num_rendered), _ptr(out_color),
                                                   _ptr(out_others), pairs_ptr, scattered, st),
                 "gs2d_forward_render")
+        if num_rendered:
+            num_rendered.pairs.event.record(stream)
     return num_rendered, out_color, out_others, radii, geom, binning, img
 
 
@@ -213,14 +241,20 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
 
     num_pairs = 0
     if int(R) > 0:
-        entry = _pair_of_binning.get(binningBuffer.data_ptr())
-        if entry is None:
-            raise RuntimeError("rasterize_gaussians_backward: binningBuffer does not come from a forward pass of this "
-                               "process (pair-slot count unknown)")
-        cell = C.c_int64.from_address(entry)
-        while cell.value < 0:       # copied right after the footprint scan, long before the forward pass ended
-            pass
-        num_pairs = int(cell.value)
+        holder = getattr(R, "pairs", None)
+        if holder is not None:
+            num_pairs = holder.wait()
+        else:
+            # R is a plain int (a caller that did not keep the object the forward returned): ask the binning buffer
+            with torch.cuda.device(dev):
+                cell = torch.zeros(1, dtype=torch.int64).pin_memory()
+                s0 = _settings(P, W, H, degree, 0, use_sa, False, debug, tan_fovx, tan_fovy, scale_modifier)
+                b0 = L.Buffers(geom=None, geom_bytes=0, binning=_ptr(binningBuffer), binning_bytes=binningBuffer.numel(),
+                               image=None, image_bytes=0)
+                L.check(lib.gs2d_forward_pair_count(C.byref(s0), C.byref(b0), int(R), cell.data_ptr(), _stream_ptr(dev)),
+                        "gs2d_forward_pair_count")
+                torch.cuda.current_stream(dev).synchronize()
+                num_pairs = int(cell[0])
     with torch.cuda.device(dev):
         st = _stream_ptr(dev)
         scratch = torch.empty((_bucket(lib.gs2d_backward_scratch_bytes(P, int(R), num_pairs, W, H)),),

@@ -14,7 +14,10 @@
  *   gs2d_dist2      replaces distCUDA2 / SimpleKNN::knn        KNN/spatial.cu:15-26, KNN/simple_knn.cu:186-222
  *
  * Rules of the ABI
- *   - plain C: pointers, sizes, scalars; no torch types, no exceptions, no global state.
+ *   - plain C: pointers, sizes, scalars; no torch types, no exceptions, no state that a result depends on: calls on
+ *     different streams / devices / threads are independent.  Process-wide are only diagnostics (the launch counter,
+ *     the opt-in kernel timing of gs2d_timing_*), the one-time per-device kernel attribute opt-ins, and the static
+ *     scratch of gs2d_sort_pairs_static.
  *   - every pointer is a DEVICE pointer owned by the caller unless its name ends in
  *     `_host`; nothing is allocated or freed behind the caller's back.
  *   - every function that launches work takes the CUDA stream to launch on
@@ -166,13 +169,20 @@ int gs2d_forward_pair_count(const gs2d_settings* s, const gs2d_buffers* buffers,
 
 /* Backward (CR/backward.cu:143-463 render, :466-664 preprocess).  `radii` and the three
  * buffers are those of the matching forward; dL_dout_color [3,H,W], dL_dout_others [7,H,W].
- * `scratch` must hold gs2d_backward_scratch_bytes(P, num_rendered, num_pairs, W, H) bytes. */
+ * `scratch` must hold gs2d_backward_scratch_bytes(P, num_rendered, num_pairs, W, H) bytes.  `num_pairs` must be the
+ * count of THAT forward (gs2d_forward_render's num_pairs_host, or gs2d_forward_pair_count).  A smaller value cannot
+ * corrupt memory: a tile whose pair slots would end beyond `num_pairs` writes nothing (its gradient rows stay
+ * undefined) and sets the overflow word of the binning state, which gs2d_backward_overflowed() reads back. */
 size_t gs2d_backward_scratch_bytes(int32_t P, int64_t num_rendered, int64_t num_pairs, int32_t image_width,
                                    int32_t image_height);
 int gs2d_backward(const gs2d_settings* s, const gs2d_inputs* in, const gs2d_buffers* buffers,
                   const int32_t* radii, int64_t num_rendered, int64_t num_pairs,
                   const float* dL_dout_color, const float* dL_dout_others,
                   const gs2d_grads* grads, void* scratch, void* stream);
+/* 1 in *flag_host (pinned or pageable host int32) if the last gs2d_backward on these buffers skipped tiles because
+ * num_pairs was too small, else 0.  Synchronises the stream. */
+int gs2d_backward_overflowed(const gs2d_settings* s, const gs2d_buffers* buffers, int64_t num_rendered,
+                             int32_t* flag_host, void* stream);
 
 /* present[i] = view-space z of means3D[i] > 0.2 (CR/rasterizer_impl.cu:54-66, CR/auxiliary.h:184-209).
  * `present` is one byte per surfel (torch.bool). */

@@ -66,6 +66,9 @@ class _FakeEvent:
     def synchronize(self):
         pass
 
+    def query(self):
+        return True
+
 
 def _fake_torch():
     fake = types.SimpleNamespace(**{k: getattr(torch, k) for k in dir(torch) if not k.startswith("__")})
