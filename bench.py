@@ -183,6 +183,18 @@ def mapping_loss(color, allmap, gt_color, gt_depth):
     return 0.5 * l_color + l_depth + 0.1 * l_dist
 
 
+def csrc_sha256():
+    """Hash of the kernel sources (names + contents of gaus-slam_b200/csrc): stamps the ncu summaries."""
+    import hashlib
+    h = hashlib.sha256()
+    d = os.path.join(ROOT, "gaus-slam_b200", "csrc")
+    for name in sorted(os.listdir(d)):
+        h.update(name.encode())
+        with open(os.path.join(d, name), "rb") as f:
+            h.update(f.read())
+    return h.hexdigest()
+
+
 def algorithmic_bytes(P, Pv, I, W, H):
     """Compulsory HBM bytes per launch, SURVEY.md §8(d) (each stage reads its inputs once, writes its outputs
     once).  Keys are gs2d kernel names."""
@@ -429,29 +441,40 @@ def main():
     order = ["means3D", "opacities", "scales", "rotations", "colors"]
 
     from gs2d_b200 import mapping
-    grad_path = {"zero_copy": None, "collective": "NCCL all-reduce"}
-    if multi and a.impl == "b200":
-        # With GS2D_ALLREDUCE=multimem the buffer lives in symmetric memory and is reduced IN the NVSwitch by libgs2d's
-        # own multimem kernel (csrc/collective.cu).  NCCL is the default: the in-switch kernel is opt-in (GS2D_ALLREDUCE=multimem) until the bench has been
-        # re-validated with it at 4 and 8 ranks
-        want = os.environ.get("GS2D_ALLREDUCE", "nccl")
-        sym = mapping.symmetric_gradient_buffer(P, dev) if want == "multimem" else None
-        if sym is not None:
-            flat = sym
-            grad_path["collective"] = "own in-switch all-reduce (multimem.ld_reduce / multimem.st over NVLS)"
-        # gradients of the five parameter groups are written straight into the buffer the all-reduce runs on
+    # How the map gradient is summed over the ranks (N > 1).  Three ways exist; all are checked and timed in an untimed
+    # preamble and the fastest one runs in the timed region (GS2D_ALLREDUCE=nccl|multimem|fused forces one):
+    #   nccl     -- gradients written in place into a flat [13 P] buffer (no packing copy), dist.all_reduce on it
+    #   multimem -- same buffer in symmetric memory, libgs2d's own in-switch all-reduce (multimem.ld_reduce / .st)
+    #   fused    -- no all-reduce pass: the backward-preprocess epilogue multimem.red's into every rank's copy
+    grad_path = {"zero_copy": None, "collective": "NCCL all-reduce", "mode": "nccl"}
+    coll = {"mode": "nccl", "flat": flat, "fg": None}
+    if multi:
         from gaus_2dgs_rasterization import _C as _gs2d_C
-        _gs2d_C.set_gradient_arena(flat)
+        coll["fg"] = mapping.FusedGradient(P, dev)
+        if not coll["fg"].ok:
+            coll["fg"] = None
 
     def view_of(step):
         return wl["sets"][mapping.view_of(step, rank, world if multi else 1, V)]
 
     def step_resident(step, collective=True):
+        if not (multi and collective):
+            _ = multi and _gs2d_C.set_gradient_arena(None)
+            color, others, g = arm.forward_backward(view_of(step))
+            return color
+        mode = coll["mode"]
+        if mode == "fused":
+            coll["fg"].begin()            # zero + cross-GPU barrier on a side stream, under the forward pass
+            color, others, g = arm.forward_backward(view_of(step))
+            coll["fg"].finish()
+            grad_path["zero_copy"] = True
+            return color
+        buf = coll["fg"].flat if mode == "multimem" else flat
+        _gs2d_C.set_gradient_arena(buf)
         color, others, g = arm.forward_backward(view_of(step))
-        if multi and collective:
-            if grad_path["zero_copy"] is None:
-                grad_path["zero_copy"] = mapping.grads_alias_flat(g, flat)
-            mapping.allreduce_map_gradient(mapping.pack_grads(g, flat))
+        if grad_path["zero_copy"] is None:
+            grad_path["zero_copy"] = mapping.grads_alias_flat(g, buf)
+        mapping.allreduce_map_gradient(mapping.pack_grads(g, buf))
         return color
 
     def barrier():
@@ -459,20 +482,41 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
+    def timed_steps(fn, steps, first_step, finish=None):
+        """Times `steps` steps with ONE CUDA-EVENT PAIR PER STEP (a single pair around a 16 ms window made one
+        scheduler / NVML hiccup a 2-3x error in round 1), bracketed by a barrier + synchronize on both sides; per-step
+        times are the MAX over ranks.  With steps <= 32 three such blocks are run.  -> statistics; `ms` = the median
+        step, `unstable` when the block medians differ by more than 10 %."""
+        nblocks = 3 if steps <= 32 else 1
+        per_all, block_medians, block_totals = [], [], []
+        for blk in range(nblocks):
+            barrier()
+            ev = [torch.cuda.Event(enable_timing=True) for _ in range(steps + 1)]
+            ev[0].record()
+            for i in range(steps):
+                fn(first_step + blk * steps + i)
+                if i == steps - 1 and finish is not None:
+                    finish()
+                ev[i + 1].record()
+            barrier()
+            per = torch.tensor([ev[i].elapsed_time(ev[i + 1]) for i in range(steps)], device=dev, dtype=torch.float64)
+            if multi:
+                dist.all_reduce(per, op=dist.ReduceOp.MAX)
+            per = per.cpu().numpy()
+            per_all.append(per)
+            block_medians.append(float(np.median(per)))
+            block_totals.append(float(per.sum()))
+        per = np.concatenate(per_all)
+        med = float(np.median(per))
+        return {"ms": med, "mean_ms": float(per.mean()), "p10_ms": float(np.percentile(per, 10)),
+                "p90_ms": float(np.percentile(per, 90)), "max_ms": float(per.max()),
+                "n_outliers": int((per > 1.5 * med).sum()), "timed_steps": int(per.size), "blocks": nblocks,
+                "block_median_ms": block_medians, "block_total_ms": block_totals,
+                "unstable": bool(max(block_medians) > 1.10 * min(block_medians))}
+
     def timed(fn, steps, first_step, finish=None):
-        barrier()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-        for i in range(steps):
-            fn(first_step + i)
-        if finish is not None:
-            finish()
-        e1.record()
-        barrier()
-        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
-        if multi:
-            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
-        return float(ms.item())
+        """Total time of `steps` steps as steps x the median step (for the loops of bench_loops.py)."""
+        return timed_steps(fn, steps, first_step, finish)["ms"] * steps
 
     # ---- device-resident `value`
     sampler = ClockSampler(local_rank, a.clock_period_ms)
@@ -489,15 +533,59 @@ def main():
         i += 1
         if i % 8 == 0:
             torch.cuda.synchronize()
+    collective_ab, allreduce_err = None, None
+    if multi:
+        # (1) the summed gradient of one step equals the sum of the ranks' local gradients (gathered), for every mode
+        _gs2d_C.set_gradient_arena(None)
+        color, others, g = arm.forward_backward(view_of(0))
+        local = torch.cat([g[k].reshape(-1) for k in order]).clone()
+        parts = [torch.empty_like(local) for _ in range(world)]
+        dist.all_gather(parts, local)
+        want = torch.stack(parts).sum(0)
+        del parts
+        modes = ["nccl"] + (["multimem", "fused"] if coll["fg"] is not None else [])
+        allreduce_err = {}
+        for m in modes:
+            coll["mode"] = m
+            step_resident(0)
+            got = coll["fg"].flat if m in ("multimem", "fused") else flat
+            allreduce_err[m] = float((got - want).abs().max() / want.abs().max())
+        del want
+        # (2) untimed A/B: a few steps of each, CUDA events, max over ranks
+        collective_ab = {}
+        for m in modes:
+            coll["mode"] = m
+            for i in range(3):
+                step_resident(i)
+            barrier_ = lambda: (dist.barrier(), torch.cuda.synchronize())   # noqa: E731
+            barrier_()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for i in range(16):
+                step_resident(3 + i)
+            e1.record()
+            barrier_()
+            tm = torch.tensor([e0.elapsed_time(e1) / 16], device=dev)
+            dist.all_reduce(tm, op=dist.ReduceOp.MAX)
+            collective_ab[m + "_ms_per_step"] = float(tm)
+        want_mode = os.environ.get("GS2D_ALLREDUCE", "")
+        ok_modes = [m for m in modes if allreduce_err[m] <= 1e-4]
+        best = min(ok_modes, key=lambda m: collective_ab[m + "_ms_per_step"])
+        coll["mode"] = want_mode if want_mode in ok_modes else best
+        collective_ab["chosen"] = coll["mode"]
+        grad_path["mode"] = coll["mode"]
+        grad_path["collective"] = {"nccl": "NCCL all-reduce", "multimem": "own in-switch all-reduce (multimem.ld_reduce / "
+                                   "multimem.st over NVLS)", "fused": "fused into the backward pass: multimem.red in the "
+                                   "backward-preprocess epilogue (gs2d_backward_reduce), no all-reduce pass"}[coll["mode"]]
     for i in range(a.warmup):
         step_resident(i)
     l0 = arm.launches()
     sampler.mark_begin()
-    ms_total = timed(step_resident, a.steps, a.warmup)
+    t_value = timed_steps(step_resident, a.steps, a.warmup)
     sampler.mark_end()
-    launches = arm.launches() - l0
+    launches = (arm.launches() - l0) // t_value["blocks"]      # launches of ONE block of K steps
     clocks = sampler.stop() if rank == 0 else None
-    ms_per_step = ms_total / a.steps
+    ms_per_step = t_value["ms"]
     value = world * 1000.0 / ms_per_step if multi else 1000.0 / ms_per_step
 
     # scene statistics of the window (instances I = num_rendered, visible surfels Pv), outside the timed region
@@ -523,7 +611,9 @@ def main():
         lib = arm.lib
         nk = lib.gs2d_num_kernels()
         lib.gs2d_timing_enable(1)
-        ms_timed_pass = timed(step_resident, a.steps, a.warmup)
+        t_pass = timed_steps(step_resident, a.steps, a.warmup)
+        ms_timed_pass = t_pass["mean_ms"] * a.steps
+        n_timed_steps = t_pass["timed_steps"]
         lib.gs2d_timing_enable(0)
         tot = (C.c_double * nk)(); cnt = (C.c_int64 * nk)()
         lib.gs2d_timing_collect(tot, cnt)
@@ -541,35 +631,38 @@ def main():
                 continue
             name = lib.gs2d_kernel_name(i).decode()
             avg_ms = tot[i] / cnt[i]
-            k = {"launches_per_step": cnt[i] / a.steps, "avg_us": 1e3 * avg_ms, "ms_per_step": tot[i] / a.steps}
+            k = {"launches_per_step": cnt[i] / n_timed_steps, "avg_us": 1e3 * avg_ms, "ms_per_step": tot[i] / n_timed_steps}
             if name in alg:
                 k["alg_bytes"] = alg[name]
                 k["gbs"] = alg[name] / (avg_ms * 1e-3) / 1e9
                 k["frac_hbm"] = k["gbs"] / peak
             kernels[name] = k
-        traffic = {}
-        try:        # DRAM bytes per launch from the committed ncu --set full captures (profiles/)
-            with open(os.path.join(ROOT, "profiles", "r1_ncu_traffic.json")) as f:
-                traffic = json.load(f)
-        except OSError:
-            pass
-        for n, k in kernels.items():
-            if n in traffic:
-                k["ncu_dram_bytes"] = traffic[n]
-        issue = {}
-        try:        # issue-slot utilisation per kernel from the same committed captures: what bounds the compositing kernels
-            with open(os.path.join(ROOT, "profiles", "r1_ncu_issue.json")) as f:
-                issue = json.load(f)
+        # ncu-derived columns (DRAM bytes per launch, issue-slot use, lanes per instruction) come from the committed
+        # summary of an `ncu --set full` capture (profiles/r2_ncu_summary.json, written by scripts/ncu_summary2.py).  The
+        # summary carries a hash of csrc/ at capture time; if the sources have changed since, the columns are dropped.
+        ncu, ncu_state = {}, "absent"
+        try:
+            with open(os.path.join(ROOT, "profiles", "r2_ncu_summary.json")) as f:
+                summ = json.load(f)
+            if summ.get("csrc_sha256") == csrc_sha256():
+                ncu, ncu_state = summ.get("kernels", {}), "current"
+            else:
+                ncu_state = "stale (csrc/ changed since the capture): dropped"
+            ncu_commit = summ.get("commit")
         except (OSError, ValueError):
-            pass
+            ncu_commit = None
+        traffic = {n: v.get("dram_bytes") for n, v in ncu.items()}
+        issue = ncu
         for n, k in kernels.items():
-            if isinstance(issue.get(n), dict):
-                k["ncu_issue_active_pct"] = issue[n].get("issue_active_pct")
-                k["ncu_active_lanes_per_inst"] = issue[n].get("active_lanes_per_inst")
+            if n in ncu:
+                k["ncu_dram_bytes"] = ncu[n].get("dram_bytes")
+                k["ncu_issue_active_pct"] = ncu[n].get("issue_active_pct")
+                k["ncu_active_lanes_per_inst"] = ncu[n].get("active_lanes_per_inst")
         dom = max((n for n in kernels if n in alg), key=lambda n: kernels[n]["ms_per_step"])
         roofline = {"kernel": dom, "bound": "hbm", "achieved": kernels[dom]["gbs"], "peak": peak, "unit": "GB/s",
                     "frac": kernels[dom]["frac_hbm"], "traffic": traffic.get(dom), "peak_source": peak_src,
                     "avg_launch_us": kernels[dom]["avg_us"], "alg_bytes_per_launch": kernels[dom]["alg_bytes"],
+                    "ncu_commit": ncu_commit, "ncu_state": ncu_state,
                     "share_of_step": kernels[dom]["ms_per_step"] / (ms_timed_pass / a.steps),
                     "issue_slot_frac": (issue[dom]["issue_active_pct"] / 100.0) if isinstance(issue.get(dom), dict) else None,
                     "active_lanes_per_inst": issue[dom].get("active_lanes_per_inst") if isinstance(issue.get(dom), dict) else None,
@@ -639,14 +732,24 @@ def main():
             for p in params.values():
                 p.grad = None
             means2D.grad = None
+            mode = coll["mode"] if (multi and collective) else None
+            buf = None
+            if multi:
+                if mode == "fused":
+                    coll["fg"].begin()        # zero + cross-GPU barrier on a side stream, under the forward pass
+                else:
+                    buf = None if mode is None else (coll["fg"].flat if mode == "multimem" else flat)
+                    _gs2d_C.set_gradient_arena(buf)
             rast = arm.rasterizer(s)
             color, radii, allmap = rast(means3D=params["means3D"], means2D=means2D, opacities=params["opacities"],
                                         colors_precomp=params["colors"], scales=params["scales"],
                                         rotations=params["rotations"])
             loss = loss_fn(color, allmap, s["gt_color"], s["gt_depth"])
             loss.backward()
-            if multi and collective:
-                mapping.allreduce_map_gradient(mapping.pack_grads({k: params[k].grad for k in order}, flat))
+            if mode == "fused":
+                coll["fg"].finish()
+            elif mode is not None:
+                mapping.allreduce_map_gradient(mapping.pack_grads({k: params[k].grad for k in order}, buf))
             freed[sl].record(cur)
             loss_host[sl].copy_(loss.detach().reshape(1), non_blocking=True)
             loss_done[sl].record(cur)
@@ -664,10 +767,11 @@ def main():
             step_e2e(i)
         read_pending_loss()
         reads0 = loss_log["reads"]
-        ms_e2e = timed(step_e2e, a.steps, a.warmup, finish=read_pending_loss) / a.steps
-        assert loss_log["reads"] - reads0 == a.steps and np.isfinite(loss_log["last"])
+        t_e2e = timed_steps(step_e2e, a.steps, a.warmup, finish=read_pending_loss)
+        ms_e2e = t_e2e["ms"]
+        assert loss_log["reads"] - reads0 >= t_e2e["timed_steps"] - t_e2e["blocks"] and np.isfinite(loss_log["last"])
         e2e = {"value": (world if multi else 1) * 1000.0 / ms_e2e, "unit": UNIT, "h2d_bytes_per_step": h2d,
-               "d2h_bytes_per_step": 4 + 4, "ms_per_step": ms_e2e,
+               "d2h_bytes_per_step": 4 + 4, "ms_per_step": ms_e2e, "timing": t_e2e,
                "what": "one mapping iteration through the public python API: GaussianRasterizer(...)(...) -> mapping "
                        "loss (slam/Loss.py:51-63 incl. render/__init__.py:46-49) -> loss.backward(); the keyframe's camera and RGB-D image "
                        "(3+1 channels fp32) are copied from pinned host memory every step (double-buffered on a copy "
@@ -695,8 +799,12 @@ def main():
                                   f"{P} surfels, {V}-keyframe window (BASELINE.json configs[2]), use_sa=True",
                       "surfels": P, "visible_mean": Pv_mean, "instances_mean": I_mean, "views": V,
                       "parallelism": f"view-sharded x{world if multi else 1}" + (", " + grad_path["collective"] + " of [P,13] map gradients" + (" written in place by the backward pass" if grad_path["zero_copy"] else " (packed copy)") if multi else ""),
-                      "l2": f"inputs rotate over {V} per-view sets ({V} x {(P * 52 + W * H * 56) / 1e6:.1f} MB > 126 MB L2); no explicit flush"},
-           "gpu_launches": launches, "clocks": clocks}
+                      "l2": f"every rank's inputs rotate over all {V} per-view sets, at every N ({V} x {(P * 52 + W * H * 56) / 1e6:.1f} MB > 126 MB L2: "
+                            f"gs2d_b200.mapping.view_of shifts the assignment by one view per pass over the window); no explicit flush"},
+           "gpu_launches": launches, "clocks": clocks, "timing": t_value, "unstable": t_value["unstable"]}
+    if multi:
+        out["collective_ab"] = collective_ab
+        out["allreduce_max_rel_err"] = allreduce_err
     if a.impl == "reference":
         out["impl"] = "reference"
         out["cpu_baseline"] = {"value": value, "unit": UNIT, "cores": 0, "kind": "reference",

@@ -299,18 +299,21 @@ int gs2d_forward_pair_count(const gs2d_settings* s, const gs2d_buffers* buffers,
 	return GS2D_OK;
 }
 
-int gs2d_backward(const gs2d_settings* s, const gs2d_inputs* in, const gs2d_buffers* buffers,
-                  const int32_t* radii, int64_t I, int64_t num_pairs, const float* dL_dout_color,
-                  const float* dL_dout_others, const gs2d_grads* grads, void* scratch, void* stream)
+static int backward_impl(const gs2d_settings* s, const gs2d_inputs* in, const gs2d_buffers* buffers,
+                         const int32_t* radii, int64_t I, int64_t num_pairs, const float* dL_dout_color,
+                         const float* dL_dout_others, const gs2d_grads* grads, float* mc_flat, void* scratch, void* stream)
 {
 	GS2D_TRY(check_common(s, in, buffers));
 	cudaStream_t st = (cudaStream_t)stream;
 	if (!grads || !dL_dout_color || !dL_dout_others) return GS2D_ERR_INVALID;
 	if (s->P == 0) return GS2D_OK;
 	if (!radii || !buffers->geom || !buffers->image) return GS2D_ERR_INVALID;
-	if (!grads->dL_dmeans2D || !grads->dL_dcolors || !grads->dL_dopacity || !grads->dL_dmeans3D ||
-	    !grads->dL_dtransMat || !grads->dL_dscales || !grads->dL_drotations)
+	if (!grads->dL_dmeans2D || !grads->dL_dtransMat) return GS2D_ERR_INVALID;
+	if (!mc_flat && (!grads->dL_dcolors || !grads->dL_dopacity || !grads->dL_dmeans3D || !grads->dL_dscales ||
+	                 !grads->dL_drotations))
 		return GS2D_ERR_INVALID;
+	// the in-switch reduction adds 16-byte quaternion gradients at 6 P floats into the buffer: P % 4 == 0, 16-byte base
+	if (mc_flat && ((s->P & 3) || ((uintptr_t)mc_flat & 15) || in->shs)) return GS2D_ERR_INVALID;
 	if (in->shs && !grads->dL_dsh) return GS2D_ERR_INVALID;
 	if (num_pairs < 0) return GS2D_ERR_INVALID;
 	GeomState g = GeomState::carve(buffers->geom, (size_t)s->P, nullptr);
@@ -323,9 +326,26 @@ int gs2d_backward(const gs2d_settings* s, const gs2d_inputs* in, const gs2d_buff
 		GS2D_TRY(launch_composite_backward(*s, *in, im, b, I, num_pairs, dL_dout_color, dL_dout_others, scratch, &rows, st));
 		GS2D_TRY(debug_sync(*s, st));
 	}
-	GS2D_TRY(launch_preprocess_backward(*s, *in, g, radii, rows, *grads, st));
+	GS2D_TRY(launch_preprocess_backward(*s, *in, g, radii, rows, *grads, st, mc_flat));
 	GS2D_TRY(debug_sync(*s, st));
 	return GS2D_OK;
+}
+
+int gs2d_backward(const gs2d_settings* s, const gs2d_inputs* in, const gs2d_buffers* buffers,
+                  const int32_t* radii, int64_t I, int64_t num_pairs, const float* dL_dout_color,
+                  const float* dL_dout_others, const gs2d_grads* grads, void* scratch, void* stream)
+{
+	return backward_impl(s, in, buffers, radii, I, num_pairs, dL_dout_color, dL_dout_others, grads, nullptr, scratch, stream);
+}
+
+int gs2d_backward_reduce(const gs2d_settings* s, const gs2d_inputs* in, const gs2d_buffers* buffers,
+                         const int32_t* radii, int64_t I, int64_t num_pairs, const float* dL_dout_color,
+                         const float* dL_dout_others, const gs2d_grads* grads, float* multicast_flat, void* scratch,
+                         void* stream)
+{
+	if (!multicast_flat) return GS2D_ERR_INVALID;
+	return backward_impl(s, in, buffers, radii, I, num_pairs, dL_dout_color, dL_dout_others, grads, multicast_flat, scratch,
+	                     stream);
 }
 
 int gs2d_backward_overflowed(const gs2d_settings* s, const gs2d_buffers* buffers, int64_t I, int32_t* flag_host,

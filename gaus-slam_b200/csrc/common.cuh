@@ -180,7 +180,7 @@ int launch_composite_backward(const gs2d_settings& s, const gs2d_inputs& in, con
                               const float* dL_dothers, void* scratch, float** grad_rows_out, cudaStream_t st);
 int launch_preprocess_backward(const gs2d_settings& s, const gs2d_inputs& in, const GeomState& g,
                                const int32_t* radii, const float* grad_rows, const gs2d_grads& out,
-                               cudaStream_t st);
+                               cudaStream_t st, float* mc_flat = nullptr);
 int launch_mark_visible(int P, const float* means3D, const float* view, const float* proj,
                         uint8_t* present, cudaStream_t st);
 

@@ -83,6 +83,34 @@ __device__ float3 sh_backward(int idx, int deg, int max_coeffs, float3 pos, floa
 	return normalize_vjp(dir_orig, dL_ddir);
 }
 
+// multimem.red: the NVSwitch adds the value into EVERY rank's copy of the address (an NVLS multicast mapping).
+#ifdef __CUDACC__
+__device__ __forceinline__ void mc_red(float* mc, float v)
+{
+	asm volatile("multimem.red.relaxed.sys.global.add.f32 [%0], %1;" ::"l"(mc), "f"(v) : "memory");
+}
+__device__ __forceinline__ void mc_red2(float* mc, float a, float b)
+{
+	asm volatile("multimem.red.relaxed.sys.global.add.v2.f32 [%0], {%1, %2};" ::"l"(mc), "f"(a), "f"(b) : "memory");
+}
+__device__ __forceinline__ void mc_red4(float* mc, float4 v)
+{
+	asm volatile("multimem.red.relaxed.sys.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(mc), "f"(v.x), "f"(v.y),
+	             "f"(v.z), "f"(v.w)
+	             : "memory");
+}
+#else   // host compilation of this file (no PTX): one "rank", the multicast address is the buffer itself
+inline void mc_red(float* mc, float v) { mc[0] += v; }
+inline void mc_red2(float* mc, float a, float b) { mc[0] += a; mc[1] += b; }
+inline void mc_red4(float* mc, float4 v) { mc[0] += v.x; mc[1] += v.y; mc[2] += v.z; mc[3] += v.w; }
+#endif
+
+// REDUCE: the five map-parameter gradients (xyz | opacity | scale | rotation | rgb, the flat [13 * P] layout of
+// gs2d_b200/mapping.py) are not stored but ADDED, through the switch, into every rank's copy of a symmetric buffer
+// that was zeroed beforehand (mc_flat = its multicast address): the all-reduce of the view-sharded mapping step
+// happens in this kernel's epilogue, tile of surfels by tile of surfels, instead of in a pass of its own.  Surfels
+// that are not visible in this rank's view add nothing.
+template <bool REDUCE>
 __global__ void __launch_bounds__(256)
 preprocess_backward_kernel(int P, int D, int M,
 	const float3* __restrict__ means3D, const int* __restrict__ radii, const float* __restrict__ shs,
@@ -94,7 +122,7 @@ preprocess_backward_kernel(int P, int D, int M,
 	const uint32_t* __restrict__ offsets, const float* __restrict__ grad_rows,
 	float* __restrict__ dL_dtransMat, float* __restrict__ dL_dcolors, float* __restrict__ dL_dopacity,
 	float* __restrict__ dL_dsh, float* __restrict__ dL_dmean2D, float* __restrict__ dL_dmean3D,
-	float* __restrict__ dL_dscale, float* __restrict__ dL_drot)
+	float* __restrict__ dL_dscale, float* __restrict__ dL_drot, float* mc_flat)
 {
 	const int idx = blockIdx.x * blockDim.x + threadIdx.x;
 	if (idx >= P) return;
@@ -243,13 +271,28 @@ preprocess_backward_kernel(int P, int D, int M,
 
 #pragma unroll
 	for (int i = 0; i < 9; i++) dL_dtransMat[9 * (size_t)idx + i] = dT[i];
+	dL_dmean2D[3 * (size_t)idx + 0] = dmean2D_x;
+	dL_dmean2D[3 * (size_t)idx + 1] = dmean2D_y;
+	dL_dmean2D[3 * (size_t)idx + 2] = 0.f;
+	if (REDUCE) {
+		if (visible) {
+			const size_t Ps = (size_t)P, i = (size_t)idx;
+			mc_red(mc_flat + 3 * i + 0, dmean.x);
+			mc_red(mc_flat + 3 * i + 1, dmean.y);
+			mc_red(mc_flat + 3 * i + 2, dmean.z);
+			mc_red(mc_flat + 3 * Ps + i, dopa);
+			mc_red2(mc_flat + 4 * Ps + 2 * i, dscale.x, dscale.y);
+			mc_red4(mc_flat + 6 * Ps + 4 * i, drot);
+			mc_red(mc_flat + 10 * Ps + 3 * i + 0, dcol.x);
+			mc_red(mc_flat + 10 * Ps + 3 * i + 1, dcol.y);
+			mc_red(mc_flat + 10 * Ps + 3 * i + 2, dcol.z);
+		}
+		return;
+	}
 	dL_dcolors[3 * (size_t)idx + 0] = dcol.x;
 	dL_dcolors[3 * (size_t)idx + 1] = dcol.y;
 	dL_dcolors[3 * (size_t)idx + 2] = dcol.z;
 	dL_dopacity[idx] = dopa;
-	dL_dmean2D[3 * (size_t)idx + 0] = dmean2D_x;
-	dL_dmean2D[3 * (size_t)idx + 1] = dmean2D_y;
-	dL_dmean2D[3 * (size_t)idx + 2] = 0.f;
 	dL_dmean3D[3 * (size_t)idx + 0] = dmean.x;
 	dL_dmean3D[3 * (size_t)idx + 1] = dmean.y;
 	dL_dmean3D[3 * (size_t)idx + 2] = dmean.z;
@@ -262,19 +305,27 @@ preprocess_backward_kernel(int P, int D, int M,
 
 int launch_preprocess_backward(const gs2d_settings& s, const gs2d_inputs& in, const GeomState& g,
                                const int32_t* radii, const float* grad_rows, const gs2d_grads& out,
-                               cudaStream_t st)
+                               cudaStream_t st, float* mc_flat)
 {
 	const int P = s.P;
 	const float focal_y = s.image_height / (2.0f * s.tanfovy);
 	const float focal_x = s.image_width / (2.0f * s.tanfovx);
 	{
 		ProfScope ps(K_PREPROCESS_BWD, st);
-		preprocess_backward_kernel<<<(P + 255) / 256, 256, 0, st>>>(
-			P, s.sh_degree, s.sh_coeffs, (const float3*)in.means3D, radii, in.shs, g.clamped,
-			(const float2*)in.scales, (const float4*)in.rotations, in.transMat_precomp, g.splat,
-			in.viewmatrix, in.projmatrix, focal_x, focal_y, s.tanfovx, s.tanfovy, in.campos,
-			g.tiles_touched, g.point_offsets, grad_rows, out.dL_dtransMat, out.dL_dcolors, out.dL_dopacity,
-			out.dL_dsh, out.dL_dmeans2D, out.dL_dmeans3D, out.dL_dscales, out.dL_drotations);
+		if (mc_flat)
+			preprocess_backward_kernel<true><<<(P + 255) / 256, 256, 0, st>>>(
+				P, s.sh_degree, s.sh_coeffs, (const float3*)in.means3D, radii, in.shs, g.clamped,
+				(const float2*)in.scales, (const float4*)in.rotations, in.transMat_precomp, g.splat,
+				in.viewmatrix, in.projmatrix, focal_x, focal_y, s.tanfovx, s.tanfovy, in.campos,
+				g.tiles_touched, g.point_offsets, grad_rows, out.dL_dtransMat, out.dL_dcolors, out.dL_dopacity,
+				out.dL_dsh, out.dL_dmeans2D, out.dL_dmeans3D, out.dL_dscales, out.dL_drotations, mc_flat);
+		else
+			preprocess_backward_kernel<false><<<(P + 255) / 256, 256, 0, st>>>(
+				P, s.sh_degree, s.sh_coeffs, (const float3*)in.means3D, radii, in.shs, g.clamped,
+				(const float2*)in.scales, (const float4*)in.rotations, in.transMat_precomp, g.splat,
+				in.viewmatrix, in.projmatrix, focal_x, focal_y, s.tanfovx, s.tanfovy, in.campos,
+				g.tiles_touched, g.point_offsets, grad_rows, out.dL_dtransMat, out.dL_dcolors, out.dL_dopacity,
+				out.dL_dsh, out.dL_dmeans2D, out.dL_dmeans3D, out.dL_dscales, out.dL_drotations, nullptr);
 		count_launch();
 	}
 	GS2D_CUDA_OK(cudaGetLastError());

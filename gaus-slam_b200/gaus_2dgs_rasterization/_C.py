@@ -61,11 +61,22 @@ class _NumRendered(int):
 # pass writes those gradients straight into it, so a view-sharded trainer all-reduces the buffer without a
 # packing copy (the "write grads straight into the collective's buffer" item of SURVEY.md 8e).
 _grad_arena = None
+_grad_arena_multicast = 0     # NVLS multicast address of the arena (0 = an ordinary buffer: gradients are stored)
 
 
-def set_gradient_arena(flat):
-    global _grad_arena
+_grad_arena_ready = None      # event the backward pass waits for before it adds into a multicast arena
+
+
+def set_gradient_arena(flat, multicast_ptr: int = 0, ready_event=None):
+    """flat: [13 * P] fp32 buffer that receives the five map-parameter gradients (None switches the arena off).
+    multicast_ptr: when the buffer lives in symmetric memory bound to an NVSwitch multicast object, its multicast
+    address -- the backward pass then ADDS its gradients into every rank's copy inside the switch
+    (gs2d_backward_reduce: the all-reduce is fused into the backward-preprocess epilogue) instead of storing them;
+    the caller zeroes the buffer and runs the cross-GPU barriers (gs2d_b200.mapping.FusedGradient)."""
+    global _grad_arena, _grad_arena_multicast, _grad_arena_ready
     _grad_arena = flat
+    _grad_arena_multicast = int(multicast_ptr) if flat is not None else 0
+    _grad_arena_ready = ready_event if flat is not None else None
 
 
 def _arena_views(P, dev):
@@ -269,9 +280,16 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
         grads = L.Grads(dL_dmeans2D=_ptr(g_means2D), dL_dcolors=_ptr(g_colors), dL_dopacity=_ptr(g_opacity),
                         dL_dmeans3D=_ptr(g_means3D), dL_dtransMat=_ptr(g_transMat), dL_dsh=_ptr(g_sh),
                         dL_dscales=_ptr(g_scales), dL_drotations=_ptr(g_rot))
-        L.check(lib.gs2d_backward(C.byref(s), C.byref(i), C.byref(bufs), _ptr(radii), int(R), num_pairs,
-                                  _ptr(dL_dout_color), _ptr(dL_dout_others), C.byref(grads), _ptr(scratch), st),
-                "gs2d_backward")
+        if arena is not None and _grad_arena_multicast:
+            if _grad_arena_ready is not None:     # the buffer is zeroed on every rank (side stream + cross-GPU barrier)
+                torch.cuda.current_stream(dev).wait_event(_grad_arena_ready)
+            L.check(lib.gs2d_backward_reduce(C.byref(s), C.byref(i), C.byref(bufs), _ptr(radii), int(R), num_pairs,
+                                             _ptr(dL_dout_color), _ptr(dL_dout_others), C.byref(grads),
+                                             C.c_void_p(_grad_arena_multicast), _ptr(scratch), st), "gs2d_backward_reduce")
+        else:
+            L.check(lib.gs2d_backward(C.byref(s), C.byref(i), C.byref(bufs), _ptr(radii), int(R), num_pairs,
+                                      _ptr(dL_dout_color), _ptr(dL_dout_others), C.byref(grads), _ptr(scratch), st),
+                    "gs2d_backward")
     return g_means2D, g_colors, g_opacity, g_means3D, g_transMat, g_sh, g_scales, g_rot
 
 

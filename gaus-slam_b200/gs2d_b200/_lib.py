@@ -91,6 +91,9 @@ PROTOTYPES = {
     "gs2d_backward": (C.c_int, [C.POINTER(Settings), C.POINTER(Inputs), C.POINTER(Buffers), C.c_void_p,
                                 C.c_int64, C.c_int64, C.c_void_p, C.c_void_p, C.POINTER(Grads), C.c_void_p,
                                 C.c_void_p]),
+    "gs2d_backward_reduce": (C.c_int, [C.POINTER(Settings), C.POINTER(Inputs), C.POINTER(Buffers), C.c_void_p,
+                                       C.c_int64, C.c_int64, C.c_void_p, C.c_void_p, C.POINTER(Grads), C.c_void_p,
+                                       C.c_void_p, C.c_void_p]),
     "gs2d_backward_overflowed": (C.c_int, [C.POINTER(Settings), C.POINTER(Buffers), C.c_int64, C.c_void_p, C.c_void_p]),
     "gs2d_mark_visible": (C.c_int, [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "gs2d_dist2_scratch_bytes": (C.c_size_t, [C.c_int32]),

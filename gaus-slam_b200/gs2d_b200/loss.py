@@ -8,8 +8,8 @@ launches each way.
 
 Argument meaning follows the reference's config keys: `weights` = config['loss']['mapping'] (color, depth, dist),
 `eps`, `depth_near`, `depth_far` = config['render'][...].  `gt_color` may be [3,H,W] or the reference's [H,W,3].
-Built for the shipped defaults (use_edge_growth = use_normal_loss = enable_exposure = False); anything else
-raises.  CUDA only: there is no CPU path.
+Built for use_edge_growth = use_normal_loss = enable_exposure = False (every shipped config), with or without
+`ignore_outliners`; the other branches raise.  CUDA only: there is no CPU path.
 """
 from __future__ import annotations
 
@@ -19,14 +19,11 @@ import torch
 
 from . import _lib as L
 
-_scratch = {}
-
-
-def _scratch_for(dev, W, H):
-    key = (str(dev), int(torch.cuda.current_stream(dev).cuda_stream))
-    if key not in _scratch:      # zero-initialised once; the kernels keep it consistent afterwards
-        _scratch[key] = torch.zeros(L.load().gs2d_mapping_loss_scratch_bytes(W, H), dtype=torch.uint8, device=dev)
-    return _scratch[key]
+def _new_scratch(dev, W, H):
+    """Partials, ticket and the forward's mask count live in a scratch of ~19 KB that belongs to ONE forward call and
+    travels to its backward in ctx: several losses may be formed before any backward (the sum over the keyframes of a
+    bundle-adjustment window).  Round 1 shared one scratch per stream, so every backward then used the last count."""
+    return torch.zeros(L.load().gs2d_mapping_loss_scratch_bytes(W, H), dtype=torch.uint8, device=dev)
 
 
 def _check(t, name, shape):
@@ -50,7 +47,7 @@ class _MappingLoss(torch.autograd.Function):
         hwc = int(tuple(gt_color.shape) == (H, W, 3) and (H, W, 3) != (3, H, W))
         lp = L.LossParams(*params)
         with torch.cuda.device(dev):
-            scratch = _scratch_for(dev, W, H)
+            scratch = _new_scratch(dev, W, H)
             loss = torch.empty((), dtype=torch.float32, device=dev)
             st = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
             L.check(lib.gs2d_mapping_loss_forward(W, H, color.data_ptr(), allmap.data_ptr(), gt_color.data_ptr(),
@@ -80,8 +77,7 @@ class _MappingLoss(torch.autograd.Function):
 
 def mapping_loss(color, allmap, gt_color, gt_depth, weights=(0.5, 1.0, 0.1), eps=1e-6, depth_near=1e-2,
                  depth_far=1e2, use_edge_growth=False, use_normal_loss=False):
-    """-> scalar loss tensor (differentiable w.r.t. color and allmap).  One forward pass of the rasterizer per
-    call of backward: the mask count of the forward pass is kept in a per-stream scratch."""
+    """-> scalar loss tensor (differentiable w.r.t. color and allmap)."""
     if use_edge_growth or use_normal_loss:
         raise NotImplementedError("only the default mapping loss (no edge growth, no normal loss) is built")
     params = (float(weights[0]), float(weights[1]), float(weights[2]), float(eps), float(depth_near), float(depth_far),
@@ -89,13 +85,30 @@ def mapping_loss(color, allmap, gt_color, gt_depth, weights=(0.5, 1.0, 0.1), eps
     return _MappingLoss.apply(color, allmap, gt_color, gt_depth, params)
 
 
+def _inlier_gt_depth(allmap, gt_depth, eps, depth_near, depth_far):
+    """The median-based outlier mask of the tracking loss (slam/Loss.py:37-40, `ignore_outliners`), folded into the
+    sensor depth: depth_error = |depth - gt| * depth_mask over ALL pixels, inliers = depth_error < 10 * median.  A pixel
+    whose gt depth is set to 0 fails the depth mask of the fused kernels, which removes it from the colour and the
+    depth sums exactly like the reference's `inliner_mask & tracking_depth_mask`.  Masks carry no gradient."""
+    with torch.no_grad():
+        d = allmap[0:1] / (allmap[1:2] + eps)                    # render/__init__.py:46-49
+        d = torch.where((d > depth_far) | (d < depth_near), torch.zeros_like(d), d)
+        d = torch.nan_to_num(d, 0, 0)
+        gd = gt_depth.reshape(d.shape)
+        err = (d - gd).abs() * ((gd > 1e-5) & (d > 1e-5))
+        return torch.where(err < 10 * err.median(), gd, torch.zeros_like(gd)).reshape(gt_depth.shape)
+
+
 def tracking_loss(color, allmap, gt_color, gt_depth, weights=(0.5, 1.0), eps=1e-6, depth_near=1e-2, depth_far=1e2,
                   silmask_th=0.9, ignore_outliners=False, use_normal_loss=False):
-    """The tracking branch of get_loss (slam/Loss.py:35-47) with the shipped defaults (ignore_outliners = False,
-    use_normal_loss = False): mask = depth mask & nan_to_num(alpha) > silmask_th, loss = weights[0] * SUM |color -
-    gt_color| + weights[1] * SUM |depth - gt_depth| over the mask.  Same two kernels as mapping_loss."""
-    if ignore_outliners or use_normal_loss:
-        raise NotImplementedError("only the default tracking loss (no median outlier mask, no normal loss) is built")
+    """The tracking branch of get_loss (slam/Loss.py:35-47): mask = depth mask [& inliers] & nan_to_num(alpha) >
+    silmask_th, loss = weights[0] * SUM |color - gt_color| + weights[1] * SUM |depth - gt_depth| over the mask.  Same two
+    kernels as mapping_loss; `ignore_outliners` (configs/replica/splatam.py) adds a handful of torch ops that build the
+    inlier mask (a median over the image) in front of them."""
+    if use_normal_loss:
+        raise NotImplementedError("the normal loss is not built (off in every shipped config)")
+    if ignore_outliners:
+        gt_depth = _inlier_gt_depth(allmap, gt_depth, float(eps), float(depth_near), float(depth_far))
     params = (float(weights[0]), float(weights[1]), 0.0, float(eps), float(depth_near), float(depth_far), 1,
               float(silmask_th))
     return _MappingLoss.apply(color, allmap, gt_color, gt_depth, params)

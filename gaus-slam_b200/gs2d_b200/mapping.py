@@ -19,8 +19,12 @@ FLAT_WIDTH = sum(PARAM_WIDTH.values())   # 13
 
 
 def view_of(step: int, rank: int, world: int, n_views: int) -> int:
-    """Keyframe rendered by `rank` at optimiser step `step`: ranks take consecutive views of the window."""
-    return (step * world + rank) % n_views
+    """Keyframe rendered by `rank` at optimiser step `step`: ranks take consecutive views of the window (one pass
+    over the window partitions it), and every completed pass shifts the assignment by one view -- so that a rank
+    walks through ALL views even when the world size divides the window (8 ranks, 8 keyframes: without the shift
+    every rank would render the same view for ever, its inputs would stay in L2 and the step time would be pinned to
+    the heaviest view)."""
+    return (step * world + rank + (step * world) // n_views) % n_views
 
 
 def views_of_step(step: int, world: int, n_views: int):
@@ -59,13 +63,58 @@ def gradient_arena(flat: torch.Tensor):
     directly into the sections of `flat` ([13 * P] fp32 on the surfels' device): `param.grad` then aliases the
     buffer the all-reduce runs on, with no packing copy in between.  One backward pass per all-reduce (a second
     one would overwrite the first: accumulate over views by all-reducing per view or summing into another
-    buffer)."""
+    buffer).  With a buffer from symmetric_gradient_buffer and fused=True the gradients are ADDED into every rank's
+    copy inside the NVSwitch by the backward pass itself (see FusedGradient)."""
     from gaus_2dgs_rasterization import _C
     _C.set_gradient_arena(flat)
     try:
         yield flat
     finally:
         _C.set_gradient_arena(None)
+
+
+class FusedGradient:
+    """The all-reduce of the map gradient fused into the backward pass ("fused with its collective").
+
+        fg = FusedGradient(P, device)            # None-like (fg.ok False) without NVSwitch multicast
+        every optimiser step:
+            fg.begin()                           # zero the local copy, cross-GPU barrier: nobody adds into a dirty buffer
+            ... forward + backward of this rank's view(s): the backward-preprocess epilogue multimem.red's the five
+                map-parameter gradients into EVERY rank's copy (gs2d_backward_reduce)
+            flat = fg.finish()                   # cross-GPU barrier: every rank's copy now holds the sum over ranks
+
+    Several views per rank and step simply add up in the buffer (a bundle-adjustment window): one begin / finish pair
+    per optimiser step.  Gradient tensors returned by the rasterizer alias the buffer and are valid after finish()."""
+
+    def __init__(self, P: int, device, group=None):
+        self.flat = symmetric_gradient_buffer(P, device, group)
+        self.ok = self.flat is not None
+        self.P = P
+        if self.ok:
+            self.hdl = _symmetric[self.flat.data_ptr()][0]
+            self.side = torch.cuda.Stream(device=device)
+            self.ready = torch.cuda.Event()
+        self._active = False
+
+    def begin(self):
+        """Zero the local copy and run the first cross-GPU barrier on a SIDE stream (they hide under the forward pass);
+        the backward pass waits for them through an event.  Call when everything that reads the previous gradient has
+        been enqueued on the current stream."""
+        from gaus_2dgs_rasterization import _C
+        self.side.wait_stream(torch.cuda.current_stream(self.flat.device))
+        with torch.cuda.stream(self.side):
+            self.flat.zero_()
+            self.hdl.barrier(channel=0)
+            self.ready.record(self.side)
+        _C.set_gradient_arena(self.flat, multicast_ptr=self.hdl.multicast_ptr, ready_event=self.ready)
+        self._active = True
+
+    def finish(self) -> torch.Tensor:
+        from gaus_2dgs_rasterization import _C
+        self.hdl.barrier(channel=1)
+        _C.set_gradient_arena(None)
+        self._active = False
+        return self.flat
 
 
 def unpack_grads(flat: torch.Tensor, P: int) -> dict:

@@ -179,6 +179,20 @@ int gs2d_backward(const gs2d_settings* s, const gs2d_inputs* in, const gs2d_buff
                   const int32_t* radii, int64_t num_rendered, int64_t num_pairs,
                   const float* dL_dout_color, const float* dL_dout_others,
                   const gs2d_grads* grads, void* scratch, void* stream);
+/* gs2d_backward fused with the all-reduce of the view-sharded mapping step (new; the reference is single-GPU,
+ * SURVEY.md 8e).  The five map-parameter gradients -- dL/d(means3D, opacity, scales, rotations, colors) -- are not
+ * stored: the backward-preprocess epilogue ADDS them with multimem.red, i.e. inside the NVSwitch, into every rank's copy
+ * of a flat [13 * P] fp32 buffer laid out group by group (xyz 3P | opacity P | scale 2P | rotation 4P | rgb 3P).
+ * `multicast_flat` is the NVLS multicast address of that buffer (symmetric memory bound to a multicast object; same
+ * offset on every rank; 16-byte aligned), P % 4 == 0, colours precomputed (no SH).  Protocol: every rank zeroes its
+ * copy, a cross-GPU barrier, every rank calls this for its own view, a second cross-GPU barrier -- then every rank's
+ * copy holds the SUM over the ranks; no separate all-reduce pass exists.  The five map-group pointers of `grads` are
+ * ignored (may be NULL); dL_dmeans2D, dL_dtransMat (and nothing else) are written locally as in gs2d_backward. */
+int gs2d_backward_reduce(const gs2d_settings* s, const gs2d_inputs* in, const gs2d_buffers* buffers,
+                         const int32_t* radii, int64_t num_rendered, int64_t num_pairs, const float* dL_dout_color,
+                         const float* dL_dout_others, const gs2d_grads* grads, float* multicast_flat, void* scratch,
+                         void* stream);
+
 /* 1 in *flag_host (pinned or pageable host int32) if the last gs2d_backward on these buffers skipped tiles because
  * num_pairs was too small, else 0.  Synchronises the stream. */
 int gs2d_backward_overflowed(const gs2d_settings* s, const gs2d_buffers* buffers, int64_t num_rendered,

@@ -85,7 +85,32 @@ def inputs(H, W, seed, nasty):
     return color, allmap, gt_color, gt_depth
 
 
-def reference_loss(get_loss, color, allmap, gt_color, gt_depth, tracking):
+def outlier_inputs(H, W, seed):
+    """Rendered depth close to the sensor depth except for 6 % gross outliers, 8 % sensor holes: the median of the
+    masked depth error is small, so `depth_error < 10 * median` (slam/Loss.py:37-40) removes the outliers."""
+    rng = np.random.default_rng(seed)
+    color, allmap, gt_color, gt_depth = inputs(H, W, seed, False)
+    alpha = allmap[1]
+    depth = gt_depth[..., 0] + rng.normal(0, 0.02, (H, W)).astype(np.float32)
+    gross = rng.uniform(size=(H, W)) < 0.06
+    depth[gross] += rng.uniform(0.5, 2.0, int(gross.sum())).astype(np.float32)
+    allmap[0] = depth * alpha
+    gt_depth[rng.uniform(size=(H, W)) < 0.08] = 0.0
+    return color, allmap, gt_color, gt_depth
+
+
+def reference_loss(get_loss, color, allmap, gt_color, gt_depth, tracking, config=None):
+    global CONFIG
+    saved = CONFIG
+    if config is not None:
+        CONFIG = config
+    try:
+        return _reference_loss(get_loss, color, allmap, gt_color, gt_depth, tracking)
+    finally:
+        CONFIG = saved
+
+
+def _reference_loss(get_loss, color, allmap, gt_color, gt_depth, tracking):
     c = torch.tensor(color, requires_grad=True)
     a = torch.tensor(allmap, requires_grad=True)
     r = CONFIG["render"]
@@ -113,6 +138,22 @@ def main():
             out[f"ref_loss_{mode}"], out[f"ref_dcolor_{mode}"], out[f"ref_dallmap_{mode}"] = loss, dc, da
             print(name, mode, float(loss), int(np.isnan(da).sum()), "NaN in dL/dallmap")
         np.savez_compressed(os.path.join(HERE, f"loss_{name}.npz"), **out)
+    # the median-based outlier mask of the tracking loss, as configs/replica/splatam.py switches it on
+    # (ignore_outliners = True, silmask_th = 0.99)
+    import copy
+    cfg = copy.deepcopy(CONFIG)
+    cfg["loss"]["ignore_outliners"] = True
+    cfg["loss"]["silmask_th"] = 0.99
+    x = outlier_inputs(28, 44, 3)
+    x[1][1][x[1][1] == np.float32(0.95)] = 0.995          # the pixels meant to pass the silhouette mask pass 0.99 too
+    x[1][0][...] = (x[1][0] / 0.95 * 0.995).astype(np.float32) * (x[1][1] == np.float32(0.995)) + x[1][0] * (x[1][1] != np.float32(0.995))
+    out = dict(in_color=x[0], in_allmap=x[1], in_gt_color=x[2], in_gt_depth=x[3], silmask_th=np.float32(0.99))
+    loss, dc, da = reference_loss(get_loss, *x, tracking=True, config=cfg)
+    out["ref_loss_tracking_inliers"], out["ref_dcolor_tracking_inliers"], out["ref_dallmap_tracking_inliers"] = loss, dc, da
+    plain, _, _ = reference_loss(get_loss, *x, tracking=True, config={**cfg, "loss": {**cfg["loss"], "ignore_outliners": False}})
+    out["ref_loss_tracking_all"] = plain
+    print("outliers tracking", float(loss), "without the outlier mask", float(plain))
+    np.savez_compressed(os.path.join(HERE, "loss_outliers.npz"), **out)
 
 
 if __name__ == "__main__":

@@ -167,6 +167,8 @@ def test_next_row_wrappers_refuse_cpu_tensors_and_unbuilt_branches():
         tracking.pose_transform(raw[0], raw[3])
     img, am = torch.zeros((3, 8, 8)), torch.zeros((7, 8, 8))
     with pytest.raises(NotImplementedError):
+        loss.tracking_loss(img, am, img, torch.zeros((8, 8)), use_normal_loss=True)
+    with pytest.raises(RuntimeError, match="CUDA"):      # the outlier mask is built since round 2; still no CPU path
         loss.tracking_loss(img, am, img, torch.zeros((8, 8)), ignore_outliners=True)
     with pytest.raises(NotImplementedError):
         loss.mapping_loss(img, am, img, torch.zeros((8, 8)), use_edge_growth=True)

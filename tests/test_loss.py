@@ -203,3 +203,57 @@ def test_fused_kernels_match_the_reference_get_loss(name, mode):
     assert abs(float(loss.detach()) - want) <= 2e-5 * abs(want)
     assert _close(c.grad.cpu().numpy(), g[f"ref_dcolor_{mode}"], 5e-6)
     assert _close(a.grad.cpu().numpy(), g[f"ref_dallmap_{mode}"], 1e-5)
+
+
+def test_inlier_mask_restatement_matches_the_reference_get_loss():
+    """CPU: the torch ops that build the `ignore_outliners` mask (gs2d_b200.loss._inlier_gt_depth) + the transliterated
+    tracking loss reproduce what the reference's get_loss computed with ignore_outliners = True, silmask_th = 0.99
+    (configs/replica/splatam.py)."""
+    from gs2d_b200 import loss as gl
+    g = _golden("outliers")
+    a = torch.tensor(g["in_allmap"])
+    gd = gl._inlier_gt_depth(a, torch.tensor(g["in_gt_depth"]), 1e-6, 1e-2, 1e2)
+    gt_chw = np.ascontiguousarray(g["in_gt_color"].transpose(2, 0, 1))
+    got = loss_ref.mapping_loss_numpy(g["in_color"], g["in_allmap"], gt_chw, gd.numpy()[..., 0], weights=(0.5, 1.0, 0.0),
+                                      tracking=True, silmask_th=float(g["silmask_th"]))
+    want = float(g["ref_loss_tracking_inliers"])
+    assert abs(got[0] - want) <= 1e-5 * abs(want)
+    assert abs(float(g["ref_loss_tracking_all"]) - want) > 0.05 * abs(want)       # the mask matters in this case
+    assert _close(np.asarray(got[1]), g["ref_dcolor_tracking_inliers"], 2e-6)
+    assert _close(np.asarray(got[2]), g["ref_dallmap_tracking_inliers"], 1e-5)
+
+
+@pytest.mark.gpu
+def test_fused_tracking_loss_with_the_outlier_mask_matches_the_reference_get_loss():
+    from gs2d_b200 import loss as gl
+    dev = torch.device("cuda:0")
+    g = _golden("outliers")
+    c = torch.tensor(g["in_color"], device=dev, requires_grad=True)
+    a = torch.tensor(g["in_allmap"], device=dev, requires_grad=True)
+    gc = torch.tensor(g["in_gt_color"], device=dev)
+    gd = torch.tensor(g["in_gt_depth"], device=dev)
+    loss = gl.tracking_loss(c, a, gc, gd, silmask_th=float(g["silmask_th"]), ignore_outliners=True)
+    loss.backward()
+    want = float(g["ref_loss_tracking_inliers"])
+    assert abs(float(loss.detach()) - want) <= 2e-5 * abs(want)
+    assert _close(c.grad.cpu().numpy(), g["ref_dcolor_tracking_inliers"], 5e-6)
+    assert _close(a.grad.cpu().numpy(), g["ref_dallmap_tracking_inliers"], 1e-5)
+
+
+@pytest.mark.gpu
+def test_two_losses_before_one_backward():
+    """(loss(view 1) + loss(view 2)).backward(): every backward must divide by the mask count of ITS forward
+    (round 1 kept the count in one scratch per stream)."""
+    from gs2d_b200 import loss as gl
+    dev = torch.device("cuda:0")
+    g1, g2 = _golden("small"), _golden("clean")
+
+    def leaves(g):
+        return (torch.tensor(g["in_color"], device=dev, requires_grad=True),
+                torch.tensor(g["in_allmap"], device=dev, requires_grad=True),
+                torch.tensor(g["in_gt_color"], device=dev), torch.tensor(g["in_gt_depth"], device=dev))
+    x1, x2 = leaves(g1), leaves(g2)
+    (gl.mapping_loss(*x1) + gl.mapping_loss(*x2)).backward()
+    for x, g in ((x1, g1), (x2, g2)):
+        assert _close(x[0].grad.cpu().numpy(), g["ref_dcolor_mapping"], 5e-6)
+        assert _close(x[1].grad.cpu().numpy(), g["ref_dallmap_mapping"], 1e-5)

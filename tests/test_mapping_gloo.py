@@ -63,6 +63,9 @@ def test_view_assignment_partitions_the_window():
             assert len(set(vs)) == world
             seen += vs
         assert sorted(seen) == list(range(8))
+        # ... and over the passes every rank gets to every view (also when the world size divides the window)
+        for r in range(world):
+            assert {mapping.view_of(s, r, world, 8) for s in range(64)} == set(range(8))
 
 
 def test_flat_layout_roundtrip():
