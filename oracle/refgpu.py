@@ -90,6 +90,11 @@ class RefRasterizer:
     def forward(self, *, bg, means3D, opacities, viewmatrix, projmatrix, campos, W, H, tanfovx, tanfovy,
                 colors=None, shs=None, scales=None, rotations=None, transMat=None, scale_modifier=1.0,
                 sh_degree=0, use_sa=True, prefiltered=False, debug=False, out=None):
+        # raw pointers go to the reference kernels: every tensor must be dense (RAST/rasterize_points.cu calls
+        # .contiguous() on its inputs too)
+        c = lambda x: x.contiguous() if isinstance(x, torch.Tensor) else x   # noqa: E731
+        bg, means3D, opacities, viewmatrix, projmatrix, campos = (c(x) for x in (bg, means3D, opacities, viewmatrix, projmatrix, campos))
+        colors, shs, scales, rotations, transMat = (c(x) for x in (colors, shs, scales, rotations, transMat))
         dev = means3D.device
         P = means3D.shape[0]
         M = shs.shape[1] if shs is not None and shs.numel() else 0
@@ -136,6 +141,9 @@ class RefRasterizer:
     def backward(self, *, bg, means3D, radii, viewmatrix, projmatrix, campos, W, H, tanfovx, tanfovy,
                  dL_dcolor, dL_dothers, colors=None, shs=None, scales=None, rotations=None, transMat=None,
                  scale_modifier=1.0, sh_degree=0, use_sa=True, debug=False, out=None):
+        c = lambda x: x.contiguous() if isinstance(x, torch.Tensor) else x   # noqa: E731
+        bg, means3D, radii, viewmatrix, projmatrix, campos = (c(x) for x in (bg, means3D, radii, viewmatrix, projmatrix, campos))
+        dL_dcolor, dL_dothers, colors, shs, scales, rotations, transMat = (c(x) for x in (dL_dcolor, dL_dothers, colors, shs, scales, rotations, transMat))
         dev = means3D.device
         P = means3D.shape[0]
         M = shs.shape[1] if shs is not None and shs.numel() else 0

@@ -141,7 +141,7 @@ def test_fused_tracking_loss_equals_the_reference_loss(H, W, seed, hwc):
     for got, want in ((c.grad, dc_np), (a.grad, da_np), (c.grad, dc_t), (a.grad, da_t)):
         assert _close(got.cpu().numpy(), want, 2e-6)
     with pytest.raises(NotImplementedError):
-        gl.tracking_loss(c, a, gc, torch.tensor(gt_depth, device=dev), ignore_outliners=True)
+        gl.tracking_loss(c, a, gc, torch.tensor(gt_depth, device=dev), use_normal_loss=True)
 
 
 @pytest.mark.gpu
