@@ -53,6 +53,8 @@ def parse_args():
     ap.add_argument("--no-torch-cpu", action="store_true", help="skip the pure-PyTorch CPU transliteration in cpu_baseline")
     ap.add_argument("--no-loops", action="store_true",
                     help="skip the whole-iteration loops (mapping_iteration / tracking_iteration keys, bench_loops.py)")
+    ap.add_argument("--no-extra", action="store_true",
+                    help="skip the extra workloads (scannetpp_frame: 1752x1168 / 4 M surfels; ba_step: 2 M surfels / 64 keyframes)")
     ap.add_argument("--clock-period-ms", type=int, default=100, help="nvidia-smi sampling period; 0 = no sampling (diagnosis)")
     return ap.parse_args()
 
@@ -786,6 +788,18 @@ def main():
         loops["mapping_iteration"] = bench_loops.mapping_iteration(arm, wl, dev, timed, a.steps, a.warmup, view_of,
                                                                    loss_fn, a.impl, multi, None)
         loops["tracking_iteration"] = bench_loops.tracking_iteration(arm, dev, timed, a.steps, a.warmup, a.impl)
+    # ---- the two larger configurations of BASELINE.json as extra keys (both arms): configs[4] in shape (1752 x 1168,
+    # 4 M surfels) at N = 1, configs[3] in shape (BA step, 2 M surfels, 64 keyframes sharded over the ranks) at every N
+    if not a.no_extra and (a.impl == "b200" or not multi):
+        import bench_loops
+        torch.cuda.empty_cache()
+        if multi:
+            from gaus_2dgs_rasterization import _C as _gs2d_C2
+            _gs2d_C2.set_gradient_arena(None)
+        if not multi:
+            loops["scannetpp_frame"] = bench_loops.scannetpp_frame(arm, dev, timed, min(a.steps, 16), 3)
+            torch.cuda.empty_cache()
+        loops["ba_step"] = bench_loops.ba_step(arm, dev, timed, 3, 1, a.impl, rank if multi else 0, world if multi else 1)
 
     if rank != 0:
         if multi:

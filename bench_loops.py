@@ -171,3 +171,125 @@ def tracking_iteration(arm, dev, timed, steps, warmup, impl, surfels=300_000):
     return {"value": 1000.0 / ms, "unit": "iterations/s", "ms_per_iteration": ms, "surfels": surfels,
             "frames_per_s_at_40_iters": 1000.0 / ms / 40.0, "final_loss": float(last["loss"].detach()),
             "what": "pose -> camera-frame map -> render (identity camera) -> tracking loss -> backward -> Adam on 7 pose scalars (slam/Frontend.py:80-92, BASELINE.json configs[1]); " + how}
+
+
+def scannetpp_frame(arm, dev, timed, steps, warmup, surfels=4_000_000, views=4):
+    """BASELINE.json configs[4] in shape: fwd + bwd of one 1752 x 1168 view of a 4 M-surfel map per step (8030 tiles,
+    45 sort bits), through the arm's public API, inputs resident, views rotating over `views` per-view input sets."""
+    import torch
+    sys.path.insert(0, os.path.join(ROOT, "gaus-slam_b200"))
+    from gs2d_b200 import scene
+    intr = scene.SCANNETPP
+    W, H = intr["W"], intr["H"]
+    sc = scene.room_scene(surfels, intr, seed=4)
+    cams = scene.view_sweep(8, intr, seed=4)[:views]
+    t = lambda x: torch.tensor(np.ascontiguousarray(x, dtype=np.float32), device=dev)     # noqa: E731
+    params = {k: t(sc[k]).requires_grad_(True) for k in ("means3D", "opacities", "scales", "rotations", "colors")}
+    means2D = torch.zeros((surfels, 3), device=dev, requires_grad=True)
+    sets = []
+    for v, cam in enumerate(cams):
+        gc, go = scene.image_grads(W, H, seed=v)
+        s = dict(viewmatrix=t(cam.viewmatrix.reshape(16)), projmatrix=t(cam.projmatrix.reshape(16)), campos=t(cam.campos),
+                 tanfovx=float(cam.tanfovx), tanfovy=float(cam.tanfovy), dL_dcolor=t(gc), dL_dothers=t(go))
+        s["rast"] = _rasterizer(arm, s, W, H, dev)
+        sets.append(s)
+
+    def step(i):
+        s = sets[i % views]
+        for p in params.values():
+            p.grad = None
+        means2D.grad = None
+        color, radii, allmap = s["rast"](means3D=params["means3D"], means2D=means2D, opacities=params["opacities"],
+                                         colors_precomp=params["colors"], scales=params["scales"],
+                                         rotations=params["rotations"])
+        torch.autograd.backward([color, allmap], [s["dL_dcolor"], s["dL_dothers"]])
+    for i in range(warmup):
+        step(i)
+    ms = timed(step, steps, warmup) / steps
+    return {"value": 1000.0 / ms, "unit": "frames/s", "ms_per_step": ms, "surfels": surfels, "image": f"{W}x{H}",
+            "what": f"fwd + bwd of one {W}x{H} view of a {surfels}-surfel map per step (BASELINE.json configs[4] in shape: "
+                    f"8030 tiles, 45 sort bits), public API, inputs resident, {views} views rotating"}
+
+
+def _rasterizer(arm, s, W, H, dev):
+    import torch
+    G = getattr(arm, "G", None)
+    if G is None:                       # the C-shim fallback arm builds its own autograd node
+        return arm.rasterizer(s)
+    st = G.GaussianRasterizationSettings(image_height=H, image_width=W, tanfovx=s["tanfovx"], tanfovy=s["tanfovy"],
+                                         bg=torch.zeros(3, device=dev), scale_modifier=1.0, viewmatrix=s["viewmatrix"],
+                                         projmatrix=s["projmatrix"], sh_degree=0, campos=s["campos"], use_sa=True,
+                                         prefiltered=False, debug=False)
+    return G.GaussianRasterizer(st)
+
+
+def ba_step(arm, dev, timed, steps, warmup, impl, rank=0, world=1, surfels=2_000_000, keyframes=64):
+    """BASELINE.json configs[3] in shape: ONE joint pose + map gradient step of the backend's bundle adjustment over a
+    window of 64 keyframes of a 2 M-surfel map (render/__init__.py:84-111 Renderer_BA per keyframe: means3D' = R x + t with
+    the map AND the keyframe's pose attached, rotations detached; slam/Backend.py:130-155).  The keyframes are sharded
+    over the ranks; every rank accumulates the map gradient of its keyframes IN PLACE in one flat [13 P] buffer
+    (param.grad are views of it) and keeps its keyframes' pose gradients; the buffer (104 MB) goes through one all-reduce
+    per step.  value = keyframes per second."""
+    import torch
+    import torch.distributed as dist
+    sys.path.insert(0, os.path.join(ROOT, "gaus-slam_b200"))
+    from gs2d_b200 import mapping, scene
+    intr = scene.REPLICA
+    W, H, P = intr["W"], intr["H"], surfels
+    sc = scene.room_scene(P, intr, seed=2)
+    cams = scene.view_sweep(keyframes, intr, seed=2)
+    mine = [k for k in range(keyframes) if k % world == rank]
+    t = lambda x: torch.tensor(np.ascontiguousarray(x, dtype=np.float32), device=dev)     # noqa: E731
+    params = {k: t(sc[k]).requires_grad_(True) for k in mapping.PARAM_ORDER}
+    flat = torch.zeros(13 * P, device=dev)
+    views_of_flat = mapping.unpack_grads(flat, P)
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import pose_ref
+    ident = scene.make_camera(np.eye(4, dtype=np.float32), **intr)       # Renderer_BA renders with the identity camera
+    s_id = dict(viewmatrix=t(ident.viewmatrix.reshape(16)), projmatrix=t(ident.projmatrix.reshape(16)), campos=t(ident.campos),
+                tanfovx=float(ident.tanfovx), tanfovy=float(ident.tanfovy))
+    rast = _rasterizer(arm, s_id, W, H, dev)
+    kfs = []
+    for k in mine:
+        w2c = cams[k].w2c.astype(np.float32)
+        q = pose_ref.matrix_to_quaternion(torch.tensor(w2c[None, :3, :3], dtype=torch.float64))[0].numpy()
+        gc, go = scene.image_grads(W, H, seed=k % 8)
+        kfs.append(dict(cam_rot=t(q).requires_grad_(True), cam_trans=t(w2c[:3, 3]).requires_grad_(True), dL_dcolor=t(gc),
+                        dL_dothers=t(go)))
+    if impl == "b200":
+        from gs2d_b200 import tracking
+
+        def to_camera(kf):
+            return tracking.pose_transform(params["means3D"], params["rotations"], cam_rot=kf["cam_rot"], cam_trans=kf["cam_trans"])
+        how = "gs2d_b200.tracking.pose_transform + the drop-in rasterizer"
+    else:
+        def to_camera(kf):
+            return pose_ref.pose_transform_torch(params["means3D"], params["rotations"],
+                                                 pose_ref.get_transform_matrix(kf["cam_rot"], kf["cam_trans"]))
+        how = "the reference's torch expressions (pytorch3d algebra restated) + the reference rasterizer"
+    means2D = torch.zeros((P, 3), device=dev, requires_grad=True)
+
+    def step(i):
+        flat.zero_()
+        for k in mapping.PARAM_ORDER:            # autograd accumulates the keyframes' gradients in place in `flat`
+            params[k].grad = views_of_flat[k] if k != "rotations" else None
+        means2D.grad = None
+        for kf in kfs:
+            kf["cam_rot"].grad = None
+            kf["cam_trans"].grad = None
+            means_c, rots_c = to_camera(kf)
+            color, radii, allmap = rast(means3D=means_c, means2D=means2D, opacities=params["opacities"],
+                                        colors_precomp=params["colors"], scales=params["scales"], rotations=rots_c)
+            torch.autograd.backward([color, allmap], [kf["dL_dcolor"], kf["dL_dothers"]])
+        if world > 1:
+            dist.all_reduce(flat)
+    for i in range(warmup):
+        step(i)
+    in_place = params["means3D"].grad.data_ptr() == flat.data_ptr()
+    ms = timed(step, steps, warmup) / steps
+    return {"value": keyframes * 1000.0 / ms, "unit": "keyframes/s", "ms_per_step": ms, "surfels": P, "keyframes": keyframes,
+            "keyframes_per_rank": len(mine), "allreduce_bytes": int(flat.numel() * 4) if world > 1 else 0,
+            "map_gradient_accumulated_in_place": bool(in_place),
+            "what": f"one joint pose + map gradient step over a {keyframes}-keyframe window of a {P}-surfel map (BASELINE.json "
+                    f"configs[3] in shape), keyframes sharded over {world} rank(s), one all-reduce of the flat [13 P] buffer per "
+                    f"step; " + how}

@@ -2,8 +2,8 @@
 # bench.py at N = 1 and N = $1 on one box (product arm), short runs: timing statistics, gradient check, collective A/B
 N="${1:-2}"
 mkdir -p gpurun_out
-timeout 300 python bench.py --steps 32 --warmup 4 --no-cpu-baseline --no-loops > gpurun_out/scale_n1.json 2> gpurun_out/scale_n1.err; echo "n1 rc=$?"; tail -2 gpurun_out/scale_n1.err
-GS2D_BENCH_WATCHDOG_S=200 timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29531 bench.py --gpus $N --steps 32 --warmup 4 --no-cpu-baseline --no-loops > gpurun_out/scale_n$N.json 2> gpurun_out/scale_n$N.err; echo "n$N rc=$?"; tail -3 gpurun_out/scale_n$N.err
+timeout 300 python bench.py --steps 32 --warmup 4 --no-cpu-baseline --no-loops --no-extra > gpurun_out/scale_n1.json 2> gpurun_out/scale_n1.err; echo "n1 rc=$?"; tail -2 gpurun_out/scale_n1.err
+GS2D_BENCH_WATCHDOG_S=200 timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29531 bench.py --gpus $N --steps 32 --warmup 4 --no-cpu-baseline --no-loops --no-extra > gpurun_out/scale_n$N.json 2> gpurun_out/scale_n$N.err; echo "n$N rc=$?"; tail -3 gpurun_out/scale_n$N.err
 python - <<'PY'
 import json,sys,glob
 for f in sorted(glob.glob("gpurun_out/scale_n*.json")):

@@ -14,5 +14,8 @@ for f in sys.argv[1:]:
     for k in ("mapping_iteration", "tracking_iteration"):
         if k in d:
             print(f"   {k}: {d[k]['value']:.1f} it/s ({d[k]['ms_per_iteration']:.3f} ms)")
+    for k in ("scannetpp_frame", "ba_step"):
+        if k in d:
+            print(f"   {k}: {d[k]['value']:.1f} {d[k]['unit']} ({d[k]['ms_per_step']:.3f} ms/step)")
     for n, k in (d.get("kernels") or {}).items():
         print(f"   {n:32s} {k['avg_us']:8.1f} us x {k['launches_per_step']:.0f}   hbm {k.get('frac_hbm', 0):.3f}")
