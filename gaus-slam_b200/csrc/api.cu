@@ -128,6 +128,47 @@ BinningState BinningState::carve(void* base, size_t I, size_t tiles, size_t* byt
 	return b;
 }
 
+// A per-device side stream + a small pool of events for the one fork / join inside the forward pass (the pair-count
+// scan runs beside the forward compositing).  The wait on an event is enqueued in the same critical section as its
+// record, so a pooled event can be re-recorded by a later call without affecting an earlier wait.
+struct SideStream {
+	cudaStream_t stream = nullptr;
+	cudaEvent_t ev[32] = {};
+	unsigned next = 0;
+};
+static std::mutex g_side_mu;
+static SideStream g_side[64];
+
+// fork: `side` waits for everything enqueued on `st` so far.  Returns the side stream (nullptr = run serially on st).
+static cudaStream_t side_fork(cudaStream_t st)
+{
+	int dev = 0;
+	if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
+	std::lock_guard<std::mutex> lk(g_side_mu);
+	SideStream& ss = g_side[dev];
+	if (!ss.stream) {
+		if (cudaStreamCreateWithFlags(&ss.stream, cudaStreamNonBlocking) != cudaSuccess) { ss.stream = nullptr; return nullptr; }
+		for (auto& e : ss.ev)
+			if (cudaEventCreateWithFlags(&e, cudaEventDisableTiming) != cudaSuccess) return nullptr;
+	}
+	cudaEvent_t e = ss.ev[ss.next++ % 32];
+	if (cudaEventRecord(e, st) != cudaSuccess || cudaStreamWaitEvent(ss.stream, e, 0) != cudaSuccess) return nullptr;
+	return ss.stream;
+}
+
+// join: everything enqueued on `st` after this call waits for what was enqueued on the side stream so far
+static int side_join(cudaStream_t st, cudaStream_t side)
+{
+	int dev = 0;
+	GS2D_CUDA_OK(cudaGetDevice(&dev));
+	std::lock_guard<std::mutex> lk(g_side_mu);
+	SideStream& ss = g_side[dev];
+	cudaEvent_t e = ss.ev[ss.next++ % 32];
+	GS2D_CUDA_OK(cudaEventRecord(e, side));
+	GS2D_CUDA_OK(cudaStreamWaitEvent(st, e, 0));
+	return GS2D_OK;
+}
+
 static inline size_t tiles_of(int W, int H)
 {
 	return (size_t)((W + TILE - 1) / TILE) * (size_t)((H + TILE - 1) / TILE);
@@ -257,12 +298,18 @@ int gs2d_forward_render_scattered(const gs2d_settings* s, const gs2d_inputs* in,
 	if (!scattered_pairs) GS2D_TRY(launch_scatter(*s, g, im, pairs, false, I, st));
 	GS2D_TRY(launch_tile_sort(*s, g, im, b, pairs, I, st));
 	GS2D_TRY(debug_sync(*s, st));
-	// (pair_status / pair_counters were zeroed by tile_sort_kernel)
-	GS2D_TRY(launch_scan_u32(b.hit_count, b.pair_incl, I, b.pair_status, b.pair_counters, st, false));
-	if (num_pairs_host)   // 8 bytes: counters[1] = total, counters[2] = 0 -> a whole int64, before the compositing kernel
-		GS2D_CUDA_OK(cudaMemcpyAsync(num_pairs_host, b.pair_counters + 1, 2 * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+	// The pair-slot layout of the backward pass (inclusive scan of the footprint popcounts) and its total are not needed
+	// by the forward compositing: they run BESIDE it on the library's side stream (fork after the tile sort, join after
+	// the compositing launch), which takes the scan's ~13 us off the critical path.  (pair_status / pair_counters were
+	// zeroed by tile_sort_kernel.)
+	cudaStream_t side = (s->debug || g_timing_on) ? nullptr : side_fork(st);
+	cudaStream_t scan_st = side ? side : st;
+	GS2D_TRY(launch_scan_u32(b.hit_count, b.pair_incl, I, b.pair_status, b.pair_counters, scan_st, false));
+	if (num_pairs_host)   // 8 bytes: counters[1] = total, counters[2] = 0 -> a whole int64
+		GS2D_CUDA_OK(cudaMemcpyAsync(num_pairs_host, b.pair_counters + 1, 2 * sizeof(uint32_t), cudaMemcpyDeviceToHost, scan_st));
 	GS2D_TRY(debug_sync(*s, st));
 	GS2D_TRY(launch_composite_forward(*s, *in, im, b.instances, b.hit_inst, b.hit_pix, out_color, out_others, st));
+	if (side) GS2D_TRY(side_join(st, side));
 	GS2D_TRY(debug_sync(*s, st));
 	return GS2D_OK;
 }

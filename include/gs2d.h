@@ -16,8 +16,9 @@
  * Rules of the ABI
  *   - plain C: pointers, sizes, scalars; no torch types, no exceptions, no state that a result depends on: calls on
  *     different streams / devices / threads are independent.  Process-wide are only diagnostics (the launch counter,
- *     the opt-in kernel timing of gs2d_timing_*), the one-time per-device kernel attribute opt-ins, and the static
- *     scratch of gs2d_sort_pairs_static.
+ *     the opt-in kernel timing of gs2d_timing_*), the one-time per-device kernel attribute opt-ins, one internal
+ *     side stream per device (the forward pass forks one scan onto it and joins it again), and the static scratch of
+ *     gs2d_sort_pairs_static.
  *   - every pointer is a DEVICE pointer owned by the caller unless its name ends in
  *     `_host`; nothing is allocated or freed behind the caller's back.
  *   - every function that launches work takes the CUDA stream to launch on

@@ -123,6 +123,10 @@ inline cudaError_t cudaStreamSynchronize(cudaStream_t) { return cudaSuccess; }
 inline cudaError_t cudaEventCreate(cudaEvent_t* e) { *e = nullptr; return cudaSuccess; }
 inline cudaError_t cudaEventRecord(cudaEvent_t, cudaStream_t) { return cudaSuccess; }
 inline cudaError_t cudaEventSynchronize(cudaEvent_t) { return cudaSuccess; }
+constexpr unsigned cudaStreamNonBlocking = 1, cudaEventDisableTiming = 2;
+inline cudaError_t cudaStreamCreateWithFlags(cudaStream_t* s, unsigned) { static int one; *s = &one; return cudaSuccess; }   // work runs synchronously anyway
+inline cudaError_t cudaEventCreateWithFlags(cudaEvent_t* e, unsigned) { static int one; *e = &one; return cudaSuccess; }
+inline cudaError_t cudaStreamWaitEvent(cudaStream_t, cudaEvent_t, unsigned) { return cudaSuccess; }
 inline cudaError_t cudaEventElapsedTime(float* ms, cudaEvent_t, cudaEvent_t) { *ms = 0.f; return cudaSuccess; }
 inline cudaError_t cudaMemset(void* p, int v, size_t n) { std::memset(p, v, n); return cudaSuccess; }
 enum cudaFuncAttribute { cudaFuncAttributeMaxDynamicSharedMemorySize };
