@@ -73,6 +73,9 @@ def main():
     walk = {"rows": 0, "blk8x4": 0, "sorted": 0, "sorted_tile": 0, "tileperm_batch128": 0, "tileperm_batch256": 0,
             "blk8x4_batch256": 0, "blk8x4_tile": 0, "ideal": 0}
     per_pixel_len, batch_pairs = [], []
+    # phase B of the backward pass (a group of lanes per instance, lanes over the instance's pair slots): warp iterations
+    phb = {"grp8": 0, "grp8_sorted": 0, "grp4": 0, "grp4_sorted": 0, "grp16_sorted": 0, "adaptive_sorted": 0, "ideal": 0}
+    inst_slots = []
     lane = np.arange(256)
     # thread -> row-major pixel id of the 8x4 block layout (pair.cuh thread_lx / thread_ly with BLOCK = 1)
     blk_pix = ((((lane >> 6) << 2) | ((lane >> 3) & 3)) << 4) | ((((lane >> 5) & 1) << 3) | (lane & 7))
@@ -102,11 +105,38 @@ def main():
         walk["blk8x4_batch256"] += int(fb2[:, blk_pix].reshape(-1, 8, 32).max(2).sum()) * 32
         walk["blk8x4_tile"] += int(fb.sum(0)[blk_pix].reshape(8, 32).max(1).sum()) * 32
         walk["ideal"] += int(fb.sum())
+        # slots per instance: pixels whose footprint word has the instance's bit set
+        bits = (w[:, 1, :, None] >> np.arange(32, dtype=np.uint32)[None, None, :]) & 1     # [word, pixel, bit]
+        sl = bits.sum(1).reshape(-1)[:nn].astype(np.int64)
+        inst_slots.append(sl)
+        phb["ideal"] += int(sl.sum())
+
+        def warp_iters(s_, lanes):
+            per_warp = 32 // lanes
+            it = -(-s_ // lanes)
+            pad = (-len(it)) % per_warp
+            it = np.concatenate([it, np.zeros(pad, it.dtype)]).reshape(-1, per_warp)
+            return int(it.max(1).sum()) * 32
+        phb["grp8"] += warp_iters(sl, 8)
+        phb["grp4"] += warp_iters(sl, 4)
+        ss = np.sort(sl)[::-1]
+        phb["grp8_sorted"] += warp_iters(ss, 8)
+        phb["grp4_sorted"] += warp_iters(ss, 4)
+        phb["grp16_sorted"] += warp_iters(ss, 16)
+        # lanes per instance chosen by size class (<= 4 slots: 4 lanes ... > 32: 32 lanes), classes processed separately
+        tot = 0
+        for lanes, lo, hi in ((4, 0, 8), (8, 8, 24), (16, 24, 64), (32, 64, 1 << 30)):
+            c = ss[(ss > lo) & (ss <= hi)]
+            if len(c):
+                tot += warp_iters(c, lanes)
+        phb["adaptive_sorted"] += tot
     bp = np.array(batch_pairs)
     out.update(footprint_pairs=tot_foot, used_pairs=tot_used, used_over_footprint=tot_used / max(tot_foot, 1),
                pairs_per_instance=tot_foot / max(I, 1), pixel_list_len=pct(np.concatenate(per_pixel_len)),
                batch_pairs=pct(bp),
-               lane_efficiency={k: walk["ideal"] / v for k, v in walk.items() if k != "ideal" and v})
+               lane_efficiency={k: walk["ideal"] / v for k, v in walk.items() if k != "ideal" and v},
+               phase_b_lane_efficiency={k: phb["ideal"] / v for k, v in phb.items() if k != "ideal" and v},
+               slots_per_instance=pct(np.concatenate(inst_slots)))
     for k in (2048, 3072, 4096):
         out["batch_pairs"][f"frac_gt{k}"] = float((bp > k).mean())
     print(json.dumps(out, indent=1))
