@@ -24,6 +24,8 @@
 // Records + masks of a tile arrive in batches of 128 by TMA (two-stage mbarrier ring).  Rows are indexed by
 // the instance's position in surfel-major (unsorted) order, so preprocess_bwd.cu reads each surfel's rows
 // contiguously.
+#include <atomic>
+
 #include "common.cuh"
 #include "tma.cuh"
 #include "pair.cuh"
@@ -38,8 +40,19 @@ namespace {
 #ifndef GS2D_BWD_PREFETCH
 #define GS2D_BWD_PREFETCH 1
 #endif
-constexpr int BWD_BATCH = 128;
-constexpr int BWD_STAGES = 2;
+constexpr int BWD_BATCH = 128;                        // instances per TMA chunk
+// Instances resident at once ("super-batch").  352 keeps the kernel's shared memory under 56 KB (four CTAs per SM);
+// the tiles of the BASELINE mapping views hold 307 instances on average (p99 360): a denser tile takes a second round.
+#ifndef GS2D_BWD_SUPER
+#define GS2D_BWD_SUPER 352
+#endif
+constexpr int BWD_SUPER = GS2D_BWD_SUPER;
+static_assert(BWD_SUPER % 32 == 0, "super-batches start at a word boundary of the per-pixel words");
+constexpr int BWD_CHUNKS = (BWD_SUPER + BWD_BATCH - 1) / BWD_BATCH;
+constexpr int BWD_WORDS = BWD_SUPER / 32;             // contribution words per pixel per super-batch
+constexpr int BWD_PIX_BINS = 64;                      // pixel list lengths 0 .. 62, 63 = longer
+constexpr int BWD_INST_BINS = 16;                     // phase-B iterations of an instance 0 .. 14, 15 = more
+static_assert(BWD_BATCH / 32 <= HIT_PIX_PAD, "hit_pix padding");
 
 struct PixelConst {
 	float T_final, final_A, final_D, final_D2;
@@ -63,13 +76,21 @@ struct PixelBwd {
 };
 
 struct BwdSmem {
-	float4 rec[BWD_STAGES][BWD_BATCH * 5];
-	uint32_t mask[BWD_STAGES][BWD_BATCH * 8];
-	uint2 pref[BWD_BATCH];              // 8 packed bytes: hits of the instance in mask words 0..k-1
-	uint32_t base[BWD_BATCH];           // first pair slot of every instance of the batch (global index)
-	float pix[6][TILE_PIXELS];          // dL_dpix (3), dL_dnormal (3) per pixel, for phase B
+	float4 rec[BWD_SUPER * 5];                // contiguous: instance i of the super-batch is rec[5 * i]
+	uint32_t mask[BWD_SUPER * 8];
+	union {
+		uint32_t used[BWD_WORDS][TILE_PIXELS];    // phase A: per-pixel contribution words, column = row-major pixel id
+		struct {
+			float pix[6][TILE_PIXELS];            // phase B: dL_dpix (3), dL_dnormal (3) per pixel (row-major pixel id)
+			uint16_t ord[BWD_SUPER];              // phase B: instances of the super-batch, longest slot list first
+		} b;
+	};
+	uint2 pref[BWD_SUPER];                    // 8 packed bytes: hits of the instance in mask words 0..k-1
+	uint32_t base[BWD_SUPER + 1];             // first pair slot of every instance of the super-batch (global index)
+	uint32_t bins[BWD_PIX_BINS];
+	uint8_t order[TILE_PIXELS];               // phase A: thread -> row-major id of the pixel it walks
 	uint32_t max_last[8];
-	uint64_t bar[BWD_STAGES];
+	uint64_t bar[BWD_CHUNKS];
 };
 
 // Phase A for one (pixel, instance) pair: CR/backward.cu:283-410 minus the geometric chain.
@@ -216,19 +237,16 @@ composite_backward_pixels_kernel(int W, int H, unsigned gx, const uint2* __restr
                                  const float* __restrict__ dL_dothers, float4* __restrict__ slots,
                                  float* __restrict__ grad_rows, uint32_t slot_cap, uint32_t* __restrict__ overflow)
 {
-	__shared__ BwdSmem sm;
+	extern __shared__ __align__(128) unsigned char bwd_smem_raw[];
+	BwdSmem& sm = *reinterpret_cast<BwdSmem*>(bwd_smem_raw);
 
+	// Thread t is the NATURAL owner of row-major tile pixel t (warp k = tile rows 2k, 2k+1 = footprint-mask word k,
+	// lane = bit): it moves that pixel's words.  The back-to-front WALK of a pixel is done by another thread: pixels
+	// are sorted by list length once per tile so that the 32 lists a warp walks in lockstep are alike.
 	const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 	const unsigned tile = blockIdx.x;
 	const unsigned tx = tile % gx, ty = tile / gx;
-	const int lx = thread_lx<GS2D_BWD_BLOCK>(tid), ly = thread_ly<GS2D_BWD_BLOCK>(tid);   // thread <-> tile pixel: pair.cuh
-	const int ptid = pixel_thread(lx, ly);               // row-major pixel index: this pixel's words in hit_pix
-	const unsigned pix_x = tx * TILE + lx;
-	const unsigned pix_y = ty * TILE + ly;
-	const bool inside = pix_x < (unsigned)W && pix_y < (unsigned)H;
-	const float pxf = (float)pix_x, pyf = (float)pix_y;
 	const size_t HW = (size_t)H * W;
-	const size_t pid = (size_t)W * pix_y + pix_x;
 
 	const uint2 range = ranges[tile];
 	const int n = (int)(range.y - range.x);
@@ -239,51 +257,16 @@ composite_backward_pixels_kernel(int W, int H, unsigned gx, const uint2* __restr
 		return;
 	}
 
-	PixelConst pc;
-	pc.T_final = inside ? final_T[pid] : 0.f;
-	const uint32_t last_contributor = inside ? n_contrib[pid] : 0u;
-	pc.median_contributor = inside ? n_contrib[pid + HW] : 0u;
-	pc.final_A = 1 - pc.T_final;
-	pc.final_D = inside ? final_T[pid + HW] : 0.f;
-	pc.final_D2 = inside ? final_T[pid + 2 * HW] : 0.f;
-	pc.dpix0 = pc.dpix1 = pc.dpix2 = 0.f;
-	pc.dL_ddepth = pc.dL_daccum = pc.dL_dreg = pc.dL_dmedian = 0.f;
-	pc.dn0 = pc.dn1 = pc.dn2 = 0.f;
-	pc.mm = 0.f;
-	pc.inv_4std = 0.f;
-	if (inside) {
-		pc.dpix0 = dL_dpix[pid];
-		pc.dpix1 = dL_dpix[pid + HW];
-		pc.dpix2 = dL_dpix[pid + 2 * HW];
-		pc.dL_ddepth = dL_dothers[pid + 0 * HW];
-		pc.dL_daccum = dL_dothers[pid + 1 * HW];
-		pc.dn0 = dL_dothers[pid + 2 * HW];
-		pc.dn1 = dL_dothers[pid + 3 * HW];
-		pc.dn2 = dL_dothers[pid + 4 * HW];
-		pc.dL_dmedian = dL_dothers[pid + 5 * HW];
-		pc.dL_dreg = dL_dothers[pid + 6 * HW];
-		pc.mm = median_depth[pid];
-		pc.inv_4std = 1.0f / (4 * fmaxf(depth_std[pid] / (1 - pc.T_final), 1e-7f));
-	}
-	{
-		float acc = 0;
-		acc += bg[0] * pc.dpix0;
-		acc += bg[1] * pc.dpix1;
-		acc += bg[2] * pc.dpix2;
-		pc.bg_dot = acc;
-	}
-	sm.pix[0][tid] = pc.dpix0; sm.pix[1][tid] = pc.dpix1; sm.pix[2][tid] = pc.dpix2;
-	sm.pix[3][tid] = pc.dn0;   sm.pix[4][tid] = pc.dn1;   sm.pix[5][tid] = pc.dn2;
-	PixelBwd st;
-	st.T = pc.T_final;
-
 	// deepest last contributor of the tile: nothing behind it is ever visited
-	uint32_t wmax = last_contributor;
+	{
+		const unsigned nx = tx * TILE + (tid & 15), ny = ty * TILE + (tid >> 4);
+		uint32_t wmax = (nx < (unsigned)W && ny < (unsigned)H) ? n_contrib[(size_t)W * ny + nx] : 0u;
 #pragma unroll
-	for (int o = 16; o >= 1; o >>= 1) wmax = max(wmax, __shfl_xor_sync(0xffffffffu, wmax, o));
-	if (lane == 0) sm.max_last[warp] = wmax;
+		for (int o = 16; o >= 1; o >>= 1) wmax = max(wmax, __shfl_xor_sync(0xffffffffu, wmax, o));
+		if (lane == 0) sm.max_last[warp] = wmax;
+	}
 	if (tid == 0) {
-		for (int s = 0; s < BWD_STAGES; s++) mbar_init(&sm.bar[s], 1);
+		for (int c = 0; c < BWD_CHUNKS; c++) mbar_init(&sm.bar[c], 1);
 		mbar_fence_init();
 	}
 	__syncthreads();
@@ -291,8 +274,7 @@ composite_backward_pixels_kernel(int W, int H, unsigned gx, const uint2* __restr
 #pragma unroll
 	for (int i = 0; i < 8; i++) bmax = max(bmax, sm.max_last[i]);
 	const int n_used = min((int)bmax, n);            // instances [0, n_used) can matter
-	const int nb = (n_used + BWD_BATCH - 1) / BWD_BATCH;
-	const int n_done = min(nb * BWD_BATCH, n);       // instances of whole batches: all their slots get written
+	const int n_done = min(((n_used + BWD_BATCH - 1) / BWD_BATCH) * BWD_BATCH, n);   // whole chunks: all their slots get written
 	const float4* tile_rec = instances + 5 * (size_t)range.x;
 	// rows of the instances nobody reaches (behind every pixel's last contributor): zeros
 	for (int q = n_done + (tid >> 2); q < n; q += 64) {
@@ -301,136 +283,272 @@ composite_backward_pixels_kernel(int W, int H, unsigned gx, const uint2* __restr
 		dst[tid & 3] = make_float4(0.f, 0.f, 0.f, 0.f);
 		if ((tid & 3) == 0) dst[4] = make_float4(0.f, 0.f, 0.f, 0.f);
 	}
-	if (nb == 0) return;
+	if (n_done == 0) return;
+	const int nsb = (n_done + BWD_SUPER - 1) / BWD_SUPER;
 
 	const uint32_t* tile_mask = hit_inst + 8 * (size_t)range.x;
-	auto issue = [&](int b, int stage) {
-		const uint32_t cnt = (uint32_t)min(n - b * BWD_BATCH, BWD_BATCH);
-		mbar_arrive_expect_tx(&sm.bar[stage], cnt * (80u + 32u));
-		tma_load_1d(&sm.rec[stage][0], tile_rec + 5 * (size_t)b * BWD_BATCH, cnt * 80u, &sm.bar[stage]);
-		tma_load_1d(&sm.mask[stage][0], tile_mask + 8 * (size_t)b * BWD_BATCH, cnt * 32u, &sm.bar[stage]);
-	};
-	if (tid == 0) issue(nb - 1, 0);
-
-	const uint32_t lane_lt = (1u << lane) - 1u;
 	const uint32_t* pix_words = hit_pix + ((size_t)(range.x >> 5) + HIT_PIX_PAD * (size_t)tile) * 2 * TILE_PIXELS;
 	const float4 empty = make_float4(0.f, 0.f, 0.f, __int_as_float(-1));
+	const float4* recs = &sm.rec[0];
+	const uint32_t* masks = &sm.mask[0];
 
-	for (int it = 0; it < nb; it++) {
-		const int b = nb - 1 - it;
-		const int stage = it & 1;
-		const uint32_t parity = (uint32_t)(it >> 1) & 1u;
-		__syncthreads();   // batch it-1 fully consumed -> its stage and pref/base may be overwritten
-		if (tid == 0 && it + 1 < nb) issue(b - 1, stage ^ 1);
-		const int cnt = min(n - b * BWD_BATCH, BWD_BATCH);
-		// words of this pixel: pairs that contributed / pairs that own a slot
-		uint32_t used[BWD_BATCH / 32], foot[BWD_BATCH / 32];
+	// pair slot of (instance j of the super-batch, pixel with mask word `word`, bits below it `lt`)
+	auto slot_of = [&](int j, int word, uint32_t lt) -> float4* {
+		const uint2 pf = sm.pref[j];
+		const uint32_t before = (uint32_t)((((unsigned long long)pf.y << 32) | pf.x) >> (8 * word)) & 0xffu;
+		return slots + (sm.base[j] + before + __popc(masks[j * 8 + word] & lt));
+	};
+
+	PixelConst pc;
+	PixelBwd st;
+	int o = tid;                                      // row-major id of the pixel this thread walks
+	float pxf = 0.f, pyf = 0.f;
+	uint32_t o_lt = 0;
+	uint32_t bar_phase = 0;
+
+	for (int it = 0; it < nsb; it++) {
+		const int sb = nsb - 1 - it;
+		const int first = sb * BWD_SUPER;                       // first instance of the super-batch (in the tile)
+		const int cnt_sb = min(n_done - first, BWD_SUPER);
+		const int nch = (cnt_sb + BWD_BATCH - 1) / BWD_BATCH;
+		const int nw = (cnt_sb + 31) >> 5;
+		if (it > 0) __syncthreads();   // the previous super-batch is fully consumed
+		if (tid == 0) {
+			for (int c = 0; c < nch; c++) {
+				const uint32_t cnt = (uint32_t)min(cnt_sb - c * BWD_BATCH, BWD_BATCH);
+				const size_t at = (size_t)first + (size_t)c * BWD_BATCH;
+				mbar_arrive_expect_tx(&sm.bar[c], cnt * (80u + 32u));
+				tma_load_1d(&sm.rec[5 * c * BWD_BATCH], tile_rec + 5 * at, cnt * 80u, &sm.bar[c]);
+				tma_load_1d(&sm.mask[8 * c * BWD_BATCH], tile_mask + 8 * at, cnt * 32u, &sm.bar[c]);
+			}
+		}
+		// natural owners: the pixel's contribution words of this super-batch (coalesced) -> shared memory
+		int len = 0;
+		for (int w = 0; w < nw; w++) {
+			const uint32_t u = pix_words[(size_t)(((first >> 5) + w) * 2 + 0) * TILE_PIXELS + tid];
+			sm.used[w][tid] = u;
+			len += __popc(u);
+		}
+		for (int i = tid; i <= cnt_sb; i += 256) {
+			const size_t gi = (size_t)range.x + first + i;
+			sm.base[i] = gi ? pair_incl[gi - 1] : 0u;
+		}
+		if (it == 0) {
+			// counting sort of the 256 pixels by the length of their list (deepest super-batch), longest first
+			const int c = (BWD_PIX_BINS - 1) - min(len, BWD_PIX_BINS - 1);
+			if (tid < BWD_PIX_BINS) sm.bins[tid] = 0u;
+			__syncthreads();
+			const uint32_t rank = atomicAdd(&sm.bins[c], 1u);
+			__syncthreads();
+			if (warp == 0) {
+				const uint32_t a = sm.bins[2 * lane], b = sm.bins[2 * lane + 1];
+				uint32_t incl = a + b;
 #pragma unroll
-		for (int g = 0; g < BWD_BATCH / 32; g++) {
-			used[g] = pix_words[(size_t)((b * (BWD_BATCH / 32) + g) * 2 + 0) * TILE_PIXELS + ptid];
-			foot[g] = pix_words[(size_t)((b * (BWD_BATCH / 32) + g) * 2 + 1) * TILE_PIXELS + ptid];
+				for (int d = 1; d < 32; d <<= 1) {
+					const uint32_t t = __shfl_up_sync(0xffffffffu, incl, d);
+					if (lane >= d) incl += t;
+				}
+				sm.bins[2 * lane] = incl - a - b;
+				sm.bins[2 * lane + 1] = incl - b;
+			}
+			__syncthreads();
+			sm.order[sm.bins[c] + rank] = (uint8_t)tid;
+			__syncthreads();
+			o = sm.order[tid];
+			o_lt = (1u << (o & 31)) - 1u;
+			const unsigned pix_x = tx * TILE + (o & 15), pix_y = ty * TILE + (o >> 4);
+			const bool inside = pix_x < (unsigned)W && pix_y < (unsigned)H;
+			pxf = (float)pix_x;
+			pyf = (float)pix_y;
+			const size_t pid = (size_t)W * pix_y + pix_x;
+			pc.T_final = inside ? final_T[pid] : 0.f;
+			pc.median_contributor = inside ? n_contrib[pid + HW] : 0u;
+			pc.final_A = 1 - pc.T_final;
+			pc.final_D = inside ? final_T[pid + HW] : 0.f;
+			pc.final_D2 = inside ? final_T[pid + 2 * HW] : 0.f;
+			pc.dpix0 = pc.dpix1 = pc.dpix2 = 0.f;
+			pc.dL_ddepth = pc.dL_daccum = pc.dL_dreg = pc.dL_dmedian = 0.f;
+			pc.dn0 = pc.dn1 = pc.dn2 = 0.f;
+			pc.mm = 0.f;
+			pc.inv_4std = 0.f;
+			if (inside) {
+				pc.dpix0 = dL_dpix[pid];
+				pc.dpix1 = dL_dpix[pid + HW];
+				pc.dpix2 = dL_dpix[pid + 2 * HW];
+				pc.dL_ddepth = dL_dothers[pid + 0 * HW];
+				pc.dL_daccum = dL_dothers[pid + 1 * HW];
+				pc.dn0 = dL_dothers[pid + 2 * HW];
+				pc.dn1 = dL_dothers[pid + 3 * HW];
+				pc.dn2 = dL_dothers[pid + 4 * HW];
+				pc.dL_dmedian = dL_dothers[pid + 5 * HW];
+				pc.dL_dreg = dL_dothers[pid + 6 * HW];
+				pc.mm = median_depth[pid];
+				pc.inv_4std = 1.0f / (4 * fmaxf(depth_std[pid] / (1 - pc.T_final), 1e-7f));
+			}
+			{
+				float acc = 0;
+				acc += bg[0] * pc.dpix0;
+				acc += bg[1] * pc.dpix1;
+				acc += bg[2] * pc.dpix2;
+				pc.bg_dot = acc;
+			}
+			st.T = pc.T_final;
 		}
-		if (tid < cnt) {
-			const size_t gi = (size_t)range.x + (size_t)b * BWD_BATCH + tid;
-			sm.base[tid] = gi ? pair_incl[gi - 1] : 0u;
-		}
-		if (warp == 0) mbar_wait(&sm.bar[stage], parity);
+		// a chunk barrier completes one phase per super-batch that USES it (the deepest super-batch, taken first, may
+		// use fewer chunks than the others): bar_phase holds the parity of every barrier's next phase
+		if (warp == 0)
+			for (int c = 0; c < nch; c++) mbar_wait(&sm.bar[c], (bar_phase >> c) & 1u);
+		bar_phase ^= (1u << nch) - 1u;
 		__syncthreads();
-
-		const float4* recs = &sm.rec[stage][0];
-		const uint32_t* masks = &sm.mask[stage][0];
-#if GS2D_BWD_BLOCK
-		// re-order every mask in place from row-pair words to warp-block words (pair.cuh): word pair (2m, 2m+1) holds
-		// tile rows 4m..4m+3, i.e. exactly the two 8 x 4 blocks of block row m
-		for (int e = tid; e < cnt * 4; e += 256) {
-			uint2* w2 = reinterpret_cast<uint2*>(&sm.mask[stage][0]) + e;
-			const uint2 rows = *w2;
-			*w2 = make_uint2(__byte_perm(rows.x, rows.y, 0x6420), __byte_perm(rows.x, rows.y, 0x7531));
-		}
-		__syncthreads();
-#endif
-		if (tid < cnt) {
+		for (int i = tid; i < cnt_sb; i += 256) {
 			uint32_t run = 0, lo = 0, hi = 0;
 #pragma unroll
 			for (int k = 0; k < 8; k++) {
 				if (k < 4) lo |= run << (8 * k); else hi |= run << (8 * (k - 4));
-				run += __popc(masks[tid * 8 + k]);
+				run += __popc(masks[i * 8 + k]);
 			}
-			sm.pref[tid] = make_uint2(lo, hi);
+			sm.pref[i] = make_uint2(lo, hi);
 		}
 		__syncthreads();
 
-		// every pixel walks the pairs of its footprint words of the WHOLE batch, back to front, in one loop (a warp
-		// iterates as often as its longest pixel list; lists of 128 instances balance better than lists of 32)
+		// ---- phase A.  Natural owners first mark the footprint pairs that did not contribute (1.4 % of the slots:
+		// rejected by the exact tests, or behind the pixel's termination point) ...
 		{
-			constexpr int NG = BWD_BATCH / 32;
-			int g = NG - 1;
-			uint32_t m = foot[NG - 1], u = used[NG - 1];
+			const uint32_t lane_lt = (1u << lane) - 1u;
+			for (int w = 0; w < nw; w++) {
+				uint32_t e = pix_words[(size_t)(((first >> 5) + w) * 2 + 1) * TILE_PIXELS + tid] & ~sm.used[w][tid];
+				while (e) {
+					const int jl = __ffs(e) - 1;
+					e &= e - 1;
+					*slot_of(w * 32 + jl, warp, lane_lt) = empty;
+				}
+			}
+		}
+		// ... then every (sorted) pixel walks ITS contributing pairs of the WHOLE super-batch back to front in one loop
+		// (a warp iterates as often as its longest list; lists of a whole tile, sorted, are alike).
+		{
+			const int oword = o >> 5;
+			int g = nw - 1;
+			uint32_t m = sm.used[g][o];
 			for (;;) {
 				while (m == 0u && g > 0) {     // advance to the next non-empty word (towards the front)
 					g--;
-#pragma unroll
-					for (int k = 0; k < NG - 1; k++)
-						if (g == k) { m = foot[k]; u = used[k]; }
+					m = sm.used[g][o];
 				}
 				if (!__any_sync(0xffffffffu, m != 0u)) break;
 				if (m != 0u) {
 					const int jl = 31 - __clz(m);
 					m &= ~(1u << jl);
 					const int j = g * 32 + jl;
-					const uint2 pf = sm.pref[j];
-					const uint32_t before = ((warp < 4 ? pf.x >> (8 * warp) : pf.y >> (8 * (warp - 4))) & 0xffu);
-					float4* dst = slots + (sm.base[j] + before + __popc(masks[j * 8 + warp] & lane_lt));
-					if ((u >> jl) & 1u) {
-						float A, dz, w;
-						pixel_step<USE_SA>(recs + j * 5, pxf, pyf, (uint32_t)(b * BWD_BATCH + j), pc, st, A, dz, w);
-						*dst = make_float4(A, dz, w, __int_as_float(tid));
-					} else {
-						*dst = empty;
-					}
+					float4* dst = slot_of(j, oword, o_lt);
+					float A, dz, w;
+					pixel_step<USE_SA>(recs + j * 5, pxf, pyf, (uint32_t)(first + j), pc, st, A, dz, w);
+					*dst = make_float4(A, dz, w, __int_as_float(o));
 				}
 			}
 		}
 	}
+	__syncthreads();   // every slot of the tile's instances is written; the words are dead
+	// the pixel's gradient constants for phase B take the place of the words
+	sm.b.pix[0][o] = pc.dpix0; sm.b.pix[1][o] = pc.dpix1; sm.b.pix[2][o] = pc.dpix2;
+	sm.b.pix[3][o] = pc.dn0;   sm.b.pix[4][o] = pc.dn1;   sm.b.pix[5][o] = pc.dn2;
 
-	// ---- phase B: a quarter-warp per instance of the tile, lanes over the instance's pair slots (just written by
-	// this CTA: L2-hot); pixel constants from shared memory, the record straight from global memory.
-	__syncthreads();
-	const int grp = tid >> 3, gl = tid & 7;
-	for (int q0 = 0; q0 < n_done; q0 += 32) {
-		const int q = q0 + grp;
-		float g[24];
-#pragma unroll
-		for (int k = 0; k < 24; k++) g[k] = 0.f;
-		uint32_t row = 0;
-		if (q < n_done) {
-			const float4* rec = tile_rec + 5 * (size_t)q;
-			const float4 r0 = rec[0], r1 = rec[1], r2 = rec[2];
-			row = __float_as_uint(rec[4].w);
-			const size_t gi = (size_t)range.x + q;
-			const uint32_t s0 = gi ? pair_incl[gi - 1] : 0u, s1 = pair_incl[gi];
-#if GS2D_BWD_PREFETCH
-			// the next slot is requested before the current one is worked on (phase B waits on L2 otherwise)
-			float4 nx = (s0 + gl < s1) ? slots[s0 + gl] : make_float4(0.f, 0.f, 0.f, __int_as_float(-1));
-#endif
-			for (uint32_t k = s0 + gl; k < s1; k += 8) {
-#if GS2D_BWD_PREFETCH
-				const float4 sl = nx;
-				if (k + 8 < s1) nx = slots[k + 8];
-#else
-				const float4 sl = slots[k];
-#endif
-				const int p = __float_as_int(sl.w);
-				if (p >= 0)
-					instance_step(r0, r1, r2, (float)(tx * TILE + thread_lx<GS2D_BWD_BLOCK>(p)), (float)(ty * TILE + thread_ly<GS2D_BWD_BLOCK>(p)), sl.x, sl.y,
-					              sl.z, &sm.pix[0][0], p, g);
+	// ---- phase B: a quarter-warp per instance, lanes over the instance's pair slots (just written by this CTA:
+	// L2-hot); pixel constants from shared memory; the record from shared memory when the whole tile is resident (one
+	// super-batch), else from global memory.  Instances are taken, window by window, in the order of their slot counts
+	// (counting sort by ceil(slots / 8)) so that the four of a warp iterate equally often.
+	const bool resident = nsb == 1;
+	for (int first = 0; first < n_done; first += BWD_SUPER) {
+		const int cnt_sb = min(n_done - first, BWD_SUPER);
+		if (!resident) {
+			__syncthreads();   // the previous window's order / bases are consumed
+			for (int i = tid; i <= cnt_sb; i += 256) {
+				const size_t gi = (size_t)range.x + first + i;
+				sm.base[i] = gi ? pair_incl[gi - 1] : 0u;
 			}
 		}
-		__syncwarp();
-		oct_reduce24(g, lane);
-		if (q < n_done && gl < 6) {
-			float* dst = grad_rows + (size_t)row * GRAD_WORDS + 3 * gl;
-			dst[0] = g[0]; dst[1] = g[1]; dst[2] = g[2];
+		{
+			constexpr int PER = (BWD_SUPER + 255) / 256;
+			int cls[PER];
+			uint32_t rnk[PER];
+			if (tid < BWD_INST_BINS) sm.bins[tid] = 0u;
+			__syncthreads();
+#pragma unroll
+			for (int r = 0; r < PER; r++) {
+				const int i = r * 256 + tid;
+				int c = BWD_INST_BINS;      // beyond the list: a class of its own
+				if (i < cnt_sb) {
+					const uint32_t cnt = sm.base[i + 1] - sm.base[i];
+					c = (BWD_INST_BINS - 1) - (int)min((cnt + 7u) >> 3, (uint32_t)(BWD_INST_BINS - 1));
+				}
+				const uint32_t peers = __match_any_sync(0xffffffffu, c);
+				const int leader = __ffs(peers) - 1;
+				uint32_t at = 0;
+				if (lane == leader && c < BWD_INST_BINS) at = atomicAdd(&sm.bins[c], (uint32_t)__popc(peers));
+				at = __shfl_sync(0xffffffffu, at, leader);
+				cls[r] = c;
+				rnk[r] = at + __popc(peers & ((1u << lane) - 1u));
+			}
+			__syncthreads();
+			if (warp == 0) {
+				const uint32_t v = lane < BWD_INST_BINS ? sm.bins[lane] : 0u;
+				uint32_t incl = v;
+#pragma unroll
+				for (int d = 1; d < 32; d <<= 1) {
+					const uint32_t t = __shfl_up_sync(0xffffffffu, incl, d);
+					if (lane >= d) incl += t;
+				}
+				if (lane < BWD_INST_BINS) sm.bins[lane] = incl - v;
+			}
+			__syncthreads();
+#pragma unroll
+			for (int r = 0; r < PER; r++)
+				if (cls[r] < BWD_INST_BINS) sm.b.ord[sm.bins[cls[r]] + rnk[r]] = (uint16_t)(r * 256 + tid);
+			__syncthreads();
+		}
+		const int grp = tid >> 3, gl = tid & 7;
+		for (int q0 = 0; q0 < cnt_sb; q0 += 32) {
+			const int qi = q0 + grp;
+			float g[24];
+#pragma unroll
+			for (int k = 0; k < 24; k++) g[k] = 0.f;
+			uint32_t row = 0;
+			if (qi < cnt_sb) {
+				const int q = sm.b.ord[qi];
+				float4 r0, r1, r2;
+				if (resident) {
+					const float4* rec = recs + 5 * q;
+					r0 = rec[0]; r1 = rec[1]; r2 = rec[2];
+					row = __float_as_uint(rec[4].w);
+				} else {
+					const float4* rec = tile_rec + 5 * (size_t)(first + q);
+					r0 = rec[0]; r1 = rec[1]; r2 = rec[2];
+					row = __float_as_uint(rec[4].w);
+				}
+				const uint32_t s0 = sm.base[q], s1 = sm.base[q + 1];
+#if GS2D_BWD_PREFETCH
+				// the next slot is requested before the current one is worked on (phase B waits on L2 otherwise)
+				float4 nx = (s0 + gl < s1) ? slots[s0 + gl] : make_float4(0.f, 0.f, 0.f, __int_as_float(-1));
+#endif
+				for (uint32_t k = s0 + gl; k < s1; k += 8) {
+#if GS2D_BWD_PREFETCH
+					const float4 sl = nx;
+					if (k + 8 < s1) nx = slots[k + 8];
+#else
+					const float4 sl = slots[k];
+#endif
+					const int p = __float_as_int(sl.w);
+					if (p >= 0)
+						instance_step(r0, r1, r2, (float)(tx * TILE + (p & 15)), (float)(ty * TILE + (p >> 4)), sl.x, sl.y,
+						              sl.z, &sm.b.pix[0][0], p, g);
+				}
+			}
+			__syncwarp();
+			oct_reduce24(g, lane);
+			if (qi < cnt_sb && gl < 6) {
+				float* dst = grad_rows + (size_t)row * GRAD_WORDS + 3 * gl;
+				dst[0] = g[0]; dst[1] = g[1]; dst[2] = g[2];
+			}
 		}
 	}
 #if GS2D_BWD_DISCARD
@@ -446,6 +564,22 @@ composite_backward_pixels_kernel(int W, int H, unsigned gx, const uint2* __restr
 			asm volatile("discard.global.L2 [%0], 128;" ::"l"(a) : "memory");
 	}
 #endif
+}
+
+template <bool USE_SA, typename... Args>
+int launch_bwd_variant(unsigned blocks, cudaStream_t st, Args... args)
+{
+	// the opt-in to > 48 KB of dynamic shared memory is per device: made once for every device this variant runs on
+	static std::atomic<unsigned long long> opted_in{0};
+	int dev = 0;
+	GS2D_CUDA_OK(cudaGetDevice(&dev));
+	if (dev >= 64 || !((opted_in.load(std::memory_order_relaxed) >> dev) & 1ull)) {
+		GS2D_CUDA_OK(cudaFuncSetAttribute(composite_backward_pixels_kernel<USE_SA>,
+		                                  cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(BwdSmem)));
+		if (dev < 64) opted_in.fetch_or(1ull << dev, std::memory_order_relaxed);
+	}
+	composite_backward_pixels_kernel<USE_SA><<<blocks, 256, sizeof(BwdSmem), st>>>(args...);
+	return GS2D_OK;
 }
 
 }  // namespace
@@ -472,16 +606,19 @@ int launch_composite_backward(const gs2d_settings& s, const gs2d_inputs& in, con
 	if (gx * gy == 0 || I <= 0) return GS2D_OK;
 	{
 		ProfScope ps(K_COMPOSITE_BWD, st);
-		if (s.use_sa)
-			composite_backward_pixels_kernel<true><<<gx * gy, 256, 0, st>>>(
-				W, H, gx, (const uint2*)im.ranges, (const float4*)b.instances, b.hit_inst, b.hit_pix, b.pair_incl,
-				in.background, im.final_T, im.n_contrib, im.median_depth, im.depth_std, dL_dcolor, dL_dothers, slots,
-				rows, (uint32_t)(pairs > 0 ? pairs : 0), b.pair_counters + 3);
-		else
-			composite_backward_pixels_kernel<false><<<gx * gy, 256, 0, st>>>(
-				W, H, gx, (const uint2*)im.ranges, (const float4*)b.instances, b.hit_inst, b.hit_pix, b.pair_incl,
-				in.background, im.final_T, im.n_contrib, im.median_depth, im.depth_std, dL_dcolor, dL_dothers, slots,
-				rows, (uint32_t)(pairs > 0 ? pairs : 0), b.pair_counters + 3);
+		const uint32_t cap = (uint32_t)(pairs > 0 ? pairs : 0);
+		const int rc = s.use_sa
+			? launch_bwd_variant<true>(gx * gy, st, W, H, gx, (const uint2*)im.ranges, (const float4*)b.instances,
+			                           (const uint32_t*)b.hit_inst, (const uint32_t*)b.hit_pix, (const uint32_t*)b.pair_incl,
+			                           (const float*)in.background, (const float*)im.final_T, (const uint32_t*)im.n_contrib,
+			                           (const float*)im.median_depth, (const float*)im.depth_std, dL_dcolor, dL_dothers,
+			                           slots, rows, cap, b.pair_counters + 3)
+			: launch_bwd_variant<false>(gx * gy, st, W, H, gx, (const uint2*)im.ranges, (const float4*)b.instances,
+			                            (const uint32_t*)b.hit_inst, (const uint32_t*)b.hit_pix, (const uint32_t*)b.pair_incl,
+			                            (const float*)in.background, (const float*)im.final_T, (const uint32_t*)im.n_contrib,
+			                            (const float*)im.median_depth, (const float*)im.depth_std, dL_dcolor, dL_dothers,
+			                            slots, rows, cap, b.pair_counters + 3);
+		if (rc != GS2D_OK) return rc;
 		count_launch();
 	}
 	GS2D_CUDA_OK(cudaGetLastError());
