@@ -80,8 +80,8 @@ ImageState ImageState::carve(void* base, size_t W, size_t H, size_t* bytes)
 	im.median_depth = c.take<float>(px);
 	im.depth_std = c.take<float>(px);
 	im.ranges = c.take<uint32_t>(2 * tiles);
-	im.tile_count = c.take<uint32_t>(tiles);
-	im.tile_cursor = c.take<uint32_t>(tiles);
+	im.tile_count = c.take<uint32_t>(tiles * TC_STRIDE);
+	im.tile_cursor = c.take<uint32_t>(tiles * TC_STRIDE);
 	if (bytes) *bytes = c.total();
 	return im;
 }
@@ -235,7 +235,7 @@ int gs2d_forward_preprocess(const gs2d_settings* s, const gs2d_inputs* in, const
 	ImageState im = ImageState::carve(buffers->image, (size_t)s->image_width, (size_t)s->image_height, nullptr);
 	{
 		ProfScope ps(K_MEMSET, st);
-		GS2D_CUDA_OK(cudaMemsetAsync(im.tile_count, 0, sizeof(uint32_t) * tiles_of(s->image_width, s->image_height), st));
+		GS2D_CUDA_OK(cudaMemsetAsync(im.tile_count, 0, sizeof(uint32_t) * TC_STRIDE * tiles_of(s->image_width, s->image_height), st));
 	}
 	GS2D_TRY(launch_preprocess_forward(*s, *in, g, im.tile_count, radii, st));
 	GS2D_TRY(debug_sync(*s, st));

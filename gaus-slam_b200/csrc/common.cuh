@@ -55,6 +55,12 @@ struct Carver {
 // hit_pix holds, per tile, one word pair per 32 instances rounded up to whole compositing batches: HIT_PIX_PAD
 // spare words per tile cover the rounding for batches of up to 32 * HIT_PIX_PAD instances.
 constexpr int HIT_PIX_PAD = 8;
+// The per-tile instance counters / scatter cursors are hit by one atomic per instance (~250 per tile and frame).  L2
+// serialises atomics that fall into the same line, so every tile's word sits in a line of its own (TC_STRIDE words).
+#ifndef GS2D_TC_STRIDE
+#define GS2D_TC_STRIDE 32
+#endif
+constexpr int TC_STRIDE = GS2D_TC_STRIDE;
 constexpr int SCAN_THREADS = 256;
 #ifndef GS2D_SCAN_ITEMS
 #define GS2D_SCAN_ITEMS 8
@@ -92,8 +98,8 @@ struct ImageState {
 	float* median_depth;      // [H,W]
 	float* depth_std;         // [H,W]
 	uint32_t* ranges;         // [tiles,2]
-	uint32_t* tile_count;     // [tiles] instances per tile (counted by preprocess_forward; zeroed before it)
-	uint32_t* tile_cursor;    // [tiles] write cursor of the scatter (starts at the tile's range start)
+	uint32_t* tile_count;     // [tiles * TC_STRIDE] instances per tile at word t * TC_STRIDE (counted by preprocess_forward; zeroed before it)
+	uint32_t* tile_cursor;    // [tiles * TC_STRIDE] write cursor of the scatter at word t * TC_STRIDE (starts at the tile's range start)
 	static __host__ ImageState carve(void* base, size_t W, size_t H, size_t* bytes);
 };
 

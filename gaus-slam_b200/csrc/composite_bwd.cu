@@ -40,6 +40,9 @@ namespace {
 #ifndef GS2D_BWD_PREFETCH
 #define GS2D_BWD_PREFETCH 1
 #endif
+#ifndef GS2D_BWD_ROW128
+#define GS2D_BWD_ROW128 0
+#endif
 constexpr int BWD_BATCH = 128;                        // instances per TMA chunk
 // Instances resident at once ("super-batch").  352 keeps the kernel's shared memory under 56 KB (four CTAs per SM);
 // the tiles of the BASELINE mapping views hold 307 instances on average (p99 360): a denser tile takes a second round.
@@ -53,6 +56,8 @@ constexpr int BWD_WORDS = BWD_SUPER / 32;             // contribution words per 
 constexpr int BWD_PIX_BINS = 64;                      // pixel list lengths 0 .. 62, 63 = longer
 constexpr int BWD_INST_BINS = 16;                     // phase-B iterations of an instance 0 .. 14, 15 = more
 static_assert(BWD_BATCH / 32 <= HIT_PIX_PAD, "hit_pix padding");
+constexpr int BWD_PIX_SLOTS = TILE_PIXELS + 3 * TILE;
+__device__ __forceinline__ int pix_slot(int p) { return p + 3 * (p >> 4); }
 
 struct PixelConst {
 	float T_final, final_A, final_D, final_D2;
@@ -81,7 +86,11 @@ struct BwdSmem {
 	union {
 		uint32_t used[BWD_WORDS][TILE_PIXELS];    // phase A: per-pixel contribution words, column = row-major pixel id
 		struct {
-			float pix[6][TILE_PIXELS];            // phase B: dL_dpix (3), dL_dnormal (3) per pixel (row-major pixel id)
+			// phase B: the pixel's image gradients, dL_dpix (3) | dL_dnormal.x and dL_dnormal.yz, at index pix_slot(pixel):
+			// two vector loads per pair, and the padding keeps the pixels of one instance (neighbours in x and y, read by
+			// the lanes of one quarter-warp) in different banks
+			float4 pixa[BWD_PIX_SLOTS];
+			float2 pixb[BWD_PIX_SLOTS];
 			uint16_t ord[BWD_SUPER];              // phase B: instances of the super-batch, longest slot list first
 		} b;
 	};
@@ -150,7 +159,7 @@ __device__ __forceinline__ void pixel_step(const float4* __restrict__ rec, float
 // Phase B for one (instance, pixel) pair: the geometric chain (CR/backward.cu:343, :396, :412-460).
 // A = dL/dalpha, dz = dL/dz, w = alpha * T from phase A; adds the 18 per-instance terms into g.
 __device__ __forceinline__ void instance_step(const float4 r0, const float4 r1, const float4 r2, float pxf, float pyf,
-                                              float A, float dz, float w, const float* __restrict__ pixc, int pid,
+                                              float A, float dz, float w, const float4 pa, const float2 pb,
                                               float (&g)[24])
 {
 	PairFront f;
@@ -158,12 +167,12 @@ __device__ __forceinline__ void instance_step(const float4 r0, const float4 r1, 
 	pair_geom_fast(r0, r1, r2, pxf, pyf, f, inv_pz);
 	const float3 Tw = make_float3(r2.x, r2.y, r2.z);
 	const float opa = r2.w, G = f.G;
-	g[GR_COL + 0] += w * pixc[0 * TILE_PIXELS + pid];
-	g[GR_COL + 1] += w * pixc[1 * TILE_PIXELS + pid];
-	g[GR_COL + 2] += w * pixc[2 * TILE_PIXELS + pid];
-	g[GR_NRM + 0] += w * pixc[3 * TILE_PIXELS + pid];
-	g[GR_NRM + 1] += w * pixc[4 * TILE_PIXELS + pid];
-	g[GR_NRM + 2] += w * pixc[5 * TILE_PIXELS + pid];
+	g[GR_COL + 0] += w * pa.x;
+	g[GR_COL + 1] += w * pa.y;
+	g[GR_COL + 2] += w * pa.z;
+	g[GR_NRM + 0] += w * pa.w;
+	g[GR_NRM + 1] += w * pb.x;
+	g[GR_NRM + 2] += w * pb.y;
 	const float dL_dG = opa * A;
 	if (f.rho3d <= f.rho2d) {
 		const float dL_dsx = dL_dG * -G * f.s.x + dz * Tw.x;
@@ -450,8 +459,8 @@ composite_backward_pixels_kernel(int W, int H, unsigned gx, const uint2* __restr
 	}
 	__syncthreads();   // every slot of the tile's instances is written; the words are dead
 	// the pixel's gradient constants for phase B take the place of the words
-	sm.b.pix[0][o] = pc.dpix0; sm.b.pix[1][o] = pc.dpix1; sm.b.pix[2][o] = pc.dpix2;
-	sm.b.pix[3][o] = pc.dn0;   sm.b.pix[4][o] = pc.dn1;   sm.b.pix[5][o] = pc.dn2;
+	sm.b.pixa[pix_slot(o)] = make_float4(pc.dpix0, pc.dpix1, pc.dpix2, pc.dn0);
+	sm.b.pixb[pix_slot(o)] = make_float2(pc.dn1, pc.dn2);
 
 	// ---- phase B: a quarter-warp per instance, lanes over the instance's pair slots (just written by this CTA:
 	// L2-hot); pixel constants from shared memory; the record from shared memory when the whole tile is resident (one
@@ -540,15 +549,35 @@ composite_backward_pixels_kernel(int W, int H, unsigned gx, const uint2* __restr
 					const int p = __float_as_int(sl.w);
 					if (p >= 0)
 						instance_step(r0, r1, r2, (float)(tx * TILE + (p & 15)), (float)(ty * TILE + (p >> 4)), sl.x, sl.y,
-						              sl.z, &sm.b.pix[0][0], p, g);
+						              sl.z, sm.b.pixa[pix_slot(p)], sm.b.pixb[pix_slot(p)], g);
 				}
 			}
 			__syncwarp();
 			oct_reduce24(g, lane);
+			// lane L of a group holds row words 3L .. 3L+2; regroup so that lane M < 5 holds words 4M .. 4M+3 (word e
+			// sits in lane e / 3, slot e % 3; words 18, 19 are the zero padding of lane 6) and the row goes out as five
+			// 16-byte stores instead of eighteen 4-byte ones
+#if GS2D_BWD_ROW128
+			float4 out;
+			{
+				const int gbase = lane & ~7;
+				float v[4];
+#pragma unroll
+				for (int i = 0; i < 4; i++) {
+					const int slot = (i + gl) & 3;
+					const float send = slot == 0 ? g[0] : (slot == 1 ? g[1] : g[2]);
+					v[i] = __shfl_sync(0xffffffffu, send, gbase + min((4 * gl + i) / 3, 7));
+				}
+				out = make_float4(v[0], v[1], v[2], v[3]);
+			}
+			if (qi < cnt_sb && gl < 5)
+				reinterpret_cast<float4*>(grad_rows + (size_t)row * GRAD_WORDS)[gl] = out;
+#else
 			if (qi < cnt_sb && gl < 6) {
 				float* dst = grad_rows + (size_t)row * GRAD_WORDS + 3 * gl;
 				dst[0] = g[0]; dst[1] = g[1]; dst[2] = g[2];
 			}
+#endif
 		}
 	}
 #if GS2D_BWD_DISCARD

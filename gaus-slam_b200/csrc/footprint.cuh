@@ -22,94 +22,69 @@ __device__ __forceinline__ uint32_t span_bits(int xa, int xb, int lo, int hi)
 	return ((2u << xb) - 1u) & ~((1u << xa) - 1u);
 }
 
-// Quarter-warp cooperative: the 8 lanes of a group (gl = lane & 7) compute the 256-bit footprint mask of the
-// instance whose record is `rec` (in its tile at pixel origin (ox, oy)).  ALL 32 lanes of the warp must call it
-// (groups without an instance pass live = false).  Lane gl returns word gl of the mask (tile rows 2gl and 2gl+1:
-// the 32 pixels warp gl of a compositing CTA owns); `count` receives the number of set bits (all 8 lanes).
-__device__ __forceinline__ uint32_t footprint_word(bool live, const float4* rec, float ox, float oy,
-                                                   int lane, uint32_t& count)
+// One thread per instance: calls emit(row, bits) for every tile row by0 .. by1 of the instance's footprint box with
+// the row's 16-bit column mask (tile-local x), for the instance whose record is `rec`, in its tile at pixel origin
+// (ox, oy).  The row-independent part (the quadratic's leading coefficient, the expansion point) is evaluated once.
+template <typename Emit>
+__device__ __forceinline__ void footprint_rows(const float4* rec, float ox, float oy, Emit emit)
 {
-	const int gl = lane & 7;
-	uint32_t packed = 0;          // bits of row by0 + gl (low half) and of row by0 + gl + 8 (high half)
-	int by0 = 0, by1 = -1;
-	if (live) {
-		const float4 r0 = rec[0], r1 = rec[1], r2 = rec[2];
-		const uint32_t bw = __float_as_uint(rec[3].w);
-		const int bx0 = bw & 15, bx1 = (bw >> 8) & 15;
-		const float a255 = 255.0f * r2.w;
-		if (((bw >> 16) & 1u) && !(a255 * 1.001f < 1.0f)) {
-			by0 = (bw >> 4) & 15; by1 = (bw >> 12) & 15;
-			const uint32_t full = span_bits(bx0, bx1, 0, 15);                 // fallback: the whole box row
-			const bool nan_opacity = !(a255 == a255);   // NaN opacity: no culling
-			const float c = 2.0f * __logf(fmaxf(a255, 1.0f)) * FOOT_C_SCALE + FOOT_C_BIAS;
-			const float3 Tu = make_float3(r0.x, r0.y, r0.z), Tv = make_float3(r1.x, r1.y, r1.z),
-			             Tw = make_float3(r2.x, r2.y, r2.z);
-			// expansion point: the integer pixel nearest to the splat centre, clamped near the tile
-			const float xc = fminf(fmaxf(rintf(r0.w), ox - 64.f), ox + 80.f);
-			const float yc = fminf(fmaxf(rintf(r1.w), oy - 64.f), oy + 80.f);
-			const float3 k0 = make_float3(xc * Tw.x - Tu.x, xc * Tw.y - Tu.y, xc * Tw.z - Tu.z);
-			const float3 l0 = make_float3(yc * Tw.x - Tv.x, yc * Tw.y - Tv.y, yc * Tw.z - Tv.z);
-			const float3 g = cross3(k0, l0), A = cross3(Tw, l0), B = cross3(k0, Tw);
-			const float qa = A.x * A.x + A.y * A.y - c * A.z * A.z;
-			// scale-free conditioning test: qa must be clearly positive (an ellipse section along the row)
-			const float a2 = A.x * A.x + A.y * A.y;
-			const bool conic = !nan_opacity && qa > 1e-3f * a2 && qa == qa;
-			const float inv = 1.0f / qa;
-			const float off = xc - ox;   // u -> tile-local x
-			const float cx = r0.w - ox;
-#pragma unroll
-			for (int half = 0; half < 2; half++) {
-				const int row = by0 + gl + 8 * half;
-				if (row > by1) continue;
-				uint32_t bits = full;
-				const float yrow = oy + (float)row;
-				const float v = yrow - yc;
-				const float3 q = make_float3(g.x + v * B.x, g.y + v * B.y, g.z + v * B.z);
-				const float qb = q.x * A.x + q.y * A.y - c * q.z * A.z;
-				const float qc = q.x * q.x + q.y * q.y - c * q.z * q.z;
-				if (conic && qb == qb && qc == qc) {
-					const float disc = qb * qb - qa * qc;
-					uint32_t m = 0;
-					// widen the discriminant a little: roots of a nearly tangent row must not vanish
-					const float dpos = disc + 1e-4f * (qb * qb + fabsf(qa * qc));
-					if (dpos >= 0.0f) {
-						const float sq = sqrtf(dpos);
-						const float u1 = (-qb - sq) * inv, u2 = (-qb + sq) * inv;
-						if (u1 == u1 && u2 == u2 && fabsf(u1) < 1e6f && fabsf(u2) < 1e6f) {
-							const float slack = FOOT_MARGIN_PX + 1e-4f * (fabsf(u1) + fabsf(u2));
-							m = span_bits((int)ceilf(u1 + off - slack), (int)floorf(u2 + off + slack), bx0, bx1);
-						} else {
-							m = full;
-						}
-					}
-					// 2D low-pass filter disc around the stored centre: 100 * |d|^2 <= c
-					const float dy = r1.w - yrow;
-					const float r2d = 0.01f * c - dy * dy;
-					if (r2d >= 0.0f) {
-						const float h = sqrtf(r2d) + FOOT_MARGIN_PX;
-						m |= span_bits((int)ceilf(cx - h), (int)floorf(cx + h), bx0, bx1);
-					}
-					bits = m;
+	const float4 r0 = rec[0], r1 = rec[1], r2 = rec[2];
+	const uint32_t bw = __float_as_uint(rec[3].w);
+	const int bx0 = bw & 15, bx1 = (bw >> 8) & 15;
+	const float a255 = 255.0f * r2.w;
+	if (!(((bw >> 16) & 1u) && !(a255 * 1.001f < 1.0f))) return;
+	const int by0 = (bw >> 4) & 15, by1 = (bw >> 12) & 15;
+	const uint32_t full = span_bits(bx0, bx1, 0, 15);                 // fallback: the whole box row
+	const bool nan_opacity = !(a255 == a255);   // NaN opacity: no culling
+	const float c = 2.0f * __logf(fmaxf(a255, 1.0f)) * FOOT_C_SCALE + FOOT_C_BIAS;
+	const float3 Tu = make_float3(r0.x, r0.y, r0.z), Tv = make_float3(r1.x, r1.y, r1.z),
+	             Tw = make_float3(r2.x, r2.y, r2.z);
+	// expansion point: the integer pixel nearest to the splat centre, clamped near the tile
+	const float xc = fminf(fmaxf(rintf(r0.w), ox - 64.f), ox + 80.f);
+	const float yc = fminf(fmaxf(rintf(r1.w), oy - 64.f), oy + 80.f);
+	const float3 k0 = make_float3(xc * Tw.x - Tu.x, xc * Tw.y - Tu.y, xc * Tw.z - Tu.z);
+	const float3 l0 = make_float3(yc * Tw.x - Tv.x, yc * Tw.y - Tv.y, yc * Tw.z - Tv.z);
+	const float3 g = cross3(k0, l0), A = cross3(Tw, l0), B = cross3(k0, Tw);
+	const float qa = A.x * A.x + A.y * A.y - c * A.z * A.z;
+	// scale-free conditioning test: qa must be clearly positive (an ellipse section along the row)
+	const float a2 = A.x * A.x + A.y * A.y;
+	const bool conic = !nan_opacity && qa > 1e-3f * a2 && qa == qa;
+	const float inv = 1.0f / qa;
+	const float off = xc - ox;   // u -> tile-local x
+	const float cx = r0.w - ox;
+	for (int row = by0; row <= by1; row++) {
+		uint32_t bits = full;
+		const float yrow = oy + (float)row;
+		const float v = yrow - yc;
+		const float3 q = make_float3(g.x + v * B.x, g.y + v * B.y, g.z + v * B.z);
+		const float qb = q.x * A.x + q.y * A.y - c * q.z * A.z;
+		const float qc = q.x * q.x + q.y * q.y - c * q.z * q.z;
+		if (conic && qb == qb && qc == qc) {
+			const float disc = qb * qb - qa * qc;
+			uint32_t m = 0;
+			// widen the discriminant a little: roots of a nearly tangent row must not vanish
+			const float dpos = disc + 1e-4f * (qb * qb + fabsf(qa * qc));
+			if (dpos >= 0.0f) {
+				const float sq = sqrtf(dpos);
+				const float u1 = (-qb - sq) * inv, u2 = (-qb + sq) * inv;
+				if (u1 == u1 && u2 == u2 && fabsf(u1) < 1e6f && fabsf(u2) < 1e6f) {
+					const float slack = FOOT_MARGIN_PX + 1e-4f * (fabsf(u1) + fabsf(u2));
+					m = span_bits((int)ceilf(u1 + off - slack), (int)floorf(u2 + off + slack), bx0, bx1);
+				} else {
+					m = full;
 				}
-				packed |= bits << (16 * half);
 			}
+			// 2D low-pass filter disc around the stored centre: 100 * |d|^2 <= c
+			const float dy = r1.w - yrow;
+			const float r2d = 0.01f * c - dy * dy;
+			if (r2d >= 0.0f) {
+				const float h = sqrtf(r2d) + FOOT_MARGIN_PX;
+				m |= span_bits((int)ceilf(cx - h), (int)floorf(cx + h), bx0, bx1);
+			}
+			bits = m;
 		}
+		emit(row, bits);
 	}
-	// lane l of the group emits word l of the instance's mask: tile rows 2l (low half) and 2l + 1 (high half);
-	// row r was computed by lane (r - by0) & 7 of the group, in half (r - by0) >> 3
-	const int gbase = lane & ~7;
-	const int da = 2 * gl - by0, db = da + 1;
-	const uint32_t pa = __shfl_sync(0xffffffffu, packed, gbase + (da & 7));
-	const uint32_t pb = __shfl_sync(0xffffffffu, packed, gbase + (db & 7));
-	const int span = by1 - by0;
-	const uint32_t ra = (da >= 0 && da <= span) ? ((pa >> (da & 8 ? 16 : 0)) & 0xffffu) : 0u;
-	const uint32_t rb = (db >= 0 && db <= span) ? ((pb >> (db & 8 ? 16 : 0)) & 0xffffu) : 0u;
-	uint32_t cnt = __popc(packed);
-	cnt += __shfl_xor_sync(0xffffffffu, cnt, 4);
-	cnt += __shfl_xor_sync(0xffffffffu, cnt, 2);
-	cnt += __shfl_xor_sync(0xffffffffu, cnt, 1);
-	count = cnt;
-	return ra | (rb << 16);
 }
 
 }  // namespace gs2d

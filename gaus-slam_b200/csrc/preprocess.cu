@@ -182,7 +182,7 @@ preprocess_forward_kernel(int P, int D, int M,
 	// instances per tile, for the tile-local sort (tile_sort.cu): one RED per instance
 	if (tile_count)
 		for (unsigned y = rmin.y; y < rmax.y; y++)
-			for (unsigned x = rmin.x; x < rmax.x; x++) atomicAdd(&tile_count[y * gx + x], 1u);
+			for (unsigned x = rmin.x; x < rmax.x; x++) atomicAdd(&tile_count[(size_t)(y * gx + x) * TC_STRIDE], 1u);
 }
 
 // ---- inclusive scan of tiles_touched: single pass, decoupled look-back -----------------------
@@ -198,7 +198,7 @@ __device__ void side_scan_block(int side_n, const uint32_t* __restrict__ cnt, ui
 	uint32_t carry = 0;
 	for (int base = 0; base < side_n; base += SCAN_THREADS) {
 		const int i = base + tid;
-		const uint32_t v = i < side_n ? cnt[i] : 0u;
+		const uint32_t v = i < side_n ? cnt[(size_t)i * TC_STRIDE] : 0u;
 		uint32_t incl = v;
 #pragma unroll
 		for (int o = 1; o < 32; o <<= 1) {
@@ -218,7 +218,7 @@ __device__ void side_scan_block(int side_n, const uint32_t* __restrict__ cnt, ui
 		const uint32_t start = carry + woff + incl - v;
 		if (i < side_n) {
 			ranges[i] = v ? make_uint2(start, start + v) : make_uint2(0u, 0u);
-			cursor[i] = start;
+			cursor[(size_t)i * TC_STRIDE] = start;
 		}
 		carry += total;
 	}

@@ -52,7 +52,7 @@ scatter_kernel(int P, unsigned gx, const float* __restrict__ depths, const ushor
 			const unsigned e = e0 + k;
 			if (e < cnt) {
 				const unsigned yy = e / w;
-				slot[k] = atomicAdd(&cursor[(r.y + yy) * gx + r.x + (e - yy * w)], 1u);
+				slot[k] = atomicAdd(&cursor[(size_t)((r.y + yy) * gx + r.x + (e - yy * w)) * TC_STRIDE], 1u);
 			}
 		}
 #pragma unroll
@@ -61,7 +61,7 @@ scatter_kernel(int P, unsigned gx, const float* __restrict__ depths, const ushor
 	}
 #else
 	for (unsigned y = r.y; y < r.w; y++)
-		for (unsigned x = r.x; x < r.z; x++) pairs[atomicAdd(&cursor[y * gx + x], 1u)] = word;
+		for (unsigned x = r.x; x < r.z; x++) pairs[atomicAdd(&cursor[(size_t)(y * gx + x) * TC_STRIDE], 1u)] = word;
 #endif
 }
 
@@ -164,7 +164,7 @@ tile_sort_kernel(int W, int H, unsigned gx, const uint2* __restrict__ ranges, ui
                  uint32_t* __restrict__ zero_words, int n_zero_words)
 {
 	__shared__ uint64_t s_keys[TS_CAP];
-	const int tid = threadIdx.x, lane = tid & 31;
+	const int tid = threadIdx.x;
 	const unsigned tile = blockIdx.x;
 	// status words + counters of the pair-count scan that follows (instead of a memset launch)
 	if (tile == 0)
@@ -208,18 +208,31 @@ tile_sort_kernel(int W, int H, unsigned gx, const uint2* __restrict__ ranges, ui
 		}
 		tile_rec[t] = v;
 	}
-	__syncthreads();   // the records just written are read back below (same CTA)
-	// footprints: a quarter-warp per instance
+	__syncthreads();   // the records just written are read back below (same CTA); the sorted keys are dead
+	// Footprints: a thread per instance walks the rows of the instance's box (the row-independent half of the closed
+	// form is evaluated once per instance, not once per lane of a quarter-warp).  A thread ORs its rows into its own 8
+	// words in shared memory (stride 9: conflict-free for the owners and for the coalesced copy-out that follows).
+	uint32_t* s_words = reinterpret_cast<uint32_t*>(s_keys);
+	static_assert(sizeof(uint64_t) * TS_CAP >= sizeof(uint32_t) * 256 * 9, "footprint words alias the sorted keys");
 	const float ox = (float)(tx * TILE), oy = (float)(ty * TILE);
-	for (int q0 = 0; q0 < n; q0 += 32) {
-		const int k = q0 + (tid >> 3);
-		const bool live = k < n;
-		uint32_t cnt;
-		const uint32_t word = footprint_word(live, tile_rec + 5 * (size_t)(live ? k : 0), ox, oy, lane, cnt);
-		if (live) {
-			hit_words[8 * ((size_t)range.x + k) + (lane & 7)] = word;
-			if ((lane & 7) == 0) hit_count[range.x + k] = cnt;
+	for (int q0 = 0; q0 < n; q0 += 256) {
+		const int k = q0 + tid;
+		uint32_t* mine = s_words + 9 * tid;
+#pragma unroll
+		for (int w = 0; w < 8; w++) mine[w] = 0u;
+		if (k < n) {
+			uint32_t cnt = 0;
+			footprint_rows(tile_rec + 5 * (size_t)k, ox, oy, [&](int row, uint32_t bits) {
+				mine[row >> 1] |= bits << (16 * (row & 1));
+				cnt += __popc(bits);
+			});
+			hit_count[range.x + k] = cnt;
 		}
+		__syncthreads();
+		const int words = 8 * min(n - q0, 256);
+		uint32_t* dst = hit_words + 8 * ((size_t)range.x + q0);
+		for (int e = tid; e < words; e += 256) dst[e] = s_words[9 * (e >> 3) + (e & 7)];
+		__syncthreads();
 	}
 }
 
