@@ -40,6 +40,14 @@ namespace {
 #ifndef GS2D_BWD_PREFETCH
 #define GS2D_BWD_PREFETCH 1
 #endif
+#ifndef GS2D_BWD_SLOT_CG
+#define GS2D_BWD_SLOT_CG 0
+#endif
+#if GS2D_BWD_SLOT_CG
+#define SLOT_LD(p) __ldcg(p)
+#else
+#define SLOT_LD(p) (*(p))
+#endif
 #ifndef GS2D_BWD_ROW128
 #define GS2D_BWD_ROW128 0
 #endif
@@ -54,7 +62,7 @@ static_assert(BWD_SUPER % 32 == 0, "super-batches start at a word boundary of th
 constexpr int BWD_CHUNKS = (BWD_SUPER + BWD_BATCH - 1) / BWD_BATCH;
 constexpr int BWD_WORDS = BWD_SUPER / 32;             // contribution words per pixel per super-batch
 constexpr int BWD_PIX_BINS = 64;                      // pixel list lengths 0 .. 62, 63 = longer
-constexpr int BWD_INST_BINS = 16;                     // phase-B iterations of an instance 0 .. 14, 15 = more
+constexpr int BWD_INST_BINS = 32;                     // phase-B iterations of an instance 0 .. 30, 31 = more
 static_assert(BWD_BATCH / 32 <= HIT_PIX_PAD, "hit_pix padding");
 constexpr int BWD_PIX_SLOTS = TILE_PIXELS + 3 * TILE;
 __device__ __forceinline__ int pix_slot(int p) { return p + 3 * (p >> 4); }
@@ -156,6 +164,16 @@ __device__ __forceinline__ void pixel_step(const float4* __restrict__ rec, float
 	w_out = w;
 }
 
+// Lanes per instance in phase B (8 or 4).  With 4 lanes the 20 row words are reduce-scattered to 5 per lane; GP maps row
+// word w to its position in the accumulator array so that lane L ends up with words 4L .. 4L+3 (one 16-byte store) and
+// word 16 + L.  With 8 lanes GP is the identity.
+#ifndef GS2D_BWD_GRP
+#define GS2D_BWD_GRP 4
+#endif
+constexpr int BWD_GRP = GS2D_BWD_GRP;
+static_assert(BWD_GRP == 8 || BWD_GRP == 4, "phase B: a quarter or an eighth of a warp per instance");
+__host__ __device__ constexpr int GP(int w) { return BWD_GRP == 8 ? w : (w < 16 ? 5 * (w / 4) + (w % 4) : 5 * (w - 16) + 4); }
+
 // Phase B for one (instance, pixel) pair: the geometric chain (CR/backward.cu:343, :396, :412-460).
 // A = dL/dalpha, dz = dL/dz, w = alpha * T from phase A; adds the 18 per-instance terms into g.
 __device__ __forceinline__ void instance_step(const float4 r0, const float4 r1, const float4 r2, float pxf, float pyf,
@@ -167,12 +185,12 @@ __device__ __forceinline__ void instance_step(const float4 r0, const float4 r1, 
 	pair_geom_fast(r0, r1, r2, pxf, pyf, f, inv_pz);
 	const float3 Tw = make_float3(r2.x, r2.y, r2.z);
 	const float opa = r2.w, G = f.G;
-	g[GR_COL + 0] += w * pa.x;
-	g[GR_COL + 1] += w * pa.y;
-	g[GR_COL + 2] += w * pa.z;
-	g[GR_NRM + 0] += w * pa.w;
-	g[GR_NRM + 1] += w * pb.x;
-	g[GR_NRM + 2] += w * pb.y;
+	g[GP(GR_COL + 0)] += w * pa.x;
+	g[GP(GR_COL + 1)] += w * pa.y;
+	g[GP(GR_COL + 2)] += w * pa.z;
+	g[GP(GR_NRM + 0)] += w * pa.w;
+	g[GP(GR_NRM + 1)] += w * pb.x;
+	g[GP(GR_NRM + 2)] += w * pb.y;
 	const float dL_dG = opa * A;
 	if (f.rho3d <= f.rho2d) {
 		const float dL_dsx = dL_dG * -G * f.s.x + dz * Tw.x;
@@ -185,17 +203,17 @@ __device__ __forceinline__ void instance_step(const float4 r0, const float4 r1, 
 		                                 l.x * dL_dp.y - l.y * dL_dp.x);
 		const float3 dL_dl = make_float3(dL_dp.y * k.z - dL_dp.z * k.y, dL_dp.z * k.x - dL_dp.x * k.z,
 		                                 dL_dp.x * k.y - dL_dp.y * k.x);
-		g[0] += -dL_dk.x; g[1] += -dL_dk.y; g[2] += -dL_dk.z;
-		g[3] += -dL_dl.x; g[4] += -dL_dl.y; g[5] += -dL_dl.z;
-		g[6] += pxf * dL_dk.x + pyf * dL_dl.x + dz * f.s.x;
-		g[7] += pxf * dL_dk.y + pyf * dL_dl.y + dz * f.s.y;
-		g[8] += pxf * dL_dk.z + pyf * dL_dl.z + dz * 1.0f;
+		g[GP(0)] += -dL_dk.x; g[GP(1)] += -dL_dk.y; g[GP(2)] += -dL_dk.z;
+		g[GP(3)] += -dL_dl.x; g[GP(4)] += -dL_dl.y; g[GP(5)] += -dL_dl.z;
+		g[GP(6)] += pxf * dL_dk.x + pyf * dL_dl.x + dz * f.s.x;
+		g[GP(7)] += pxf * dL_dk.y + pyf * dL_dl.y + dz * f.s.y;
+		g[GP(8)] += pxf * dL_dk.z + pyf * dL_dl.z + dz * 1.0f;
 	} else {
-		g[8] += dz;
-		g[GR_M2D + 0] += dL_dG * (-G * GS2D_FILTER_INV_SQUARE * f.d.x);
-		g[GR_M2D + 1] += dL_dG * (-G * GS2D_FILTER_INV_SQUARE * f.d.y);
+		g[GP(8)] += dz;
+		g[GP(GR_M2D + 0)] += dL_dG * (-G * GS2D_FILTER_INV_SQUARE * f.d.x);
+		g[GP(GR_M2D + 1)] += dL_dG * (-G * GS2D_FILTER_INV_SQUARE * f.d.y);
 	}
-	g[GR_OPA] += G * A;
+	g[GP(GR_OPA)] += G * A;
 }
 
 // Sum g[0..17] over the 8 lanes of each quarter-warp (reduce-scatter: 12 + 6 + 3 shuffles for four instances
@@ -227,6 +245,30 @@ __device__ __forceinline__ void oct_reduce24(float (&g)[24], int lane)
 		for (int i = 0; i < 3; i++) {
 			const float send = up ? g[i] : g[i + 3];
 			const float keep = up ? g[i + 3] : g[i];
+			g[i] = keep + __shfl_xor_sync(0xffffffffu, send, 1);
+		}
+	}
+}
+
+// Four lanes per instance: sum g[0..19] over the 4 lanes of each group (reduce-scatter: 10 + 5 shuffles for eight
+// instances at once); on return lane L of a group (L = lane & 3) holds the totals of positions 5L .. 5L+4 in g[0..4].
+__device__ __forceinline__ void quad_reduce20(float (&g)[24], int lane)
+{
+	{
+		const bool up = lane & 2;
+#pragma unroll
+		for (int i = 0; i < 10; i++) {
+			const float send = up ? g[i] : g[i + 10];
+			const float keep = up ? g[i + 10] : g[i];
+			g[i] = keep + __shfl_xor_sync(0xffffffffu, send, 2);
+		}
+	}
+	{
+		const bool up = lane & 1;
+#pragma unroll
+		for (int i = 0; i < 5; i++) {
+			const float send = up ? g[i] : g[i + 5];
+			const float keep = up ? g[i + 5] : g[i];
 			g[i] = keep + __shfl_xor_sync(0xffffffffu, send, 1);
 		}
 	}
@@ -452,7 +494,11 @@ composite_backward_pixels_kernel(int W, int H, unsigned gx, const uint2* __restr
 					float4* dst = slot_of(j, oword, o_lt);
 					float A, dz, w;
 					pixel_step<USE_SA>(recs + j * 5, pxf, pyf, (uint32_t)(first + j), pc, st, A, dz, w);
+#if GS2D_BWD_SLOT_CG
+					__stcg(dst, make_float4(A, dz, w, __int_as_float(o)));   // L2 only: phase B of this CTA reads it back once
+#else
 					*dst = make_float4(A, dz, w, __int_as_float(o));
+#endif
 				}
 			}
 		}
@@ -488,7 +534,7 @@ composite_backward_pixels_kernel(int W, int H, unsigned gx, const uint2* __restr
 				int c = BWD_INST_BINS;      // beyond the list: a class of its own
 				if (i < cnt_sb) {
 					const uint32_t cnt = sm.base[i + 1] - sm.base[i];
-					c = (BWD_INST_BINS - 1) - (int)min((cnt + 7u) >> 3, (uint32_t)(BWD_INST_BINS - 1));
+					c = (BWD_INST_BINS - 1) - (int)min((cnt + (uint32_t)(BWD_GRP - 1)) / (uint32_t)BWD_GRP, (uint32_t)(BWD_INST_BINS - 1));
 				}
 				const uint32_t peers = __match_any_sync(0xffffffffu, c);
 				const int leader = __ffs(peers) - 1;
@@ -515,8 +561,8 @@ composite_backward_pixels_kernel(int W, int H, unsigned gx, const uint2* __restr
 				if (cls[r] < BWD_INST_BINS) sm.b.ord[sm.bins[cls[r]] + rnk[r]] = (uint16_t)(r * 256 + tid);
 			__syncthreads();
 		}
-		const int grp = tid >> 3, gl = tid & 7;
-		for (int q0 = 0; q0 < cnt_sb; q0 += 32) {
+		const int grp = tid / BWD_GRP, gl = tid % BWD_GRP;
+		for (int q0 = 0; q0 < cnt_sb; q0 += 256 / BWD_GRP) {
 			const int qi = q0 + grp;
 			float g[24];
 #pragma unroll
@@ -537,14 +583,14 @@ composite_backward_pixels_kernel(int W, int H, unsigned gx, const uint2* __restr
 				const uint32_t s0 = sm.base[q], s1 = sm.base[q + 1];
 #if GS2D_BWD_PREFETCH
 				// the next slot is requested before the current one is worked on (phase B waits on L2 otherwise)
-				float4 nx = (s0 + gl < s1) ? slots[s0 + gl] : make_float4(0.f, 0.f, 0.f, __int_as_float(-1));
+				float4 nx = (s0 + gl < s1) ? SLOT_LD(slots + s0 + gl) : make_float4(0.f, 0.f, 0.f, __int_as_float(-1));
 #endif
-				for (uint32_t k = s0 + gl; k < s1; k += 8) {
+				for (uint32_t k = s0 + gl; k < s1; k += BWD_GRP) {
 #if GS2D_BWD_PREFETCH
 					const float4 sl = nx;
-					if (k + 8 < s1) nx = slots[k + 8];
+					if (k + BWD_GRP < s1) nx = SLOT_LD(slots + k + BWD_GRP);
 #else
-					const float4 sl = slots[k];
+					const float4 sl = SLOT_LD(slots + k);
 #endif
 					const int p = __float_as_int(sl.w);
 					if (p >= 0)
@@ -553,6 +599,14 @@ composite_backward_pixels_kernel(int W, int H, unsigned gx, const uint2* __restr
 				}
 			}
 			__syncwarp();
+#if GS2D_BWD_GRP == 4
+			quad_reduce20(g, lane);
+			if (qi < cnt_sb) {
+				float* dst = grad_rows + (size_t)row * GRAD_WORDS;
+				reinterpret_cast<float4*>(dst)[gl] = make_float4(g[0], g[1], g[2], g[3]);
+				dst[16 + gl] = g[4];
+			}
+#else
 			oct_reduce24(g, lane);
 			// lane L of a group holds row words 3L .. 3L+2; regroup so that lane M < 5 holds words 4M .. 4M+3 (word e
 			// sits in lane e / 3, slot e % 3; words 18, 19 are the zero padding of lane 6) and the row goes out as five
@@ -577,6 +631,7 @@ composite_backward_pixels_kernel(int W, int H, unsigned gx, const uint2* __restr
 				float* dst = grad_rows + (size_t)row * GRAD_WORDS + 3 * gl;
 				dst[0] = g[0]; dst[1] = g[1]; dst[2] = g[2];
 			}
+#endif
 #endif
 		}
 	}

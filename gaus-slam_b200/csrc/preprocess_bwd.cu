@@ -110,8 +110,11 @@ inline void mc_red4(float* mc, float4 v) { mc[0] += v.x; mc[1] += v.y; mc[2] += 
 // that was zeroed beforehand (mc_flat = its multicast address): the all-reduce of the view-sharded mapping step
 // happens in this kernel's epilogue, tile of surfels by tile of surfels, instead of in a pass of its own.  Surfels
 // that are not visible in this rank's view add nothing.
+#ifndef GS2D_PBWD_MIN_BLOCKS
+#define GS2D_PBWD_MIN_BLOCKS 4
+#endif
 template <bool REDUCE>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, GS2D_PBWD_MIN_BLOCKS)
 preprocess_backward_kernel(int P, int D, int M,
 	const float3* __restrict__ means3D, const int* __restrict__ radii, const float* __restrict__ shs,
 	const uint8_t* __restrict__ clamped, const float2* __restrict__ scales,
