@@ -19,6 +19,7 @@
 #include "common.cuh"
 
 #include <cfloat>
+#include <initializer_list>
 
 namespace gs2d {
 
@@ -68,6 +69,68 @@ __device__ __forceinline__ LossPixel load_pixel(size_t p, size_t HW, const float
 
 constexpr int LOSS_THREADS = 256;
 
+// Four consecutive pixels at once (128-bit loads of every plane): HW % 4 == 0 and 16-byte aligned planes.
+struct Quad {
+	float v[4];
+};
+__device__ __forceinline__ Quad ldq(const float* __restrict__ p)
+{
+	const float4 t = *reinterpret_cast<const float4*>(p);
+	Quad q;
+	q.v[0] = t.x; q.v[1] = t.y; q.v[2] = t.z; q.v[3] = t.w;
+	return q;
+}
+__device__ __forceinline__ void stq(float* __restrict__ p, const float (&v)[4])
+{
+	*reinterpret_cast<float4*>(p) = make_float4(v[0], v[1], v[2], v[3]);
+}
+// the same pixel record as load_pixel(), for pixel i of a quad whose planes were loaded with ldq()
+__device__ __forceinline__ LossPixel quad_pixel(int i, const Quad (&c)[3], const Quad (&gcq)[3], const Quad& gdq,
+                                                const Quad& Dq, const Quad& Aq, const Quad& Rq, int gt_hwc, float eps,
+                                                float near_, float far_, float silmask_th)
+{
+	LossPixel px;
+#pragma unroll
+	for (int k = 0; k < 3; k++) {
+		px.c[k] = nan_to_num00(c[k].v[i], px.c_ok[k]);
+		// HWC: the quad's 12 colour values are consecutive: pixel i, channel k sits at 3 i + k
+		px.gc[k] = gt_hwc ? gcq[(3 * i + k) >> 2].v[(3 * i + k) & 3] : gcq[k].v[i];
+	}
+	px.gd = gdq.v[i];
+	const float D = Dq.v[i], A = Aq.v[i];
+	px.inv_a = 1.0f / (A + eps);
+	float d = D * px.inv_a;
+	const bool outlier = (d > far_) || (d < near_);
+	if (outlier) d = 0.f;
+	bool d_ok;
+	d = nan_to_num00(d, d_ok);
+	px.depth = d;
+	px.dist = nan_to_num00(Rq.v[i], px.dist_ok);
+	px.mask = (px.gd > 1e-5f) && (d > 1e-5f);
+	if (silmask_th >= 0.f) px.mask = px.mask && isfinite(A) && (A > silmask_th);
+	return px;
+}
+struct QuadIn {
+	Quad c[3], gc[3], gd, D, A, R;
+};
+__device__ __forceinline__ QuadIn load_quad(size_t p, size_t HW, const float* __restrict__ color,
+                                            const float* __restrict__ allmap, const float* __restrict__ gt_color,
+                                            const float* __restrict__ gt_depth, int gt_hwc)
+{
+	QuadIn q;
+#pragma unroll
+	for (int k = 0; k < 3; k++) {
+		q.c[k] = ldq(color + k * HW + p);
+		q.gc[k] = gt_hwc ? ldq(gt_color + 3 * p + 4 * k) : ldq(gt_color + k * HW + p);
+	}
+	q.gd = ldq(gt_depth + p);
+	q.D = ldq(allmap + p);
+	q.A = ldq(allmap + HW + p);
+	q.R = ldq(allmap + 6 * HW + p);
+	return q;
+}
+
+template <bool VEC>
 __global__ void __launch_bounds__(LOSS_THREADS)
 mapping_loss_forward_kernel(size_t HW, const float* __restrict__ color, const float* __restrict__ allmap,
                             const float* __restrict__ gt_color, const float* __restrict__ gt_depth, int gt_hwc,
@@ -76,8 +139,24 @@ mapping_loss_forward_kernel(size_t HW, const float* __restrict__ color, const fl
                             float* __restrict__ partials, uint32_t* __restrict__ ticket, float* __restrict__ state)
 {
 	float cnt = 0.f, sc = 0.f, sd = 0.f, sr = 0.f;
+	const float sil = tracking ? silmask_th : -1.f;
+	if (VEC) {
+		for (size_t p = 4 * ((size_t)blockIdx.x * LOSS_THREADS + threadIdx.x); p < HW; p += 4 * (size_t)gridDim.x * LOSS_THREADS) {
+			const QuadIn q = load_quad(p, HW, color, allmap, gt_color, gt_depth, gt_hwc);
+#pragma unroll
+			for (int i = 0; i < 4; i++) {
+				const LossPixel px = quad_pixel(i, q.c, q.gc, q.gd, q.D, q.A, q.R, gt_hwc, eps, near_, far_, sil);
+				if (px.mask) {
+					cnt += 1.f;
+					sc += fabsf(px.c[0] - px.gc[0]) + fabsf(px.c[1] - px.gc[1]) + fabsf(px.c[2] - px.gc[2]);
+					sd += fabsf(px.depth - px.gd);
+					sr += px.dist;
+				}
+			}
+		}
+	} else
 	for (size_t p = (size_t)blockIdx.x * LOSS_THREADS + threadIdx.x; p < HW; p += (size_t)gridDim.x * LOSS_THREADS) {
-		const LossPixel px = load_pixel(p, HW, color, allmap, gt_color, gt_depth, gt_hwc, eps, near_, far_, tracking ? silmask_th : -1.f);
+		const LossPixel px = load_pixel(p, HW, color, allmap, gt_color, gt_depth, gt_hwc, eps, near_, far_, sil);
 		if (px.mask) {
 			cnt += 1.f;
 			sc += fabsf(px.c[0] - px.gc[0]) + fabsf(px.c[1] - px.gc[1]) + fabsf(px.c[2] - px.gc[2]);
@@ -141,6 +220,7 @@ mapping_loss_forward_kernel(size_t HW, const float* __restrict__ color, const fl
 	}
 }
 
+template <bool VEC>
 __global__ void __launch_bounds__(LOSS_THREADS)
 mapping_loss_backward_kernel(size_t HW, const float* __restrict__ color, const float* __restrict__ allmap,
                              const float* __restrict__ gt_color, const float* __restrict__ gt_depth, int gt_hwc,
@@ -154,9 +234,11 @@ mapping_loss_backward_kernel(size_t HW, const float* __restrict__ color, const f
 	const float gc = tracking ? g * w_color : (n > 0.f ? g * w_color / (3.0f * n) : 0.f);
 	const float gd = tracking ? g * w_depth : (n > 0.f ? g * w_depth / n : 0.f);
 	const float gr = tracking ? 0.f : (n > 0.f ? g * w_dist / n : 0.f);
-	for (size_t p = (size_t)blockIdx.x * LOSS_THREADS + threadIdx.x; p < HW; p += (size_t)gridDim.x * LOSS_THREADS) {
-		const LossPixel px = load_pixel(p, HW, color, allmap, gt_color, gt_depth, gt_hwc, eps, near_, far_, tracking ? silmask_th : -1.f);
-		float dc[3] = {0.f, 0.f, 0.f}, dD = 0.f, dA = 0.f, dR = 0.f;
+	const float sil = tracking ? silmask_th : -1.f;
+	// per-pixel gradients of one pixel record: (dc[3], dD, dA, dR)
+	auto pixel_grads = [&](const LossPixel& px, float (&dc)[3], float& dD, float& dA, float& dR) {
+		dc[0] = dc[1] = dc[2] = 0.f;
+		dD = dA = dR = 0.f;
 		if (px.mask) {
 #pragma unroll
 			for (int k = 0; k < 3; k++) {
@@ -169,6 +251,30 @@ mapping_loss_backward_kernel(size_t HW, const float* __restrict__ color, const f
 			dA = -dd * px.depth * px.inv_a;
 			dR = px.dist_ok ? gr : 0.f;
 		}
+	};
+	if (VEC) {
+		const float zero[4] = {0.f, 0.f, 0.f, 0.f};
+		for (size_t p = 4 * ((size_t)blockIdx.x * LOSS_THREADS + threadIdx.x); p < HW; p += 4 * (size_t)gridDim.x * LOSS_THREADS) {
+			const QuadIn q = load_quad(p, HW, color, allmap, gt_color, gt_depth, gt_hwc);
+			float o_c[3][4], o_D[4], o_A[4], o_R[4];
+#pragma unroll
+			for (int i = 0; i < 4; i++) {
+				const LossPixel px = quad_pixel(i, q.c, q.gc, q.gd, q.D, q.A, q.R, gt_hwc, eps, near_, far_, sil);
+				float dc[3];
+				pixel_grads(px, dc, o_D[i], o_A[i], o_R[i]);
+				o_c[0][i] = dc[0]; o_c[1][i] = dc[1]; o_c[2][i] = dc[2];
+			}
+			stq(dL_dcolor + p, o_c[0]); stq(dL_dcolor + HW + p, o_c[1]); stq(dL_dcolor + 2 * HW + p, o_c[2]);
+			stq(dL_dallmap + p, o_D); stq(dL_dallmap + HW + p, o_A);
+			stq(dL_dallmap + 2 * HW + p, zero); stq(dL_dallmap + 3 * HW + p, zero); stq(dL_dallmap + 4 * HW + p, zero);
+			stq(dL_dallmap + 5 * HW + p, zero); stq(dL_dallmap + 6 * HW + p, o_R);
+		}
+		return;
+	}
+	for (size_t p = (size_t)blockIdx.x * LOSS_THREADS + threadIdx.x; p < HW; p += (size_t)gridDim.x * LOSS_THREADS) {
+		const LossPixel px = load_pixel(p, HW, color, allmap, gt_color, gt_depth, gt_hwc, eps, near_, far_, sil);
+		float dc[3], dD, dA, dR;
+		pixel_grads(px, dc, dD, dA, dR);
 		dL_dcolor[p] = dc[0]; dL_dcolor[HW + p] = dc[1]; dL_dcolor[2 * HW + p] = dc[2];
 		dL_dallmap[p] = dD; dL_dallmap[HW + p] = dA;
 		dL_dallmap[2 * HW + p] = 0.f; dL_dallmap[3 * HW + p] = 0.f; dL_dallmap[4 * HW + p] = 0.f;
@@ -176,9 +282,18 @@ mapping_loss_backward_kernel(size_t HW, const float* __restrict__ color, const f
 	}
 }
 
-inline int loss_blocks(size_t HW)
+inline bool loss_vec_ok(size_t HW, std::initializer_list<const void*> ptrs)
 {
-	const size_t want = (HW + LOSS_THREADS - 1) / LOSS_THREADS;
+	if (HW & 3) return false;
+	for (const void* q : ptrs)
+		if ((uintptr_t)q & 15) return false;
+	return true;
+}
+
+inline int loss_blocks(size_t HW, bool vec)
+{
+	const size_t items = vec ? HW / 4 : HW;
+	const size_t want = (items + LOSS_THREADS - 1) / LOSS_THREADS;
 	const size_t cap = 148 * 8;   // one wave of 8 CTAs per SM
 	return (int)(want < cap ? (want ? want : 1) : cap);
 }
@@ -217,9 +332,16 @@ int gs2d_mapping_loss_forward(int32_t W, int32_t H, const float* color, const fl
 	const size_t HW = (size_t)W * H;
 	{
 		ProfScope ps(K_LOSS, st);
-		mapping_loss_forward_kernel<<<loss_blocks(HW), LOSS_THREADS, 0, st>>>(
-			HW, color, allmap, gt_color, gt_depth, gt_color_hwc, lp->w_color, lp->w_depth, lp->w_dist, lp->eps,
-			lp->depth_near, lp->depth_far, lp->tracking, lp->silmask_th, partials, ticket, state);
+		const bool vec = loss_vec_ok(HW, {color, allmap, gt_color, gt_depth});
+		const int blocks = loss_blocks(HW, vec);
+		if (vec)
+			mapping_loss_forward_kernel<true><<<blocks, LOSS_THREADS, 0, st>>>(
+				HW, color, allmap, gt_color, gt_depth, gt_color_hwc, lp->w_color, lp->w_depth, lp->w_dist, lp->eps,
+				lp->depth_near, lp->depth_far, lp->tracking, lp->silmask_th, partials, ticket, state);
+		else
+			mapping_loss_forward_kernel<false><<<blocks, LOSS_THREADS, 0, st>>>(
+				HW, color, allmap, gt_color, gt_depth, gt_color_hwc, lp->w_color, lp->w_depth, lp->w_dist, lp->eps,
+				lp->depth_near, lp->depth_far, lp->tracking, lp->silmask_th, partials, ticket, state);
 		count_launch();
 	}
 	GS2D_CUDA_OK(cudaGetLastError());
@@ -241,9 +363,16 @@ int gs2d_mapping_loss_backward(int32_t W, int32_t H, const float* color, const f
 	const size_t HW = (size_t)W * H;
 	{
 		ProfScope ps(K_LOSS, st);
-		mapping_loss_backward_kernel<<<loss_blocks(HW), LOSS_THREADS, 0, st>>>(
-			HW, color, allmap, gt_color, gt_depth, gt_color_hwc, lp->w_color, lp->w_depth, lp->w_dist, lp->eps,
-			lp->depth_near, lp->depth_far, lp->tracking, lp->silmask_th, state, grad_loss, dL_dcolor, dL_dallmap);
+		const bool vec = loss_vec_ok(HW, {color, allmap, gt_color, gt_depth, dL_dcolor, dL_dallmap});
+		const int blocks = loss_blocks(HW, vec);
+		if (vec)
+			mapping_loss_backward_kernel<true><<<blocks, LOSS_THREADS, 0, st>>>(
+				HW, color, allmap, gt_color, gt_depth, gt_color_hwc, lp->w_color, lp->w_depth, lp->w_dist, lp->eps,
+				lp->depth_near, lp->depth_far, lp->tracking, lp->silmask_th, state, grad_loss, dL_dcolor, dL_dallmap);
+		else
+			mapping_loss_backward_kernel<false><<<blocks, LOSS_THREADS, 0, st>>>(
+				HW, color, allmap, gt_color, gt_depth, gt_color_hwc, lp->w_color, lp->w_depth, lp->w_dist, lp->eps,
+				lp->depth_near, lp->depth_far, lp->tracking, lp->silmask_th, state, grad_loss, dL_dcolor, dL_dallmap);
 		count_launch();
 	}
 	GS2D_CUDA_OK(cudaGetLastError());

@@ -190,16 +190,24 @@ preprocess_forward_kernel(int P, int D, int M,
 constexpr unsigned long long ST_AGG = 1ull << 62, ST_PREFIX = 2ull << 62, ST_MASK = (1ull << 62) - 1;
 
 // Exclusive scan of side_n counts by one CTA of SCAN_THREADS threads: ranges[t] = (start, end) -- (0, 0) for an
-// empty tile, like the reference's memset -- and cursor[t] = start.
+// empty tile, like the reference's memset -- and cursor[t] = start.  This CTA is the tail of the launch, so it is
+// written for latency: a thread owns SIDE_ITEMS consecutive tiles and requests all its counts (one line each, see
+// TC_STRIDE) before it uses any; one block scan per SCAN_THREADS * SIDE_ITEMS tiles.
+constexpr int SIDE_ITEMS = 16;
 __device__ void side_scan_block(int side_n, const uint32_t* __restrict__ cnt, uint2* __restrict__ ranges,
                                 uint32_t* __restrict__ cursor, uint32_t* s_warp)
 {
 	const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 	uint32_t carry = 0;
-	for (int base = 0; base < side_n; base += SCAN_THREADS) {
-		const int i = base + tid;
-		const uint32_t v = i < side_n ? cnt[(size_t)i * TC_STRIDE] : 0u;
-		uint32_t incl = v;
+	for (int base = 0; base < side_n; base += SCAN_THREADS * SIDE_ITEMS) {
+		const int i0 = base + tid * SIDE_ITEMS;
+		uint32_t v[SIDE_ITEMS];
+#pragma unroll
+		for (int k = 0; k < SIDE_ITEMS; k++) v[k] = (i0 + k) < side_n ? cnt[(size_t)(i0 + k) * TC_STRIDE] : 0u;
+		uint32_t tsum = 0;
+#pragma unroll
+		for (int k = 0; k < SIDE_ITEMS; k++) tsum += v[k];
+		uint32_t incl = tsum;
 #pragma unroll
 		for (int o = 1; o < 32; o <<= 1) {
 			const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
@@ -215,10 +223,14 @@ __device__ void side_scan_block(int side_n, const uint32_t* __restrict__ cnt, ui
 			if (w < warp) woff += t;
 			total += t;
 		}
-		const uint32_t start = carry + woff + incl - v;
-		if (i < side_n) {
-			ranges[i] = v ? make_uint2(start, start + v) : make_uint2(0u, 0u);
-			cursor[(size_t)i * TC_STRIDE] = start;
+		uint32_t start = carry + woff + incl - tsum;
+#pragma unroll
+		for (int k = 0; k < SIDE_ITEMS; k++) {
+			if (i0 + k < side_n) {
+				ranges[i0 + k] = v[k] ? make_uint2(start, start + v[k]) : make_uint2(0u, 0u);
+				cursor[(size_t)(i0 + k) * TC_STRIDE] = start;
+			}
+			start += v[k];
 		}
 		carry += total;
 	}
