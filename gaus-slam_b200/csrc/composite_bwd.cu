@@ -48,6 +48,9 @@ namespace {
 #else
 #define SLOT_LD(p) (*(p))
 #endif
+#ifndef GS2D_BWD_PREFETCH_PIX
+#define GS2D_BWD_PREFETCH_PIX 1
+#endif
 #ifndef GS2D_BWD_ROW128
 #define GS2D_BWD_ROW128 0
 #endif
@@ -66,6 +69,15 @@ constexpr int BWD_INST_BINS = 32;                     // phase-B iterations of a
 static_assert(BWD_BATCH / 32 <= HIT_PIX_PAD, "hit_pix padding");
 constexpr int BWD_PIX_SLOTS = TILE_PIXELS + 3 * TILE;
 __device__ __forceinline__ int pix_slot(int p) { return p + 3 * (p >> 4); }
+
+__device__ __forceinline__ void prefetch_l1(const void* p)
+{
+#ifdef __CUDA_ARCH__
+	asm volatile("prefetch.global.L1 [%0];" ::"l"(p));
+#else
+	(void)p;
+#endif
+}
 
 struct PixelConst {
 	float T_final, final_A, final_D, final_D2;
@@ -311,7 +323,20 @@ composite_backward_pixels_kernel(int W, int H, unsigned gx, const uint2* __restr
 	// deepest last contributor of the tile: nothing behind it is ever visited
 	{
 		const unsigned nx = tx * TILE + (tid & 15), ny = ty * TILE + (tid >> 4);
-		uint32_t wmax = (nx < (unsigned)W && ny < (unsigned)H) ? n_contrib[(size_t)W * ny + nx] : 0u;
+		const bool nin = nx < (unsigned)W && ny < (unsigned)H;
+		const size_t npid = (size_t)W * ny + nx;
+		uint32_t wmax = nin ? n_contrib[npid] : 0u;
+#if GS2D_BWD_PREFETCH_PIX
+		// The per-pixel state is loaded further down by the thread that WALKS the pixel (known only after the sort of
+		// the pixels by list length): request the tile's lines now, in natural order, so that those loads hit L1 / L2.
+		if (nin) {
+			prefetch_l1(final_T + npid); prefetch_l1(final_T + npid + HW); prefetch_l1(final_T + npid + 2 * HW);
+			prefetch_l1(n_contrib + npid + HW); prefetch_l1(median_depth + npid); prefetch_l1(depth_std + npid);
+			prefetch_l1(dL_dpix + npid); prefetch_l1(dL_dpix + npid + HW); prefetch_l1(dL_dpix + npid + 2 * HW);
+#pragma unroll
+			for (int c = 0; c < 7; c++) prefetch_l1(dL_dothers + npid + c * HW);
+		}
+#endif
 #pragma unroll
 		for (int o = 16; o >= 1; o >>= 1) wmax = max(wmax, __shfl_xor_sync(0xffffffffu, wmax, o));
 		if (lane == 0) sm.max_last[warp] = wmax;
