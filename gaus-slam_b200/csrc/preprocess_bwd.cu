@@ -110,6 +110,9 @@ inline void mc_red4(float* mc, float4 v) { mc[0] += v.x; mc[1] += v.y; mc[2] += 
 // that was zeroed beforehand (mc_flat = its multicast address): the all-reduce of the view-sharded mapping step
 // happens in this kernel's epilogue, tile of surfels by tile of surfels, instead of in a pass of its own.  Surfels
 // that are not visible in this rank's view add nothing.
+#ifndef GS2D_PBWD_ROWS2
+#define GS2D_PBWD_ROWS2 1
+#endif
 #ifndef GS2D_PBWD_MIN_BLOCKS
 #define GS2D_PBWD_MIN_BLOCKS 4
 #endif
@@ -139,21 +142,41 @@ preprocess_backward_kernel(int P, int D, int M,
 	float2 dscale = make_float2(0.f, 0.f);
 	float4 drot = make_float4(0.f, 0.f, 0.f, 0.f);
 	float dmean2D_x = 0.f, dmean2D_y = 0.f;
-	const bool visible = radii[idx] > 0;
+	// everything a visible surfel needs besides its rows is requested up front, next to the visibility flag itself: the
+	// kernel is a chain of dependent global loads (flag -> row range -> rows), and this takes one link out of it
+	const int radius = radii[idx];
+	const uint32_t cnt_all = tiles_touched[idx];
+	const uint32_t start_all = idx == 0 ? 0u : offsets[idx - 1];
+	const bool visible = radius > 0;
 
 	if (visible) {
-		const uint32_t cnt = tiles_touched[idx];
-		const uint32_t start = idx == 0 ? 0u : offsets[idx - 1];
+		const uint32_t cnt = cnt_all;
+		const uint32_t start = start_all;
 		const float4* rows = (const float4*)(grad_rows + (size_t)start * GRAD_WORDS);
-		for (uint32_t r = 0; r < cnt; r++) {
-			const float4 a = rows[5 * r + 0], b = rows[5 * r + 1], c = rows[5 * r + 2], d = rows[5 * r + 3],
-			             e = rows[5 * r + 4];
+		auto add_row = [&](const float4 a, const float4 b, const float4 c, const float4 d, const float4 e) {
 			dT[0] += a.x; dT[1] += a.y; dT[2] += a.z; dT[3] += a.w;
 			dT[4] += b.x; dT[5] += b.y; dT[6] += b.z; dT[7] += b.w;
 			dT[8] += c.x; dm2x += c.y; dm2y += c.z; dopa += c.w;
 			dnrm.x += d.x; dnrm.y += d.y; dnrm.z += d.z; dcol.x += d.w;
 			dcol.y += e.x; dcol.z += e.y;
+		};
+#if GS2D_PBWD_ROWS2
+		// two rows per round, all ten loads requested before the first is used (a surfel has 2.1 rows on average; the
+		// kernel waits on memory, not on arithmetic); the additions stay in row order
+		uint32_t r = 0;
+		for (; r + 2 <= cnt; r += 2) {
+			const float4 a0 = rows[5 * r + 0], b0 = rows[5 * r + 1], c0 = rows[5 * r + 2], d0 = rows[5 * r + 3],
+			             e0 = rows[5 * r + 4];
+			const float4 a1 = rows[5 * r + 5], b1 = rows[5 * r + 6], c1 = rows[5 * r + 7], d1 = rows[5 * r + 8],
+			             e1 = rows[5 * r + 9];
+			add_row(a0, b0, c0, d0, e0);
+			add_row(a1, b1, c1, d1, e1);
 		}
+		if (r < cnt) add_row(rows[5 * r + 0], rows[5 * r + 1], rows[5 * r + 2], rows[5 * r + 3], rows[5 * r + 4]);
+#else
+		for (uint32_t r = 0; r < cnt; r++)
+			add_row(rows[5 * r + 0], rows[5 * r + 1], rows[5 * r + 2], rows[5 * r + 3], rows[5 * r + 4]);
+#endif
 
 		const int W = int(focal_x * tan_fovx * 2);
 		const int H = int(focal_y * tan_fovy * 2);

@@ -39,9 +39,14 @@ scatter_kernel(int P, unsigned gx, const float* __restrict__ depths, const ushor
 	// early launch (before the host knows num_rendered): only when the caller's arena is large enough
 	if (total && *total > capacity) return;
 	const int idx = blockIdx.x * blockDim.x + threadIdx.x;
-	if (idx >= P || tiles_touched[idx] == 0) return;
+	if (idx >= P) return;
+	// the rectangle and the depth are requested together with the visibility test (one memory round trip, not two;
+	// for an invisible surfel they are stale words that nobody uses)
+	const uint32_t touched = tiles_touched[idx];
 	const ushort4 r = rect[idx];
-	const uint64_t word = ((uint64_t)__float_as_uint(depths[idx]) << 32) | (uint32_t)idx;
+	const float depth = depths[idx];
+	if (touched == 0) return;
+	const uint64_t word = ((uint64_t)__float_as_uint(depth) << 32) | (uint32_t)idx;
 #if GS2D_SCATTER_UNROLL
 	// four cursor atomics in flight per thread: the returned slot is only needed by the store that follows
 	const unsigned w = r.z - r.x, cnt = w * (r.w - r.y);
