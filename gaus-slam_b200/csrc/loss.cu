@@ -27,7 +27,7 @@ namespace {
 
 struct LossPixel {
 	float c[3], depth, dist, gc[3], gd;
-	bool mask, c_ok[3], dist_ok;
+	bool mask, mask_c, c_ok[3], dist_ok;   // mask: depth term; mask_c: colour and distortion terms
 	float inv_a;     // 1 / (alpha + eps)
 };
 
@@ -43,7 +43,7 @@ __device__ __forceinline__ float nan_to_num00(float v, bool& passes)
 __device__ __forceinline__ LossPixel load_pixel(size_t p, size_t HW, const float* __restrict__ color,
                                                 const float* __restrict__ allmap, const float* __restrict__ gt_color,
                                                 const float* __restrict__ gt_depth, int gt_hwc, float eps, float near_,
-                                                float far_, float silmask_th = -1.f)
+                                                float far_, float silmask_th, float edge_thres)
 {
 	LossPixel px;
 #pragma unroll
@@ -64,10 +64,14 @@ __device__ __forceinline__ LossPixel load_pixel(size_t p, size_t HW, const float
 	px.mask = (px.gd > 1e-5f) && (d > 1e-5f);   // implies: finite, not an outlier
 	// tracking branch (slam/Loss.py:42-43): nan_to_num(alpha, 0, 0) > silmask_th as well
 	if (silmask_th >= 0.f) px.mask = px.mask && isfinite(A) && (A > silmask_th);
+	// mapping with densify.use_edge_growth (slam/Loss.py:53): colour and distortion are averaged over
+	// nan_to_num(alpha, 0, 0) > edge_thres instead of over the depth mask
+	px.mask_c = edge_thres >= 0.f ? (isfinite(A) && (A > edge_thres)) : px.mask;
 	return px;
 }
 
 constexpr int LOSS_THREADS = 256;
+constexpr int LOSS_COLS = 8;        // per-block partials: count, colour sum, depth sum, distortion sum, colour count, 3 spare
 
 // Four consecutive pixels at once (128-bit loads of every plane): HW % 4 == 0 and 16-byte aligned planes.
 struct Quad {
@@ -87,7 +91,7 @@ __device__ __forceinline__ void stq(float* __restrict__ p, const float (&v)[4])
 // the same pixel record as load_pixel(), for pixel i of a quad whose planes were loaded with ldq()
 __device__ __forceinline__ LossPixel quad_pixel(int i, const Quad (&c)[3], const Quad (&gcq)[3], const Quad& gdq,
                                                 const Quad& Dq, const Quad& Aq, const Quad& Rq, int gt_hwc, float eps,
-                                                float near_, float far_, float silmask_th)
+                                                float near_, float far_, float silmask_th, float edge_thres)
 {
 	LossPixel px;
 #pragma unroll
@@ -108,6 +112,7 @@ __device__ __forceinline__ LossPixel quad_pixel(int i, const Quad (&c)[3], const
 	px.dist = nan_to_num00(Rq.v[i], px.dist_ok);
 	px.mask = (px.gd > 1e-5f) && (d > 1e-5f);
 	if (silmask_th >= 0.f) px.mask = px.mask && isfinite(A) && (A > silmask_th);
+	px.mask_c = edge_thres >= 0.f ? (isfinite(A) && (A > edge_thres)) : px.mask;
 	return px;
 }
 struct QuadIn {
@@ -135,36 +140,36 @@ __global__ void __launch_bounds__(LOSS_THREADS)
 mapping_loss_forward_kernel(size_t HW, const float* __restrict__ color, const float* __restrict__ allmap,
                             const float* __restrict__ gt_color, const float* __restrict__ gt_depth, int gt_hwc,
                             float w_color, float w_depth, float w_dist, float eps, float near_, float far_,
-                            int tracking, float silmask_th,
+                            int tracking, float silmask_th, float edge_thres,
                             float* __restrict__ partials, uint32_t* __restrict__ ticket, float* __restrict__ state)
 {
-	float cnt = 0.f, sc = 0.f, sd = 0.f, sr = 0.f;
+	float cnt = 0.f, cntc = 0.f, sc = 0.f, sd = 0.f, sr = 0.f;
 	const float sil = tracking ? silmask_th : -1.f;
+	const float edge = tracking ? -1.f : edge_thres;
+	auto add_pixel = [&](const LossPixel& px) {
+		if (px.mask) {
+			cnt += 1.f;
+			sd += fabsf(px.depth - px.gd);
+		}
+		if (px.mask_c) {
+			cntc += 1.f;
+			sc += fabsf(px.c[0] - px.gc[0]) + fabsf(px.c[1] - px.gc[1]) + fabsf(px.c[2] - px.gc[2]);
+			sr += px.dist;
+		}
+	};
 	if (VEC) {
 		for (size_t p = 4 * ((size_t)blockIdx.x * LOSS_THREADS + threadIdx.x); p < HW; p += 4 * (size_t)gridDim.x * LOSS_THREADS) {
 			const QuadIn q = load_quad(p, HW, color, allmap, gt_color, gt_depth, gt_hwc);
 #pragma unroll
 			for (int i = 0; i < 4; i++) {
-				const LossPixel px = quad_pixel(i, q.c, q.gc, q.gd, q.D, q.A, q.R, gt_hwc, eps, near_, far_, sil);
-				if (px.mask) {
-					cnt += 1.f;
-					sc += fabsf(px.c[0] - px.gc[0]) + fabsf(px.c[1] - px.gc[1]) + fabsf(px.c[2] - px.gc[2]);
-					sd += fabsf(px.depth - px.gd);
-					sr += px.dist;
-				}
+				add_pixel(quad_pixel(i, q.c, q.gc, q.gd, q.D, q.A, q.R, gt_hwc, eps, near_, far_, sil, edge));
 			}
 		}
 	} else
 	for (size_t p = (size_t)blockIdx.x * LOSS_THREADS + threadIdx.x; p < HW; p += (size_t)gridDim.x * LOSS_THREADS) {
-		const LossPixel px = load_pixel(p, HW, color, allmap, gt_color, gt_depth, gt_hwc, eps, near_, far_, sil);
-		if (px.mask) {
-			cnt += 1.f;
-			sc += fabsf(px.c[0] - px.gc[0]) + fabsf(px.c[1] - px.gc[1]) + fabsf(px.c[2] - px.gc[2]);
-			sd += fabsf(px.depth - px.gd);
-			sr += px.dist;
-		}
+		add_pixel(load_pixel(p, HW, color, allmap, gt_color, gt_depth, gt_hwc, eps, near_, far_, sil, edge));
 	}
-	__shared__ float s_part[LOSS_THREADS / 32][4];
+	__shared__ float s_part[LOSS_THREADS / 32][LOSS_COLS];
 	__shared__ bool s_last;
 	const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 #pragma unroll
@@ -173,14 +178,18 @@ mapping_loss_forward_kernel(size_t HW, const float* __restrict__ color, const fl
 		sc += __shfl_xor_sync(0xffffffffu, sc, o);
 		sd += __shfl_xor_sync(0xffffffffu, sd, o);
 		sr += __shfl_xor_sync(0xffffffffu, sr, o);
+		cntc += __shfl_xor_sync(0xffffffffu, cntc, o);
 	}
-	if (lane == 0) { s_part[warp][0] = cnt; s_part[warp][1] = sc; s_part[warp][2] = sd; s_part[warp][3] = sr; }
+	if (lane == 0) {
+		s_part[warp][0] = cnt; s_part[warp][1] = sc; s_part[warp][2] = sd; s_part[warp][3] = sr; s_part[warp][4] = cntc;
+		s_part[warp][5] = s_part[warp][6] = s_part[warp][7] = 0.f;
+	}
 	__syncthreads();
-	if (threadIdx.x < 4) {
+	if (threadIdx.x < LOSS_COLS) {
 		float t = 0.f;
 #pragma unroll
 		for (int w = 0; w < LOSS_THREADS / 32; w++) t += s_part[w][threadIdx.x];
-		partials[4 * blockIdx.x + threadIdx.x] = t;
+		partials[LOSS_COLS * blockIdx.x + threadIdx.x] = t;
 	}
 	__threadfence();
 	__syncthreads();
@@ -188,34 +197,36 @@ mapping_loss_forward_kernel(size_t HW, const float* __restrict__ color, const fl
 	__syncthreads();
 	if (!s_last) return;
 	// last block: add the per-block partials in block order (deterministic), in double
-	// (4 columns x 64 chunks in parallel, then the chunks in order: the order of additions is fixed)
-	__shared__ double s_sum[4];
-	__shared__ double s_chunk[LOSS_THREADS / 4][4];
+	// (8 columns x 32 chunks in parallel, then the chunks in order: the order of additions is fixed)
+	__shared__ double s_sum[LOSS_COLS];
+	__shared__ double s_chunk[LOSS_THREADS / LOSS_COLS][LOSS_COLS];
 	{
-		const unsigned col = threadIdx.x & 3, chunk = threadIdx.x >> 2;
+		const unsigned col = threadIdx.x % LOSS_COLS, chunk = threadIdx.x / LOSS_COLS;
 		double t = 0.0;
-		for (unsigned b = chunk; b < gridDim.x; b += LOSS_THREADS / 4) t += (double)__ldcg(&partials[4 * b + col]);
+		for (unsigned b = chunk; b < gridDim.x; b += LOSS_THREADS / LOSS_COLS) t += (double)__ldcg(&partials[LOSS_COLS * b + col]);
 		s_chunk[chunk][col] = t;
 	}
 	__syncthreads();
-	if (threadIdx.x < 4) {
+	if (threadIdx.x < LOSS_COLS) {
 		double t = 0.0;
-		for (int c = 0; c < LOSS_THREADS / 4; c++) t += s_chunk[c][threadIdx.x];
+		for (int c = 0; c < LOSS_THREADS / LOSS_COLS; c++) t += s_chunk[c][threadIdx.x];
 		s_sum[threadIdx.x] = t;
 	}
 	__syncthreads();
 	if (threadIdx.x == 0) {
-		const double n = s_sum[0];
+		const double n = s_sum[0], nc = s_sum[4];
 		// mean over an empty selection is NaN in torch; kept
-		// mapping: masked means (slam/Loss.py:52-58); tracking: masked sums, no distortion term (:46-47)
+		// mapping: masked means (slam/Loss.py:52-58; colour and distortion over their own mask, which is the depth
+		// mask unless use_edge_growth); tracking: masked sums, no distortion term (:46-47)
 		const double loss = tracking ? (double)w_color * s_sum[1] + (double)w_depth * s_sum[2]
-		                             : (double)w_color * (s_sum[1] / (3.0 * n)) + (double)w_depth * (s_sum[2] / n) +
-		                                   (double)w_dist * (s_sum[3] / n);
+		                             : (double)w_color * (s_sum[1] / (3.0 * nc)) + (double)w_depth * (s_sum[2] / n) +
+		                                   (double)w_dist * (s_sum[3] / nc);
 		state[0] = (float)loss;
 		state[1] = (float)n;
 		state[2] = (float)s_sum[1];
 		state[3] = (float)s_sum[2];
 		state[4] = (float)s_sum[3];
+		state[5] = (float)nc;
 		*ticket = 0u;   // ready for the next call
 	}
 }
@@ -225,31 +236,34 @@ __global__ void __launch_bounds__(LOSS_THREADS)
 mapping_loss_backward_kernel(size_t HW, const float* __restrict__ color, const float* __restrict__ allmap,
                              const float* __restrict__ gt_color, const float* __restrict__ gt_depth, int gt_hwc,
                              float w_color, float w_depth, float w_dist, float eps, float near_, float far_,
-                             int tracking, float silmask_th,
+                             int tracking, float silmask_th, float edge_thres,
                              const float* __restrict__ state, const float* __restrict__ grad_out,
                              float* __restrict__ dL_dcolor, float* __restrict__ dL_dallmap)
 {
-	const float n = state[1];
+	const float n = state[1], nc = state[5];
 	const float g = grad_out ? grad_out[0] : 1.0f;
-	const float gc = tracking ? g * w_color : (n > 0.f ? g * w_color / (3.0f * n) : 0.f);
+	const float gc = tracking ? g * w_color : (nc > 0.f ? g * w_color / (3.0f * nc) : 0.f);
 	const float gd = tracking ? g * w_depth : (n > 0.f ? g * w_depth / n : 0.f);
-	const float gr = tracking ? 0.f : (n > 0.f ? g * w_dist / n : 0.f);
+	const float gr = tracking ? 0.f : (nc > 0.f ? g * w_dist / nc : 0.f);
+	const float edge = tracking ? -1.f : edge_thres;
 	const float sil = tracking ? silmask_th : -1.f;
 	// per-pixel gradients of one pixel record: (dc[3], dD, dA, dR)
 	auto pixel_grads = [&](const LossPixel& px, float (&dc)[3], float& dD, float& dA, float& dR) {
 		dc[0] = dc[1] = dc[2] = 0.f;
 		dD = dA = dR = 0.f;
-		if (px.mask) {
+		if (px.mask_c) {
 #pragma unroll
 			for (int k = 0; k < 3; k++) {
 				const float e = px.c[k] - px.gc[k];
 				dc[k] = px.c_ok[k] ? (e > 0.f ? gc : (e < 0.f ? -gc : 0.f)) : 0.f;   // sign(0) = 0 like torch.abs
 			}
+			dR = px.dist_ok ? gr : 0.f;
+		}
+		if (px.mask) {
 			const float e = px.depth - px.gd;
 			const float dd = e > 0.f ? gd : (e < 0.f ? -gd : 0.f);
 			dD = dd * px.inv_a;                       // depth = D / (A + eps)
 			dA = -dd * px.depth * px.inv_a;
-			dR = px.dist_ok ? gr : 0.f;
 		}
 	};
 	if (VEC) {
@@ -259,7 +273,7 @@ mapping_loss_backward_kernel(size_t HW, const float* __restrict__ color, const f
 			float o_c[3][4], o_D[4], o_A[4], o_R[4];
 #pragma unroll
 			for (int i = 0; i < 4; i++) {
-				const LossPixel px = quad_pixel(i, q.c, q.gc, q.gd, q.D, q.A, q.R, gt_hwc, eps, near_, far_, sil);
+				const LossPixel px = quad_pixel(i, q.c, q.gc, q.gd, q.D, q.A, q.R, gt_hwc, eps, near_, far_, sil, edge);
 				float dc[3];
 				pixel_grads(px, dc, o_D[i], o_A[i], o_R[i]);
 				o_c[0][i] = dc[0]; o_c[1][i] = dc[1]; o_c[2][i] = dc[2];
@@ -272,7 +286,7 @@ mapping_loss_backward_kernel(size_t HW, const float* __restrict__ color, const f
 		return;
 	}
 	for (size_t p = (size_t)blockIdx.x * LOSS_THREADS + threadIdx.x; p < HW; p += (size_t)gridDim.x * LOSS_THREADS) {
-		const LossPixel px = load_pixel(p, HW, color, allmap, gt_color, gt_depth, gt_hwc, eps, near_, far_, sil);
+		const LossPixel px = load_pixel(p, HW, color, allmap, gt_color, gt_depth, gt_hwc, eps, near_, far_, sil, edge);
 		float dc[3], dD, dA, dR;
 		pixel_grads(px, dc, dD, dA, dR);
 		dL_dcolor[p] = dc[0]; dL_dcolor[HW + p] = dc[1]; dL_dcolor[2 * HW + p] = dc[2];
@@ -308,16 +322,16 @@ extern "C" {
 
 size_t gs2d_mapping_loss_scratch_bytes(int32_t, int32_t)
 {
-	// per-block partials (4 floats x 148*8 blocks), the ticket, the 8-float state
-	return sizeof(float) * 4 * 148 * 8 + 128 + sizeof(float) * 8;
+	// per-block partials (LOSS_COLS floats x 148*8 blocks), the ticket, the 8-float state
+	return sizeof(float) * LOSS_COLS * 148 * 8 + 128 + sizeof(float) * 8;
 }
 
 static inline void loss_carve(void* scratch, float** partials, uint32_t** ticket, float** state)
 {
 	char* b = (char*)scratch;
 	*partials = (float*)b;
-	*ticket = (uint32_t*)(b + sizeof(float) * 4 * 148 * 8);
-	*state = (float*)(b + sizeof(float) * 4 * 148 * 8 + 128);
+	*ticket = (uint32_t*)(b + sizeof(float) * LOSS_COLS * 148 * 8);
+	*state = (float*)(b + sizeof(float) * LOSS_COLS * 148 * 8 + 128);
 }
 
 int gs2d_mapping_loss_forward(int32_t W, int32_t H, const float* color, const float* allmap, const float* gt_color,
@@ -337,11 +351,11 @@ int gs2d_mapping_loss_forward(int32_t W, int32_t H, const float* color, const fl
 		if (vec)
 			mapping_loss_forward_kernel<true><<<blocks, LOSS_THREADS, 0, st>>>(
 				HW, color, allmap, gt_color, gt_depth, gt_color_hwc, lp->w_color, lp->w_depth, lp->w_dist, lp->eps,
-				lp->depth_near, lp->depth_far, lp->tracking, lp->silmask_th, partials, ticket, state);
+				lp->depth_near, lp->depth_far, lp->tracking, lp->silmask_th, lp->edge_thres, partials, ticket, state);
 		else
 			mapping_loss_forward_kernel<false><<<blocks, LOSS_THREADS, 0, st>>>(
 				HW, color, allmap, gt_color, gt_depth, gt_color_hwc, lp->w_color, lp->w_depth, lp->w_dist, lp->eps,
-				lp->depth_near, lp->depth_far, lp->tracking, lp->silmask_th, partials, ticket, state);
+				lp->depth_near, lp->depth_far, lp->tracking, lp->silmask_th, lp->edge_thres, partials, ticket, state);
 		count_launch();
 	}
 	GS2D_CUDA_OK(cudaGetLastError());
@@ -368,11 +382,11 @@ int gs2d_mapping_loss_backward(int32_t W, int32_t H, const float* color, const f
 		if (vec)
 			mapping_loss_backward_kernel<true><<<blocks, LOSS_THREADS, 0, st>>>(
 				HW, color, allmap, gt_color, gt_depth, gt_color_hwc, lp->w_color, lp->w_depth, lp->w_dist, lp->eps,
-				lp->depth_near, lp->depth_far, lp->tracking, lp->silmask_th, state, grad_loss, dL_dcolor, dL_dallmap);
+				lp->depth_near, lp->depth_far, lp->tracking, lp->silmask_th, lp->edge_thres, state, grad_loss, dL_dcolor, dL_dallmap);
 		else
 			mapping_loss_backward_kernel<false><<<blocks, LOSS_THREADS, 0, st>>>(
 				HW, color, allmap, gt_color, gt_depth, gt_color_hwc, lp->w_color, lp->w_depth, lp->w_dist, lp->eps,
-				lp->depth_near, lp->depth_far, lp->tracking, lp->silmask_th, state, grad_loss, dL_dcolor, dL_dallmap);
+				lp->depth_near, lp->depth_far, lp->tracking, lp->silmask_th, lp->edge_thres, state, grad_loss, dL_dcolor, dL_dallmap);
 		count_launch();
 	}
 	GS2D_CUDA_OK(cudaGetLastError());

@@ -58,7 +58,8 @@ class StateView(C.Structure):
 # name -> (restype, argtypes); also the list of symbols the header declares (checked by tests).
 class LossParams(C.Structure):
     _fields_ = [("w_color", C.c_float), ("w_depth", C.c_float), ("w_dist", C.c_float), ("eps", C.c_float),
-                ("depth_near", C.c_float), ("depth_far", C.c_float), ("tracking", C.c_int32), ("silmask_th", C.c_float)]
+                ("depth_near", C.c_float), ("depth_far", C.c_float), ("tracking", C.c_int32), ("silmask_th", C.c_float),
+                ("edge_thres", C.c_float)]
 
 
 class MapState(C.Structure):
@@ -71,7 +72,7 @@ class AdamParams(C.Structure):
                 ("step", C.c_int64), ("group_step", C.c_int64 * 5)]
 
 
-ABI_VERSION = 3      # GS2D_ABI_VERSION of the include/gs2d.h these structs mirror (checked when the library is loaded)
+ABI_VERSION = 4      # GS2D_ABI_VERSION of the include/gs2d.h these structs mirror (checked when the library is loaded)
 
 PROTOTYPES = {
     "gs2d_geom_bytes": (C.c_size_t, [C.c_int32, C.c_int32]),

@@ -123,3 +123,83 @@ def save_w2cs(directory, w2cs, name="w2cs.npz"):
 def load_w2cs(directory, name="w2cs.npz"):
     """load_scence reads 'w2cs.npz.npy' (scene/__init__.py:31-45)."""
     return np.load(os.path.join(directory, name + ".npy"))
+
+
+# ---- LocalMap queue payload (SURVEY.md 8f row f4, scene/Frame.py:202-235, slam/Frontend.py:201-204) -----------------
+# The reference's frontend hands a finished submap to the backend as `copy.deepcopy(LocalMap)` through an mp.Queue:
+# a pickle of Python objects whose bulk is `local_map_params = Gaussians.extract_params()` (scene/Gaussians.py:349-360:
+# the five RAW parameter tensors xyz, opacity, scaling, rotation, rgb, detached) plus one 4x4 pose per frame.  When
+# frontend and backend sit on different GPUs (or processes without CUDA IPC) what has to cross is exactly that, so the
+# wire format is one flat little-endian buffer: a 64-byte header, the [P, 3+1+S+4+3] float32 parameter table in the
+# column order of gaussians.ply without the (all-zero) normals, the [F,4,4] float32 world-to-camera estimates of the
+# submap's frames and their int64 time indices.  Packing is one concatenation on the device and one device-to-host
+# copy; the receiver gets the dict `Gaussians.create_params` / `add_params` take (scene/Gaussians.py:362-392).
+# Not carried: what the backend recomputes or does not read from the payload (gt images are already in host memory on
+# the reference's side of the queue, the NetVLAD descriptor is out of scope, SURVEY.md 2).
+LOCAL_MAP_MAGIC = b"GS2DLMAP"
+LOCAL_MAP_VERSION = 1
+_LM_HEADER = np.dtype([("magic", "S8"), ("version", "<u4"), ("lmid", "<i4"), ("tracking_ok", "<u4"), ("P", "<u8"),
+                       ("scale_cols", "<u4"), ("frames", "<u4"), ("reserved", "V28")])
+assert _LM_HEADER.itemsize == 64
+LOCAL_MAP_KEYS = ("xyz", "opacity", "scaling", "rotation", "rgb")      # Gaussians.extract_params, use_sh = False
+
+
+def pack_local_map(lmid, params, frame_w2cs, frame_time_idx=None, tracking_ok=True):
+    """-> numpy uint8 buffer.  params: the dict of Gaussians.extract_params() (torch tensors on any device, or arrays);
+    frame_w2cs: [F,4,4] (or a list of 4x4) estimated world-to-camera matrices of the submap's frames."""
+    missing = [k for k in LOCAL_MAP_KEYS if k not in params]
+    if missing:
+        raise KeyError(f"local map parameters lack {missing} (f_dc / f_rest maps are not carried: use_sh is False in "
+                       "every shipped config)")
+    cols = [params[k] for k in LOCAL_MAP_KEYS]
+    if hasattr(cols[0], "detach"):
+        import torch
+        with torch.no_grad():
+            table = torch.cat([c.detach().to(torch.float32).reshape(c.shape[0], c.shape[1]) for c in cols], dim=1).cpu().numpy()
+    else:
+        table = np.concatenate([np.asarray(c, np.float32).reshape(np.shape(c)[0], np.shape(c)[1]) for c in cols], axis=1)
+    S = int(np.shape(params["scaling"])[1])
+    if table.shape[1] != 3 + 1 + S + 4 + 3:
+        raise ValueError(f"expected {3 + 1 + S + 4 + 3} parameter columns, got {table.shape[1]}")
+    w2c = np.stack([_np(w) for w in frame_w2cs], axis=0).astype("<f4") if not isinstance(frame_w2cs, np.ndarray) \
+        else frame_w2cs.astype("<f4")
+    if w2c.ndim != 3 or w2c.shape[1:] != (4, 4):
+        raise ValueError("frame_w2cs must be [F,4,4]")
+    t_idx = np.arange(w2c.shape[0], dtype="<i8") if frame_time_idx is None else np.asarray(frame_time_idx, "<i8")
+    if t_idx.shape != (w2c.shape[0],):
+        raise ValueError("one time index per frame")
+    hdr = np.zeros(1, _LM_HEADER)
+    hdr["magic"], hdr["version"], hdr["lmid"], hdr["tracking_ok"] = LOCAL_MAP_MAGIC, LOCAL_MAP_VERSION, int(lmid), int(bool(tracking_ok))
+    hdr["P"], hdr["scale_cols"], hdr["frames"] = table.shape[0], S, w2c.shape[0]
+    return np.concatenate([hdr.view(np.uint8).ravel(), np.ascontiguousarray(table, "<f4").view(np.uint8).ravel(),
+                           np.ascontiguousarray(w2c).view(np.uint8).ravel(), t_idx.view(np.uint8).ravel()])
+
+
+def unpack_local_map(buf, device=None):
+    """-> dict(lmid, tracking_ok, params={xyz, opacity, scaling, rotation, rgb}, frame_w2cs [F,4,4], frame_time_idx [F]).
+    With `device` the five parameter tensors are torch tensors there (one host-to-device copy of the table, then views:
+    the columns of one submap stay one allocation); without it they are numpy arrays."""
+    buf = np.frombuffer(buf, np.uint8) if not isinstance(buf, np.ndarray) else buf.view(np.uint8).ravel()
+    if buf.size < 64:
+        raise ValueError("not a local-map buffer (shorter than its header)")
+    hdr = buf[:64].view(_LM_HEADER)[0]
+    if bytes(hdr["magic"]) != LOCAL_MAP_MAGIC or int(hdr["version"]) != LOCAL_MAP_VERSION:
+        raise ValueError("not a local-map buffer of this version")
+    P, S, F = int(hdr["P"]), int(hdr["scale_cols"]), int(hdr["frames"])
+    K = 3 + 1 + S + 4 + 3
+    need = 64 + 4 * P * K + 64 * F + 8 * F
+    if buf.size != need:
+        raise ValueError(f"local-map buffer has {buf.size} bytes, its header describes {need}")
+    o = 64
+    table = buf[o:o + 4 * P * K].view("<f4").reshape(P, K); o += 4 * P * K
+    w2c = buf[o:o + 64 * F].view("<f4").reshape(F, 4, 4).copy(); o += 64 * F
+    t_idx = buf[o:o + 8 * F].view("<i8").copy()
+    edges = np.cumsum([0, 3, 1, S, 4, 3])
+    if device is not None:
+        import torch
+        t = torch.from_numpy(np.ascontiguousarray(table)).to(device)
+        params = {k: t[:, edges[i]:edges[i + 1]] for i, k in enumerate(LOCAL_MAP_KEYS)}
+    else:
+        params = {k: np.ascontiguousarray(table[:, edges[i]:edges[i + 1]]) for i, k in enumerate(LOCAL_MAP_KEYS)}
+    return dict(lmid=int(hdr["lmid"]), tracking_ok=bool(hdr["tracking_ok"]), params=params, frame_w2cs=w2c,
+                frame_time_idx=t_idx)

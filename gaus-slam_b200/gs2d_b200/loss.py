@@ -8,8 +8,10 @@ launches each way.
 
 Argument meaning follows the reference's config keys: `weights` = config['loss']['mapping'] (color, depth, dist),
 `eps`, `depth_near`, `depth_far` = config['render'][...].  `gt_color` may be [3,H,W] or the reference's [H,W,3].
-Built for use_edge_growth = use_normal_loss = enable_exposure = False (every shipped config), with or without
-`ignore_outliners`; the other branches raise.  CUDA only: there is no CPU path.
+Built for every branch of get_loss but the normal loss (`use_normal_loss`, off in every shipped config: it raises):
+`use_edge_growth`, the tracking branch, `ignore_outliners`.  `enable_exposure` is not part of get_loss: the caller
+applies `exposure[0] * color + exposure[1]` (render/__init__.py:105-107) to the rendered colour before the loss, as a
+torch op, exactly like the reference.  CUDA only: there is no CPU path.
 """
 from __future__ import annotations
 
@@ -76,12 +78,16 @@ class _MappingLoss(torch.autograd.Function):
 
 
 def mapping_loss(color, allmap, gt_color, gt_depth, weights=(0.5, 1.0, 0.1), eps=1e-6, depth_near=1e-2,
-                 depth_far=1e2, use_edge_growth=False, use_normal_loss=False):
-    """-> scalar loss tensor (differentiable w.r.t. color and allmap)."""
-    if use_edge_growth or use_normal_loss:
-        raise NotImplementedError("only the default mapping loss (no edge growth, no normal loss) is built")
+                 depth_far=1e2, use_edge_growth=False, edge_thres=0.4, use_normal_loss=False):
+    """-> scalar loss tensor (differentiable w.r.t. color and allmap).  `use_edge_growth` / `edge_thres` =
+    config['densify'][...] (slam/Loss.py:53): colour and distortion are then averaged over alpha > edge_thres instead of
+    over the depth mask."""
+    if use_normal_loss:
+        raise NotImplementedError("the normal loss is not built (off in every shipped config)")
+    if use_edge_growth and not float(edge_thres) >= 0.0:
+        raise ValueError("edge_thres must be >= 0")
     params = (float(weights[0]), float(weights[1]), float(weights[2]), float(eps), float(depth_near), float(depth_far),
-              0, 0.0)
+              0, 0.0, float(edge_thres) if use_edge_growth else -1.0)
     return _MappingLoss.apply(color, allmap, gt_color, gt_depth, params)
 
 
@@ -110,5 +116,5 @@ def tracking_loss(color, allmap, gt_color, gt_depth, weights=(0.5, 1.0), eps=1e-
     if ignore_outliners:
         gt_depth = _inlier_gt_depth(allmap, gt_depth, float(eps), float(depth_near), float(depth_far))
     params = (float(weights[0]), float(weights[1]), 0.0, float(eps), float(depth_near), float(depth_far), 1,
-              float(silmask_th))
+              float(silmask_th), -1.0)
     return _MappingLoss.apply(color, allmap, gt_color, gt_depth, params)

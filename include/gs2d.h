@@ -38,7 +38,7 @@ extern "C" {
 #endif
 
 /* 3: gs2d_adam_params gained group_step[5] (and negative lr = "no gradient"); gs2d_map_compact_* added */
-#define GS2D_ABI_VERSION 3
+#define GS2D_ABI_VERSION 4
 
 typedef enum gs2d_status {
 	GS2D_OK = 0,
@@ -287,6 +287,9 @@ typedef struct gs2d_loss_params {
 	                                   * mask also needs nan_to_num(alpha) > silmask_th; loss = w_color * SUM |dc|
 	                                   * + w_depth * SUM |dd| over the mask (sums, not means; no distortion term) */
 	float silmask_th;                 /* loss.silmask_th = 0.9 (tracking only)                    */
+	float edge_thres;                 /* ABI v4.  < 0: densify.use_edge_growth = False (every shipped config) -- colour and
+	                                   * distortion are averaged over the depth mask.  >= 0 (densify.edge_thres = 0.4):
+	                                   * over nan_to_num(alpha, 0, 0) > edge_thres instead (slam/Loss.py:53, mapping only) */
 } gs2d_loss_params;
 
 size_t gs2d_mapping_loss_scratch_bytes(int32_t image_width, int32_t image_height);

@@ -11,7 +11,7 @@ import numpy as np
 
 
 def mapping_loss_torch(color, allmap, gt_color_hwc, gt_depth_hw1, weights=(0.5, 1.0, 0.1), eps=1e-6,
-                       depth_near=1e-2, depth_far=1e2):
+                       depth_near=1e-2, depth_far=1e2, use_edge_growth=False, edge_thres=0.4):
     import torch
     # render/__init__.py:46-49 (use_weight_norm)
     render_depth = allmap[0:1] / (allmap[1:2] + eps)
@@ -24,10 +24,14 @@ def mapping_loss_torch(color, allmap, gt_color_hwc, gt_depth_hw1, weights=(0.5, 
     render_dist = torch.nan_to_num(allmap[6:7], 0, 0).permute(1, 2, 0)
     # :36
     depth_mask = (gt_depth_hw1 > 1e-5).view(-1) & (render_depth > 1e-5).view(-1)
-    # :52-58 (use_edge_growth False: colour mask = depth mask)
-    l_color = (torch.abs(render_color - gt_color_hwc).view(-1, 3))[depth_mask].mean()
+    # :52-58 (use_edge_growth False: colour mask = depth mask; True: alpha > edge_thres, :53)
+    color_mask = depth_mask
+    if use_edge_growth:
+        render_alpha = torch.nan_to_num(allmap[1:2], 0, 0).permute(1, 2, 0)        # :22
+        color_mask = (render_alpha > edge_thres).reshape(-1)
+    l_color = (torch.abs(render_color - gt_color_hwc).view(-1, 3))[color_mask].mean()
     l_depth = (torch.abs(render_depth - gt_depth_hw1).view(-1, 1))[depth_mask].mean()
-    l_dist = (render_dist.reshape(-1, 1)[depth_mask]).mean()
+    l_dist = (render_dist.reshape(-1, 1)[color_mask]).mean()
     return weights[0] * l_color + weights[1] * l_depth + weights[2] * l_dist
 
 

@@ -126,6 +126,9 @@ def _reference_loss(get_loss, color, allmap, gt_color, gt_depth, tracking):
 
 
 CASES = dict(small=(24, 40, 0, True), ragged=(17, 33, 1, True), clean=(32, 48, 2, False))
+# densify.use_edge_growth = True, edge_thres = 0.4 (the values of configs/*/config.py when edge growth is switched on):
+# colour and distortion are averaged over alpha > 0.4, depth over the depth mask (slam/Loss.py:53)
+EDGE_CASES = dict(edge=(24, 40, 5, True), edge_ragged=(19, 35, 6, True))
 
 
 def main():
@@ -137,6 +140,16 @@ def main():
             loss, dc, da = reference_loss(get_loss, *x, tracking=tracking)
             out[f"ref_loss_{mode}"], out[f"ref_dcolor_{mode}"], out[f"ref_dallmap_{mode}"] = loss, dc, da
             print(name, mode, float(loss), int(np.isnan(da).sum()), "NaN in dL/dallmap")
+        np.savez_compressed(os.path.join(HERE, f"loss_{name}.npz"), **out)
+    import copy
+    cfg = copy.deepcopy(CONFIG)
+    cfg["densify"] = dict(use_edge_growth=True, edge_thres=0.4)
+    for name, (H, W, seed, nasty) in EDGE_CASES.items():
+        x = inputs(H, W, seed, nasty)
+        out = dict(in_color=x[0], in_allmap=x[1], in_gt_color=x[2], in_gt_depth=x[3], edge_thres=np.float32(0.4))
+        loss, dc, da = reference_loss(get_loss, *x, tracking=False, config=cfg)
+        out["ref_loss_mapping"], out["ref_dcolor_mapping"], out["ref_dallmap_mapping"] = loss, dc, da
+        print(name, "mapping + edge growth", float(loss), int(np.isnan(da).sum()), "NaN in dL/dallmap")
         np.savez_compressed(os.path.join(HERE, f"loss_{name}.npz"), **out)
     # the median-based outlier mask of the tracking loss, as configs/replica/splatam.py switches it on
     # (ignore_outliners = True, silmask_th = 0.99)

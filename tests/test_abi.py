@@ -29,7 +29,7 @@ def test_library_exports_every_declared_symbol():
 
 def test_abi_version_and_strerror():
     lib = L.load()
-    assert lib.gs2d_abi_version() == 3
+    assert lib.gs2d_abi_version() == 4
     assert lib.gs2d_strerror(0).decode().lower().startswith("ok") or lib.gs2d_strerror(0)
     for code in (-1, -2, -3, -4):
         assert lib.gs2d_strerror(code).decode()
@@ -170,8 +170,10 @@ def test_next_row_wrappers_refuse_cpu_tensors_and_unbuilt_branches():
         loss.tracking_loss(img, am, img, torch.zeros((8, 8)), use_normal_loss=True)
     with pytest.raises(RuntimeError, match="CUDA"):      # the outlier mask is built since round 2; still no CPU path
         loss.tracking_loss(img, am, img, torch.zeros((8, 8)), ignore_outliners=True)
-    with pytest.raises(NotImplementedError):
+    with pytest.raises(RuntimeError, match="CUDA"):      # edge growth is built since round 2; still no CPU path
         loss.mapping_loss(img, am, img, torch.zeros((8, 8)), use_edge_growth=True)
+    with pytest.raises(NotImplementedError):
+        loss.mapping_loss(img, am, img, torch.zeros((8, 8)), use_normal_loss=True)
     with pytest.raises(RuntimeError):
         loss.mapping_loss(img, am, img, torch.zeros((8, 8)))
 

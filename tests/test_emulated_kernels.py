@@ -119,6 +119,21 @@ def test_loss_kernel_text_matches_the_reference_get_loss(loss, name, mode):
         assert TL._close(a.grad.numpy(), g[f"ref_dallmap_{mode}"], 1e-5)
 
 
+@pytest.mark.parametrize("name", TL.GOLDEN_EDGE)
+def test_loss_kernel_text_with_edge_growth_matches_the_reference_get_loss(loss, name):
+    """densify.use_edge_growth = True: colour and distortion over alpha > edge_thres (slam/Loss.py:53)."""
+    g = TL._golden(name)
+    c = torch.tensor(g["in_color"], requires_grad=True)
+    a = torch.tensor(g["in_allmap"], requires_grad=True)
+    out = loss.mapping_loss(c, a, torch.tensor(g["in_gt_color"]), torch.tensor(g["in_gt_depth"]), use_edge_growth=True,
+                            edge_thres=float(g["edge_thres"]))
+    out.backward()
+    want = float(g["ref_loss_mapping"])
+    assert abs(float(out.detach()) - want) <= 2e-5 * abs(want)
+    assert TL._close(c.grad.numpy(), g["ref_dcolor_mapping"], 5e-6)
+    assert TL._close(a.grad.numpy(), g["ref_dallmap_mapping"], 1e-5)
+
+
 def test_loss_kernel_text_on_nasty_inputs_and_upstream_scale(loss):
     """NaN / inf in every input channel, CHW ground truth, upstream gradient 2: against the float64 restatement."""
     import loss_ref

@@ -119,3 +119,45 @@ def test_load_ply_selects_what_the_reference_load_ply_selects(tmp_path, name):
         assert back[k].dtype == want.dtype == np.float32 and back[k].shape == want.shape, k
         assert np.array_equal(back[k], want), k
         assert np.array_equal(back[k], g["in_" + k]), k
+
+
+# ---- LocalMap queue payload ------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("P,S,as_torch", [(0, 2, False), (1, 2, True), (257, 1, True), (1000, 2, False)])
+def test_local_map_payload_round_trip(P, S, as_torch):
+    """What crosses the frontend -> backend queue (scene/Frame.py:202-235): the five raw parameter tensors of
+    Gaussians.extract_params (scene/Gaussians.py:349-360) + one pose per frame, bit for bit through the wire format."""
+    from gs2d_b200 import io as gio
+    rng = np.random.default_rng(P + S)
+    params = dict(xyz=rng.normal(size=(P, 3)), opacity=rng.normal(size=(P, 1)), scaling=rng.normal(size=(P, S)),
+                  rotation=rng.normal(size=(P, 4)), rgb=rng.uniform(size=(P, 3)))
+    params = {k: v.astype(np.float32) for k, v in params.items()}
+    assert tuple(params) == gio.LOCAL_MAP_KEYS                      # the keys create_params / add_params read (:362-392)
+    w2cs = rng.normal(size=(5, 4, 4)).astype(np.float32)
+    tix = np.array([3, 10, 17, 24, 31])
+    src = {k: torch.from_numpy(v) for k, v in params.items()} if as_torch else params
+    buf = gio.pack_local_map(7, src, list(w2cs) if as_torch else w2cs, tix, tracking_ok=False)
+    assert buf.dtype == np.uint8 and buf.size == 64 + 4 * P * (11 + S) + 64 * 5 + 8 * 5
+    out = gio.unpack_local_map(buf.tobytes())
+    assert out["lmid"] == 7 and out["tracking_ok"] is False
+    assert np.array_equal(out["frame_w2cs"], w2cs) and np.array_equal(out["frame_time_idx"], tix)
+    for k in gio.LOCAL_MAP_KEYS:
+        assert out["params"][k].dtype == np.float32 and np.array_equal(out["params"][k], params[k]), k
+    t = gio.unpack_local_map(buf, device="cpu")["params"]
+    for k in gio.LOCAL_MAP_KEYS:
+        assert torch.equal(t[k], torch.from_numpy(params[k])), k
+
+
+def test_local_map_payload_rejects_what_it_cannot_carry():
+    from gs2d_b200 import io as gio
+    p = dict(xyz=np.zeros((2, 3), np.float32), opacity=np.zeros((2, 1), np.float32), scaling=np.zeros((2, 2), np.float32),
+             rotation=np.zeros((2, 4), np.float32), rgb=np.zeros((2, 3), np.float32))
+    buf = gio.pack_local_map(0, p, np.zeros((1, 4, 4), np.float32))
+    with pytest.raises(ValueError):
+        gio.unpack_local_map(buf[:-1])
+    bad = buf.copy(); bad[0] ^= 1
+    with pytest.raises(ValueError):
+        gio.unpack_local_map(bad)
+    with pytest.raises(KeyError):
+        gio.pack_local_map(0, {k: v for k, v in p.items() if k != "rgb"}, np.zeros((1, 4, 4), np.float32))
+    with pytest.raises(ValueError):
+        gio.pack_local_map(0, p, np.zeros((1, 3, 4), np.float32))

@@ -205,6 +205,46 @@ def test_fused_kernels_match_the_reference_get_loss(name, mode):
     assert _close(a.grad.cpu().numpy(), g[f"ref_dallmap_{mode}"], 1e-5)
 
 
+GOLDEN_EDGE = ["edge", "edge_ragged"]
+
+
+@pytest.mark.parametrize("name", GOLDEN_EDGE)
+def test_edge_growth_restatement_matches_the_reference_get_loss(name):
+    """CPU: the transliteration with densify.use_edge_growth = True (colour and distortion averaged over
+    alpha > edge_thres, slam/Loss.py:53) against what the reference's own get_loss computed."""
+    g = _golden(name)
+    c = torch.tensor(g["in_color"], requires_grad=True)
+    a = torch.tensor(g["in_allmap"], requires_grad=True)
+    loss = loss_ref.mapping_loss_torch(c, a, torch.tensor(g["in_gt_color"]), torch.tensor(g["in_gt_depth"]),
+                                       use_edge_growth=True, edge_thres=float(g["edge_thres"]))
+    loss.backward()
+    want = float(g["ref_loss_mapping"])
+    assert abs(float(loss.detach()) - want) <= 1e-5 * abs(want)
+    assert _close(c.grad.numpy(), g["ref_dcolor_mapping"], 2e-6) and _close(a.grad.numpy(), g["ref_dallmap_mapping"], 1e-5)
+    # the branch is really exercised: the two masks differ
+    plain = loss_ref.mapping_loss_torch(torch.tensor(g["in_color"]), torch.tensor(g["in_allmap"]),
+                                        torch.tensor(g["in_gt_color"]), torch.tensor(g["in_gt_depth"]))
+    assert abs(float(plain) - want) > 1e-3 * abs(want)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", GOLDEN_EDGE)
+def test_fused_mapping_loss_with_edge_growth_matches_the_reference_get_loss(name):
+    from gs2d_b200 import loss as gl
+    dev = torch.device("cuda:0")
+    g = _golden(name)
+    c = torch.tensor(g["in_color"], device=dev, requires_grad=True)
+    a = torch.tensor(g["in_allmap"], device=dev, requires_grad=True)
+    gc = torch.tensor(g["in_gt_color"], device=dev)
+    gd = torch.tensor(g["in_gt_depth"], device=dev)
+    loss = gl.mapping_loss(c, a, gc, gd, use_edge_growth=True, edge_thres=float(g["edge_thres"]))
+    loss.backward()
+    want = float(g["ref_loss_mapping"])
+    assert abs(float(loss.detach()) - want) <= 2e-5 * abs(want)
+    assert _close(c.grad.cpu().numpy(), g["ref_dcolor_mapping"], 5e-6)
+    assert _close(a.grad.cpu().numpy(), g["ref_dallmap_mapping"], 1e-5)
+
+
 def test_inlier_mask_restatement_matches_the_reference_get_loss():
     """CPU: the torch ops that build the `ignore_outliners` mask (gs2d_b200.loss._inlier_gt_depth) + the transliterated
     tracking loss reproduce what the reference's get_loss computed with ignore_outliners = True, silmask_th = 0.99
