@@ -23,13 +23,12 @@ __device__ __forceinline__ uint32_t span_bits(int xa, int xb, int lo, int hi)
 }
 
 // One thread per instance: calls emit(row, bits) for every tile row by0 .. by1 of the instance's footprint box with
-// the row's 16-bit column mask (tile-local x), for the instance whose record is `rec`, in its tile at pixel origin
+// the row's 16-bit column mask (tile-local x), for the instance whose record is `rec` and box word `bw`, in its tile at pixel origin
 // (ox, oy).  The row-independent part (the quadratic's leading coefficient, the expansion point) is evaluated once.
 template <typename Emit>
-__device__ __forceinline__ void footprint_rows(const float4* rec, float ox, float oy, Emit emit)
+__device__ __forceinline__ void footprint_rows(const float4* rec, const uint32_t bw, float ox, float oy, Emit emit)
 {
 	const float4 r0 = rec[0], r1 = rec[1], r2 = rec[2];
-	const uint32_t bw = __float_as_uint(rec[3].w);
 	const int bx0 = bw & 15, bx1 = (bw >> 8) & 15;
 	const float a255 = 255.0f * r2.w;
 	if (!(((bw >> 16) & 1u) && !(a255 * 1.001f < 1.0f))) return;

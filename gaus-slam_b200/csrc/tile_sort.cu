@@ -160,7 +160,10 @@ __device__ __forceinline__ void cta_sort_regs(const uint64_t* seg, int n, uint64
 	__syncthreads();
 }
 
-__global__ void __launch_bounds__(256)
+#ifndef GS2D_TS_MIN_BLOCKS
+#define GS2D_TS_MIN_BLOCKS 5
+#endif
+__global__ void __launch_bounds__(256, GS2D_TS_MIN_BLOCKS)
 tile_sort_kernel(int W, int H, unsigned gx, const uint2* __restrict__ ranges, uint64_t* pairs,
                  const float4* __restrict__ splat, const ushort4* __restrict__ rect,
                  const float4* __restrict__ cull, const uint32_t* __restrict__ offsets,
@@ -197,37 +200,38 @@ tile_sort_kernel(int W, int H, unsigned gx, const uint2* __restrict__ ranges, ui
 		keys_sorted[range.x + k] = ((uint64_t)tile << 32) | (w >> 32);
 		point_list[range.x + k] = (uint32_t)w;
 	}
-	// gather: 5 consecutive threads copy the 5 float4 of a record -> the tile's list is written contiguously.
-	// Word 15 = in-tile footprint box, word 19 = the instance's gradient row (surfel-major, see common.cuh).
+	// gather: 5 consecutive threads copy the 5 float4 of a record -> the tile's list is written contiguously (a pure
+	// copy: the two record words that depend on the tile are patched in below by the instance's own thread, so no lane
+	// of this loop takes a special path).
 	float4* tile_rec = instances + 5 * (size_t)range.x;
 	for (int t = tid; t < 5 * n; t += 256) {
 		const int k = t / 5, part = t - 5 * k;
 		const uint32_t idx = (uint32_t)kp[k];
-		float4 v = splat[5 * (size_t)idx + part];
-		if (part == 3) {
-			v.w = __uint_as_float(tile_box_word(cull[idx], tx, ty, W, H));
-		} else if (part == 4) {
-			const ushort4 r = rect[idx];
-			const uint32_t first = idx == 0 ? 0u : offsets[idx - 1];
-			v.w = __uint_as_float(first + (uint32_t)(ty - r.y) * (uint32_t)(r.z - r.x) + (uint32_t)(tx - r.x));
-		}
-		tile_rec[t] = v;
+		tile_rec[t] = splat[5 * (size_t)idx + part];
 	}
-	__syncthreads();   // the records just written are read back below (same CTA); the sorted keys are dead
-	// Footprints: a thread per instance walks the rows of the instance's box (the row-independent half of the closed
-	// form is evaluated once per instance, not once per lane of a quarter-warp).  A thread ORs its rows into its own 8
-	// words in shared memory (stride 9: conflict-free for the owners and for the coalesced copy-out that follows).
-	uint32_t* s_words = reinterpret_cast<uint32_t*>(s_keys);
-	static_assert(sizeof(uint64_t) * TS_CAP >= sizeof(uint32_t) * 256 * 9, "footprint words alias the sorted keys");
+	__syncthreads();   // the records are complete copies: they are patched and read back below by other threads
+	// Footprints: a thread per instance.  It first finishes its record -- word 15 = in-tile footprint box, word 19 = the
+	// instance's gradient row (surfel-major, see common.cuh) -- then walks the rows of the box (the row-independent half
+	// of the closed form is evaluated once per instance, not once per lane of a quarter-warp).  A thread ORs its rows
+	// into its own 8 words in shared memory (stride 9: conflict-free for the owners and for the coalesced copy-out that
+	// follows).  The sorted keys are still needed (surfel index), so the words have their own array.
+	__shared__ uint32_t s_words[256 * 9];
 	const float ox = (float)(tx * TILE), oy = (float)(ty * TILE);
 	for (int q0 = 0; q0 < n; q0 += 256) {
 		const int k = q0 + tid;
 		uint32_t* mine = s_words + 9 * tid;
 #pragma unroll
 		for (int w = 0; w < 8; w++) mine[w] = 0u;
+		uint32_t bw = 0, cnt = 0;
 		if (k < n) {
-			uint32_t cnt = 0;
-			footprint_rows(tile_rec + 5 * (size_t)k, ox, oy, [&](int row, uint32_t bits) {
+			const uint32_t idx = (uint32_t)kp[k];
+			bw = tile_box_word(cull[idx], tx, ty, W, H);
+			const ushort4 r = rect[idx];
+			const uint32_t first = idx == 0 ? 0u : offsets[idx - 1];
+			float* rec_words = reinterpret_cast<float*>(tile_rec + 5 * (size_t)k);
+			rec_words[REC_MASK] = __uint_as_float(bw);
+			rec_words[REC_ROW] = __uint_as_float(first + (uint32_t)(ty - r.y) * (uint32_t)(r.z - r.x) + (uint32_t)(tx - r.x));
+			footprint_rows(tile_rec + 5 * (size_t)k, bw, ox, oy, [&](int row, uint32_t bits) {
 				mine[row >> 1] |= bits << (16 * (row & 1));
 				cnt += __popc(bits);
 			});
