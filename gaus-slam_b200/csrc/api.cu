@@ -128,6 +128,13 @@ BinningState BinningState::carve(void* base, size_t I, size_t tiles, size_t* byt
 	return b;
 }
 
+// Runs of tiles the forward pass is cut into (tile sort of run k+1 beside the compositing of run k, see
+// gs2d_forward_render_scattered).  Measured on the BASELINE frame: 1 run 0.662 ms / step, 2 runs 0.681, 4 runs 0.739,
+// 8 runs 0.828 -- the two kernels do not share an SM well (whichever gets there first fills it), so the default is 1.
+#ifndef GS2D_FWD_PIPE
+#define GS2D_FWD_PIPE 1
+#endif
+
 // A per-device side stream + a small pool of events for the one fork / join inside the forward pass (the pair-count
 // scan runs beside the forward compositing).  The wait on an event is enqueued in the same critical section as its
 // record, so a pooled event can be re-recorded by a later call without affecting an earlier wait.
@@ -296,21 +303,41 @@ int gs2d_forward_render_scattered(const gs2d_settings* s, const gs2d_inputs* in,
 	// footprint masks
 	uint64_t* pairs = scattered_pairs ? scattered_pairs : b.keys_a;
 	if (!scattered_pairs) GS2D_TRY(launch_scatter(*s, g, im, pairs, false, I, st));
-	GS2D_TRY(launch_tile_sort(*s, g, im, b, pairs, I, st));
-	GS2D_TRY(debug_sync(*s, st));
+	const int tiles = (int)(gx * gy);
 	// The pair-slot layout of the backward pass (inclusive scan of the footprint popcounts) and its total are not needed
-	// by the forward compositing: they run BESIDE it on the library's side stream (fork after the tile sort, join after
-	// the compositing launch), which takes the scan's ~13 us off the critical path.  (pair_status / pair_counters were
-	// zeroed by tile_sort_kernel.)
+	// by the forward compositing: they run BESIDE it on the library's side stream, which takes the scan's ~13 us off the
+	// critical path.  (pair_status / pair_counters were zeroed by the tile-0 block of tile_sort_kernel.)
+	// The compositing of a tile needs only the sort of THAT tile, so the frame can also be cut into GS2D_FWD_PIPE runs
+	// of tiles -- sorts back to back on the caller's stream, each run's compositing on the side stream as soon as its
+	// sort has finished -- but that measured slower (see GS2D_FWD_PIPE above) and is off by default.  One stream when
+	// debugging or timing kernel by kernel.
 	cudaStream_t side = (s->debug || g_timing_on) ? nullptr : side_fork(st);
-	cudaStream_t scan_st = side ? side : st;
-	GS2D_TRY(launch_scan_u32(b.hit_count, b.pair_incl, I, b.pair_status, b.pair_counters, scan_st, false));
-	if (num_pairs_host)   // 8 bytes: counters[1] = total, counters[2] = 0 -> a whole int64
-		GS2D_CUDA_OK(cudaMemcpyAsync(num_pairs_host, b.pair_counters + 1, 2 * sizeof(uint32_t), cudaMemcpyDeviceToHost, scan_st));
-	GS2D_TRY(debug_sync(*s, st));
-	GS2D_TRY(launch_composite_forward(*s, *in, im, b.instances, b.hit_inst, b.hit_pix, out_color, out_others, st));
-	if (side) GS2D_TRY(side_join(st, side));
-	GS2D_TRY(debug_sync(*s, st));
+	const int runs = (side && GS2D_FWD_PIPE > 1 && tiles >= GS2D_FWD_PIPE * 296) ? GS2D_FWD_PIPE : 1;
+	if (!side || runs == 1) {
+		GS2D_TRY(launch_tile_sort(*s, g, im, b, pairs, I, st));
+		GS2D_TRY(debug_sync(*s, st));
+		if (side) GS2D_TRY(side_join(side, st));     // the side stream waits for the sort (it forked before it)
+		cudaStream_t scan_st = side ? side : st;
+		GS2D_TRY(launch_scan_u32(b.hit_count, b.pair_incl, I, b.pair_status, b.pair_counters, scan_st, false));
+		if (num_pairs_host)   // 8 bytes: counters[1] = total, counters[2] = 0 -> a whole int64
+			GS2D_CUDA_OK(cudaMemcpyAsync(num_pairs_host, b.pair_counters + 1, 2 * sizeof(uint32_t), cudaMemcpyDeviceToHost, scan_st));
+		GS2D_TRY(debug_sync(*s, st));
+		GS2D_TRY(launch_composite_forward(*s, *in, im, b.instances, b.hit_inst, b.hit_pix, out_color, out_others, st));
+		if (side) GS2D_TRY(side_join(st, side));
+		GS2D_TRY(debug_sync(*s, st));
+		return GS2D_OK;
+	}
+	for (int r = 0; r < runs; r++) {
+		const int t0 = (int)((long long)tiles * r / runs), t1 = (int)((long long)tiles * (r + 1) / runs);
+		GS2D_TRY(launch_tile_sort(*s, g, im, b, pairs, I, st, t0, t1 - t0));
+		GS2D_TRY(side_join(side, st));          // the side stream waits for this run's sort
+		GS2D_TRY(launch_composite_forward(*s, *in, im, b.instances, b.hit_inst, b.hit_pix, out_color, out_others, side,
+		                                  t0, t1 - t0));
+	}
+	GS2D_TRY(launch_scan_u32(b.hit_count, b.pair_incl, I, b.pair_status, b.pair_counters, st, false));
+	if (num_pairs_host)
+		GS2D_CUDA_OK(cudaMemcpyAsync(num_pairs_host, b.pair_counters + 1, 2 * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+	GS2D_TRY(side_join(st, side));              // the caller's stream waits for the last compositing
 	return GS2D_OK;
 }
 

@@ -163,7 +163,7 @@ int launch_preprocess_forward(const gs2d_settings& s, const gs2d_inputs& in, con
 int launch_scatter(const gs2d_settings& s, const GeomState& g, const ImageState& im, uint64_t* pairs, bool early,
                    int64_t capacity, cudaStream_t st);
 int launch_tile_sort(const gs2d_settings& s, const GeomState& g, const ImageState& im, const BinningState& b,
-                     uint64_t* pairs, int64_t I, cudaStream_t st);
+                     uint64_t* pairs, int64_t I, cudaStream_t st, int tile0 = 0, int ntiles = -1);
 // [scan_status, counters + 8) must be zero (preprocess_forward_kernel clears them); one extra block turns the per-tile counts into ranges + cursors
 int launch_scan_tiles(const GeomState& g, int P, cudaStream_t st, int tiles, const uint32_t* tile_count,
                       uint32_t* ranges, uint32_t* tile_cursor);
@@ -179,7 +179,7 @@ int launch_footprint_audit(const gs2d_settings& s, const float* instances, const
                            const uint32_t* hit_inst, int64_t I, unsigned long long* counts, cudaStream_t st);
 int launch_composite_forward(const gs2d_settings& s, const gs2d_inputs& in, const ImageState& im,
                              const float* instances, const uint32_t* hit_inst, uint32_t* hit_pix, float* out_color,
-                             float* out_others, cudaStream_t st);
+                             float* out_others, cudaStream_t st, int tile0 = 0, int ntiles = -1);
 size_t composite_backward_scratch_bytes(int64_t I, int64_t pairs, int64_t tiles);
 int launch_composite_backward(const gs2d_settings& s, const gs2d_inputs& in, const ImageState& im,
                               const BinningState& b, int64_t I, int64_t pairs, const float* dL_dcolor,

@@ -138,14 +138,14 @@ composite_forward_kernel(int W, int H, unsigned gx, const uint2* __restrict__ ra
                          uint32_t* __restrict__ hit_pix, const float* __restrict__ bg, float* __restrict__ final_T,
                          uint32_t* __restrict__ n_contrib, float* __restrict__ median_depth_out,
                          float* __restrict__ depth_std_out, float* __restrict__ out_color,
-                         float* __restrict__ out_others)
+                         float* __restrict__ out_others, unsigned tile0)
 {
 	extern __shared__ __align__(128) unsigned char fwd_smem_raw[];
 	FwdSmem& sm = *reinterpret_cast<FwdSmem*>(fwd_smem_raw);
 	uint64_t* s_bar = sm.bar;
 
 	const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-	const unsigned tile = blockIdx.x;
+	const unsigned tile = blockIdx.x + tile0;      // the launch covers tiles [tile0, tile0 + gridDim.x)
 	const unsigned tx = tile % gx, ty = tile / gx;
 	// The transposition below hands thread t the hit words of its NATURAL pixel (warp k = 8 x 4 block k, pair.cuh).
 	// The walk is done by another thread: pixels are sorted by list length once per tile, so that the 32 lists of a
@@ -319,7 +319,7 @@ composite_forward_kernel(int W, int H, unsigned gx, const uint2* __restrict__ ra
 template <bool USE_SA>
 int launch_variant(const gs2d_settings& s, const gs2d_inputs& in, const ImageState& im, const float* instances,
                    const uint32_t* hit_inst, uint32_t* hit_pix, float* out_color, float* out_others, unsigned gx,
-                   unsigned gy, cudaStream_t st)
+                   unsigned tile0, unsigned ntiles, cudaStream_t st)
 {
 	// the opt-in to > 48 KB of dynamic shared memory is per device: made once for every device this variant runs on
 	static std::atomic<unsigned long long> opted_in{0};
@@ -330,9 +330,9 @@ int launch_variant(const gs2d_settings& s, const gs2d_inputs& in, const ImageSta
 		                                  cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(FwdSmem)));
 		if (dev < 64) opted_in.fetch_or(1ull << dev, std::memory_order_relaxed);
 	}
-	composite_forward_kernel<USE_SA><<<gx * gy, 256, sizeof(FwdSmem), st>>>(
+	composite_forward_kernel<USE_SA><<<ntiles, 256, sizeof(FwdSmem), st>>>(
 		s.image_width, s.image_height, gx, (const uint2*)im.ranges, (const float4*)instances, hit_inst, hit_pix,
-		in.background, im.final_T, im.n_contrib, im.median_depth, im.depth_std, out_color, out_others);
+		in.background, im.final_T, im.n_contrib, im.median_depth, im.depth_std, out_color, out_others, tile0);
 	return GS2D_OK;
 }
 
@@ -340,14 +340,16 @@ int launch_variant(const gs2d_settings& s, const gs2d_inputs& in, const ImageSta
 
 int launch_composite_forward(const gs2d_settings& s, const gs2d_inputs& in, const ImageState& im,
                              const float* instances, const uint32_t* hit_inst, uint32_t* hit_pix, float* out_color,
-                             float* out_others, cudaStream_t st)
+                             float* out_others, cudaStream_t st, int tile0, int ntiles)
 {
 	const int W = s.image_width, H = s.image_height;
 	const unsigned gx = (W + TILE - 1) / TILE, gy = (H + TILE - 1) / TILE;
 	if (gx * gy == 0) return GS2D_OK;
+	if (ntiles < 0) { tile0 = 0; ntiles = (int)(gx * gy); }     // the whole frame
+	if (ntiles == 0) return GS2D_OK;
 	ProfScope ps(K_COMPOSITE_FWD, st);
-	const int rc = s.use_sa ? launch_variant<true>(s, in, im, instances, hit_inst, hit_pix, out_color, out_others, gx, gy, st)
-	                        : launch_variant<false>(s, in, im, instances, hit_inst, hit_pix, out_color, out_others, gx, gy, st);
+	const int rc = s.use_sa ? launch_variant<true>(s, in, im, instances, hit_inst, hit_pix, out_color, out_others, gx, (unsigned)tile0, (unsigned)ntiles, st)
+	                        : launch_variant<false>(s, in, im, instances, hit_inst, hit_pix, out_color, out_others, gx, (unsigned)tile0, (unsigned)ntiles, st);
 	if (rc != GS2D_OK) return rc;
 	count_launch();
 	GS2D_CUDA_OK(cudaGetLastError());

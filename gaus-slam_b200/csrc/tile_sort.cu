@@ -169,11 +169,11 @@ tile_sort_kernel(int W, int H, unsigned gx, const uint2* __restrict__ ranges, ui
                  const float4* __restrict__ cull, const uint32_t* __restrict__ offsets,
                  uint64_t* __restrict__ keys_sorted, uint32_t* __restrict__ point_list, float4* instances,
                  uint32_t* __restrict__ hit_words, uint32_t* __restrict__ hit_count,
-                 uint32_t* __restrict__ zero_words, int n_zero_words)
+                 uint32_t* __restrict__ zero_words, int n_zero_words, unsigned tile0)
 {
 	__shared__ uint64_t s_keys[TS_CAP];
 	const int tid = threadIdx.x;
-	const unsigned tile = blockIdx.x;
+	const unsigned tile = blockIdx.x + tile0;      // the launch covers tiles [tile0, tile0 + gridDim.x)
 	// status words + counters of the pair-count scan that follows (instead of a memset launch)
 	if (tile == 0)
 		for (int i = tid; i < n_zero_words; i += 256) zero_words[i] = 0u;
@@ -265,19 +265,22 @@ int launch_scatter(const gs2d_settings& s, const GeomState& g, const ImageState&
 
 // `pairs`: the scattered words (b.keys_a, or the caller's arena when the scatter was launched early).
 int launch_tile_sort(const gs2d_settings& s, const GeomState& g, const ImageState& im, const BinningState& b,
-                     uint64_t* pairs, int64_t I, cudaStream_t st)
+                     uint64_t* pairs, int64_t I, cudaStream_t st, int tile0, int ntiles)
 {
 	const int W = s.image_width, H = s.image_height;
 	const unsigned gx = (W + TILE - 1) / TILE, gy = (H + TILE - 1) / TILE;
 	const int tiles = (int)(gx * gy);
 	if (tiles == 0 || I <= 0) return GS2D_OK;
+	if (ntiles < 0) { tile0 = 0; ntiles = tiles; }     // the whole frame
+	if (ntiles == 0) return GS2D_OK;
 	// (tile ranges and cursors come from the extra block of the tiles_touched scan, preprocess.cu)
 	ProfScope ps(K_TILE_SORT, st);
-	tile_sort_kernel<<<tiles, 256, 0, st>>>(W, H, gx, (const uint2*)im.ranges, pairs, (const float4*)g.splat,
+	tile_sort_kernel<<<ntiles, 256, 0, st>>>(W, H, gx, (const uint2*)im.ranges, pairs, (const float4*)g.splat,
 	                                        (const ushort4*)g.rect, (const float4*)g.cull, g.point_offsets, b.keys_b,
 	                                        b.vals_b, (float4*)b.instances, b.hit_inst, b.hit_count,
 	                                        (uint32_t*)b.pair_status,
-	                                        (int)(((char*)(b.pair_counters + 8) - (char*)b.pair_status) / sizeof(uint32_t)));
+	                                        (int)(((char*)(b.pair_counters + 8) - (char*)b.pair_status) / sizeof(uint32_t)),
+	                                        (unsigned)tile0);
 	count_launch();
 	GS2D_CUDA_OK(cudaGetLastError());
 	return GS2D_OK;
