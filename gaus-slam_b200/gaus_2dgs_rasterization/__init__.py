@@ -81,6 +81,9 @@ class _RasterizeGaussians(torch.autograd.Function):
         ctx.save_for_backward(colors_precomp, means3D, scales, rotations, cov3Ds_precomp, radii, sh,
                               geom, binning, img)
         ctx.mark_non_differentiable(radii)
+        # no zero-filled stand-ins for the gradients nobody supplied (radii always, colour / allmap when only one of
+        # them feeds the loss): backward() gets None and handles it, which saves a fill launch per step
+        ctx.set_materialize_grads(False)
         return color, radii, others
 
     @staticmethod
