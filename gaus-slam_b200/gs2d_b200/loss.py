@@ -21,11 +21,32 @@ import torch
 
 from . import _lib as L
 
+class _Scratch:
+    """Partials, ticket and the forward's mask counts: ~38 KB that belong to ONE forward call and travel to its backward
+    in ctx -- several losses may be formed before any backward (the sum over the keyframes of a bundle-adjustment
+    window; round 1 shared one scratch per stream, so every backward then used the last count).  The kernel leaves the
+    ticket at zero when it is done, so a buffer whose loss object has died goes back to a free list and is handed out
+    again as it is: no allocation and no fill launch per step once the pool is warm."""
+    _free = {}
+
+    def __init__(self, dev, W, H):
+        # (per stream: a buffer is reused in stream order, behind the kernels of its previous owner)
+        self.key = (str(dev), int(torch.cuda.current_stream(dev).cuda_stream), L.load().gs2d_mapping_loss_scratch_bytes(W, H))
+        pool = _Scratch._free.get(self.key)
+        self.buf = pool.pop() if pool else torch.zeros(self.key[2], dtype=torch.uint8, device=dev)
+
+    def __del__(self):
+        try:
+            _Scratch._free.setdefault(self.key, []).append(self.buf)
+        except Exception:       # interpreter shutdown
+            pass
+
+    def data_ptr(self):
+        return self.buf.data_ptr()
+
+
 def _new_scratch(dev, W, H):
-    """Partials, ticket and the forward's mask count live in a scratch of ~19 KB that belongs to ONE forward call and
-    travels to its backward in ctx: several losses may be formed before any backward (the sum over the keyframes of a
-    bundle-adjustment window).  Round 1 shared one scratch per stream, so every backward then used the last count."""
-    return torch.zeros(L.load().gs2d_mapping_loss_scratch_bytes(W, H), dtype=torch.uint8, device=dev)
+    return _Scratch(dev, W, H)
 
 
 def _check(t, name, shape):
