@@ -89,7 +89,7 @@ def _arena_views(P, dev):
 
 
 def _stream_ptr(device) -> C.c_void_p:
-    return C.c_void_p(torch.cuda.current_stream(device).cuda_stream)
+    return C.c_void_p(L.raw_stream(torch, device))
 
 
 def _f32(t: torch.Tensor, name: str) -> torch.Tensor:
@@ -184,15 +184,14 @@ def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations,
                     viewmatrix, projmatrix, campos)
         bufs = L.Buffers(geom=_ptr(geom), geom_bytes=geom.numel(), binning=None, binning_bytes=0,
                          image=_ptr(img), image_bytes=img.numel())
-        stream = torch.cuda.current_stream(dev)
-        sid = int(stream.cuda_stream)
+        sid = L.raw_stream(torch, dev)
         n_host = _pinned_i64(dev, sid)
         L.check(lib.gs2d_forward_preprocess(C.byref(s), C.byref(i), C.byref(bufs), _ptr(radii),
                                             n_host.data_ptr(), st), "gs2d_forward_preprocess")
         ev = _events.get((str(dev), sid))
         if ev is None:
             ev = _events[(str(dev), sid)] = torch.cuda.Event()
-        ev.record(stream)
+        ev.record()           # on the current stream of dev (this block runs under torch.cuda.device(dev))
         arena = _arena(dev, sid) if P and not debug else None
         if arena is not None:
             L.check(lib.gs2d_forward_scatter_early(C.byref(s), C.byref(bufs), arena[0].data_ptr(), arena[1], st),
@@ -216,7 +215,7 @@ def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations,
                                                   _ptr(out_others), pairs_ptr, scattered, st),
                 "gs2d_forward_render")
         if num_rendered:
-            num_rendered.pairs.event.record(stream)
+            num_rendered.pairs.event.record()
     return num_rendered, out_color, out_others, radii, geom, binning, img
 
 

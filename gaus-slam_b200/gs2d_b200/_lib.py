@@ -171,3 +171,13 @@ def check(status: int, what: str) -> None:
         if status == GS2D_ERR_CUDA:
             extra = f" (cudaError_t {lib.gs2d_last_cuda_error()})"
         raise Gs2dError(f"{what}: {msg}{extra}")
+
+
+def raw_stream(torch, device) -> int:
+    """The cudaStream_t of torch's current stream on `device` as an integer -- what
+    torch.cuda.current_stream(device).cuda_stream returns, without building a Stream object (~3 us a call, five calls
+    per mapping iteration on the path the GPU waits for)."""
+    idx = device.index
+    if idx is None:
+        idx = torch.cuda.current_device()
+    return int(torch._C._cuda_getCurrentRawStream(idx))

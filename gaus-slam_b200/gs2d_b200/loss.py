@@ -31,7 +31,7 @@ class _Scratch:
 
     def __init__(self, dev, W, H):
         # (per stream: a buffer is reused in stream order, behind the kernels of its previous owner)
-        self.key = (str(dev), int(torch.cuda.current_stream(dev).cuda_stream), L.load().gs2d_mapping_loss_scratch_bytes(W, H))
+        self.key = (str(dev), L.raw_stream(torch, dev), L.load().gs2d_mapping_loss_scratch_bytes(W, H))
         pool = _Scratch._free.get(self.key)
         self.buf = pool.pop() if pool else torch.zeros(self.key[2], dtype=torch.uint8, device=dev)
 
@@ -72,7 +72,7 @@ class _MappingLoss(torch.autograd.Function):
         with torch.cuda.device(dev):
             scratch = _new_scratch(dev, W, H)
             loss = torch.empty((), dtype=torch.float32, device=dev)
-            st = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+            st = C.c_void_p(L.raw_stream(torch, dev))
             L.check(lib.gs2d_mapping_loss_forward(W, H, color.data_ptr(), allmap.data_ptr(), gt_color.data_ptr(),
                                                   gt_depth.data_ptr(), hwc, C.byref(lp), scratch.data_ptr(),
                                                   loss.data_ptr(), st), "gs2d_mapping_loss_forward")
@@ -90,7 +90,7 @@ class _MappingLoss(torch.autograd.Function):
         d_color = torch.empty_like(color)
         d_allmap = torch.empty_like(allmap)
         with torch.cuda.device(dev):
-            st = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+            st = C.c_void_p(L.raw_stream(torch, dev))
             L.check(lib.gs2d_mapping_loss_backward(W, H, color.data_ptr(), allmap.data_ptr(), gt_color.data_ptr(),
                                                    gt_depth.data_ptr(), ctx.hwc, C.byref(ctx.lp),
                                                    ctx.scratch.data_ptr(), g.data_ptr(), d_color.data_ptr(),

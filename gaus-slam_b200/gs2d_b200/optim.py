@@ -68,7 +68,7 @@ class MapOptimizer:
             s.exp_avg_sq[i] = exp_avg_sq[k].data_ptr()
 
     def _stream(self):
-        return C.c_void_p(torch.cuda.current_stream(self.dev).cuda_stream)
+        return C.c_void_p(L.raw_stream(torch, self.dev))
 
     def activate(self):
         """Render parameters of the current raw parameters (get_render_params)."""

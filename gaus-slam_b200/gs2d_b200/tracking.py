@@ -27,7 +27,7 @@ _scratch = {}
 
 
 def _scratch_for(dev):
-    key = (str(dev), int(torch.cuda.current_stream(dev).cuda_stream))
+    key = (str(dev), L.raw_stream(torch, dev))
     if key not in _scratch:      # zero-initialised once; the backward kernel resets its ticket itself
         _scratch[key] = torch.zeros(L.load().gs2d_pose_transform_scratch_bytes(), dtype=torch.uint8, device=dev)
     return _scratch[key]
@@ -59,7 +59,7 @@ class _PoseTransform(torch.autograd.Function):
         means_out = torch.empty_like(xyz)
         rot_out = torch.empty_like(rotations)
         with torch.cuda.device(dev):
-            st = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+            st = C.c_void_p(L.raw_stream(torch, dev))
             L.check(L.load().gs2d_pose_transform_forward(P, xyz.data_ptr(), rotations.data_ptr(), _ptr(cam_rot),
                                                          _ptr(cam_trans), _ptr(w2c), means_out.data_ptr(),
                                                          rot_out.data_ptr(), st), "gs2d_pose_transform_forward")
@@ -81,7 +81,7 @@ class _PoseTransform(torch.autograd.Function):
             d_w2c = torch.empty((4, 4), device=dev)
         d_xyz = torch.empty_like(xyz) if ctx.need_xyz else None
         with torch.cuda.device(dev):
-            st = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+            st = C.c_void_p(L.raw_stream(torch, dev))
             L.check(L.load().gs2d_pose_transform_backward(P, xyz.data_ptr(), _ptr(cam_rot), _ptr(cam_trans), _ptr(w2c),
                                                           g.data_ptr(), _scratch_for(dev).data_ptr(), _ptr(d_rot),
                                                           _ptr(d_trans), _ptr(d_w2c), _ptr(d_xyz), st),

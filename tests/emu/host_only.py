@@ -51,6 +51,7 @@ def load(module: str):
     exec(compile(src, f"<host-only {module}.py>", "exec"), mod.__dict__)
     ns = types.SimpleNamespace(**{k: getattr(L, k) for k in dir(L) if not k.startswith("__")})
     ns.load = emulated_library
+    ns.raw_stream = lambda torch_, device: 0
     mod.L = ns
     fake_torch = types.SimpleNamespace(**{k: getattr(torch, k) for k in dir(torch) if not k.startswith("__")})
     fake_torch.cuda = types.SimpleNamespace(device=lambda d: contextlib.nullcontext(),
@@ -92,6 +93,7 @@ def load_rasterizer():
     exec(compile(src, "<host-only _C.py>", "exec"), glue.__dict__)
     ns = types.SimpleNamespace(**{k: getattr(L, k) for k in dir(L) if not k.startswith("__")})
     ns.load = emu_run.library
+    ns.raw_stream = lambda torch_, device: 0
     glue.L, glue.torch = ns, _fake_torch()
     src = open(os.path.join(pkg, "__init__.py")).read()
     assert "from . import _C" in src
