@@ -196,20 +196,27 @@ def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations,
         if arena is not None:
             L.check(lib.gs2d_forward_scatter_early(C.byref(s), C.byref(bufs), arena[0].data_ptr(), arena[1], st),
                     "gs2d_forward_scatter_early")
+        # Everything the host can prepare for the second half is prepared BEFORE it waits: the device is idle between the
+        # scatter and the tile sort for as long as the host needs from its wake-up to that launch.
+        binning = None
+        if arena is not None:     # sized for the arena's capacity (>= this frame's count unless the arena is too small)
+            binning = torch.empty((_bucket(lib.gs2d_binning_bytes(arena[1], W, H)),), **u8)
+        pairs_holder = _PairCount() if P else None
         ev.synchronize()                                   # the reference's one host wait (num_rendered)
         num_rendered = C.c_int64.from_address(n_host.data_ptr()).value if P else 0
         scattered = None
         if arena is not None and num_rendered <= arena[1]:
             scattered = arena[0].data_ptr()
-        elif num_rendered and not debug:
-            _grow_arena(dev, sid, num_rendered)             # for the next frames
-        binning = torch.empty((_bucket(lib.gs2d_binning_bytes(num_rendered, W, H)) if num_rendered else 0,), **u8)
+        else:
+            if num_rendered and not debug:
+                _grow_arena(dev, sid, num_rendered)         # for the next frames
+            binning = torch.empty((_bucket(lib.gs2d_binning_bytes(num_rendered, W, H)) if num_rendered else 0,), **u8)
         bufs.binning = _ptr(binning)
         bufs.binning_bytes = binning.numel()
         num_rendered = _NumRendered(num_rendered)
         pairs_ptr = None
         if num_rendered:
-            num_rendered.pairs = _PairCount()
+            num_rendered.pairs = pairs_holder
             pairs_ptr = num_rendered.pairs.ptr()
         L.check(lib.gs2d_forward_render_scattered(C.byref(s), C.byref(i), C.byref(bufs), int(num_rendered), _ptr(out_color),
                                                   _ptr(out_others), pairs_ptr, scattered, st),
