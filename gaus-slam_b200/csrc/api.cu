@@ -235,6 +235,9 @@ int gs2d_forward_preprocess(const gs2d_settings* s, const gs2d_inputs* in, const
 	cudaStream_t st = (cudaStream_t)stream;
 	if (num_rendered_host) *num_rendered_host = 0;
 	if (s->P == 0) return GS2D_OK;
+	// "not there yet": the copy enqueued below overwrites the whole int64 (count, 0), so a host that polls the pinned
+	// cell sees a negative value until the count has landed
+	if (num_rendered_host) *num_rendered_host = -1;
 	if (!buffers->geom || !radii || !buffers->image) return GS2D_ERR_INVALID;
 	if (buffers->geom_bytes < gs2d_geom_bytes(s->P, s->sh_coeffs)) return GS2D_ERR_CAPACITY;
 	if (buffers->image_bytes < gs2d_image_bytes(s->image_width, s->image_height)) return GS2D_ERR_CAPACITY;
@@ -250,8 +253,8 @@ int gs2d_forward_preprocess(const gs2d_settings* s, const gs2d_inputs* in, const
 	                           im.tile_cursor));
 	GS2D_TRY(debug_sync(*s, st));
 	if (num_rendered_host) {
-		// 4-byte read-back into the low half of the (zeroed) int64
-		GS2D_CUDA_OK(cudaMemcpyAsync(num_rendered_host, g.counters + 1, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+		// 8-byte read-back: counters[1] = total, counters[2] = 0 -> a whole int64
+		GS2D_CUDA_OK(cudaMemcpyAsync(num_rendered_host, g.counters + 1, 2 * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
 	}
 	return GS2D_OK;
 }

@@ -202,8 +202,16 @@ def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations,
         if arena is not None:     # sized for the arena's capacity (>= this frame's count unless the arena is too small)
             binning = torch.empty((_bucket(lib.gs2d_binning_bytes(arena[1], W, H)),), **u8)
         pairs_holder = _PairCount() if P else None
-        ev.synchronize()                                   # the reference's one host wait (num_rendered)
-        num_rendered = C.c_int64.from_address(n_host.data_ptr()).value if P else 0
+        # the reference's one host wait (num_rendered): the pinned cell is polled (it is negative until the copy has
+        # landed) -- a shorter wake-up than an event wait; the event bounds the wait if the forward's stream has faulted
+        cell = C.c_int64.from_address(n_host.data_ptr())
+        spins = 0
+        while P and cell.value < 0:
+            spins += 1
+            if (spins & 1023) == 0 and ev.query():
+                if cell.value < 0:
+                    raise RuntimeError("rasterize_gaussians: the preprocess stage finished without delivering num_rendered")
+        num_rendered = cell.value if P else 0
         scattered = None
         if arena is not None and num_rendered <= arena[1]:
             scattered = arena[0].data_ptr()

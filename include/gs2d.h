@@ -107,7 +107,8 @@ size_t gs2d_binning_bytes(int64_t num_rendered, int32_t image_width, int32_t ima
  * Also counts the instances of every tile and turns the counts into the tile ranges
  * (the output of identifyTileRanges, CR/rasterizer_impl.cu:116-138) for the tile-local sort.
  * Enqueues an async copy of num_rendered to `num_rendered_host` (pinned host int64) when
- * that pointer is not NULL. Needs buffers->geom (gs2d_geom_bytes) and buffers->image
+ * that pointer is not NULL: the cell is set to -1 by the call and becomes the count (>= 0) when the copy has
+ * landed, so the host may poll it instead of synchronising (0 at once for an empty map). Needs buffers->geom (gs2d_geom_bytes) and buffers->image
  * (gs2d_image_bytes). */
 int gs2d_forward_preprocess(const gs2d_settings* s, const gs2d_inputs* in,
                             const gs2d_buffers* buffers, int32_t* radii,
