@@ -5,25 +5,29 @@
 // *final* per-pixel statistics, opacity gradient through the clamped alpha), but the work is split by
 // what it depends on, so that every lane does useful work and nothing is reduced with atomics:
 //
-//   kernel A (per PIXEL, sequential back to front; one CTA per tile, lanes = 32 pixels of a warp):
+//   phase A (per PIXEL, sequential back to front; one CTA per tile):
 //       the order-dependent part only -- transmittance T = T / (1 - alpha), the suffix recurrences for
 //       colour / depth / alpha / normal / dL_dT (CR/backward.cu:323-410).  Every pixel walks ITS OWN list of
 //       the pairs that contributed in the forward pass (recorded there, one word per pixel and 32
-//       instances), i.e. ~17 instances per tile instead of ~250 and no skip tests, and leaves three scalars
+//       instances), i.e. ~18 instances per tile instead of ~300 and no skip tests, and leaves three scalars
 //       per pair -- dL/dalpha, dL/dz, w = alpha * T -- plus its pixel id in the pair's 16-byte slot.  Slots
 //       live in global memory (L2), laid out per instance: slot = first slot of the instance (exclusive
 //       scan of the footprint-mask popcounts, computed in the forward pass) + rank of the pixel inside the
 //       instance's mask.  Pairs of the mask that did not contribute get an "empty" marker.
-//   kernel B (per INSTANCE, fully parallel over all instances of the frame, half a warp per instance):
+//       Up to BWD_SUPER instances of the tile (all of it for the BASELINE views) are resident at once, and the
+//       walk of a pixel is done by a thread chosen by a counting sort of the 256 pixels by list length: the 32
+//       lists a warp walks in lockstep are alike (27 of 32 lanes busy per instruction, 16 before).
+//   phase B (per INSTANCE, same CTA, four lanes per instance, instances in the order of their slot counts):
 //       the geometric chain rule dL/d{Tu,Tv,Tw}, dL/dmean2D, dL/dopacity, dL/dnormal, dL/dcolour
 //       (CR/backward.cu:343, :396, :412-460) from the instance's slots (one coalesced read) + its record,
-//       summed over the instance's pixels with 19 shuffles, and written as ONE plain 72-byte store into the
-//       instance's own gradient row: the reference issues 16 global atomicAdd per contributing
+//       reduce-scattered over the four lanes with 15 shuffles and written as one 16-byte + one 4-byte store per
+//       lane into the instance's own gradient row: the reference issues 16 global atomicAdd per contributing
 //       (pixel, instance) pair; here a row is written exactly once, so no atomics and no zero-fill.
 //
-// Records + masks of a tile arrive in batches of 128 by TMA (two-stage mbarrier ring).  Rows are indexed by
-// the instance's position in surfel-major (unsorted) order, so preprocess_bwd.cu reads each surfel's rows
-// contiguously.
+// Records + masks of a tile arrive by TMA bulk copies in chunks of 128 instances, all chunks of a super-batch
+// requested at once, one mbarrier each.  Rows are indexed by the instance's position in surfel-major (unsorted)
+// order, so preprocess_bwd.cu reads each surfel's rows contiguously.  What bounds the kernel now is the L1 /
+// shared-memory data pipe (an 80-byte record from a random row per pair), not the schedulers.
 #include <atomic>
 
 #include "common.cuh"

@@ -7,8 +7,8 @@
 // pixel (xc, yc) next to the splat centre, the intersection vector of pixel (xc+u, yc+v) is
 //        p(u, v) = k0 x l0 + u * (Tw x l0) + v * (k0 x Tw)          (exactly bilinear-free: Tw x Tw = 0)
 // so along a tile row the test rho3d = (p.x^2 + p.y^2) / p.z^2 <= c  (c = 2 ln(255 * opacity): alpha >= 1/255)
-// is ONE quadratic in u.  A quarter-warp handles one instance, a lane per box row (two when the box is higher
-// than 8 rows), after the row-independent part has been evaluated once: solve the quadratic,
+// is ONE quadratic in u.  One thread handles one instance (footprint.cuh, called from tile_sort_kernel): the
+// row-independent part is evaluated once, then for every row of the instance's box: solve the quadratic,
 // widen the root interval by a safety margin, union it with the (<= 0.34 px) disc of the 2D low-pass
 // filter, clip to the instance's footprint box, emit the row's 16-bit mask.  Rows whose quadratic is not
 // an ellipse section (grazing views) or not finite fall back to the whole box row.  The result is a

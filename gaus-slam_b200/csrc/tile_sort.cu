@@ -6,7 +6,8 @@
 // produces is a total order that can be stated without the sort: tiles ascending; inside a tile depth bits
 // ascending; equal depths by surfel index ascending (duplicateWithKeys emits surfels in index order and a
 // surfel touches a tile once, so "stable" means exactly that).  Hence:
-//   1. preprocess_forward counts the instances of every tile (one RED per instance, preprocess.cu);
+//   1. preprocess_forward counts the instances of every tile (one RED per instance, preprocess.cu; every tile's
+//      counter and cursor sit in a 128-byte line of their own, TC_STRIDE: L2 serialises atomics on a line);
 //   2. one extra block of the tiles_touched scan (preprocess.cu) scans the 3 225 counts -> tile ranges
 //      (identifyTileRanges's output) + write cursors;
 //   3. scatter_kernel drops every instance's (depth bits << 32 | surfel) word into its tile's segment, in
