@@ -137,7 +137,10 @@ def tracking_iteration(arm, dev, timed, steps, warmup, impl, surfels=300_000):
             return tracking.pose_transform(xyz, rot, cam_rot=cam_rot, cam_trans=cam_trans)
         from gs2d_b200 import loss as gs2d_loss
         loss_fn = gs2d_loss.tracking_loss
-        how = "gs2d_b200.tracking.pose_transform (one kernel each way, pose chain rule inside) + fused tracking loss"
+        # the tracker's Adam over the seven pose scalars (scene/Frame.py:70-73) as one launch per step
+        optimizer = tracking.PoseOptimizer(cam_rot, cam_trans, lr_rot=4e-4, lr_trans=2e-3, betas=(0.7, 0.99), eps=1e-8)
+        how = ("gs2d_b200.tracking.pose_transform (one kernel each way, pose chain rule inside) + fused tracking loss + "
+               "gs2d_b200.tracking.PoseOptimizer (torch.optim.Adam's update of the 7 scalars as one launch)")
     else:
         sys.path.insert(0, os.path.join(ROOT, "oracle"))
         import pose_ref

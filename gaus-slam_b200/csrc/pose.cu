@@ -248,7 +248,74 @@ inline int pose_blocks(int P)
 
 using namespace gs2d;
 
+namespace gs2d {
+namespace {
+
+// Adam on the tracker's seven pose scalars (scene/Frame.py:66-73: torch.optim.Adam over cam_rot [4] and cam_trans [3],
+// one learning rate each) in torch's operation order (torch/optim/adam.py: lerp for the first moment,
+// sqrt(v) / sqrt(bc2) + eps, scalars computed in double on the host): one 7-thread launch instead of the ~25 foreach
+// launches torch issues for two tiny parameters.
+struct PoseAdamArgs {
+	float* param[2];
+	const float* grad[2];
+	float* state;            // exp_avg[7] | exp_avg_sq[7], cam_rot first
+	float step_size[2];      // lr / (1 - beta1^t), per parameter (torch keeps one step counter per parameter)
+	float bc2_sqrt[2];
+	float w1, beta2, w2, eps;
+};
+
+__global__ void pose_adam_kernel(const PoseAdamArgs a)
+{
+	const int i = threadIdx.x;
+	if (i >= 7) return;
+	const int grp = i < 4 ? 0 : 1, k = i < 4 ? i : i - 4;
+	if (a.grad[grp] == nullptr) return;      // no gradient: parameter and moments untouched, like torch
+	const float g = a.grad[grp][k];
+	float m = a.state[i], v = a.state[7 + i], p = a.param[grp][k];
+	const float diff = g - m;
+	m = (a.w1 < 0.5f) ? m + a.w1 * diff : g - diff * (1.0f - a.w1);      // exp_avg.lerp_(grad, 1 - beta1)
+	v = v * a.beta2 + a.w2 * g * g;                                        // mul_(beta2).addcmul_(grad, grad, 1 - beta2)
+	const float denom = sqrtf(v) / a.bc2_sqrt[grp] + a.eps;
+	p = p - a.step_size[grp] * (m / denom);                                // addcdiv_(exp_avg, denom, value=-step_size)
+	a.state[i] = m;
+	a.state[7 + i] = v;
+	a.param[grp][k] = p;
+}
+
+}  // namespace
+}  // namespace gs2d
+
 extern "C" {
+
+int gs2d_pose_adam_step(float* cam_rot, float* cam_trans, const float* dL_dcam_rot, const float* dL_dcam_trans,
+                        float* state, const gs2d_pose_adam_params* ap, void* stream)
+{
+	if (!cam_rot || !cam_trans || !state || !ap) return GS2D_ERR_INVALID;
+	if (!dL_dcam_rot && !dL_dcam_trans) return GS2D_OK;
+	PoseAdamArgs a;
+	a.param[0] = cam_rot; a.param[1] = cam_trans;
+	a.grad[0] = dL_dcam_rot; a.grad[1] = dL_dcam_trans;
+	a.state = state;
+	for (int k = 0; k < 2; k++) {
+		const long long t = ap->step[k];
+		if (a.grad[k] && t < 1) return GS2D_ERR_INVALID;
+		const double bc1 = 1.0 - pow(ap->beta1, (double)(t > 0 ? t : 1)), bc2 = 1.0 - pow(ap->beta2, (double)(t > 0 ? t : 1));
+		a.step_size[k] = (float)(ap->lr[k] / bc1);
+		a.bc2_sqrt[k] = (float)sqrt(bc2);
+	}
+	a.w1 = (float)(1.0 - ap->beta1);
+	a.beta2 = (float)ap->beta2;
+	a.w2 = (float)(1.0 - ap->beta2);
+	a.eps = (float)ap->eps;
+	cudaStream_t st = (cudaStream_t)stream;
+	{
+		ProfScope ps(K_POSE, st);
+		pose_adam_kernel<<<1, 32, 0, st>>>(a);
+		count_launch();
+	}
+	GS2D_CUDA_OK(cudaGetLastError());
+	return GS2D_OK;
+}
 
 int gs2d_pose_transform_forward(int32_t P, const float* xyz, const float* rotations, const float* cam_rot,
                                 const float* cam_trans, const float* w2c, float* means3D_out, float* rotations_out,

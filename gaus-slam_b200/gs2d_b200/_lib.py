@@ -67,6 +67,11 @@ class MapState(C.Structure):
                 ("rgb", C.c_void_p), ("exp_avg", C.c_void_p * 5), ("exp_avg_sq", C.c_void_p * 5)]
 
 
+class PoseAdamParams(C.Structure):
+    _fields_ = [("lr", C.c_double * 2), ("beta1", C.c_double), ("beta2", C.c_double), ("eps", C.c_double),
+                ("step", C.c_int64 * 2)]
+
+
 class AdamParams(C.Structure):
     _fields_ = [("lr", C.c_double * 5), ("beta1", C.c_double), ("beta2", C.c_double), ("eps", C.c_double),
                 ("step", C.c_int64), ("group_step", C.c_int64 * 5)]
@@ -123,6 +128,8 @@ PROTOTYPES = {
                                         C.c_void_p, C.c_void_p]),
     "gs2d_pose_transform_forward": (C.c_int, [C.c_int32] + [C.c_void_p] * 8),
     "gs2d_pose_transform_scratch_bytes": (C.c_size_t, []),
+    "gs2d_pose_adam_step": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                      C.POINTER(PoseAdamParams), C.c_void_p]),
     "gs2d_pose_transform_backward": (C.c_int, [C.c_int32] + [C.c_void_p] * 11),
     "gs2d_allreduce_multimem": (C.c_int, [C.c_void_p, C.c_int64, C.c_int32, C.c_int32, C.c_int32, C.c_void_p]),
     "gs2d_timing_enable": (C.c_int, [C.c_int]),

@@ -94,3 +94,50 @@ def pose_transform(means3D, rotations, cam_rot=None, cam_trans=None, w2c=None):
     if (w2c is None) == (cam_rot is None or cam_trans is None) or (w2c is not None and (cam_rot is not None or cam_trans is not None)):
         raise Exception("Please provide exactly one of either the (cam_rot, cam_trans) pair or w2c!")
     return _PoseTransform.apply(means3D, rotations, cam_rot, cam_trans, w2c)
+
+
+class PoseOptimizer:
+    """The tracker's pose optimiser (scene/Frame.py:66-73: torch.optim.Adam over `cam_rot` [4] and `cam_trans` [3] with
+    one learning rate each, betas (0.7, 0.99), eps 1e-8; stepped once per tracking iteration, slam/Frontend.py:92) as
+    one kernel launch per step: torch's foreach Adam issues ~25 launches for these two tiny parameters, which is most
+    of the host time of a tracking iteration once the rasterizer is fast.
+
+        opt = PoseOptimizer(cam_rot, cam_trans, lr_rot=4e-4, lr_trans=2e-3)
+        opt.zero_grad(); loss.backward(); opt.step()
+
+    Same results as torch.optim.Adam (operation order of torch/optim/adam.py); a parameter whose .grad is None is
+    skipped together with its moments and its step counter, like torch."""
+
+    def __init__(self, cam_rot, cam_trans, lr_rot, lr_trans, betas=(0.7, 0.99), eps=1e-8):
+        for t, name, n in ((cam_rot, "cam_rot", 4), (cam_trans, "cam_trans", 3)):
+            if not t.is_cuda or t.dtype != torch.float32 or tuple(t.shape) != (n,) or not t.is_contiguous():
+                raise RuntimeError(f"{name} must be a contiguous float32 CUDA tensor of shape ({n},) (there is no CPU path)")
+        self.cam_rot, self.cam_trans = cam_rot, cam_trans
+        self.lr = [float(lr_rot), float(lr_trans)]
+        self.betas, self.eps = (float(betas[0]), float(betas[1])), float(eps)
+        self.state = torch.zeros(14, dtype=torch.float32, device=cam_rot.device)
+        self.steps = [0, 0]
+
+    def zero_grad(self, set_to_none=True):
+        for p in (self.cam_rot, self.cam_trans):
+            if set_to_none or p.grad is None:
+                p.grad = None
+            else:
+                p.grad.zero_()
+
+    def step(self):
+        g = [self.cam_rot.grad, self.cam_trans.grad]
+        for k in range(2):
+            gk = g[k]
+            if gk is not None:
+                if not gk.is_cuda or gk.dtype != torch.float32:
+                    raise RuntimeError("pose gradients must be float32 CUDA tensors")
+                g[k] = gk.contiguous()
+                self.steps[k] += 1
+        ap = L.PoseAdamParams(lr=(C.c_double * 2)(*self.lr), beta1=self.betas[0], beta2=self.betas[1], eps=self.eps,
+                              step=(C.c_int64 * 2)(*self.steps))
+        dev = self.cam_rot.device
+        with torch.cuda.device(dev):
+            st = C.c_void_p(L.raw_stream(torch, dev))
+            L.check(L.load().gs2d_pose_adam_step(self.cam_rot.data_ptr(), self.cam_trans.data_ptr(), _ptr(g[0]), _ptr(g[1]),
+                                                 self.state.data_ptr(), C.byref(ap), st), "gs2d_pose_adam_step")

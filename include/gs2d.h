@@ -378,6 +378,21 @@ int gs2d_pose_transform_backward(int32_t P, const float* xyz, const float* cam_r
                                  const float* w2c, const float* dL_dmeans3D, void* scratch, float* dL_dcam_rot,
                                  float* dL_dcam_trans, float* dL_dw2c, float* dL_dxyz, void* stream);
 
+/* Adam step of the tracker's seven pose scalars -- scene/Frame.py:66-73: torch.optim.Adam over `cam_rot` [4] and
+ * `cam_trans` [3], one learning rate each (cameras.*_lr), betas (0.7, 0.99), stepped once per tracking iteration
+ * (slam/Frontend.py:92) -- in torch's operation order, as ONE launch.  `state` = 14 device floats, exp_avg[7] |
+ * exp_avg_sq[7] (cam_rot first), zero before the first step.  A NULL gradient = that parameter has no gradient in
+ * this step: it, its moments and its step counter stay untouched, like torch.  step[k] = 1 for a parameter's
+ * first update. */
+typedef struct gs2d_pose_adam_params {
+	double lr[2];           /* cam_rot, cam_trans                      */
+	double beta1, beta2;    /* 0.7, 0.99 (scene/Frame.py:70-73)        */
+	double eps;             /* 1e-8                                    */
+	int64_t step[2];        /* per-parameter step counts, 1-based      */
+} gs2d_pose_adam_params;
+int gs2d_pose_adam_step(float* cam_rot, float* cam_trans, const float* dL_dcam_rot, const float* dL_dcam_trans,
+                        float* state, const gs2d_pose_adam_params* params, void* stream);
+
 /* ---- multi-GPU (new; the reference is single-GPU) -----------------------------------------
  * In-switch all-reduce (sum, fp32) of a buffer that lives in symmetric memory bound to an NVLS multicast
  * object: `multicast_ptr` is the multicast address of the buffer (same offset on every rank), n_floats a

@@ -46,7 +46,7 @@ def test_emulated_library_exports_the_next_row_entry_points():
     for name in ("gs2d_map_activate", "gs2d_map_adam_step", "gs2d_map_compact_scratch_bytes", "gs2d_map_compact_plan",
                  "gs2d_map_compact_move", "gs2d_mapping_loss_scratch_bytes", "gs2d_mapping_loss_forward",
                  "gs2d_mapping_loss_backward", "gs2d_pose_transform_forward", "gs2d_pose_transform_scratch_bytes",
-                 "gs2d_pose_transform_backward"):
+                 "gs2d_pose_transform_backward", "gs2d_pose_adam_step"):
         assert hasattr(lib, name), name
 
 
@@ -209,3 +209,11 @@ def test_groups_without_gradient_are_left_untouched_like_torch_adam(optim):
             assert np.array_equal(opt.raw["rotation"].numpy(), raw["rotation"]) and not opt.exp_avg["rotation"].any()
     with pytest.raises(KeyError):
         opt.step(torch.zeros(13 * opt.P), skip=("f_dc",))
+
+
+def test_pose_adam_kernel_text_equals_torch_adam(tracking):
+    """The fused optimiser of the seven pose scalars (host build of its kernel) against torch.optim.Adam with the
+    tracker's settings (scene/Frame.py:70-73), including a step without a gradient for one parameter."""
+    want = TP.pose_adam_sequence(TP.torch_pose_adam, "cpu")
+    got = TP.pose_adam_sequence(lambda q, t: tracking.PoseOptimizer(q, t, lr_rot=4e-4, lr_trans=2e-3), "cpu")
+    TP.check_pose_adam(got, want)

@@ -157,3 +157,46 @@ def test_pose_transform_argument_errors():
         tracking.pose_transform(x, r, cam_rot=q, cam_trans=t, w2c=torch.eye(4, device=dev))
     with pytest.raises(RuntimeError):
         tracking.pose_transform(x.cpu(), r.cpu(), cam_rot=q.cpu(), cam_trans=t.cpu())
+
+
+def pose_adam_sequence(make_optimizer, device, steps=6):
+    """Drives an optimiser over cam_rot / cam_trans with a fixed gradient sequence (step 3: cam_trans has no gradient,
+    which torch skips together with its moments and step counter) -> the parameters after every step."""
+    rng = np.random.default_rng(11)
+    q = torch.tensor([0.9995, 0.01, -0.02, 0.015], dtype=torch.float32, device=device, requires_grad=True)
+    t = torch.tensor([0.03, -0.02, 0.05], dtype=torch.float32, device=device, requires_grad=True)
+    opt = make_optimizer(q, t)
+    out = []
+    for i in range(steps):
+        opt.zero_grad(set_to_none=True)
+        q.grad = torch.tensor(rng.normal(0, 10.0 ** rng.integers(-3, 2), 4), dtype=torch.float32, device=device)
+        if i != 3:
+            t.grad = torch.tensor(rng.normal(0, 10.0 ** rng.integers(-3, 2), 3), dtype=torch.float32, device=device)
+        opt.step()
+        out.append((q.detach().cpu().numpy().copy(), t.detach().cpu().numpy().copy()))
+    return out
+
+
+def torch_pose_adam(q, t):
+    # scene/Frame.py:70-73
+    return torch.optim.Adam([{"params": [q], "lr": 4e-4, "name": "cam_rots"}, {"params": [t], "lr": 2e-3, "name": "cam_trans"}],
+                            lr=0.0, eps=1e-8, betas=(0.7, 0.99))
+
+
+def check_pose_adam(got, want):
+    for i, ((q1, t1), (q0, t0)) in enumerate(zip(got, want)):
+        assert np.allclose(q1, q0, rtol=2e-6, atol=1e-9), (i, q1, q0)
+        assert np.allclose(t1, t0, rtol=2e-6, atol=1e-9), (i, t1, t0)
+
+
+@pytest.mark.gpu
+def test_fused_pose_adam_equals_torch_adam():
+    """gs2d_b200.tracking.PoseOptimizer (one launch per step) against the reference's optimiser for the seven pose
+    scalars, torch.optim.Adam with Frame.py's settings, including a step in which one parameter has no gradient."""
+    from gs2d_b200 import tracking
+    dev = torch.device("cuda:0")
+    want = pose_adam_sequence(torch_pose_adam, dev)
+    got = pose_adam_sequence(lambda q, t: tracking.PoseOptimizer(q, t, lr_rot=4e-4, lr_trans=2e-3), dev)
+    check_pose_adam(got, want)
+    with pytest.raises(RuntimeError):
+        tracking.PoseOptimizer(torch.zeros(4), torch.zeros(3), 1e-3, 1e-3)
