@@ -161,6 +161,9 @@ __device__ __forceinline__ void cta_sort_regs(const uint64_t* seg, int n, uint64
 	__syncthreads();
 }
 
+#ifndef GS2D_TS_GATHER_ILP
+#define GS2D_TS_GATHER_ILP 4      // record parts in flight per thread in the gather (0 = one at a time)
+#endif
 #ifndef GS2D_TS_MIN_BLOCKS
 #define GS2D_TS_MIN_BLOCKS 5
 #endif
@@ -205,11 +208,33 @@ tile_sort_kernel(int W, int H, unsigned gx, const uint2* __restrict__ ranges, ui
 	// copy: the two record words that depend on the tile are patched in below by the instance's own thread, so no lane
 	// of this loop takes a special path).
 	float4* tile_rec = instances + 5 * (size_t)range.x;
+#if GS2D_TS_GATHER_ILP
+	// GU record parts per thread and round, all loads requested before the first store (the records sit at
+	// random places of a 40 MB array: the loop waits on DRAM, not on anything it computes)
+	constexpr int GU = GS2D_TS_GATHER_ILP;
+	for (int t0 = tid; t0 < 5 * n; t0 += GU * 256) {
+		float4 v[GU];
+#pragma unroll
+		for (int u = 0; u < GU; u++) {
+			const int t = t0 + u * 256;
+			if (t < 5 * n) {
+				const int k = t / 5, part = t - 5 * k;
+				v[u] = splat[5 * (size_t)(uint32_t)kp[k] + part];
+			}
+		}
+#pragma unroll
+		for (int u = 0; u < GU; u++) {
+			const int t = t0 + u * 256;
+			if (t < 5 * n) tile_rec[t] = v[u];
+		}
+	}
+#else
 	for (int t = tid; t < 5 * n; t += 256) {
 		const int k = t / 5, part = t - 5 * k;
 		const uint32_t idx = (uint32_t)kp[k];
 		tile_rec[t] = splat[5 * (size_t)idx + part];
 	}
+#endif
 	__syncthreads();   // the records are complete copies: they are patched and read back below by other threads
 	// Footprints: a thread per instance.  It first finishes its record -- word 15 = in-tile footprint box, word 19 = the
 	// instance's gradient row (surfel-major, see common.cuh) -- then walks the rows of the box (the row-independent half
