@@ -403,11 +403,18 @@ composite_backward_pixels_kernel(int W, int H, unsigned gx, const uint2* __restr
 			}
 		}
 		// natural owners: the pixel's contribution words of this super-batch (coalesced) -> shared memory
+		// (all words are requested before the first is used: the loop would otherwise pay one L2 round trip per word)
 		int len = 0;
-		for (int w = 0; w < nw; w++) {
-			const uint32_t u = pix_words[(size_t)(((first >> 5) + w) * 2 + 0) * TILE_PIXELS + tid];
-			sm.used[w][tid] = u;
-			len += __popc(u);
+		{
+			uint32_t u[BWD_WORDS];
+#pragma unroll
+			for (int w = 0; w < BWD_WORDS; w++)
+				u[w] = w < nw ? pix_words[(size_t)(((first >> 5) + w) * 2 + 0) * TILE_PIXELS + tid] : 0u;
+#pragma unroll
+			for (int w = 0; w < BWD_WORDS; w++) {
+				if (w < nw) sm.used[w][tid] = u[w];
+				len += __popc(u[w]);
+			}
 		}
 		for (int i = tid; i <= cnt_sb; i += 256) {
 			const size_t gi = (size_t)range.x + first + i;
@@ -495,8 +502,13 @@ composite_backward_pixels_kernel(int W, int H, unsigned gx, const uint2* __restr
 		// rejected by the exact tests, or behind the pixel's termination point) ...
 		{
 			const uint32_t lane_lt = (1u << lane) - 1u;
-			for (int w = 0; w < nw; w++) {
-				uint32_t e = pix_words[(size_t)(((first >> 5) + w) * 2 + 1) * TILE_PIXELS + tid] & ~sm.used[w][tid];
+			uint32_t ew[BWD_WORDS];
+#pragma unroll
+			for (int w = 0; w < BWD_WORDS; w++)
+				ew[w] = w < nw ? (pix_words[(size_t)(((first >> 5) + w) * 2 + 1) * TILE_PIXELS + tid] & ~sm.used[w][tid]) : 0u;
+#pragma unroll
+			for (int w = 0; w < BWD_WORDS; w++) {
+				uint32_t e = ew[w];
 				while (e) {
 					const int jl = __ffs(e) - 1;
 					e &= e - 1;
