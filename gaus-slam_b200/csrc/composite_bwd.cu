@@ -315,6 +315,23 @@ composite_backward_pixels_kernel(int W, int H, unsigned gx, const uint2* __restr
 	const unsigned tx = tile % gx, ty = tile / gx;
 	const size_t HW = (size_t)H * W;
 
+	// The loads that do not depend on the tile's range go out first (the pixel's last contributor, the lines of the
+	// per-pixel state), so that they travel beside the range and the overflow check, not behind them.
+	const unsigned nat_x = tx * TILE + (tid & 15), nat_y = ty * TILE + (tid >> 4);
+	const bool nin = nat_x < (unsigned)W && nat_y < (unsigned)H;
+	const size_t npid = (size_t)W * nat_y + nat_x;
+	uint32_t wmax = nin ? n_contrib[npid] : 0u;
+#if GS2D_BWD_PREFETCH_PIX
+	// The per-pixel state is loaded further down by the thread that WALKS the pixel (known only after the sort of
+	// the pixels by list length): request the tile's lines now, in natural order, so that those loads hit L1 / L2.
+	if (nin) {
+		prefetch_l1(final_T + npid); prefetch_l1(final_T + npid + HW); prefetch_l1(final_T + npid + 2 * HW);
+		prefetch_l1(n_contrib + npid + HW); prefetch_l1(median_depth + npid); prefetch_l1(depth_std + npid);
+		prefetch_l1(dL_dpix + npid); prefetch_l1(dL_dpix + npid + HW); prefetch_l1(dL_dpix + npid + 2 * HW);
+#pragma unroll
+		for (int c = 0; c < 7; c++) prefetch_l1(dL_dothers + npid + c * HW);
+	}
+#endif
 	const uint2 range = ranges[tile];
 	const int n = (int)(range.y - range.x);
 	// Memory safety against a wrong pair count from the caller (it sized `slots`): a tile whose slots would end beyond
@@ -326,21 +343,6 @@ composite_backward_pixels_kernel(int W, int H, unsigned gx, const uint2* __restr
 
 	// deepest last contributor of the tile: nothing behind it is ever visited
 	{
-		const unsigned nx = tx * TILE + (tid & 15), ny = ty * TILE + (tid >> 4);
-		const bool nin = nx < (unsigned)W && ny < (unsigned)H;
-		const size_t npid = (size_t)W * ny + nx;
-		uint32_t wmax = nin ? n_contrib[npid] : 0u;
-#if GS2D_BWD_PREFETCH_PIX
-		// The per-pixel state is loaded further down by the thread that WALKS the pixel (known only after the sort of
-		// the pixels by list length): request the tile's lines now, in natural order, so that those loads hit L1 / L2.
-		if (nin) {
-			prefetch_l1(final_T + npid); prefetch_l1(final_T + npid + HW); prefetch_l1(final_T + npid + 2 * HW);
-			prefetch_l1(n_contrib + npid + HW); prefetch_l1(median_depth + npid); prefetch_l1(depth_std + npid);
-			prefetch_l1(dL_dpix + npid); prefetch_l1(dL_dpix + npid + HW); prefetch_l1(dL_dpix + npid + 2 * HW);
-#pragma unroll
-			for (int c = 0; c < 7; c++) prefetch_l1(dL_dothers + npid + c * HW);
-		}
-#endif
 #pragma unroll
 		for (int o = 16; o >= 1; o >>= 1) wmax = max(wmax, __shfl_xor_sync(0xffffffffu, wmax, o));
 		if (lane == 0) sm.max_last[warp] = wmax;
@@ -416,9 +418,18 @@ composite_backward_pixels_kernel(int W, int H, unsigned gx, const uint2* __restr
 				len += __popc(u[w]);
 			}
 		}
-		for (int i = tid; i <= cnt_sb; i += 256) {
-			const size_t gi = (size_t)range.x + first + i;
-			sm.base[i] = gi ? pair_incl[gi - 1] : 0u;
+		{
+			constexpr int PERB = (BWD_SUPER + 256) / 256;       // both loads of a thread are requested before either is stored
+			uint32_t bv[PERB];
+#pragma unroll
+			for (int r = 0; r < PERB; r++) {
+				const int i = r * 256 + tid;
+				const size_t gi = (size_t)range.x + first + i;
+				bv[r] = (i <= cnt_sb && gi) ? pair_incl[gi - 1] : 0u;
+			}
+#pragma unroll
+			for (int r = 0; r < PERB; r++)
+				if (r * 256 + tid <= cnt_sb) sm.base[r * 256 + tid] = bv[r];
 		}
 		if (it == 0) {
 			// counting sort of the 256 pixels by the length of their list (deepest super-batch), longest first
