@@ -692,8 +692,11 @@ composite_backward_pixels_kernel(int W, int H, unsigned gx, const uint2* __restr
 	// that lie wholly inside this tile's slot range instead of writing them back to HBM (16 B x ~15 M pairs a frame).
 	__syncthreads();
 	{
+		// (with the whole tile resident the two ends of its slot range are still in shared memory: no global round trip
+		// at the very end of the CTA, where nothing is left to hide it)
 		const size_t gi0 = (size_t)range.x;
-		const uint32_t t0 = gi0 ? pair_incl[gi0 - 1] : 0u, t1 = pair_incl[gi0 + n_done - 1];
+		const uint32_t t0 = resident ? sm.base[0] : (gi0 ? pair_incl[gi0 - 1] : 0u);
+		const uint32_t t1 = resident ? sm.base[n_done] : pair_incl[gi0 + n_done - 1];
 		const uintptr_t a0 = (reinterpret_cast<uintptr_t>(slots + t0) + 127) & ~(uintptr_t)127;
 		const uintptr_t a1 = reinterpret_cast<uintptr_t>(slots + t1) & ~(uintptr_t)127;
 		for (uintptr_t a = a0 + (uintptr_t)tid * 128; a < a1; a += 256 * 128)
