@@ -42,7 +42,7 @@ namespace {
 #define GS2D_BWD_DISCARD 1
 #endif
 #ifndef GS2D_BWD_PREFETCH
-#define GS2D_BWD_PREFETCH 1
+#define GS2D_BWD_PREFETCH 2
 #endif
 #ifndef GS2D_BWD_SLOT_CG
 #define GS2D_BWD_SLOT_CG 0
@@ -634,13 +634,21 @@ composite_backward_pixels_kernel(int W, int H, unsigned gx, const uint2* __restr
 				}
 				const uint32_t s0 = sm.base[q], s1 = sm.base[q + 1];
 #if GS2D_BWD_PREFETCH
-				// the next slot is requested before the current one is worked on (phase B waits on L2 otherwise)
-				float4 nx = (s0 + gl < s1) ? SLOT_LD(slots + s0 + gl) : make_float4(0.f, 0.f, 0.f, __int_as_float(-1));
+				// GS2D_BWD_PREFETCH slots of the lane are in flight while one is worked on (a slot takes ~100 instructions,
+				// an L2 round trip is longer than that)
+				constexpr int PF = GS2D_BWD_PREFETCH;
+				float4 nx[PF];
+#pragma unroll
+				for (int d = 0; d < PF; d++)
+					nx[d] = (s0 + gl + d * BWD_GRP < s1) ? SLOT_LD(slots + s0 + gl + d * BWD_GRP)
+					                                      : make_float4(0.f, 0.f, 0.f, __int_as_float(-1));
 #endif
 				for (uint32_t k = s0 + gl; k < s1; k += BWD_GRP) {
 #if GS2D_BWD_PREFETCH
-					const float4 sl = nx;
-					if (k + BWD_GRP < s1) nx = SLOT_LD(slots + k + BWD_GRP);
+					const float4 sl = nx[0];
+#pragma unroll
+					for (int d = 0; d + 1 < PF; d++) nx[d] = nx[d + 1];
+					if (k + PF * BWD_GRP < s1) nx[PF - 1] = SLOT_LD(slots + k + PF * BWD_GRP);
 #else
 					const float4 sl = SLOT_LD(slots + k);
 #endif
