@@ -70,6 +70,10 @@ __device__ __forceinline__ LossPixel load_pixel(size_t p, size_t HW, const float
 	return px;
 }
 
+// CTAs per SM of the two kernels (the scratch holds partials of up to 148 * 8 CTAs).  Every forward CTA ends with one
+// atomic on the same ticket word and L2 serialises those, so its grid is small: 12.0 us at 2 CTAs / SM, 12.9 at 4,
+// 13.7 at 8 (1200 x 680).  The backward kernel has no such tail: 11.5 us at 4, 12.2 at 8, 14.0 at 2.
+constexpr int LOSS_FWD_CTAS_PER_SM = 2, LOSS_BWD_CTAS_PER_SM = 4;
 constexpr int LOSS_THREADS = 256;
 constexpr int LOSS_COLS = 8;        // per-block partials: count, colour sum, depth sum, distortion sum, colour count, 3 spare
 
@@ -304,11 +308,12 @@ inline bool loss_vec_ok(size_t HW, std::initializer_list<const void*> ptrs)
 	return true;
 }
 
-inline int loss_blocks(size_t HW, bool vec)
+inline int loss_blocks(size_t HW, bool vec, int ctas_per_sm)
 {
 	const size_t items = vec ? HW / 4 : HW;
 	const size_t want = (items + LOSS_THREADS - 1) / LOSS_THREADS;
-	const size_t cap = 148 * 8;   // one wave of 8 CTAs per SM
+	// grid-stride loops over a grid of `ctas_per_sm` CTAs per SM (measured per kernel, see the callers)
+	const size_t cap = 148 * (size_t)ctas_per_sm;
 	return (int)(want < cap ? (want ? want : 1) : cap);
 }
 
@@ -347,7 +352,7 @@ int gs2d_mapping_loss_forward(int32_t W, int32_t H, const float* color, const fl
 	{
 		ProfScope ps(K_LOSS, st);
 		const bool vec = loss_vec_ok(HW, {color, allmap, gt_color, gt_depth});
-		const int blocks = loss_blocks(HW, vec);
+		const int blocks = loss_blocks(HW, vec, LOSS_FWD_CTAS_PER_SM);
 		if (vec)
 			mapping_loss_forward_kernel<true><<<blocks, LOSS_THREADS, 0, st>>>(
 				HW, color, allmap, gt_color, gt_depth, gt_color_hwc, lp->w_color, lp->w_depth, lp->w_dist, lp->eps,
@@ -378,7 +383,7 @@ int gs2d_mapping_loss_backward(int32_t W, int32_t H, const float* color, const f
 	{
 		ProfScope ps(K_LOSS, st);
 		const bool vec = loss_vec_ok(HW, {color, allmap, gt_color, gt_depth, dL_dcolor, dL_dallmap});
-		const int blocks = loss_blocks(HW, vec);
+		const int blocks = loss_blocks(HW, vec, LOSS_BWD_CTAS_PER_SM);
 		if (vec)
 			mapping_loss_backward_kernel<true><<<blocks, LOSS_THREADS, 0, st>>>(
 				HW, color, allmap, gt_color, gt_depth, gt_color_hwc, lp->w_color, lp->w_depth, lp->w_dist, lp->eps,
